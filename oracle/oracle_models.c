@@ -1,0 +1,58 @@
+/*
+ * oracle_models.c -- host-side compiled models with the rootSolve DLL signature
+ * func(neq, t, y, ydot, yout, ip) (src/steady.h:34, inst/dynload/anoxmodc.c:29-53)
+ * for the oracle and the CPU baseline.  TEST INFRASTRUCTURE ONLY.
+ *
+ * The point-wise math is shared with the CUDA models through
+ * rootsolve_b200/models/model_math.h (see the note there); these wrappers are
+ * the plain sequential "whole vector per call" form the reference expects.
+ * Parameters arrive the way compiled rootSolve models get them: an initialiser
+ * init<model>(steadyparms) that calls back steadyparms(&N, parms)
+ * (src/steady_utils.c:43-58, inst/dynload/anoxmodc.c:21-25).
+ */
+#include "../rootsolve_b200/models/model_math.h"
+
+static double p_d2[RSM_D2_NPAR], p_d3[RSM_D3_NPAR], p_rd3[RSM_RD3_NPAR], p_rt1[RSM_RT1_NPAR];
+
+void initdiff2d(void (*steadyparms)(int *, double *)) { int N = RSM_D2_NPAR; steadyparms(&N, p_d2); }
+void initdiff3d(void (*steadyparms)(int *, double *)) { int N = RSM_D3_NPAR; steadyparms(&N, p_d3); }
+void initrd3d(void (*steadyparms)(int *, double *)) { int N = RSM_RD3_NPAR; steadyparms(&N, p_rd3); }
+void initrt1d(void (*steadyparms)(int *, double *)) { int N = RSM_RT1_NPAR; steadyparms(&N, p_rt1); }
+
+void diff2d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)yout;
+    const int d1 = ip[4], d2 = ip[5], variant = ip[7];
+    for (int j = 0; j < d1; j++)
+        for (int k = 0; k < d2; k++) ydot[j * d2 + k] = rsm_diff2d_point(y, j, k, d1, d2, p_d2, variant);
+}
+
+void diff3d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)yout;
+    const int d1 = ip[4], d2 = ip[5], d3 = ip[6], variant = ip[7];
+    for (int j = 0; j < d1; j++)
+        for (int k = 0; k < d2; k++)
+            for (int l = 0; l < d3; l++)
+                ydot[(j * d2 + k) * d3 + l] = rsm_diff3d_point(y, j, k, l, d1, d2, d3, p_d3, variant);
+}
+
+void rd3d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)yout;
+    const int d1 = ip[4], d2 = ip[5], d3 = ip[6];
+    const long nc = (long)d1 * d2 * d3;
+    for (int s = 0; s < 2; s++)
+        for (int j = 0; j < d1; j++)
+            for (int k = 0; k < d2; k++)
+                for (int l = 0; l < d3; l++)
+                    ydot[s * nc + (j * d2 + k) * d3 + l] = rsm_rd3d_point(y, s, j, k, l, d1, d2, d3, p_rd3);
+}
+
+void rt1d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)yout;
+    const int nspec = ip[3], nb = ip[4];
+    for (int s = 0; s < nspec; s++)
+        for (int j = 0; j < nb; j++) ydot[(long)s * nb + j] = rsm_rt1d_point(y, s, j, nspec, nb, p_rt1);
+}

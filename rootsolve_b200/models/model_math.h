@@ -1,0 +1,157 @@
+/*
+ * model_math.h -- point-wise right-hand sides of the bundled synthetic
+ * reaction-transport models (BASELINE.json configs C1..C5).
+ *
+ * One source, two compilers: nvcc builds these as __device__ functions for the
+ * CUDA models (bundled_models.cu); gcc builds them as plain C for the host
+ * wrappers the oracle and the CPU baseline call (oracle/oracle_models.c).  The
+ * models are *user input* to the solver (what rootSolve users write as an R
+ * closure or a compiled DLL func), not part of the reference's algorithm, so
+ * sharing the source between checker and product is deliberate: it makes the
+ * residual bit-identical on both sides (device build uses -fmad=false) and
+ * leaves the solver itself as the only thing the parity tests compare.
+ *
+ * Layout (what rootSolve's R wrappers pass down, R/steady.2D.R:48-49,
+ * R/steady.3D.R:49-50, src/sparsecoeff.f:96,125,215,244): species-major; within
+ * a species the grid is stored with the *last* stodes dimension fastest,
+ *   2-D: idx = s*d1*d2 + j*d2 + k            (j in [0,d1), k in [0,d2))
+ *   3-D: idx = s*d1*d2*d3 + j*d2*d3 + k*d3 + l
+ * where (d1,d2[,d3]) = rev(dimens) of the R call.
+ *
+ * ipar convention of the bundled models (after the 3 reserved slots of
+ * src/steady_utils.c:109-124): ip[3]=nspec, ip[4]=d1, ip[5]=d2, ip[6]=d3,
+ * ip[7]=variant flag.
+ */
+#ifndef RSM_MODEL_MATH_H
+#define RSM_MODEL_MATH_H
+
+#ifdef __CUDACC__
+#define RSM_HD __host__ __device__ __forceinline__
+#else
+#define RSM_HD static inline
+#endif
+
+/* ---- parameter slots ------------------------------------------------- */
+/* diff2d (C1/C3 and man/steady.2D.Rd:110-125): 7 parameters */
+#define RSM_D2_NPAR 7
+/* p[0]=Dx p[1]=Dy p[2]=dx p[3]=dy p[4]=r (linear rate, or rmax) p[5]=ks p[6]=BND */
+/* diff3d (C5 and man/steady.3D.Rd:105-140): 8 parameters */
+#define RSM_D3_NPAR 8
+/* p[0]=Dx p[1]=Dy p[2]=Dz p[3]=dx p[4]=dy p[5]=dz p[6]=r p[7]=BND */
+/* rd3d two-species (C4): 10 parameters */
+#define RSM_RD3_NPAR 10
+/* p[0]=D1 p[1]=D2 p[2]=dx p[3]=dy p[4]=dz p[5]=k p[6]=m p[7]=BNDu p[8]=BNDv p[9]=unused */
+/* rt1d multi-species reaction-transport (C2): 6 parameters */
+#define RSM_RT1_NPAR 7
+/* p[0]=v p[1]=D p[2]=dx p[3]=r p[4]=ks p[5]=BND (upstream, all species) p[6]=r0 */
+
+/* One direction of Fickian diffusion with imposed (Dirichlet) values outside
+ * the grid, written in the flux form the man-page models use:
+ *   Flux_lo = -D*(yc - ylo)/h ; Flux_hi = -D*(yhi - yc)/h ; -(Flux_hi-Flux_lo)/h
+ * with ylo/yhi replaced by BND at the edges. */
+RSM_HD double rsm_flux_div(double ylo, double yc, double yhi, double D, double h)
+{
+    double flo = -D * (yc - ylo) / h;
+    double fhi = -D * (yhi - yc) / h;
+    return (fhi - flo) / h;
+}
+
+/* variant: 0 = first-order consumption -r*y ; 1 = Monod -rmax*y/(y+ks) */
+RSM_HD double rsm_diff2d_point(const double *y, int j, int k, int d1, int d2,
+                               const double *p, int variant)
+{
+    const double Dx = p[0], Dy = p[1], dx = p[2], dy = p[3], r = p[4], ks = p[5], bnd = p[6];
+    const int idx = j * d2 + k;
+    const double yc = y[idx];
+    double dY = (variant == 1) ? -r * yc / (yc + ks) : -r * yc;
+    /* "X" = first R dimension = fastest index k */
+    double ylo = (k > 0) ? y[idx - 1] : bnd;
+    double yhi = (k < d2 - 1) ? y[idx + 1] : bnd;
+    dY = dY - rsm_flux_div(ylo, yc, yhi, Dx, dx);
+    /* "Y" = second R dimension = j */
+    ylo = (j > 0) ? y[idx - d2] : bnd;
+    yhi = (j < d1 - 1) ? y[idx + d2] : bnd;
+    dY = dY - rsm_flux_div(ylo, yc, yhi, Dy, dy);
+    return dY;
+}
+
+/* variant: 0 = each direction once ; 1 = each direction applied twice, in the
+ * order the vignette's three loops apply them (vignettes/rootSolve.Rnw:686-722):
+ * (y,z) for fixed x-slices, (x,z), (x,y). */
+RSM_HD double rsm_diff3d_point(const double *y, int j, int k, int l, int d1, int d2, int d3,
+                               const double *p, int variant)
+{
+    const double Dx = p[0], Dy = p[1], Dz = p[2], dx = p[3], dy = p[4], dz = p[5], r = p[6],
+                 bnd = p[7];
+    const int s2 = d3, s1 = d2 * d3;
+    const int idx = j * s1 + k * s2 + l;
+    const double yc = y[idx];
+    double dY = -r * yc;
+    /* x = first R dim = l ; y = second R dim = k ; z = third R dim = j */
+    const double gx = rsm_flux_div((l > 0) ? y[idx - 1] : bnd, yc, (l < d3 - 1) ? y[idx + 1] : bnd, Dx, dx);
+    const double gy = rsm_flux_div((k > 0) ? y[idx - s2] : bnd, yc, (k < d2 - 1) ? y[idx + s2] : bnd, Dy, dy);
+    const double gz = rsm_flux_div((j > 0) ? y[idx - s1] : bnd, yc, (j < d1 - 1) ? y[idx + s1] : bnd, Dz, dz);
+    if (variant == 1) {
+        dY = dY - gy; dY = dY - gz;
+        dY = dY - gx; dY = dY - gz;
+        dY = dY - gx; dY = dY - gy;
+    } else {
+        dY = dY - gx; dY = dY - gy; dY = dY - gz;
+    }
+    return dY;
+}
+
+/* Two species u (s=0), v (s=1) on a 3-D grid:
+ *   du = D1 lap(u) - k u v ;  dv = D2 lap(v) + k u v - m v ; Dirichlet faces. */
+RSM_HD double rsm_rd3d_point(const double *y, int s, int j, int k, int l, int d1, int d2, int d3,
+                             const double *p)
+{
+    const double D = (s == 0) ? p[0] : p[1];
+    const double dx = p[2], dy = p[3], dz = p[4], kk = p[5], m = p[6];
+    const double bnd = (s == 0) ? p[7] : p[8];
+    const int s2 = d3, s1 = d2 * d3, nc = d1 * d2 * d3;
+    const int cell = j * s1 + k * s2 + l;
+    const double *ys = y + (long)s * nc;
+    const double yc = ys[cell];
+    const double u = y[cell], v = y[nc + cell];
+    const double react = kk * u * v;
+    double dY = (s == 0) ? -react : (react - m * v);
+    dY = dY - rsm_flux_div((l > 0) ? ys[cell - 1] : bnd, yc, (l < d3 - 1) ? ys[cell + 1] : bnd, D, dx);
+    dY = dY - rsm_flux_div((k > 0) ? ys[cell - s2] : bnd, yc, (k < d2 - 1) ? ys[cell + s2] : bnd, D, dy);
+    dY = dY - rsm_flux_div((j > 0) ? ys[cell - s1] : bnd, yc, (j < d1 - 1) ? ys[cell + s1] : bnd, D, dz);
+    return dY;
+}
+
+/* nspec species on a 1-D column of nb boxes: first-order upwind advection v,
+ * diffusion D, first-order loss r0, and a Monod chain in every box in which the
+ * consumption of species s is limited by the availability of species s+1,
+ *   R_s = r y_s y_{s+1}/(y_{s+1}+ks)  (s < nspec-1),  R_last = r y_last,
+ *   dy_s = transport - R_s - r0 y_s.
+ * Upstream (box 0): imposed value BND for every species; downstream: zero
+ * gradient.  The coupling is one-sided (species s depends on s+1), so the
+ * Jacobian is nonsymmetric, while sparse1d still allocates the full
+ * nspec x nspec cell block (src/sparsecoeff.f:70-75). */
+RSM_HD double rsm_rt1d_point(const double *y, int s, int j, int nspec, int nb, const double *p)
+{
+    const double v = p[0], D = p[1], dx = p[2], r = p[3], ks = p[4], bnd = p[5], r0 = p[6];
+    const double *ys = y + (long)s * nb;
+    const double yc = ys[j];
+    const double ylo = (j > 0) ? ys[j - 1] : bnd;
+    const double yhi = (j < nb - 1) ? ys[j + 1] : yc; /* zero gradient */
+    /* flux through the lower and upper interface of box j */
+    const double flo = v * ylo - D * (yc - ylo) / dx;
+    const double fhi = v * yc - D * (yhi - yc) / dx;
+    double dY = -(fhi - flo) / dx;
+    double Rs;
+    if (s < nspec - 1) {
+        const double yn = y[(long)(s + 1) * nb + j];
+        Rs = r * yc * yn / (yn + ks);
+    } else {
+        Rs = r * yc;
+    }
+    dY = dY - Rs;
+    dY = dY - r0 * yc;
+    return dY;
+}
+
+#endif /* RSM_MODEL_MATH_H */
