@@ -1,0 +1,732 @@
+// api.cu -- the C ABI (include/rootsolve_b200.h) and the Newton driver.
+//
+// rs_stsparse() is the GPU counterpart of call_stsparse() + dsparse()
+// (src/call_stsparse.c:60-320, src/sparse.f:30-195): copy the inputs in, build
+// structure / grouping / row-wise pattern once, then iterate
+//   { beta = -f(y), FD Jacobian ; test 1 ; solve J x = beta ; y += x, clamp ;
+//     test 2 ; new error weights }
+// and hand back y with the precis / steady attributes.
+#include <algorithm>
+#include <cmath>
+#include <memory>
+
+#include "solver.cuh"
+
+namespace rs {
+
+// ---- error text, context ---------------------------------------------------------
+static thread_local char g_err[512] = "";
+long long g_device_bytes = 0;
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+const char *const kKernelNames[K_COUNT] = {"structure", "scan", "transpose", "jgroup", "perturb", "residual_batched",
+                                           "fd_assemble", "spmv_csr", "krylov_vec", "precond_setup", "precond_apply",
+                                           "newton", "halo", "misc"};
+
+void Ctx::begin(int id, double algo_bytes)
+{
+    bytes[id] = algo_bytes;
+    Pending p;
+    p.id = id;
+    auto get = [&]() {
+        cudaEvent_t e;
+        if (!pool.empty()) { e = pool.back(); pool.pop_back(); }
+        else cudaEventCreate(&e);
+        return e;
+    };
+    p.a = get();
+    p.b = get();
+    cudaEventRecord(p.a, stream);
+    pending.push_back(p);
+}
+void Ctx::end(int)
+{
+    cudaEventRecord(pending.back().b, stream);
+    if (pending.size() >= 8192) resolve();
+}
+void Ctx::resolve()
+{
+    if (pending.empty()) return;
+    cudaStreamSynchronize(stream);
+    for (auto &p : pending) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, p.a, p.b) == cudaSuccess) ms[p.id] += t;
+        pool.push_back(p.a);
+        pool.push_back(p.b);
+    }
+    pending.clear();
+}
+void Ctx::reset_stats()
+{
+    resolve();
+    for (int i = 0; i < K_COUNT; i++) { ms[i] = 0; count[i] = 0; }
+    launches = 0;
+}
+Ctx::~Ctx()
+{
+    resolve();
+    for (auto e : pool) cudaEventDestroy(e);
+}
+
+int ensure_device()
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        set_error("no CUDA device available (%s); this library has no CPU path",
+                  e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+        cudaGetLastError();
+        return RS_ENODEVICE;
+    }
+    return RS_OK;
+}
+
+// ---- Newton kernels (K9) -------------------------------------------------------------
+// ewt = rtol |y| + atol with the four itol variants (errset, src/sparse.f:264-293)
+__device__ __forceinline__ double ewt_of(int itol, const double *__restrict__ rtol, const double *__restrict__ atol,
+                                         long long i, double yi)
+{
+    const double rt = (itol == 3 || itol == 4) ? rtol[i] : rtol[0];
+    const double at = (itol == 2 || itol == 4) ? atol[i] : atol[0];
+    return rt * fabs(yi) + at;
+}
+
+__global__ void errset_kernel(int n, int itol, const double *__restrict__ rtol, const double *__restrict__ atol,
+                              const double *__restrict__ y, double *__restrict__ ewt)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        ewt[i] = ewt_of(itol, rtol, atol, i, y[i]);
+}
+
+// test 1 (src/sparse.f:122-133): out = { sum |beta|, max |beta/ewt| }
+__global__ void __launch_bounds__(256) test1_kernel(int n, const double *__restrict__ beta, const double *__restrict__ ewt,
+                                                    double *partials, unsigned *ticket, double *out)
+{
+    double acc[2] = {0.0, 0.0};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double b = beta[i];
+        acc[0] += fabs(b);
+        acc[1] = fmax(acc[1], fabs(b / ewt[i]));
+    }
+    grid_reduce<2>(acc, 2u, partials, ticket, out);
+}
+
+// update (src/sparse.f:152-163, 185): out = { max |x| } ; y += x ; clamp ; ewt(y)
+__global__ void __launch_bounds__(256) update_kernel(int n, int positivity, int itol, const double *__restrict__ rtol,
+                                                     const double *__restrict__ atol, const double *__restrict__ x,
+                                                     double *__restrict__ y, double *__restrict__ ewt, double *partials,
+                                                     unsigned *ticket, double *out)
+{
+    double acc[1] = {0.0};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double xi = x[i];
+        acc[0] = fmax(acc[0], fabs(xi));
+        double yn = y[i] + xi;
+        if (positivity) yn = fmax(0.0, yn);
+        y[i] = yn;
+        ewt[i] = ewt_of(itol, rtol, atol, i, yn);
+    }
+    grid_reduce<1>(acc, 1u, partials, ticket, out);
+}
+
+// index-vector form of `positive` (src/sparse.f:159-163)
+__global__ void clamp_indices_kernel(int npos, const int *__restrict__ pos, int itol, const double *__restrict__ rtol,
+                                     const double *__restrict__ atol, double *__restrict__ y, double *__restrict__ ewt)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= npos) return;
+    const int i = pos[q] - 1;
+    const double yn = fmax(0.0, y[i]);
+    y[i] = yn;
+    ewt[i] = ewt_of(itol, rtol, atol, i, yn);
+}
+
+// test 2's extra evaluation (src/sparse.f:165-183): out = { sum |f| }
+__global__ void __launch_bounds__(256) sumabs_kernel(int n, const double *__restrict__ f, double *partials,
+                                                     unsigned *ticket, double *out)
+{
+    double acc[1] = {0.0};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        acc[0] += fabs(f[i]);
+    grid_reduce<1>(acc, 0u, partials, ticket, out);
+}
+
+}  // namespace rs
+
+using namespace rs;
+
+// ---- the handle ----------------------------------------------------------------------------
+struct rs_solver {
+    Ctx ctx;
+    int n = 0, nnz = 0, ngp = 0, maxg = 0, type = 0, imethod = 1;
+    GridDesc grid;
+    const rs_model_desc *model = nullptr;
+    double time = 0.0, ctol = 1e-8;
+    int itol = 1, maxiter = 100, Pos = 0, nout = 0, npos = 0, verbose = 0;
+    double min_atol = 0.0;
+    rs_krylov_control ctl = {RS_PRECOND_AUTO, 0, 0.0, 0.0, 0};
+    DevBuf<int> ian, jan, rowptr, col, group_of, pos;
+    DevBuf<double> val, y, beta, ewt, x, atol, rtol, ftmp;
+    DevBuf<double> partials, red;
+    DevBuf<unsigned> ticket;
+    double *h_red = nullptr;
+    FdWork fd;
+    Krylov kry;
+    bool structure_only = false;
+    std::vector<double> precis;
+    int niter = 0, steady = 0, krylov_iters = 0;
+    double t_setup = 0.0, t_newton = 0.0;
+    long long setup_launches = 0;
+    ~rs_solver() { if (h_red) cudaFreeHost(h_red); }
+};
+
+// parameters reach the model through its initialiser, as in src/call_stsparse.c:231-240
+static thread_local const double *tl_parms = nullptr;
+static thread_local int tl_nparms = 0, tl_parm_err = 0;
+static void steadyparms_cb(int *N, double *dst)
+{
+    if (*N != tl_nparms) {  // src/steady_utils.c:48-53
+        set_error("Confusion over the length of parms: passed to solver %d; in model %d", tl_nparms, *N);
+        tl_parm_err = 1;
+        return;
+    }
+    for (int i = 0; i < *N; i++) dst[i] = tl_parms[i];
+}
+
+static int init_model(const rs_model_desc *m, const double *initpar, int ninitpar)
+{
+    if (!m || m->abi != RS_MODEL_ABI || !m->launch) {
+        set_error("`func' must be a compiled device model (rs_model_desc with ABI %d)", RS_MODEL_ABI);
+        return RS_EMODEL;
+    }
+    if (m->initfunc && initpar) {
+        tl_parms = initpar; tl_nparms = ninitpar; tl_parm_err = 0;
+        m->initfunc(steadyparms_cb);
+        if (tl_parm_err) return RS_EMODEL;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("model initialiser failed: %s", cudaGetErrorString(e)); return RS_ENODEVICE; }
+    }
+    return RS_OK;
+}
+
+static int grid_from_nnz(int type, const int *nnzv, int nnnz, int n, GridDesc &g)
+{
+    const int at = std::abs(type);
+    g = GridDesc();
+    g.type = at;
+    const int need = at == RS_TYPE_1D ? 4 : at == RS_TYPE_2D ? 6 : 8;
+    if (nnnz < need) { set_error("nnz vector too short for sparsity type %d", type); return RS_EINVAL; }
+    g.nspec = nnzv[1];
+    if (at == RS_TYPE_1D) { g.d[0] = nnzv[2]; g.cyc[0] = nnzv[3]; g.ncell = g.d[0]; }
+    if (at == RS_TYPE_2D) { g.d[0] = nnzv[2]; g.d[1] = nnzv[3]; g.cyc[0] = nnzv[4]; g.cyc[1] = nnzv[5]; g.ncell = g.d[0] * g.d[1]; }
+    if (at == RS_TYPE_3D) {
+        g.d[0] = nnzv[2]; g.d[1] = nnzv[3]; g.d[2] = nnzv[4];
+        g.cyc[0] = nnzv[5]; g.cyc[1] = nnzv[6]; g.cyc[2] = nnzv[7];
+        g.ncell = g.d[0] * g.d[1] * g.d[2];
+    }
+    if (g.nspec <= 0 || g.ncell <= 0 || (long long)g.nspec * g.ncell != n) {
+        set_error("cannot generate sparse jacobian - N and nspec not compatible");
+        return RS_ESTRUCT;
+    }
+    return RS_OK;
+}
+
+static int check_args(const rs_stsparse_args *a)
+{
+    if (!a || !a->y || a->neq <= 0) { set_error("`y' must be numeric and non-empty"); return RS_EINVAL; }
+    if (a->maxiter < 1) { set_error("maxiter must be >=1"); return RS_EINVAL; }
+    if (!a->atol || !a->rtol || a->natol < 1 || a->nrtol < 1) { set_error("`atol' and `rtol' must be numeric"); return RS_EINVAL; }
+    if (a->natol > 1 && a->natol != a->neq) { set_error("`atol' must either be a scalar, or as long as `y'"); return RS_EINVAL; }
+    if (a->nrtol > 1 && a->nrtol != a->neq) { set_error("`rtol' must either be a scalar, or as long as `y'"); return RS_EINVAL; }
+    if (a->imethod != 1 && a->imethod != 10) { set_error("`spmethod' must be `yale' on this path (imethod 1 or 10)"); return RS_EINVAL; }
+    const int at = std::abs(a->Type);
+    if (at != RS_TYPE_USER && at != RS_TYPE_1D && at != RS_TYPE_2D && at != RS_TYPE_3D) {
+        set_error("cannot run stodes: sparsetype not known (Type %d is outside this path)", a->Type);
+        return RS_EINVAL;
+    }
+    if (!a->nnz || a->nnnz < 1) { set_error("nnz must be given"); return RS_EINVAL; }
+    if (a->Type == 0 && (!a->ian || !a->jan)) { set_error("'inz' must be specified if 'sparsetype' = 'sparseusr'"); return RS_EINVAL; }
+    for (int q = 0; q < a->npositive && a->Pos == 0 && a->npositive > 1; q++)
+        if (a->positive[q] < 1 || a->positive[q] > a->neq) {
+            set_error("the elements of 'positive' should be >0 and < the number of state variables");
+            return RS_EINVAL;
+        }
+    return RS_OK;
+}
+
+extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
+{
+    if (!out) return RS_EINVAL;
+    *out = nullptr;
+    RS_TRY(check_args(a));
+    RS_TRY(ensure_device());
+    std::unique_ptr<rs_solver> S(new rs_solver());
+    rs_solver &s = *S;
+    Ctx &c = s.ctx;
+    s.n = a->neq; s.type = a->Type; s.imethod = a->imethod; s.time = a->time; s.ctol = a->ctol;
+    s.itol = a->itol; s.maxiter = a->maxiter; s.Pos = a->Pos; s.nout = a->nout; s.verbose = a->verbose;
+    s.maxg = a->ngp > 0 ? a->ngp : a->neq + 1;
+    s.model = a->func;
+    s.structure_only = a->Type < 0;
+    if (a->control) s.ctl = *a->control;
+    const int n = s.n;
+    cudaEvent_t e0, e1;
+    RS_CUDA(cudaEventCreate(&e0));
+    RS_CUDA(cudaEventCreate(&e1));
+    RS_CUDA(cudaEventRecord(e0, c.stream));
+
+    // structure (xsparsestruct, src/sparse.f:300-455)
+    if (std::abs(a->Type) == RS_TYPE_USER) {
+        s.nnz = a->nnz[0];
+        RS_TRY(s.ian.alloc((size_t)n + 1));
+        RS_TRY(s.jan.alloc((size_t)s.nnz));
+        RS_TRY(s.ian.upload(a->ian, (size_t)n + 1, c.stream));
+        RS_TRY(s.jan.upload(a->jan, (size_t)s.nnz, c.stream));
+    } else {
+        RS_TRY(grid_from_nnz(a->Type, a->nnz, a->nnnz, n, s.grid));
+        RS_TRY(build_grid_structure(c, s.grid, n, s.ian, s.jan, &s.nnz));
+        if (s.nnz > a->nnz[0] && std::abs(a->Type) == RS_TYPE_3D) {  // interact's capacity check, src/sparsecoeff.f:193-196
+            set_error("cannot generate sparse jacobian - not enough room for nonzeros");
+            return RS_ESTRUCT;
+        }
+    }
+    if (!s.structure_only) {
+        RS_TRY(init_model(a->func, a->initpar, a->ninitpar));
+        RS_TRY(build_csr_pattern(c, n, s.nnz, s.ian.p, s.jan.p, s.rowptr, s.col));
+        RS_TRY(jgroup_device(c, s.grid, n, s.nnz, s.ian.p, s.jan.p, s.rowptr.p, s.col.p, s.maxg, s.group_of, &s.ngp));
+        RS_TRY(s.val.alloc((size_t)s.nnz));
+        RS_TRY(s.y.alloc(n)); RS_TRY(s.beta.alloc(n)); RS_TRY(s.ewt.alloc(n)); RS_TRY(s.x.alloc(n)); RS_TRY(s.ftmp.alloc(n));
+        RS_TRY(s.atol.alloc(a->natol)); RS_TRY(s.rtol.alloc(a->nrtol));
+        RS_TRY(s.atol.upload(a->atol, a->natol, c.stream));
+        RS_TRY(s.rtol.upload(a->rtol, a->nrtol, c.stream));
+        s.min_atol = *std::min_element(a->atol, a->atol + a->natol);
+        if (a->Pos == 0 && a->npositive > 1) {
+            s.npos = a->npositive;
+            RS_TRY(s.pos.alloc(s.npos));
+            RS_TRY(s.pos.upload(a->positive, s.npos, c.stream));
+        }
+        RS_TRY(s.partials.alloc(4 * 148 * 16));
+        RS_TRY(s.red.alloc(8));
+        RS_TRY(s.ticket.alloc(4));
+        RS_TRY(s.ticket.zero(c.stream));
+        RS_CUDA(cudaMallocHost((void **)&s.h_red, 8 * sizeof(double)));
+        RS_TRY(fd_setup(c, s.fd, n, s.ngp, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, 0, -1));
+        RS_TRY(krylov_setup(c, s.kry, n, s.nnz, s.rowptr.p, s.col.p, s.val.p, s.ctl.precond, s.grid.type ? s.grid.nspec : 1,
+                            s.grid.type ? s.grid.ncell : n, &s.ctl));
+        RS_TRY(s.y.upload(a->y, n, c.stream));
+    } else {
+        RS_TRY(s.y.alloc(n));
+        RS_TRY(s.y.upload(a->y, n, c.stream));
+    }
+    RS_CUDA(cudaEventRecord(e1, c.stream));
+    RS_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    s.t_setup = ms * 1e-3;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    s.setup_launches = c.launches;
+    *out = S.release();
+    return RS_OK;
+}
+
+extern "C" int rs_solver_set_state(rs_solver *s, const double *y, int is_device)
+{
+    if (!s || !y) return RS_EINVAL;
+    RS_CUDA(cudaMemcpyAsync(s->y.p, y, sizeof(double) * (size_t)s->n, is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                            s->ctx.stream));
+    return RS_OK;
+}
+
+extern "C" double *rs_solver_state_device(rs_solver *s) { return s ? s->y.p : nullptr; }
+
+extern "C" int rs_solver_get_state(rs_solver *s, double *y_host)
+{
+    if (!s || !y_host) return RS_EINVAL;
+    RS_TRY(s->y.download(y_host, s->n, s->ctx.stream));
+    RS_CUDA(cudaStreamSynchronize(s->ctx.stream));
+    return RS_OK;
+}
+
+static int read_red(rs_solver &s, int count)
+{
+    RS_CUDA(cudaMemcpyAsync(s.h_red, s.red.p, sizeof(double) * count, cudaMemcpyDeviceToHost, s.ctx.stream));
+    RS_CUDA(cudaStreamSynchronize(s.ctx.stream));
+    return RS_OK;
+}
+
+// The Newton loop, src/sparse.f:114-188.
+extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
+{
+    if (!sp) return RS_EINVAL;
+    rs_solver &s = *sp;
+    Ctx &c = s.ctx;
+    if (s.structure_only) { s.niter = 1; s.steady = 0; s.precis.assign(1, 0.0); return RS_OK; }
+    const int n = s.n, vb = grid_for(n, 256, 148 * 8);
+    cudaStream_t st = c.stream;
+    cudaEvent_t e0, e1;
+    RS_CUDA(cudaEventCreate(&e0));
+    RS_CUDA(cudaEventCreate(&e1));
+    RS_CUDA(cudaEventRecord(e0, st));
+    s.precis.assign(s.maxiter, 0.0);
+    s.niter = 0; s.steady = 0; s.krylov_iters = 0;
+    const long long launches0 = c.launches;
+    {
+        Launch L(c, K_NEWTON, 16.0 * n);
+        errset_kernel<<<vb, 256, 0, st>>>(n, s.itol, s.rtol.p, s.atol.p, s.y.p, s.ewt.p);
+    }
+    for (int it = 1; it <= s.maxiter; it++) {
+        s.niter = it;
+        RS_TRY(fd_jacobian(c, s.model, s.fd, n, s.nnz, s.ngp, s.time, s.y.p, s.group_of.p, s.rowptr.p, s.col.p, s.val.p,
+                           s.beta.p, n, 0, n));
+        {
+            Launch L(c, K_NEWTON, 16.0 * n);
+            test1_kernel<<<vb, 256, 0, st>>>(n, s.beta.p, s.ewt.p, s.partials.p, s.ticket.p, s.red.p);
+        }
+        RS_TRY(read_red(s, 2));
+        s.precis[it - 1] = s.h_red[0] / n;
+        if (!(s.h_red[0] == s.h_red[0])) { set_error("model returned NaN in the rate of change"); return RS_ESINGULAR; }
+        if (s.h_red[1] <= 1.0) { s.steady = 1; break; }
+
+        RS_TRY(krylov_precond_update(c, s.kry));
+        int kit = 0;
+        double relres = 0.0;
+        RS_TRY(krylov_solve(c, s.kry, s.beta.p, s.x.p, s.kry.lin_ewt_factor * s.min_atol, &kit, &relres));
+        s.krylov_iters += kit;
+        if (s.verbose) fprintf(stderr, "[rootsolve_b200] newton %d: mean|f|=%.6e  krylov its=%d relres=%.3e\n", it, s.precis[it - 1], kit, relres);
+        {
+            Launch L(c, K_NEWTON, 48.0 * n);
+            update_kernel<<<vb, 256, 0, st>>>(n, s.Pos > 0 ? 1 : 0, s.itol, s.rtol.p, s.atol.p, s.x.p, s.y.p, s.ewt.p,
+                                              s.partials.p, s.ticket.p, s.red.p);
+        }
+        if (s.Pos <= 0 && s.npos > 1) {
+            Launch L(c, K_NEWTON, 28.0 * s.npos);
+            clamp_indices_kernel<<<(s.npos + 255) / 256, 256, 0, st>>>(s.npos, s.pos.p, s.itol, s.rtol.p, s.atol.p, s.y.p, s.ewt.p);
+        }
+        RS_TRY(read_red(s, 1));
+        const double relchange = s.h_red[0];
+        if (relchange <= s.ctol) {
+            if (it < s.maxiter) {
+                RS_TRY(residual_only(c, s.model, s.fd, n, s.time, s.y.p, s.ftmp.p, n));
+                {
+                    Launch L(c, K_NEWTON, 8.0 * n);
+                    sumabs_kernel<<<vb, 256, 0, st>>>(n, s.ftmp.p, s.partials.p, s.ticket.p, s.red.p);
+                }
+                RS_TRY(read_red(s, 1));
+                s.precis[it] = s.h_red[0];  // a sum, not a mean: src/sparse.f:177
+                s.niter = it + 1;
+            }
+            s.steady = 1;
+            break;
+        }
+    }
+    RS_CUDA(cudaGetLastError());
+    RS_CUDA(cudaEventRecord(e1, st));
+    RS_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    s.t_newton = ms * 1e-3;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (meta) {
+        meta->niter = s.niter;
+        meta->steady[0] = s.steady; meta->steady[1] = s.nnz; meta->steady[2] = s.ngp;
+        meta->steady[3] = (int)std::min<long long>(g_device_bytes / 8, 2147483647LL);
+        meta->krylov_iters = s.krylov_iters;
+        meta->kernel_launches = (int)(c.launches - launches0);
+        meta->t_setup_s = s.t_setup;
+        meta->t_newton_s = s.t_newton;
+        if (meta->precis) for (int q = 0; q < s.niter && q < s.maxiter; q++) meta->precis[q] = s.precis[q];
+    }
+    return RS_OK;
+}
+
+extern "C" int rs_solver_set_profiling(rs_solver *s, int on)
+{
+    if (!s) return RS_EINVAL;
+    s->ctx.resolve();
+    s->ctx.profile = on != 0;
+    s->ctx.reset_stats();
+    return RS_OK;
+}
+
+extern "C" int rs_solver_kernel_stats(rs_solver *s, int cap, const char **names, double *ms, long long *launches, double *bytes)
+{
+    if (!s) return 0;
+    s->ctx.resolve();
+    int k = 0;
+    for (int i = 0; i < K_COUNT && k < cap; i++) {
+        if (s->ctx.count[i] == 0) continue;
+        names[k] = kKernelNames[i];
+        ms[k] = s->ctx.ms[i];
+        launches[k] = s->ctx.count[i];
+        bytes[k] = s->ctx.bytes[i];
+        k++;
+    }
+    return k;
+}
+
+extern "C" void rs_solver_destroy(rs_solver *s) { delete s; }
+
+// Fills the caller's result buffers from a finished handle (src/call_stsparse.c:278-317).
+static int pack_result(rs_solver &s, const rs_stsparse_args *a, rs_stsparse_result *r)
+{
+    Ctx &c = s.ctx;
+    const int n = s.n;
+    if (r->y) {
+        RS_TRY(s.y.download(r->y, n, c.stream));
+        if (a->nout > 0 && !s.structure_only) {  // one more derivs call for the outputs, src/call_stsparse.c:281-286
+            RS_TRY(residual_only(c, s.model, s.fd, n, s.time, s.y.p, s.ftmp.p, n));
+            RS_CUDA(cudaMemcpyAsync(r->y + n, s.fd.yout.p, sizeof(double) * a->nout, cudaMemcpyDeviceToHost, c.stream));
+        }
+    }
+    if (r->ian) RS_TRY(s.ian.download(r->ian, (size_t)n + 1, c.stream));
+    if (r->jan) RS_TRY(s.jan.download(r->jan, (size_t)std::min(s.nnz, a->nnz[0]), c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    if (!s.structure_only && (r->igp || r->jgp)) {
+        if (r->igp) for (int q = 0; q <= s.maxg; q++) r->igp[q] = 0;
+        RS_TRY(jgroup_lists(c, n, s.ngp, s.group_of.p, r->igp, r->jgp));
+    }
+    r->niter = s.niter;
+    r->steady[0] = s.structure_only ? 0 : s.steady;
+    r->steady[1] = s.nnz;
+    r->steady[2] = s.ngp;
+    if (r->precis) for (int q = 0; q < s.niter && q < a->maxiter; q++) r->precis[q] = s.precis[q];
+    return RS_OK;
+}
+
+extern "C" int rs_stsparse(const rs_stsparse_args *a, rs_stsparse_result *r)
+{
+    if (!r) { set_error("result must not be NULL"); return RS_EINVAL; }
+    rs_solver *s = nullptr;
+    int rc = rs_solver_create(a, &s);
+    if (rc != RS_OK) return rc;
+    rc = rs_solver_run(s, r);
+    if (rc == RS_OK) rc = pack_result(*s, a, r);
+    if (rc == RS_OK) {
+        r->kernel_launches = (int)s->ctx.launches;
+        r->t_setup_s = s->t_setup;
+        r->t_newton_s = s->t_newton;
+        r->krylov_iters = s->krylov_iters;
+        r->steady[3] = (int)std::min<long long>(g_device_bytes / 8, 2147483647LL);
+    }
+    rs_solver_destroy(s);
+    return rc;
+}
+
+// ---- building blocks for the parity tests ---------------------------------------------------------
+extern "C" int rs_sparse_structure(int type, int neq, int nspec, const int *dims, const int *cyclic, int *nnz, int *ian, int *jan)
+{
+    if (!dims || !nnz || !ian || !jan) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    Ctx c;
+    GridDesc g;
+    g.type = type; g.nspec = nspec;
+    const int nd = type == RS_TYPE_1D ? 1 : type == RS_TYPE_2D ? 2 : type == RS_TYPE_3D ? 3 : 0;
+    if (!nd) { set_error("type must be RS_TYPE_1D, 2D or 3D"); return RS_EINVAL; }
+    long long cells = 1;
+    for (int q = 0; q < nd; q++) { g.d[q] = dims[q]; g.cyc[q] = cyclic ? cyclic[q] : 0; cells *= dims[q]; }
+    g.ncell = (int)cells;
+    DevBuf<int> d_ian, d_jan;
+    int z = 0;
+    RS_TRY(build_grid_structure(c, g, neq, d_ian, d_jan, &z));
+    if (z > *nnz) { set_error("cannot generate sparse jacobian - not enough room for nonzeros"); return RS_ESTRUCT; }
+    RS_TRY(d_ian.download(ian, (size_t)neq + 1, c.stream));
+    RS_TRY(d_jan.download(jan, (size_t)z, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    *nnz = z;
+    return RS_OK;
+}
+
+extern "C" int rs_jgroup(int neq, const int *ian, const int *jan, int maxg, const int *grid_hint, int *ngp, int *igp, int *jgp)
+{
+    if (!ian || !jan || !ngp) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    Ctx c;
+    const int nnz = ian[neq] - 1;
+    DevBuf<int> d_ian, d_jan, rowptr, col, group_of;
+    RS_TRY(d_ian.alloc((size_t)neq + 1)); RS_TRY(d_jan.alloc((size_t)nnz));
+    RS_TRY(d_ian.upload(ian, (size_t)neq + 1, c.stream));
+    RS_TRY(d_jan.upload(jan, (size_t)nnz, c.stream));
+    GridDesc g;
+    if (grid_hint && grid_hint[0]) {
+        g.type = grid_hint[0]; g.nspec = grid_hint[1];
+        for (int q = 0; q < 3; q++) { g.d[q] = grid_hint[2 + q] > 0 ? grid_hint[2 + q] : 1; g.cyc[q] = grid_hint[5 + q]; }
+        g.ncell = g.d[0] * g.d[1] * g.d[2];
+    }
+    // the rounds variant walks rows -> needs the row-wise pattern; duplicates are legal for grouping
+    int rc = build_csr_pattern(c, neq, nnz, d_ian.p, d_jan.p, rowptr, col);
+    if (rc != RS_OK && rc != RS_EDUPLICATE) return rc;
+    RS_TRY(jgroup_device(c, g, neq, nnz, d_ian.p, d_jan.p, rowptr.p, col.p, maxg, group_of, ngp));
+    if (igp) for (int q = 0; q <= maxg; q++) igp[q] = 0;
+    RS_TRY(jgroup_lists(c, neq, *ngp, group_of.p, igp, jgp));
+    return RS_OK;
+}
+
+static int group_of_from_lists(int neq, int ngp, const int *igp, const int *jgp, std::vector<int> &g)
+{
+    g.assign((size_t)neq, -1);
+    for (int q = 0; q < ngp; q++)
+        for (int k = igp[q]; k < igp[q + 1]; k++) {
+            const int j = jgp[k - 1];
+            if (j < 1 || j > neq) { set_error("jgp out of range"); return RS_EINVAL; }
+            g[j - 1] = q;
+        }
+    for (int j = 0; j < neq; j++)
+        if (g[j] < 0) { set_error("column %d is in no group", j + 1); return RS_EINVAL; }
+    return RS_OK;
+}
+
+extern "C" int rs_fd_jacobian(const rs_model_desc *func, const double *initpar, int ninitpar, int neq, double time,
+                              const double *y, const int *ian, const int *jan, const int *igp, const int *jgp, int ngp,
+                              const double *rpar, int nrpar, const int *ipar, int nipar, double *beta, double *a)
+{
+    if (!y || !ian || !jan || !igp || !jgp) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    RS_TRY(init_model(func, initpar, ninitpar));
+    Ctx c;
+    const int nnz = ian[neq] - 1;
+    std::vector<int> g;
+    RS_TRY(group_of_from_lists(neq, ngp, igp, jgp, g));
+    DevBuf<int> d_ian, d_jan, rowptr, col, group_of;
+    DevBuf<double> d_y, d_val, d_beta, d_a;
+    RS_TRY(d_ian.alloc((size_t)neq + 1)); RS_TRY(d_jan.alloc((size_t)nnz)); RS_TRY(group_of.alloc(neq));
+    RS_TRY(d_y.alloc(neq)); RS_TRY(d_val.alloc((size_t)nnz)); RS_TRY(d_beta.alloc(neq)); RS_TRY(d_a.alloc((size_t)nnz));
+    RS_TRY(d_ian.upload(ian, (size_t)neq + 1, c.stream));
+    RS_TRY(d_jan.upload(jan, (size_t)nnz, c.stream));
+    RS_TRY(group_of.upload(g.data(), neq, c.stream));
+    RS_TRY(d_y.upload(y, neq, c.stream));
+    RS_TRY(build_csr_pattern(c, neq, nnz, d_ian.p, d_jan.p, rowptr, col));
+    FdWork w;
+    RS_TRY(fd_setup(c, w, neq, ngp, 0, rpar, nrpar, ipar, nipar, 0, -1));
+    RS_TRY(fd_jacobian(c, func, w, neq, nnz, ngp, time, d_y.p, group_of.p, rowptr.p, col.p, d_val.p, d_beta.p, neq, 0, neq));
+    RS_TRY(gather_csc_values(c, neq, nnz, d_ian.p, d_jan.p, rowptr.p, col.p, d_val.p, d_a.p));
+    if (beta) RS_TRY(d_beta.download(beta, neq, c.stream));
+    if (a) RS_TRY(d_a.download(a, (size_t)nnz, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    return RS_OK;
+}
+
+extern "C" int rs_residual(const rs_model_desc *func, const double *initpar, int ninitpar, int neq, double time,
+                           const double *y, const double *rpar, int nrpar, const int *ipar, int nipar, double *ydot)
+{
+    if (!y || !ydot) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    RS_TRY(init_model(func, initpar, ninitpar));
+    Ctx c;
+    DevBuf<double> d_y, d_f;
+    RS_TRY(d_y.alloc(neq)); RS_TRY(d_f.alloc(neq));
+    RS_TRY(d_y.upload(y, neq, c.stream));
+    RS_TRY(d_f.zero(c.stream));
+    FdWork w;
+    RS_TRY(fd_setup(c, w, neq, 0, 0, rpar, nrpar, ipar, nipar, 0, -1));
+    RS_TRY(residual_only(c, func, w, neq, time, d_y.p, d_f.p, neq));
+    RS_TRY(d_f.download(ydot, neq, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    return RS_OK;
+}
+
+__global__ void shift_down_kernel(int n, const int *__restrict__ in, int *__restrict__ out)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) out[i] = in[i] - 1;
+}
+
+// row-wise (0-based) pattern + values of J (transposed=0) or J' (transposed=1) from the column-wise input
+static int csr_from_columns(Ctx &c, int neq, int nnz, const int *ian, const int *jan, const double *a, int transposed,
+                            DevBuf<int> &rowptr, DevBuf<int> &col, DevBuf<double> &val)
+{
+    DevBuf<int> d_ian, d_jan;
+    DevBuf<double> d_a;
+    RS_TRY(d_ian.alloc((size_t)neq + 1)); RS_TRY(d_jan.alloc((size_t)nnz)); RS_TRY(d_a.alloc((size_t)nnz));
+    RS_TRY(d_ian.upload(ian, (size_t)neq + 1, c.stream));
+    RS_TRY(d_jan.upload(jan, (size_t)nnz, c.stream));
+    RS_TRY(d_a.upload(a, (size_t)nnz, c.stream));
+    RS_TRY(val.alloc((size_t)nnz));
+    if (transposed) {  // the columns of J are the rows of J'
+        RS_TRY(rowptr.alloc((size_t)neq + 1)); RS_TRY(col.alloc((size_t)nnz));
+        shift_down_kernel<<<grid_for(neq + 1, 256), 256, 0, c.stream>>>(neq + 1, d_ian.p, rowptr.p);
+        shift_down_kernel<<<grid_for(nnz, 256), 256, 0, c.stream>>>(nnz, d_jan.p, col.p);
+        c.launches += 2;
+        RS_CUDA(cudaMemcpyAsync(val.p, d_a.p, sizeof(double) * (size_t)nnz, cudaMemcpyDeviceToDevice, c.stream));
+    } else {
+        RS_TRY(build_csr_pattern(c, neq, nnz, d_ian.p, d_jan.p, rowptr, col));
+        RS_TRY(scatter_csc_values(c, neq, nnz, d_ian.p, d_jan.p, rowptr.p, col.p, d_a.p, val.p));
+    }
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    return RS_OK;
+}
+
+extern "C" int rs_spmv(int neq, const int *ian, const int *jan, const double *a, const double *x, double *y)
+{
+    if (!ian || !jan || !a || !x || !y) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    Ctx c;
+    const int nnz = ian[neq] - 1;
+    DevBuf<int> rowptr, col;
+    DevBuf<double> val, d_x, d_y;
+    RS_TRY(csr_from_columns(c, neq, nnz, ian, jan, a, 0, rowptr, col, val));
+    RS_TRY(d_x.alloc(neq)); RS_TRY(d_y.alloc(neq));
+    RS_TRY(d_x.upload(x, neq, c.stream));
+    RS_TRY(spmv_launch(c, neq, nnz, rowptr.p, col.p, val.p, d_x.p, d_y.p, pick_lanes(neq, nnz)));
+    RS_TRY(d_y.download(y, neq, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    return RS_OK;
+}
+
+extern "C" int rs_linsolve(int neq, const int *ian, const int *jan, const double *a, const double *b, int transposed,
+                           int nspec_block, const rs_krylov_control *control, double *x, int *iters, double *relres)
+{
+    if (!ian || !jan || !a || !b || !x) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    Ctx c;
+    const int nnz = ian[neq] - 1;
+    DevBuf<int> rowptr, col;
+    DevBuf<double> val, d_b, d_x;
+    RS_TRY(csr_from_columns(c, neq, nnz, ian, jan, a, transposed, rowptr, col, val));
+    RS_TRY(d_b.alloc(neq)); RS_TRY(d_x.alloc(neq));
+    RS_TRY(d_b.upload(b, neq, c.stream));
+    Krylov k;
+    const int nspec = nspec_block > 1 ? nspec_block : 1;
+    RS_TRY(krylov_setup(c, k, neq, nnz, rowptr.p, col.p, val.p, control ? control->precond : RS_PRECOND_AUTO, nspec,
+                        nspec > 1 ? neq / nspec : neq, control));
+    RS_TRY(krylov_precond_update(c, k));
+    int it = 0;
+    double rr = 0.0;
+    RS_TRY(krylov_solve(c, k, d_b.p, d_x.p, 0.0, &it, &rr));
+    RS_TRY(d_x.download(x, neq, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    if (iters) *iters = it;
+    if (relres) *relres = rr;
+    return RS_OK;
+}
+
+extern "C" int rs_errset(int neq, int itol, const double *rtol, const double *atol, const double *y, double *ewt)
+{
+    if (!rtol || !atol || !y || !ewt) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    Ctx c;
+    const int nr = (itol == 3 || itol == 4) ? neq : 1, na = (itol == 2 || itol == 4) ? neq : 1;
+    DevBuf<double> d_r, d_a, d_y, d_e;
+    RS_TRY(d_r.alloc(nr)); RS_TRY(d_a.alloc(na)); RS_TRY(d_y.alloc(neq)); RS_TRY(d_e.alloc(neq));
+    RS_TRY(d_r.upload(rtol, nr, c.stream)); RS_TRY(d_a.upload(atol, na, c.stream)); RS_TRY(d_y.upload(y, neq, c.stream));
+    errset_kernel<<<grid_for(neq, 256), 256, 0, c.stream>>>(neq, itol, d_r.p, d_a.p, d_y.p, d_e.p);
+    RS_TRY(d_e.download(ewt, neq, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    return RS_OK;
+}
+
+extern "C" const char *rs_last_error(void) { return g_err; }
+extern "C" int rs_abi_version(void) { return RS_ABI_VERSION; }
+extern "C" int rs_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}

@@ -1,0 +1,172 @@
+// fdjac.cu -- the grouped finite-difference Jacobian (replaces xSparseJacob,
+// src/sparse.f:461-525).
+//
+// The reference perturbs the columns of one group in place, calls the model,
+// harvests the group's columns, restores, and moves to the next group: ngp+1
+// sequential model calls.  Here the ngp+1 state vectors are laid out side by
+// side (K_PERTURB), ALL of them are evaluated by one batched launch of the
+// model's residual (K_RESIDUAL, grid.y = evaluation), and one assembly pass
+// (K_ASSEMBLE) writes every entry of J straight into the row-wise arrays the
+// Krylov solver reads:
+//     J(i,j) = (f_g(j)[i] - f_0[i]) / ((y_j + delta_j) - y_j)
+// with delta = max(|y_j| 1e-8, 1e-8) (Perturb, src/steady.f:219-224) and the
+// ROUNDED difference as divisor (src/sparse.f:511).  beta = -f_0.
+// The arithmetic is ordered as in the reference and this file is compiled with
+// -fmad=false, so a[] is bit-identical to the reference's when the model's own
+// arithmetic is.
+#include "solver.cuh"
+
+namespace rs {
+
+__device__ __forceinline__ double perturbed(double v)
+{
+    double d = fabs(v) * 1.0e-8;
+    if (d < 1.0e-8) d = 1.0e-8;
+    return v + d;
+}
+
+// Y[0] = y ; Y[g+1][i] = y[i] (+delta_i when column i belongs to group g), rows [r0,r1) only... all rows here.
+__global__ void __launch_bounds__(256) perturb_kernel(int n, int ngp, const double *__restrict__ y,
+                                                      const int *__restrict__ group_of, double *__restrict__ Y,
+                                                      long long ld)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double v = y[i];
+        const double vp = perturbed(v);
+        const int g = group_of[i];
+        Y[i] = v;
+        for (int q = 0; q < ngp; q++) Y[(long long)(q + 1) * ld + i] = (q == g) ? vp : v;
+    }
+}
+
+// LANES threads per row; entry p of row i: column j = col[p].
+template <int LANES>
+__global__ void __launch_bounds__(256) assemble_kernel(int row0, int row1, const int *__restrict__ rowptr,
+                                                       const int *__restrict__ col, const int *__restrict__ group_of,
+                                                       const double *__restrict__ y, const double *__restrict__ F,
+                                                       long long ld, double *__restrict__ val,
+                                                       double *__restrict__ beta)
+{
+    const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = (int)(gt % LANES);
+    const long long nrows = row1 - row0;
+    for (long long r = gt / LANES; r < nrows; r += ((long long)gridDim.x * blockDim.x) / LANES) {
+        const int i = row0 + (int)r;
+        const double f0 = F[i];
+        if (lane == 0) beta[i] = -f0;
+        const int e = rowptr[i + 1];
+        for (int p = rowptr[i] + lane; p < e; p += LANES) {
+            const int j = col[p];
+            const double yj = y[j];
+            const double divdelt = perturbed(yj) - yj;
+            const double fg = F[(long long)(group_of[j] + 1) * ld + i];
+            val[p] = (fg + (-f0)) / divdelt;
+        }
+    }
+}
+
+int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, int nrpar, const int *ipar,
+             int nipar, int slab_j0, int slab_j1)
+{
+    // 256-byte aligned leading dimension so every evaluation starts on a fresh line
+    w.ld = ((long long)n + 31) / 32 * 32;
+    RS_TRY(w.Y.alloc((size_t)w.ld * (ngp + 1)));
+    RS_TRY(w.F.alloc((size_t)w.ld * (ngp + 1)));
+    // ipar / out exactly as initOut builds them (src/steady_utils.c:109-124), then the slab bounds
+    const int lrpar = nout + nrpar, lipar = 3 + nipar;
+    w.ldout = lrpar > 0 ? lrpar : 1;
+    std::vector<int> ip((size_t)lipar + 2);
+    ip[0] = nout; ip[1] = lrpar; ip[2] = lipar;
+    for (int q = 0; q < nipar; q++) ip[3 + q] = ipar[q];
+    ip[lipar] = slab_j0; ip[lipar + 1] = slab_j1;
+    RS_TRY(w.ip.alloc(ip.size()));
+    RS_TRY(w.ip.upload(ip.data(), ip.size(), c.stream));
+    std::vector<double> out((size_t)w.ldout * (ngp + 1), 0.0);
+    for (int b = 0; b <= ngp; b++)
+        for (int q = 0; q < nrpar; q++) out[(size_t)b * w.ldout + nout + q] = rpar[q];
+    RS_TRY(w.yout.alloc(out.size()));
+    RS_TRY(w.yout.upload(out.data(), out.size(), c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    return RS_OK;
+}
+
+int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
+                const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
+                long long work, int row0, int row1)
+{
+    {
+        Launch L(c, K_PERTURB, 12.0 * n + 8.0 * n * (ngp + 1));
+        perturb_kernel<<<grid_for(n, 256), 256, 0, c.stream>>>(n, ngp, d_y, d_group_of, w.Y.p, w.ld);
+    }
+    {
+        Launch L(c, K_RESIDUAL, 16.0 * work * (ngp + 1));
+        const int e = m->launch((void *)c.stream, n, t, w.Y.p, w.F.p, w.ld, ngp + 1, w.yout.p, w.ldout, w.ip.p, work);
+        if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
+    }
+    {
+        const long long rows = row1 - row0;
+        Launch L(c, K_ASSEMBLE, 20.0 * nnz + 20.0 * n);
+        assemble_kernel<8><<<grid_for(rows * 8, 256, 148 * 16), 256, 0, c.stream>>>(row0, row1, d_rowptr, d_col, d_group_of,
+                                                                                  d_y, w.F.p, w.ld, d_val, d_beta);
+    }
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+int residual_only(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, const double *d_y, double *d_f,
+                  long long work)
+{
+    Launch L(c, K_RESIDUAL, 16.0 * work);
+    const int e = m->launch((void *)c.stream, n, t, d_y, d_f, w.ld, 1, w.yout.p, w.ldout, w.ip.p, work);
+    if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
+    return RS_OK;
+}
+
+// ---- jan-order <-> row-wise values --------------------------------------------
+__device__ __forceinline__ int find_in_row(const int *__restrict__ col, int b, int e, int j)
+{
+    while (b < e) {
+        const int mid = (b + e) >> 1;
+        const int cj = col[mid];
+        if (cj == j) return mid;
+        if (cj < j) b = mid + 1; else e = mid;
+    }
+    return -1;
+}
+
+template <bool TO_CSC>
+__global__ void csc_csr_kernel(int n, const int *__restrict__ ian, const int *__restrict__ jan,
+                               const int *__restrict__ rowptr, const int *__restrict__ col, double *__restrict__ val,
+                               double *__restrict__ a)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    for (int k = ian[j] - 1; k < ian[j + 1] - 1; k++) {
+        const int i = jan[k] - 1;
+        const int p = find_in_row(col, rowptr[i], rowptr[i + 1], j);
+        if (p < 0) continue;
+        if (TO_CSC) a[k] = val[p]; else val[p] = a[k];
+    }
+}
+
+int gather_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, const int *d_rowptr,
+                      const int *d_col, const double *d_val, double *d_a)
+{
+    Launch L(c, K_MISC, 24.0 * nnz);
+    csc_csr_kernel<true><<<(n + 255) / 256, 256, 0, c.stream>>>(n, d_ian, d_jan, d_rowptr, d_col,
+                                                                const_cast<double *>(d_val), d_a);
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+int scatter_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, const int *d_rowptr,
+                       const int *d_col, const double *d_a, double *d_val)
+{
+    Launch L(c, K_MISC, 24.0 * nnz);
+    csc_csr_kernel<false><<<(n + 255) / 256, 256, 0, c.stream>>>(n, d_ian, d_jan, d_rowptr, d_col, d_val,
+                                                                 const_cast<double *>(d_a));
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+}  // namespace rs

@@ -1,0 +1,231 @@
+// jgroup.cu -- K1: column grouping for the finite-difference Jacobian.
+//
+// Reproduces JGROUP (src/sparse.f:531-616) bit for bit.  The reference is a
+// sequential greedy: group g takes, scanning columns in ascending order, every
+// ungrouped column none of whose rows is covered by a column already taken
+// into g.  Equivalently: column j joins g iff no ungrouped column j' < j that
+// shares a row with j has joined g -- the lexicographically first maximal
+// independent set of the column-intersection graph.  Two exact device variants:
+//
+//  * wavefront (regular non-cyclic 2-D/3-D grids): with the level function
+//    phi = S*species + 4*j + 2*k + l (3-D) or S*species + 2*j + k (2-D) every
+//    pair of conflicting columns lies on different levels and the lower index
+//    is always on the lower level, so sweeping the levels in order with a
+//    "row covered" bitmap is the sequential algorithm, run one hyperplane at a
+//    time by a cooperative kernel (grid-wide barrier between levels);
+//  * rounds (any structure, used for 1-D, cyclic and user patterns): each
+//    undecided column looks at the lower-index columns it conflicts with;
+//    one of them in the group -> rejected; all of them rejected or grouped
+//    earlier -> accepted; otherwise it waits for the next round.  Decisions are
+//    only ever taken on final information, so the fixed point is the greedy's.
+#include <cooperative_groups.h>
+
+#include "solver.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace rs {
+
+enum : unsigned char { ST_UNDECIDED = 0, ST_ACCEPTED = 1, ST_REJECTED = 2, ST_DONE = 3 };
+
+__global__ void jg_round_kernel(int n, const int *__restrict__ ian, const int *__restrict__ jan,
+                                const int *__restrict__ rowptr, const int *__restrict__ col,
+                                volatile unsigned char *state, int *__restrict__ undecided)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n || state[j] != ST_UNDECIDED) return;
+    for (int attempt = 0; attempt < 8; attempt++) {
+        bool pending = false, reject = false;
+        for (int k = ian[j] - 1; k < ian[j + 1] - 1 && !reject; k++) {
+            const int i = jan[k] - 1;
+            for (int p = rowptr[i]; p < rowptr[i + 1]; p++) {
+                const int jj = col[p];
+                if (jj >= j) break;  // columns of a row are sorted ascending
+                const unsigned char st = state[jj];
+                if (st == ST_ACCEPTED) { reject = true; break; }
+                if (st == ST_UNDECIDED) pending = true;
+            }
+        }
+        if (reject) { state[j] = ST_REJECTED; return; }
+        if (!pending) { state[j] = ST_ACCEPTED; return; }
+    }
+    atomicAdd(undecided, 1);
+}
+
+__global__ void jg_commit_kernel(int n, unsigned char *__restrict__ state, int *__restrict__ group_of, int g,
+                                 int *__restrict__ accepted)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    int mine = 0;
+    if (j < n) {
+        const unsigned char st = state[j];
+        if (st == ST_ACCEPTED) { group_of[j] = g; state[j] = ST_DONE; mine = 1; }
+        else if (st == ST_REJECTED) state[j] = ST_UNDECIDED;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, mine);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(accepted, __popc(m));
+}
+
+// One group of the wavefront variant.  covered[] must be zero on entry.
+__global__ void __launch_bounds__(256) jg_wave_kernel(GridDesc g, int S, int nlevels, const int *__restrict__ ian,
+                                                      const int *__restrict__ jan, unsigned char *done,
+                                                      unsigned char *covered, int *__restrict__ group_of,
+                                                      int gidx, int *__restrict__ accepted)
+{
+    cg::grid_group grid = cg::this_grid();
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nthreads = (long long)gridDim.x * blockDim.x;
+    const int d1 = g.d[0], d2 = g.d[1], d3 = g.d[2];
+    const bool three = (g.type == RS_TYPE_3D);
+    // candidate lines: (species, j, k) in 3-D, (species, j) in 2-D; the last
+    // coordinate follows from the level
+    const long long nlines = three ? (long long)g.nspec * d1 * d2 : (long long)g.nspec * d1;
+    const int dl = three ? d3 : d2;
+    int count = 0;
+    for (int t = 0; t < nlevels; t++) {
+        for (long long q = tid; q < nlines; q += nthreads) {
+            int s, last;
+            long long c;
+            if (three) {
+                const int k = (int)(q % d2);
+                const long long r = q / d2;
+                const int j = (int)(r % d1);
+                s = (int)(r / d1);
+                last = t - S * s - 4 * j - 2 * k;
+                c = q * d3 + last;
+            } else {
+                const int j = (int)(q % d1);
+                s = (int)(q / d1);
+                last = t - S * s - 2 * j;
+                c = q * d2 + last;
+            }
+            if (last < 0 || last >= dl) continue;
+            if (done[c]) continue;
+            const int k0 = ian[c] - 1, k1 = ian[c + 1] - 1;
+            bool clash = false;
+            for (int k = k0; k < k1; k++)
+                if (covered[jan[k] - 1]) { clash = true; break; }
+            if (clash) continue;
+            done[c] = 1;
+            group_of[c] = gidx;
+            for (int k = k0; k < k1; k++) covered[jan[k] - 1] = 1;
+            count++;
+        }
+        grid.sync();
+    }
+    if (count) atomicAdd(accepted, count);
+}
+
+static bool wave_applicable(const GridDesc &g)
+{
+    if (g.type != RS_TYPE_2D && g.type != RS_TYPE_3D) return false;
+    for (int q = 0; q < 3; q++) if (g.cyc[q]) return false;
+    return true;
+}
+
+int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, const int *d_jan,
+                  const int *d_rowptr, const int *d_col, int maxg, DevBuf<int> &group_of, int *ngp)
+{
+    (void)nnz;
+    RS_TRY(group_of.alloc(n));
+    DevBuf<unsigned char> state;
+    DevBuf<int> counters;  // [0] undecided, [1] accepted
+    RS_TRY(state.alloc(n));
+    RS_TRY(counters.alloc(2));
+    RS_TRY(state.zero(c.stream));
+    int total = 0, groups = 0;
+
+    if (wave_applicable(g)) {
+        DevBuf<unsigned char> covered;
+        RS_TRY(covered.alloc(n));
+        const bool three = g.type == RS_TYPE_3D;
+        const int S = three ? 5 : 3;
+        const int nlevels = three ? S * (g.nspec - 1) + 4 * (g.d[0] - 1) + 2 * (g.d[1] - 1) + g.d[2]
+                                  : S * (g.nspec - 1) + 2 * (g.d[0] - 1) + g.d[1];
+        int dev = 0, sms = 0, per_sm = 0;
+        RS_CUDA(cudaGetDevice(&dev));
+        RS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jg_wave_kernel, 256, 0));
+        const long long nlines = three ? (long long)g.nspec * g.d[0] * g.d[1] : (long long)g.nspec * g.d[0];
+        long long want = (nlines + 255) / 256;
+        long long cap = (long long)sms * (per_sm > 2 ? 2 : per_sm);
+        int blocks = (int)(want < cap ? want : cap);
+        if (blocks < 1) blocks = 1;
+        while (total < n) {
+            if (groups >= maxg) {
+                set_error("error during grouping: NGP too small (should be more than %d)", maxg);
+                return RS_EGROUP;
+            }
+            RS_TRY(covered.zero(c.stream));
+            RS_CUDA(cudaMemsetAsync(counters.p, 0, 2 * sizeof(int), c.stream));
+            GridDesc gg = g;
+            int Sx = S, nl = nlevels, gi = groups;
+            unsigned char *dn = state.p, *cv = covered.p;
+            int *go = group_of.p, *acc = counters.p + 1;
+            void *args[] = {&gg, &Sx, &nl, (void *)&d_ian, (void *)&d_jan, &dn, &cv, &go, &gi, &acc};
+            {
+                Launch L(c, K_JGROUP, 9.0 * n + 4.0 * nnz);
+                RS_CUDA(cudaLaunchCooperativeKernel((void *)jg_wave_kernel, dim3(blocks), dim3(256), args, 0, c.stream));
+            }
+            int acc_h = 0;
+            RS_CUDA(cudaMemcpyAsync(&acc_h, counters.p + 1, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+            RS_CUDA(cudaStreamSynchronize(c.stream));
+            if (acc_h == 0) break;  // cannot happen while columns remain; guards against a hang
+            total += acc_h;
+            groups++;
+        }
+    } else {
+        const int blocks = (n + 255) / 256;
+        while (total < n) {
+            if (groups >= maxg) {
+                set_error("error during grouping: NGP too small (should be more than %d)", maxg);
+                return RS_EGROUP;
+            }
+            int guard = 0;
+            for (;;) {
+                RS_CUDA(cudaMemsetAsync(counters.p, 0, 2 * sizeof(int), c.stream));
+                {
+                    Launch L(c, K_JGROUP, 1.0 * n);
+                    jg_round_kernel<<<blocks, 256, 0, c.stream>>>(n, d_ian, d_jan, d_rowptr, d_col, state.p, counters.p);
+                }
+                int und = 0;
+                RS_CUDA(cudaMemcpyAsync(&und, counters.p, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+                RS_CUDA(cudaStreamSynchronize(c.stream));
+                if (und == 0) break;
+                if (++guard > n + 8) { set_error("internal: grouping rounds did not converge"); return RS_EGROUP; }
+            }
+            {
+                Launch L(c, K_JGROUP, 6.0 * n);
+                jg_commit_kernel<<<blocks, 256, 0, c.stream>>>(n, state.p, group_of.p, groups, counters.p + 1);
+            }
+            int acc_h = 0;
+            RS_CUDA(cudaMemcpyAsync(&acc_h, counters.p + 1, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+            RS_CUDA(cudaStreamSynchronize(c.stream));
+            if (acc_h == 0) break;
+            total += acc_h;
+            groups++;
+        }
+    }
+    *ngp = groups;
+    return RS_OK;
+}
+
+// igp/jgp exactly as JGROUP lays them out: jgp lists the columns group by group,
+// ascending inside a group; igp(g) is the 1-based start of group g, igp(ngp+1)=n+1.
+int jgroup_lists(Ctx &c, int n, int ngp, const int *d_group_of, int *igp_host, int *jgp_host)
+{
+    std::vector<int> g((size_t)n);
+    RS_CUDA(cudaMemcpyAsync(g.data(), d_group_of, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    std::vector<int> start((size_t)ngp + 1, 0);
+    for (int j = 0; j < n; j++) start[g[j] + 1]++;
+    for (int q = 0; q < ngp; q++) start[q + 1] += start[q];
+    if (igp_host) for (int q = 0; q <= ngp; q++) igp_host[q] = start[q] + 1;
+    if (jgp_host) {
+        std::vector<int> cur(start.begin(), start.end() - 1);
+        for (int j = 0; j < n; j++) jgp_host[cur[g[j]]++] = j + 1;
+    }
+    return RS_OK;
+}
+
+}  // namespace rs

@@ -1,0 +1,411 @@
+// krylov.cu -- the Newton linear solve: right-preconditioned BiCGStab around a
+// row-wise SpMV.  Stands in for the Yale sparse LDU of the reference
+// (cdrv -> nroc/nsfc/nnfc/nntc, src/sparse.f:1427-2563), which re-factors the
+// matrix symbolically and numerically on every Newton iteration.
+//
+// Kernels (all FP64, all bandwidth bound; algorithmic bytes in DESIGN.md):
+//   K_SPMV   y = A x, LANES threads per row, shuffle reduction inside the
+//            sub-warp, with the dot products that follow the product in
+//            BiCGStab fused into the same pass (block reduce -> per-block
+//            partials -> last block folds them in fixed order);
+//   K_VEC    the three fused vector updates of one BiCGStab step (direction,
+//            intermediate residual, solution + residual), each also applying
+//            the (block-)Jacobi preconditioner and producing its dots;
+//   K_PRECOND_SETUP  inverse diagonal / inverse nspec x nspec cell blocks.
+// Every scalar of the recurrence (rho, alpha, omega, beta) stays on the device:
+// kernels recompute them from the raw dot products in `scal`, so one step is
+// five launches and the host only reads ||r||^2 to decide when to stop.
+#include <cmath>
+
+#include "solver.cuh"
+
+namespace rs {
+
+constexpr int MAXS = 8;        // largest species count handled by the block preconditioner
+constexpr int SLOT = 8;        // doubles per parity slot: r0v, ts, tt, rr, rhonext
+constexpr int S_R0V = 0, S_TS = 1, S_TT = 2, S_RR = 3, S_RHONEXT = 4;
+constexpr int S_BNORM = 2 * SLOT;
+constexpr int NSCAL = 2 * SLOT + 8;
+
+Krylov::~Krylov()
+{
+    if (h_scal) cudaFreeHost(h_scal);
+}
+
+int pick_lanes(int n, int nnz)
+{
+    const double avg = n > 0 ? (double)nnz / n : 1.0;
+    if (avg <= 4.0) return 4;
+    if (avg <= 8.5) return 8;
+    if (avg <= 16.0) return 16;
+    return 32;
+}
+
+// ---- SpMV ------------------------------------------------------------------------
+// NDOT = 0: plain product.  NDOT = 1: out[0] = <w, y>.  NDOT = 2: out[0] = <y, w>, out[1] = <y, y>.
+template <int LANES, int NDOT>
+__global__ void __launch_bounds__(256) spmv_kernel(int n, const int *__restrict__ rowptr, const int *__restrict__ col,
+                                                   const double *__restrict__ val, const double *__restrict__ x,
+                                                   double *__restrict__ y, const double *__restrict__ w,
+                                                   double *partials, unsigned *ticket, double *out)
+{
+    const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x % LANES;
+    const long long stride = ((long long)gridDim.x * blockDim.x) / LANES;
+    double acc[NDOT > 0 ? NDOT : 1] = {0.0};
+    // every thread runs the same number of trips so the shuffles stay converged
+    const long long trips = (n + stride - 1) / stride;
+    long long r = gt / LANES;
+    for (long long it = 0; it < trips; it++, r += stride) {
+        double sum = 0.0;
+        if (r < n) {
+            const int e = rowptr[r + 1];
+            for (int p = rowptr[r] + lane; p < e; p += LANES) sum += val[p] * __ldg(&x[col[p]]);
+        }
+#pragma unroll
+        for (int o = LANES / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (r < n && lane == 0) {
+            y[r] = sum;
+            if (NDOT == 1) acc[0] += w[r] * sum;
+            if (NDOT == 2) { acc[0] += sum * w[r]; acc[1] += sum * sum; }
+        }
+    }
+    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out);
+}
+
+template <int NDOT>
+static void spmv_dispatch(cudaStream_t st, int lanes, int blocks, int n, const int *rowptr, const int *col,
+                          const double *val, const double *x, double *y, const double *w, double *partials,
+                          unsigned *ticket, double *out)
+{
+    switch (lanes) {
+    case 4: spmv_kernel<4, NDOT><<<blocks, 256, 0, st>>>(n, rowptr, col, val, x, y, w, partials, ticket, out); break;
+    case 8: spmv_kernel<8, NDOT><<<blocks, 256, 0, st>>>(n, rowptr, col, val, x, y, w, partials, ticket, out); break;
+    case 16: spmv_kernel<16, NDOT><<<blocks, 256, 0, st>>>(n, rowptr, col, val, x, y, w, partials, ticket, out); break;
+    default: spmv_kernel<32, NDOT><<<blocks, 256, 0, st>>>(n, rowptr, col, val, x, y, w, partials, ticket, out); break;
+    }
+}
+
+static inline double spmv_bytes(int n, int nnz) { return 12.0 * nnz + 4.0 * (n + 1) + 16.0 * n; }
+
+static inline int spmv_blocks(int n, int lanes) { return grid_for((long long)n * lanes, 256, 148 * 8); }
+
+int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const double *val, const double *x,
+                double *y, int lanes)
+{
+    Launch L(c, K_SPMV, spmv_bytes(n, nnz));
+    spmv_dispatch<0>(c.stream, lanes, spmv_blocks(n, lanes), n, rowptr, col, val, x, y, nullptr, nullptr, nullptr, nullptr);
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+// ---- preconditioner set-up ----------------------------------------------------------
+__device__ __forceinline__ double csr_entry(const int *__restrict__ rowptr, const int *__restrict__ col,
+                                            const double *__restrict__ val, int i, int j)
+{
+    int b = rowptr[i], e = rowptr[i + 1];
+    while (b < e) {
+        const int mid = (b + e) >> 1;
+        const int cj = col[mid];
+        if (cj == j) return val[mid];
+        if (cj < j) b = mid + 1; else e = mid;
+    }
+    return 0.0;
+}
+
+__global__ void jacobi_setup_kernel(int n, const int *__restrict__ rowptr, const int *__restrict__ col,
+                                    const double *__restrict__ val, double *__restrict__ dinv)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double d = csr_entry(rowptr, col, val, i, i);
+    dinv[i] = (d != 0.0) ? 1.0 / d : 1.0;
+}
+
+// One thread per cell: gathers the nspec x nspec block coupling the species of the
+// cell (the "other species in the same box" entries of src/sparsecoeff.f:70-75,
+// 162-166, 296-302 plus the diagonal) and inverts it by Gauss-Jordan with
+// partial pivoting.  binv is stored [s][s'][cell] so that applying it is coalesced.
+__global__ void block_setup_kernel(int nspec, int ncell, const int *__restrict__ rowptr, const int *__restrict__ col,
+                                   const double *__restrict__ val, double *__restrict__ binv)
+{
+    const int cidx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cidx >= ncell) return;
+    double A[MAXS][MAXS], B[MAXS][MAXS];
+    for (int s = 0; s < nspec; s++)
+        for (int q = 0; q < nspec; q++) {
+            A[s][q] = csr_entry(rowptr, col, val, s * ncell + cidx, q * ncell + cidx);
+            B[s][q] = (s == q) ? 1.0 : 0.0;
+        }
+    for (int k = 0; k < nspec; k++) {
+        int piv = k;
+        double best = fabs(A[k][k]);
+        for (int s = k + 1; s < nspec; s++)
+            if (fabs(A[s][k]) > best) { best = fabs(A[s][k]); piv = s; }
+        if (best == 0.0) {  // singular block: fall back to the identity for this cell
+            for (int s = 0; s < nspec; s++)
+                for (int q = 0; q < nspec; q++) B[s][q] = (s == q) ? 1.0 : 0.0;
+            break;
+        }
+        if (piv != k)
+            for (int q = 0; q < nspec; q++) {
+                double tA = A[k][q]; A[k][q] = A[piv][q]; A[piv][q] = tA;
+                double tB = B[k][q]; B[k][q] = B[piv][q]; B[piv][q] = tB;
+            }
+        const double inv = 1.0 / A[k][k];
+        for (int q = 0; q < nspec; q++) { A[k][q] *= inv; B[k][q] *= inv; }
+        for (int s = 0; s < nspec; s++) {
+            if (s == k) continue;
+            const double f = A[s][k];
+            if (f == 0.0) continue;
+            for (int q = 0; q < nspec; q++) { A[s][q] -= f * A[k][q]; B[s][q] -= f * B[k][q]; }
+        }
+    }
+    for (int s = 0; s < nspec; s++)
+        for (int q = 0; q < nspec; q++) binv[((long long)s * nspec + q) * ncell + cidx] = B[s][q];
+}
+
+// ---- fused vector updates --------------------------------------------------------------
+// Work item = one cell (PRE == BLOCK: all its species) or one unknown.
+// PRE: 0 none, 1 Jacobi, 2 block-Jacobi.
+
+// p = r + beta (p - omega v)  [first step: p = r] ; ph = M^-1 p
+template <int PRE>
+__global__ void __launch_bounds__(256) update_p_kernel(int n, int nspec, int ncell, int first, const double *scal,
+                                                       int cur, const double *__restrict__ r, const double *__restrict__ v,
+                                                       double *__restrict__ p, double *__restrict__ ph,
+                                                       const double *__restrict__ dinv, const double *__restrict__ binv)
+{
+    double beta = 0.0, omega = 0.0;
+    if (!first) {
+        const double *prev = scal + SLOT * (cur ^ 1), *curp = scal + SLOT * cur;
+        const double rho_k = prev[S_RHONEXT], rho_km1 = curp[S_RHONEXT];
+        const double alpha = rho_km1 / prev[S_R0V];
+        omega = prev[S_TS] / prev[S_TT];
+        beta = (rho_k / rho_km1) * (alpha / omega);
+    }
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    if (PRE == 2) {
+        for (long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < ncell; c += stride) {
+            double pv[MAXS];
+            for (int s = 0; s < nspec; s++) {
+                const long long i = (long long)s * ncell + c;
+                const double pn = first ? r[i] : r[i] + beta * (p[i] - omega * v[i]);
+                pv[s] = pn;
+                p[i] = pn;
+            }
+            for (int s = 0; s < nspec; s++) {
+                double a = 0.0;
+                for (int q = 0; q < nspec; q++) a += binv[((long long)s * nspec + q) * ncell + c] * pv[q];
+                ph[(long long)s * ncell + c] = a;
+            }
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+            const double pn = first ? r[i] : r[i] + beta * (p[i] - omega * v[i]);
+            p[i] = pn;
+            ph[i] = (PRE == 1) ? dinv[i] * pn : pn;
+        }
+    }
+}
+
+// s = r - alpha v ; sh = M^-1 s
+template <int PRE>
+__global__ void __launch_bounds__(256) update_s_kernel(int n, int nspec, int ncell, const double *scal, int cur,
+                                                       const double *__restrict__ r, const double *__restrict__ v,
+                                                       double *__restrict__ s_, double *__restrict__ sh,
+                                                       const double *__restrict__ dinv, const double *__restrict__ binv)
+{
+    const double rho = scal[SLOT * (cur ^ 1) + S_RHONEXT];
+    const double alpha = rho / scal[SLOT * cur + S_R0V];
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    if (PRE == 2) {
+        for (long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < ncell; c += stride) {
+            double sv[MAXS];
+            for (int s = 0; s < nspec; s++) {
+                const long long i = (long long)s * ncell + c;
+                sv[s] = r[i] - alpha * v[i];
+                s_[i] = sv[s];
+            }
+            for (int s = 0; s < nspec; s++) {
+                double a = 0.0;
+                for (int q = 0; q < nspec; q++) a += binv[((long long)s * nspec + q) * ncell + c] * sv[q];
+                sh[(long long)s * ncell + c] = a;
+            }
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+            const double sn = r[i] - alpha * v[i];
+            s_[i] = sn;
+            sh[i] = (PRE == 1) ? dinv[i] * sn : sn;
+        }
+    }
+}
+
+// x += alpha ph + omega sh ; r = s - omega t ; out = { <r,r>, <r0,r> }
+__global__ void __launch_bounds__(256) update_xr_kernel(int n, double *scal, int cur, const double *__restrict__ ph,
+                                                        const double *__restrict__ sh, const double *__restrict__ s_,
+                                                        const double *__restrict__ t, const double *__restrict__ r0,
+                                                        double *__restrict__ x, double *__restrict__ r,
+                                                        double *partials, unsigned *ticket)
+{
+    double *slot = scal + SLOT * cur;
+    const double rho = scal[SLOT * (cur ^ 1) + S_RHONEXT];
+    const double alpha = rho / slot[S_R0V];
+    const double omega = slot[S_TS] / slot[S_TT];
+    double acc[2] = {0.0, 0.0};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        x[i] += alpha * ph[i] + omega * sh[i];
+        const double rn = s_[i] - omega * t[i];
+        r[i] = rn;
+        acc[0] += rn * rn;
+        acc[1] += r0[i] * rn;
+    }
+    grid_reduce<2>(acc, 0u, partials, ticket, slot + S_RR);
+}
+
+// r = r0 = b ; x = 0 ; out = <b,b> into both the bnorm slot and slot(1).rhonext
+__global__ void __launch_bounds__(256) krylov_init_kernel(int n, const double *__restrict__ b, double *__restrict__ r,
+                                                          double *__restrict__ r0, double *__restrict__ x,
+                                                          double *partials, unsigned *ticket, double *scal)
+{
+    double acc[1] = {0.0};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double bi = b[i];
+        r[i] = bi; r0[i] = bi; x[i] = 0.0;
+        acc[0] += bi * bi;
+    }
+    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_BNORM);
+}
+
+__global__ void krylov_seed_kernel(double *scal)
+{
+    scal[SLOT * 1 + S_RHONEXT] = scal[S_BNORM];
+}
+
+// ---- host driver ------------------------------------------------------------------------
+int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int *col, const double *val,
+                 int precond, int nspec, int ncell, const rs_krylov_control *ctl)
+{
+    k.n = n; k.nnz = nnz; k.rowptr = rowptr; k.col = col; k.val = val;
+    k.nspec = nspec; k.ncell = ncell;
+    if (precond == RS_PRECOND_AUTO) precond = (nspec > 1 && nspec <= MAXS && ncell > 0) ? RS_PRECOND_BLOCK_JACOBI : RS_PRECOND_JACOBI;
+    if (precond == RS_PRECOND_BLOCK_JACOBI && !(nspec > 1 && nspec <= MAXS && ncell > 0 && (long long)nspec * ncell == n))
+        precond = RS_PRECOND_JACOBI;
+    k.precond = precond;
+    if (ctl) {
+        if (ctl->max_krylov > 0) k.max_iter = ctl->max_krylov;
+        if (ctl->lin_rtol > 0) k.lin_rtol = ctl->lin_rtol;
+        if (ctl->lin_ewt_factor > 0) k.lin_ewt_factor = ctl->lin_ewt_factor;
+        if (ctl->check_every > 0) k.check_every = ctl->check_every;
+    }
+    k.lanes = pick_lanes(n, nnz);
+    RS_TRY(k.r.alloc(n)); RS_TRY(k.r0.alloc(n)); RS_TRY(k.p.alloc(n)); RS_TRY(k.v.alloc(n));
+    RS_TRY(k.s.alloc(n)); RS_TRY(k.t.alloc(n)); RS_TRY(k.ph.alloc(n)); RS_TRY(k.sh.alloc(n));
+    if (precond == RS_PRECOND_JACOBI) RS_TRY(k.dinv.alloc(n));
+    if (precond == RS_PRECOND_BLOCK_JACOBI) RS_TRY(k.binv.alloc((size_t)nspec * nspec * ncell));
+    RS_TRY(k.partials.alloc(4 * 148 * 16));
+    RS_TRY(k.scal.alloc(NSCAL));
+    RS_TRY(k.ticket.alloc(4));
+    RS_TRY(k.ticket.zero(c.stream));
+    RS_TRY(k.scal.zero(c.stream));
+    if (!k.h_scal) RS_CUDA(cudaMallocHost((void **)&k.h_scal, sizeof(double) * NSCAL));
+    return RS_OK;
+}
+
+int krylov_precond_update(Ctx &c, Krylov &k)
+{
+    if (k.precond == RS_PRECOND_JACOBI) {
+        Launch L(c, K_PRECOND_SETUP, 20.0 * k.n);
+        jacobi_setup_kernel<<<(k.n + 255) / 256, 256, 0, c.stream>>>(k.n, k.rowptr, k.col, k.val, k.dinv.p);
+    } else if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
+        Launch L(c, K_PRECOND_SETUP, 20.0 * k.nspec * k.n);
+        block_setup_kernel<<<(k.ncell + 127) / 128, 128, 0, c.stream>>>(k.nspec, k.ncell, k.rowptr, k.col, k.val, k.binv.p);
+    }
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres)
+{
+    const int n = k.n;
+    cudaStream_t st = c.stream;
+    const int vb = grid_for(n, 256, 148 * 8);
+    const int cb = grid_for(k.precond == RS_PRECOND_BLOCK_JACOBI ? k.ncell : n, 256, 148 * 8);
+    const int sb = spmv_blocks(n, k.lanes);
+    const double pre_bytes = (k.precond == RS_PRECOND_BLOCK_JACOBI) ? 8.0 * k.nspec * n : (k.precond == RS_PRECOND_JACOBI ? 8.0 * n : 0.0);
+    {
+        Launch L(c, K_VEC, 32.0 * n);
+        krylov_init_kernel<<<vb, 256, 0, st>>>(n, b, k.r.p, k.r0.p, x, k.partials.p, k.ticket.p, k.scal.p);
+    }
+    if (comm_active()) RS_TRY(comm_allreduce_sum(c, k.scal.p + S_BNORM, 1));
+    krylov_seed_kernel<<<1, 1, 0, st>>>(k.scal.p);
+    c.launches++;
+    RS_CUDA(cudaMemcpyAsync(k.h_scal + S_BNORM, k.scal.p + S_BNORM, sizeof(double), cudaMemcpyDeviceToHost, st));
+    RS_CUDA(cudaStreamSynchronize(st));
+    const double bnorm = std::sqrt(k.h_scal[S_BNORM]);
+    *iters = 0;
+    *relres = 0.0;
+    if (!(bnorm > 0.0)) return RS_OK;  // b == 0 -> x = 0
+    double target = k.lin_rtol * bnorm;
+    if (abs_floor > target) target = abs_floor;
+    double rnorm = bnorm;
+    for (int it = 0; it < k.max_iter; it++) {
+        const int cur = it & 1, first = (it == 0);
+        double *slot = k.scal.p + SLOT * cur;
+        {
+            Launch L(c, K_VEC, (first ? 24.0 : 40.0) * n + pre_bytes);
+            switch (k.precond) {
+            case RS_PRECOND_BLOCK_JACOBI:
+                update_p_kernel<2><<<cb, 256, 0, st>>>(n, k.nspec, k.ncell, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, k.binv.p); break;
+            case RS_PRECOND_JACOBI:
+                update_p_kernel<1><<<cb, 256, 0, st>>>(n, 1, n, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, k.dinv.p, nullptr); break;
+            default:
+                update_p_kernel<0><<<cb, 256, 0, st>>>(n, 1, n, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, nullptr); break;
+            }
+        }
+        {
+            Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
+            spmv_dispatch<1>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, k.ph.p, k.v.p, k.r0.p, k.partials.p, k.ticket.p, slot + S_R0V);
+        }
+        if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
+        {
+            Launch L(c, K_VEC, 32.0 * n + pre_bytes);
+            switch (k.precond) {
+            case RS_PRECOND_BLOCK_JACOBI:
+                update_s_kernel<2><<<cb, 256, 0, st>>>(n, k.nspec, k.ncell, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, k.binv.p); break;
+            case RS_PRECOND_JACOBI:
+                update_s_kernel<1><<<cb, 256, 0, st>>>(n, 1, n, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, k.dinv.p, nullptr); break;
+            default:
+                update_s_kernel<0><<<cb, 256, 0, st>>>(n, 1, n, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, nullptr); break;
+            }
+        }
+        {
+            Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
+            spmv_dispatch<2>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, k.sh.p, k.t.p, k.s.p, k.partials.p, k.ticket.p, slot + S_TS);
+        }
+        if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
+        {
+            Launch L(c, K_VEC, 64.0 * n);
+            update_xr_kernel<<<vb, 256, 0, st>>>(n, k.scal.p, cur, k.ph.p, k.sh.p, k.s.p, k.t.p, k.r0.p, x, k.r.p, k.partials.p, k.ticket.p);
+        }
+        if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_RR, 2));
+        *iters = it + 1;
+        if ((it + 1) % k.check_every == 0 || it + 1 == k.max_iter) {
+            RS_CUDA(cudaMemcpyAsync(k.h_scal + SLOT * cur, slot, sizeof(double) * SLOT, cudaMemcpyDeviceToHost, st));
+            RS_CUDA(cudaStreamSynchronize(st));
+            const double rr = k.h_scal[SLOT * cur + S_RR];
+            if (!(rr == rr) || std::isinf(rr)) {
+                set_error("sparse solver: Krylov breakdown (non-finite residual after %d iterations)", it + 1);
+                return RS_ESINGULAR;
+            }
+            rnorm = std::sqrt(rr);
+            if (rnorm <= target) break;
+        }
+    }
+    RS_CUDA(cudaGetLastError());
+    *relres = rnorm / bnorm;
+    return RS_OK;
+}
+
+}  // namespace rs

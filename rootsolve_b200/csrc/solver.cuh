@@ -1,0 +1,80 @@
+// solver.cuh -- internal interfaces between the translation units of the library.
+#pragma once
+
+#include "rs_internal.cuh"
+
+namespace rs {
+
+// Regular-grid description (what dims[] carries in src/sparse.f:398-434).
+struct GridDesc {
+    int type = 0;          // RS_TYPE_1D/2D/3D, 0 = no grid knowledge
+    int nspec = 1;
+    int d[3] = {1, 1, 1};  // rev(dimens): d[0] slowest
+    int cyc[3] = {0, 0, 0};
+    int ncell = 0;
+};
+
+// structure.cu
+int exclusive_scan(Ctx &c, const int *in, int *out, int n, int base, bool write_total);
+int build_grid_structure(Ctx &c, const GridDesc &g, int n, DevBuf<int> &d_ian, DevBuf<int> &d_jan, int *nnz);
+int build_csr_pattern(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, DevBuf<int> &rowptr,
+                      DevBuf<int> &col);
+
+// jgroup.cu -- group_of[j] = 0-based group of column j; ngp = number of groups.
+int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, const int *d_jan,
+                  const int *d_rowptr, const int *d_col, int maxg, DevBuf<int> &group_of, int *ngp);
+// igp/jgp in the reference's layout (1-based) from group_of
+int jgroup_lists(Ctx &c, int n, int ngp, const int *d_group_of, int *igp_host, int *jgp_host);
+
+// fdjac.cu
+struct FdWork {
+    DevBuf<double> Y, F;     // (ngp+1) x ld
+    DevBuf<double> yout;     // (ngp+1) x ldout
+    DevBuf<int> ip;          // reference ipar block + slab bounds
+    long long ld = 0, ldout = 0;
+};
+int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, int nrpar, const int *ipar,
+             int nipar, int slab_j0, int slab_j1);
+// beta = -f(y); val[] (CSR order) = FD Jacobian; dinv (optional) = 1/diag
+int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
+                const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
+                long long work, int row0, int row1);
+int residual_only(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, const double *d_y, double *d_f,
+                  long long work);
+// a_csc[k] = val[position of (jan[k], column of k)] -- for returning the Jacobian in jan order
+int gather_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, const int *d_rowptr,
+                      const int *d_col, const double *d_val, double *d_a);
+int scatter_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, const int *d_rowptr,
+                       const int *d_col, const double *d_a, double *d_val);
+
+// krylov.cu
+struct RowRange { int n_ranges = 1; int begin[8]; int end[8]; };  // owned rows (species-major slabs)
+struct Krylov {
+    int n = 0, nnz = 0;
+    const int *rowptr = nullptr, *col = nullptr;
+    const double *val = nullptr;
+    int precond = RS_PRECOND_JACOBI, nspec = 1, ncell = 0;
+    DevBuf<double> r, r0, p, v, s, t, ph, sh, dinv, binv;
+    DevBuf<double> partials, scal;
+    DevBuf<unsigned> ticket;
+    double *h_scal = nullptr;  // pinned mirror
+    int lanes = 8;             // lanes per row of the SpMV
+    int max_iter = 10000, check_every = 1;
+    double lin_rtol = 1e-10, lin_ewt_factor = 0.05;
+    ~Krylov();
+};
+int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int *col, const double *val,
+                 int precond, int nspec, int ncell, const rs_krylov_control *ctl);
+int krylov_precond_update(Ctx &c, Krylov &k);
+// solves A x = b (x overwritten, starts from 0); abs_floor: absolute 2-norm stop
+int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres);
+int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const double *val, const double *x,
+                double *y, int lanes);
+int pick_lanes(int n, int nnz);
+
+// comm.cu
+bool comm_active();
+int comm_allreduce_sum(Ctx &c, double *d_buf, int count);
+int comm_allreduce_max(Ctx &c, double *d_buf, int count);
+
+}  // namespace rs

@@ -1,0 +1,269 @@
+// structure.cu -- sparsity structure of the Jacobian on the device.
+//
+// K0: ian/jan for 1-D / 2-D / 3-D multi-species grids, bit-exact with the
+//     reference's sparse1d / sparse2d / sparse3d (src/sparsecoeff.f:5-312): one
+//     thread per column emits its row indices in the reference's order (a count
+//     pass, a device prefix sum, a fill pass).
+// CSR: the reference's (ian, jan) lists the rows of every COLUMN of J
+//     (src/sparse.f:309-316); the Krylov solver needs J by rows, so the
+//     pattern is transposed once per solve (histogram, prefix sum, fill, per-row
+//     sort) and the values are assembled straight into the row-wise arrays.
+#include "rs_internal.cuh"
+#include "solver.cuh"
+
+namespace rs {
+
+// ---- exclusive prefix sum (int32) ------------------------------------------
+// Three-phase scan: each 512-thread block scans 2048 items in shared memory and
+// emits its total; the totals are scanned recursively; a last pass adds the
+// block offsets.  out[i] = base + sum(in[0..i)), and out[n] = base + total when
+// write_total is set (out then has n+1 entries).
+constexpr int SCAN_THREADS = 512;
+constexpr int SCAN_ITEMS = 4;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_tile_kernel(const int *__restrict__ in, int *__restrict__ out,
+                                                                 int *__restrict__ block_sums, int n)
+{
+    __shared__ int warp_tot[SCAN_THREADS / 32];
+    const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    int v[SCAN_ITEMS], tsum = 0;
+#pragma unroll
+    for (int q = 0; q < SCAN_ITEMS; q++) {
+        v[q] = (base + q < n) ? in[base + q] : 0;
+        tsum += v[q];
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int incl = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int w = (lane < SCAN_THREADS / 32) ? warp_tot[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += t;
+        }
+        if (lane < SCAN_THREADS / 32) warp_tot[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    int run = incl - tsum + (wid > 0 ? warp_tot[wid - 1] : 0);
+#pragma unroll
+    for (int q = 0; q < SCAN_ITEMS; q++) {
+        if (base + q < n) out[base + q] = run;
+        run += v[q];
+    }
+    if (threadIdx.x == SCAN_THREADS - 1) block_sums[blockIdx.x] = run;
+}
+
+__global__ void scan_add_kernel(int *__restrict__ out, const int *__restrict__ block_off, int n, int base,
+                                int write_total, const int *__restrict__ last_in)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] += block_off[i / SCAN_TILE] + base;
+    if (write_total && i == n - 1) {
+        // out[n] = out[n-1] + in[n-1]; out[n-1] is final after this thread's own update
+        out[n] = out[n - 1] + last_in[n - 1];
+    }
+}
+
+int exclusive_scan(Ctx &c, const int *in, int *out, int n, int base, bool write_total)
+{
+    if (n <= 0) {
+        if (write_total) RS_CUDA(cudaMemcpyAsync(out, &base, sizeof(int), cudaMemcpyHostToDevice, c.stream));
+        return RS_OK;
+    }
+    const int nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    DevBuf<int> sums, offs;
+    RS_TRY(sums.alloc(nb));
+    RS_TRY(offs.alloc(nb + 1));
+    {
+        Launch L(c, K_SCAN, 8.0 * n);
+        scan_tile_kernel<<<nb, SCAN_THREADS, 0, c.stream>>>(in, out, sums.p, n);
+    }
+    if (nb > 1) {
+        RS_TRY(exclusive_scan(c, sums.p, offs.p, nb, 0, false));
+    } else {
+        RS_CUDA(cudaMemsetAsync(offs.p, 0, sizeof(int), c.stream));
+    }
+    {
+        Launch L(c, K_SCAN, 8.0 * n);
+        scan_add_kernel<<<(n + 255) / 256, 256, 0, c.stream>>>(out, offs.p, n, base, write_total ? 1 : 0, in);
+    }
+    RS_CUDA(cudaGetLastError());
+    RS_CUDA(cudaStreamSynchronize(c.stream));  // sums/offs are released on return
+    return RS_OK;
+}
+
+// ---- K0: grid structures ----------------------------------------------------
+// Emits the 1-based row indices of column M (1-based) in the reference's order
+// into sink(row).  The stencil part is de-duplicated for 3-D only, as `interact`
+// does (src/sparsecoeff.f:178-201); 1-D and 2-D append blindly.
+template <typename Sink>
+__device__ __forceinline__ void emit_column(const GridDesc &g, int M, Sink &&sink)
+{
+    const int nb = g.ncell;
+    const int i = (M - 1) / nb;            // species, 0-based
+    const int cell = (M - 1) - i * nb;     // 0-based cell
+    const int isp = i * nb;
+    if (g.type == RS_TYPE_1D) {
+        const int j = cell + 1, N = nb;
+        sink(M);
+        if (j < N) sink(M + 1); else if (g.cyc[0] == 1) sink(isp + 1);
+        if (j > 1) sink(M - 1); else if (g.cyc[0] == 1) sink(isp + N);
+    } else if (g.type == RS_TYPE_2D) {
+        const int d1 = g.d[0], d2 = g.d[1];
+        const int j = cell / d2 + 1, k = cell - (j - 1) * d2 + 1;
+        sink(M);
+        if (k < d2) sink(M + 1); else if (g.cyc[1] == 1) sink(isp + (j - 1) * d2 + 1);
+        if (j < d1) sink(M + d2); else if (g.cyc[0] == 1) sink(isp + k);
+        if (j > 1) sink(M - d2); else if (g.cyc[0] == 1) sink(isp + (d1 - 1) * d2 + k);
+        if (k > 1) sink(M - 1); else if (g.cyc[1] == 1) sink(isp + j * d1);  // sic: src/sparsecoeff.f:159
+    } else {
+        const int d1 = g.d[0], d2 = g.d[1], d3 = g.d[2], s1 = d2 * d3;
+        const int j = cell / s1 + 1;
+        const int rem = cell - (j - 1) * s1;
+        const int k = rem / d3 + 1, l = rem - (k - 1) * d3 + 1;
+        const int line = isp + (j - 1) * s1 + (k - 1) * d3;
+        int seen[7], ns = 0;
+        auto put = [&](int v) {
+            for (int q = 0; q < ns; q++) if (seen[q] == v) return;
+            seen[ns++] = v;
+            sink(v);
+        };
+        put(M);
+        if (l < d3) put(M + 1); else if (g.cyc[2] == 1 && d3 > 2) put(line + 1);
+        if (l > 1) put(M - 1); else if (g.cyc[2] == 1 && d3 > 2) put(line + d3);
+        if (k < d2) put(M + d3); else if (g.cyc[1] == 1 && d2 > 2) put(isp + (j - 1) * s1 + l);
+        if (k > 1) put(M - d3); else if (g.cyc[1] == 1 && d2 > 2) put(isp + j * s1 - d3 + l);
+        if (j < d1) put(M + s1); else if (g.cyc[0] == 1 && d1 > 2) put(isp + (k - 1) * d3 + l);
+        if (j > 1) put(M - s1); else if (g.cyc[0] == 1 && d1 > 2) put(isp + (d1 - 1) * s1 + (k - 1) * d3 + l);
+    }
+    // other species of the same box, ascending (a different species can never
+    // duplicate a stencil entry, so no search is needed here)
+    for (int L = 0; L < g.nspec; L++)
+        if (L != i) sink(L * nb + cell + 1);
+}
+
+__global__ void structure_count_kernel(GridDesc g, int n, int *__restrict__ counts)
+{
+    const int M = blockIdx.x * blockDim.x + threadIdx.x + 1;
+    if (M > n) return;
+    int c = 0;
+    emit_column(g, M, [&](int) { c++; });
+    counts[M - 1] = c;
+}
+
+__global__ void structure_fill_kernel(GridDesc g, int n, const int *__restrict__ ian, int *__restrict__ jan)
+{
+    const int M = blockIdx.x * blockDim.x + threadIdx.x + 1;
+    if (M > n) return;
+    int pos = ian[M - 1] - 1;
+    emit_column(g, M, [&](int row) { jan[pos++] = row; });
+}
+
+// Builds ian (n+1, 1-based) and jan (1-based rows) on the device.  d_jan is
+// allocated here once the count is known.
+int build_grid_structure(Ctx &c, const GridDesc &g, int n, DevBuf<int> &d_ian, DevBuf<int> &d_jan, int *nnz)
+{
+    if (g.nspec <= 0 || g.ncell <= 0 || (long long)g.nspec * g.ncell != n) {
+        set_error("cannot generate sparse jacobian - N and nspec not compatible");
+        return RS_ESTRUCT;
+    }
+    DevBuf<int> counts;
+    RS_TRY(counts.alloc(n));
+    RS_TRY(d_ian.alloc((size_t)n + 1));
+    {
+        Launch L(c, K_STRUCT, 4.0 * n);
+        structure_count_kernel<<<(n + 255) / 256, 256, 0, c.stream>>>(g, n, counts.p);
+    }
+    RS_TRY(exclusive_scan(c, counts.p, d_ian.p, n, 1, true));
+    int last = 0;
+    RS_CUDA(cudaMemcpyAsync(&last, d_ian.p + n, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    *nnz = last - 1;
+    RS_TRY(d_jan.alloc((size_t)*nnz));
+    {
+        Launch L(c, K_STRUCT, 4.0 * n + 4.0 * *nnz);
+        structure_fill_kernel<<<(n + 255) / 256, 256, 0, c.stream>>>(g, n, d_ian.p, d_jan.p);
+    }
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+// ---- CSC -> CSR pattern ------------------------------------------------------
+__global__ void row_hist_kernel(const int *__restrict__ jan, int nnz, int *__restrict__ cnt)
+{
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += (long long)gridDim.x * blockDim.x)
+        atomicAdd(&cnt[jan[k] - 1], 1);
+}
+
+__global__ void row_fill_kernel(const int *__restrict__ ian, const int *__restrict__ jan, int n,
+                                const int *__restrict__ rowptr, int *__restrict__ cursor, int *__restrict__ col)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;  // column, 0-based
+    if (j >= n) return;
+    for (int k = ian[j] - 1; k < ian[j + 1] - 1; k++) {
+        const int i = jan[k] - 1;
+        const int pos = atomicAdd(&cursor[i], 1);
+        col[rowptr[i] + pos] = j;
+    }
+}
+
+// sorts every row's column indices ascending; flags duplicates
+__global__ void row_sort_kernel(const int *__restrict__ rowptr, int n, int *__restrict__ col, int *__restrict__ dup_flag)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int b = rowptr[i], e = rowptr[i + 1];
+    for (int p = b + 1; p < e; p++) {
+        const int key = col[p];
+        int q = p - 1;
+        while (q >= b && col[q] > key) { col[q + 1] = col[q]; q--; }
+        col[q + 1] = key;
+    }
+    for (int p = b + 1; p < e; p++)
+        if (col[p] == col[p - 1]) atomicMax(dup_flag, i + 1);
+}
+
+// CSR pattern of J (0-based rowptr/col) from the column-wise (ian, jan).
+int build_csr_pattern(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, DevBuf<int> &rowptr,
+                      DevBuf<int> &col)
+{
+    DevBuf<int> cnt, flag;
+    RS_TRY(cnt.alloc(n));
+    RS_TRY(flag.alloc(1));
+    RS_TRY(rowptr.alloc((size_t)n + 1));
+    RS_TRY(col.alloc((size_t)nnz));
+    RS_TRY(cnt.zero(c.stream));
+    RS_TRY(flag.zero(c.stream));
+    {
+        Launch L(c, K_TRANSPOSE, 8.0 * nnz);
+        row_hist_kernel<<<grid_for(nnz, 256, 148 * 16), 256, 0, c.stream>>>(d_jan, nnz, cnt.p);
+    }
+    RS_TRY(exclusive_scan(c, cnt.p, rowptr.p, n, 0, true));
+    RS_TRY(cnt.zero(c.stream));
+    {
+        Launch L(c, K_TRANSPOSE, 12.0 * nnz);
+        row_fill_kernel<<<(n + 255) / 256, 256, 0, c.stream>>>(d_ian, d_jan, n, rowptr.p, cnt.p, col.p);
+    }
+    {
+        Launch L(c, K_TRANSPOSE, 8.0 * nnz);
+        row_sort_kernel<<<(n + 255) / 256, 256, 0, c.stream>>>(rowptr.p, n, col.p, flag.p);
+    }
+    int dup = 0;
+    RS_CUDA(cudaMemcpyAsync(&dup, flag.p, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    if (dup) {
+        set_error("sparse solver: duplicate entry in a (row nr: %d)", dup);
+        return RS_EDUPLICATE;
+    }
+    return RS_OK;
+}
+
+}  // namespace rs
