@@ -573,12 +573,15 @@ extern "C" int rs_jgroup(int neq, const int *ian, const int *jan, int maxg, cons
 static int group_of_from_lists(int neq, int ngp, const int *igp, const int *jgp, std::vector<int> &g)
 {
     g.assign((size_t)neq, -1);
-    for (int q = 0; q < ngp; q++)
-        for (int k = igp[q]; k < igp[q + 1]; k++) {
+    for (int q = 0; q < ngp; q++) {
+        // igp(ngp+1) is left at 0 by the reference when ngp == neq (see jgroup_lists)
+        const int stop = (q == ngp - 1 && igp[q + 1] == 0) ? neq + 1 : igp[q + 1];
+        for (int k = igp[q]; k < stop; k++) {
             const int j = jgp[k - 1];
             if (j < 1 || j > neq) { set_error("jgp out of range"); return RS_EINVAL; }
             g[j - 1] = q;
         }
+    }
     for (int j = 0; j < neq; j++)
         if (g[j] < 0) { set_error("column %d is in no group", j + 1); return RS_EINVAL; }
     return RS_OK;
@@ -638,6 +641,21 @@ __global__ void shift_down_kernel(int n, const int *__restrict__ in, int *__rest
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) out[i] = in[i] - 1;
 }
 
+// sorts the (column, value) pairs of every row by column (the solver's row searches need ascending columns)
+__global__ void sort_row_pairs_kernel(int n, const int *__restrict__ rowptr, int *__restrict__ col, double *__restrict__ val)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int b = rowptr[i], e = rowptr[i + 1];
+    for (int p = b + 1; p < e; p++) {
+        const int kc = col[p];
+        const double kv = val[p];
+        int q = p - 1;
+        while (q >= b && col[q] > kc) { col[q + 1] = col[q]; val[q + 1] = val[q]; q--; }
+        col[q + 1] = kc; val[q + 1] = kv;
+    }
+}
+
 // row-wise (0-based) pattern + values of J (transposed=0) or J' (transposed=1) from the column-wise input
 static int csr_from_columns(Ctx &c, int neq, int nnz, const int *ian, const int *jan, const double *a, int transposed,
                             DevBuf<int> &rowptr, DevBuf<int> &col, DevBuf<double> &val)
@@ -655,6 +673,8 @@ static int csr_from_columns(Ctx &c, int neq, int nnz, const int *ian, const int 
         shift_down_kernel<<<grid_for(nnz, 256), 256, 0, c.stream>>>(nnz, d_jan.p, col.p);
         c.launches += 2;
         RS_CUDA(cudaMemcpyAsync(val.p, d_a.p, sizeof(double) * (size_t)nnz, cudaMemcpyDeviceToDevice, c.stream));
+        sort_row_pairs_kernel<<<(neq + 255) / 256, 256, 0, c.stream>>>(neq, rowptr.p, col.p, val.p);
+        c.launches++;
     } else {
         RS_TRY(build_csr_pattern(c, neq, nnz, d_ian.p, d_jan.p, rowptr, col));
         RS_TRY(scatter_csc_values(c, neq, nnz, d_ian.p, d_jan.p, rowptr.p, col.p, d_a.p, val.p));

@@ -220,7 +220,13 @@ int jgroup_lists(Ctx &c, int n, int ngp, const int *d_group_of, int *igp_host, i
     std::vector<int> start((size_t)ngp + 1, 0);
     for (int j = 0; j < n; j++) start[g[j] + 1]++;
     for (int q = 0; q < ngp; q++) start[q + 1] += start[q];
-    if (igp_host) for (int q = 0; q <= ngp; q++) igp_host[q] = start[q] + 1;
+    if (igp_host) {
+        for (int q = 0; q <= ngp; q++) igp_host[q] = start[q] + 1;
+        // Reference quirk: when every column ends up alone in its group (ngp == n) the DO loop of
+        // src/sparse.f:569 runs out before it meets the empty group that would write igp(ngp+1),
+        // so that slot keeps the zero call_stsparse.c:208-209 put there.  Reported the same way.
+        if (ngp == n) igp_host[ngp] = 0;
+    }
     if (jgp_host) {
         std::vector<int> cur(start.begin(), start.end() - 1);
         for (int j = 0; j < n; j++) jgp_host[cur[g[j]]++] = j + 1;

@@ -16,6 +16,7 @@
 // kernels recompute them from the raw dot products in `scal`, so one step is
 // five launches and the host only reads ||r||^2 to decide when to stop.
 #include <cmath>
+#include <cstdlib>
 
 #include "solver.cuh"
 
@@ -23,8 +24,8 @@ namespace rs {
 
 constexpr int MAXS = 8;        // largest species count handled by the block preconditioner
 constexpr int SLOT = 8;        // doubles per parity slot: r0v, ts, tt, rr, rhonext
-constexpr int S_R0V = 0, S_TS = 1, S_TT = 2, S_RR = 3, S_RHONEXT = 4;
-constexpr int S_BNORM = 2 * SLOT;
+constexpr int S_R0V = 0, S_TS = 1, S_TT = 2, S_RR = 3, S_RHONEXT = 4, S_BAD = 5;
+constexpr int S_BNORM = 2 * SLOT, S_RTRUE = 2 * SLOT + 1;
 constexpr int NSCAL = 2 * SLOT + 8;
 
 Krylov::~Krylov()
@@ -183,6 +184,7 @@ __global__ void __launch_bounds__(256) update_p_kernel(int n, int nspec, int nce
         const double alpha = rho_km1 / prev[S_R0V];
         omega = prev[S_TS] / prev[S_TT];
         beta = (rho_k / rho_km1) * (alpha / omega);
+        if (!isfinite(beta)) { beta = 0.0; omega = 0.0; }
     }
     const long long stride = (long long)gridDim.x * blockDim.x;
     if (PRE == 2) {
@@ -217,7 +219,8 @@ __global__ void __launch_bounds__(256) update_s_kernel(int n, int nspec, int nce
                                                        const double *__restrict__ dinv, const double *__restrict__ binv)
 {
     const double rho = scal[SLOT * (cur ^ 1) + S_RHONEXT];
-    const double alpha = rho / scal[SLOT * cur + S_R0V];
+    double alpha = rho / scal[SLOT * cur + S_R0V];
+    if (!isfinite(alpha)) alpha = 0.0;  // breakdown: flagged by update_xr_kernel, host restarts
     const long long stride = (long long)gridDim.x * blockDim.x;
     if (PRE == 2) {
         for (long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < ncell; c += stride) {
@@ -251,8 +254,13 @@ __global__ void __launch_bounds__(256) update_xr_kernel(int n, double *scal, int
 {
     double *slot = scal + SLOT * cur;
     const double rho = scal[SLOT * (cur ^ 1) + S_RHONEXT];
-    const double alpha = rho / slot[S_R0V];
-    const double omega = slot[S_TS] / slot[S_TT];
+    double alpha = rho / slot[S_R0V];
+    double omega = slot[S_TS] / slot[S_TT];
+    // A zero or non-finite recurrence scalar is a BiCGStab breakdown.  Leave x untouched (alpha =
+    // omega = 0 keeps x and turns r into s = r) and raise the flag the host restarts on.
+    const bool bad = !(isfinite(alpha) && isfinite(omega)) || rho == 0.0 || omega == 0.0;
+    if (bad) { alpha = 0.0; omega = 0.0; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) slot[S_BAD] = bad ? 1.0 : 0.0;
     double acc[2] = {0.0, 0.0};
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         x[i] += alpha * ph[i] + omega * sh[i];
@@ -278,9 +286,25 @@ __global__ void __launch_bounds__(256) krylov_init_kernel(int n, const double *_
     grid_reduce<1>(acc, 0u, partials, ticket, scal + S_BNORM);
 }
 
-__global__ void krylov_seed_kernel(double *scal)
+// restart: r = r0 = b - Ax (Ax given) ; out = <r,r> (the true residual)
+__global__ void __launch_bounds__(256) krylov_restart_kernel(int n, const double *__restrict__ b,
+                                                             const double *__restrict__ ax, double *__restrict__ r,
+                                                             double *__restrict__ r0, double *partials,
+                                                             unsigned *ticket, double *scal)
 {
-    scal[SLOT * 1 + S_RHONEXT] = scal[S_BNORM];
+    double acc[1] = {0.0};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double ri = b[i] - ax[i];
+        r[i] = ri; r0[i] = ri;
+        acc[0] += ri * ri;
+    }
+    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_RTRUE);
+}
+
+// rho_0 = <r0, r> = ||r||^2 goes where step 0 looks for "rho of the previous step"
+__global__ void krylov_seed_kernel(double *scal, int src)
+{
+    scal[SLOT * 1 + S_RHONEXT] = scal[src];
 }
 
 // ---- host driver ------------------------------------------------------------------------
@@ -326,6 +350,78 @@ int krylov_precond_update(Ctx &c, Krylov &k)
     return RS_OK;
 }
 
+// One BiCGStab step (five launches); the raw dot products land in slot(cur).
+static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first, int vb, int cb, int sb, double pre_bytes)
+{
+    const int n = k.n;
+    cudaStream_t st = c.stream;
+    double *slot = k.scal.p + SLOT * cur;
+    {
+        Launch L(c, K_VEC, (first ? 24.0 : 40.0) * n + pre_bytes);
+        switch (k.precond) {
+        case RS_PRECOND_BLOCK_JACOBI:
+            update_p_kernel<2><<<cb, 256, 0, st>>>(n, k.nspec, k.ncell, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, k.binv.p); break;
+        case RS_PRECOND_JACOBI:
+            update_p_kernel<1><<<cb, 256, 0, st>>>(n, 1, n, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, k.dinv.p, nullptr); break;
+        default:
+            update_p_kernel<0><<<cb, 256, 0, st>>>(n, 1, n, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, nullptr); break;
+        }
+    }
+    {
+        Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
+        spmv_dispatch<1>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, k.ph.p, k.v.p, k.r0.p, k.partials.p, k.ticket.p, slot + S_R0V);
+    }
+    if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
+    {
+        Launch L(c, K_VEC, 32.0 * n + pre_bytes);
+        switch (k.precond) {
+        case RS_PRECOND_BLOCK_JACOBI:
+            update_s_kernel<2><<<cb, 256, 0, st>>>(n, k.nspec, k.ncell, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, k.binv.p); break;
+        case RS_PRECOND_JACOBI:
+            update_s_kernel<1><<<cb, 256, 0, st>>>(n, 1, n, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, k.dinv.p, nullptr); break;
+        default:
+            update_s_kernel<0><<<cb, 256, 0, st>>>(n, 1, n, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, nullptr); break;
+        }
+    }
+    {
+        Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
+        spmv_dispatch<2>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, k.sh.p, k.t.p, k.s.p, k.partials.p, k.ticket.p, slot + S_TS);
+    }
+    if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
+    {
+        Launch L(c, K_VEC, 64.0 * n);
+        update_xr_kernel<<<vb, 256, 0, st>>>(n, k.scal.p, cur, k.ph.p, k.sh.p, k.s.p, k.t.p, k.r0.p, x, k.r.p, k.partials.p, k.ticket.p);
+    }
+    if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_RR, 2));
+    return RS_OK;
+}
+
+// r = r0 = b - A x explicitly; returns ||r||_2.  Restarts the recurrence (new shadow residual).
+static int true_residual_restart(Ctx &c, Krylov &k, const double *b, const double *x, int vb, int sb, double *rnorm)
+{
+    const int n = k.n;
+    cudaStream_t st = c.stream;
+    {
+        Launch L(c, K_SPMV, spmv_bytes(n, k.nnz));
+        spmv_dispatch<0>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, x, k.v.p, nullptr, nullptr, nullptr, nullptr);
+    }
+    {
+        Launch L(c, K_VEC, 32.0 * n);
+        krylov_restart_kernel<<<vb, 256, 0, st>>>(n, b, k.v.p, k.r.p, k.r0.p, k.partials.p, k.ticket.p, k.scal.p);
+    }
+    if (comm_active()) RS_TRY(comm_allreduce_sum(c, k.scal.p + S_RTRUE, 1));
+    krylov_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, S_RTRUE);
+    c.launches++;
+    RS_CUDA(cudaMemcpyAsync(k.h_scal + S_RTRUE, k.scal.p + S_RTRUE, sizeof(double), cudaMemcpyDeviceToHost, st));
+    RS_CUDA(cudaStreamSynchronize(st));
+    *rnorm = std::sqrt(k.h_scal[S_RTRUE]);
+    return RS_OK;
+}
+
+// Solves A x = b from x = 0.  BiCGStab's recursively updated residual can drift away from b - A x,
+// stagnate, or break down (a recurrence scalar hits zero); each of those ends the current cycle:
+// the true residual is recomputed, becomes the new shadow residual, and the recurrence restarts
+// from the x reached so far.  Convergence is only ever declared on the true residual.
 int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres)
 {
     const int n = k.n;
@@ -334,77 +430,65 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     const int cb = grid_for(k.precond == RS_PRECOND_BLOCK_JACOBI ? k.ncell : n, 256, 148 * 8);
     const int sb = spmv_blocks(n, k.lanes);
     const double pre_bytes = (k.precond == RS_PRECOND_BLOCK_JACOBI) ? 8.0 * k.nspec * n : (k.precond == RS_PRECOND_JACOBI ? 8.0 * n : 0.0);
+    static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
     {
         Launch L(c, K_VEC, 32.0 * n);
         krylov_init_kernel<<<vb, 256, 0, st>>>(n, b, k.r.p, k.r0.p, x, k.partials.p, k.ticket.p, k.scal.p);
     }
     if (comm_active()) RS_TRY(comm_allreduce_sum(c, k.scal.p + S_BNORM, 1));
-    krylov_seed_kernel<<<1, 1, 0, st>>>(k.scal.p);
+    krylov_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, S_BNORM);
     c.launches++;
     RS_CUDA(cudaMemcpyAsync(k.h_scal + S_BNORM, k.scal.p + S_BNORM, sizeof(double), cudaMemcpyDeviceToHost, st));
     RS_CUDA(cudaStreamSynchronize(st));
     const double bnorm = std::sqrt(k.h_scal[S_BNORM]);
     *iters = 0;
     *relres = 0.0;
+    if (!(bnorm == bnorm) || std::isinf(bnorm)) { set_error("sparse solver: right-hand side is not finite"); return RS_ESINGULAR; }
     if (!(bnorm > 0.0)) return RS_OK;  // b == 0 -> x = 0
     double target = k.lin_rtol * bnorm;
     if (abs_floor > target) target = abs_floor;
-    double rnorm = bnorm;
-    for (int it = 0; it < k.max_iter; it++) {
-        const int cur = it & 1, first = (it == 0);
+    double rtrue = bnorm;     // true residual at the start of the current cycle
+    double best = bnorm;      // smallest recursive residual of the current cycle
+    int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
+    bool done = false;
+    while (!done && total < k.max_iter) {
+        const int cur = cycle_it & 1;
+        RS_TRY(bicgstab_step(c, k, x, cur, cycle_it == 0, vb, cb, sb, pre_bytes));
+        total++; cycle_it++;
+        *iters = total;
+        if (total % k.check_every != 0 && total != k.max_iter) continue;
         double *slot = k.scal.p + SLOT * cur;
-        {
-            Launch L(c, K_VEC, (first ? 24.0 : 40.0) * n + pre_bytes);
-            switch (k.precond) {
-            case RS_PRECOND_BLOCK_JACOBI:
-                update_p_kernel<2><<<cb, 256, 0, st>>>(n, k.nspec, k.ncell, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, k.binv.p); break;
-            case RS_PRECOND_JACOBI:
-                update_p_kernel<1><<<cb, 256, 0, st>>>(n, 1, n, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, k.dinv.p, nullptr); break;
-            default:
-                update_p_kernel<0><<<cb, 256, 0, st>>>(n, 1, n, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, nullptr); break;
-            }
-        }
-        {
-            Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
-            spmv_dispatch<1>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, k.ph.p, k.v.p, k.r0.p, k.partials.p, k.ticket.p, slot + S_R0V);
-        }
-        if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
-        {
-            Launch L(c, K_VEC, 32.0 * n + pre_bytes);
-            switch (k.precond) {
-            case RS_PRECOND_BLOCK_JACOBI:
-                update_s_kernel<2><<<cb, 256, 0, st>>>(n, k.nspec, k.ncell, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, k.binv.p); break;
-            case RS_PRECOND_JACOBI:
-                update_s_kernel<1><<<cb, 256, 0, st>>>(n, 1, n, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, k.dinv.p, nullptr); break;
-            default:
-                update_s_kernel<0><<<cb, 256, 0, st>>>(n, 1, n, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, nullptr); break;
-            }
-        }
-        {
-            Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
-            spmv_dispatch<2>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, k.sh.p, k.t.p, k.s.p, k.partials.p, k.ticket.p, slot + S_TS);
-        }
-        if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
-        {
-            Launch L(c, K_VEC, 64.0 * n);
-            update_xr_kernel<<<vb, 256, 0, st>>>(n, k.scal.p, cur, k.ph.p, k.sh.p, k.s.p, k.t.p, k.r0.p, x, k.r.p, k.partials.p, k.ticket.p);
-        }
-        if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_RR, 2));
-        *iters = it + 1;
-        if ((it + 1) % k.check_every == 0 || it + 1 == k.max_iter) {
-            RS_CUDA(cudaMemcpyAsync(k.h_scal + SLOT * cur, slot, sizeof(double) * SLOT, cudaMemcpyDeviceToHost, st));
-            RS_CUDA(cudaStreamSynchronize(st));
-            const double rr = k.h_scal[SLOT * cur + S_RR];
-            if (!(rr == rr) || std::isinf(rr)) {
-                set_error("sparse solver: Krylov breakdown (non-finite residual after %d iterations)", it + 1);
-                return RS_ESINGULAR;
-            }
-            rnorm = std::sqrt(rr);
-            if (rnorm <= target) break;
-        }
+        RS_CUDA(cudaMemcpyAsync(k.h_scal + SLOT * cur, slot, sizeof(double) * SLOT, cudaMemcpyDeviceToHost, st));
+        RS_CUDA(cudaStreamSynchronize(st));
+        const double *h = k.h_scal + SLOT * cur;
+        const double rr = h[S_RR];
+        if (debug)
+            fprintf(stderr, "[krylov] it %d rr %.6e r0v %.6e ts %.6e tt %.6e rhonext %.6e bad %g\n", total, rr, h[S_R0V],
+                    h[S_TS], h[S_TT], h[S_RHONEXT], h[S_BAD]);
+        const bool finite = (rr == rr) && !std::isinf(rr);
+        const bool broke = !finite || h[S_BAD] != 0.0 || h[S_RHONEXT] == 0.0;
+        const double rnorm = finite ? std::sqrt(rr) : best;
+        if (finite && rnorm < 0.9 * best) { best = rnorm; since_best = 0; } else since_best++;
+        const bool looks_converged = finite && !broke && rnorm <= target;
+        const bool stagnated = since_best >= 25;
+        if (!(looks_converged || broke || stagnated || total >= k.max_iter)) continue;
+        // end of cycle: what did it really achieve?
+        double rt = 0.0;
+        RS_TRY(true_residual_restart(c, k, b, x, vb, sb, &rt));
+        if (debug) fprintf(stderr, "[krylov] cycle %d ends after %d its (%s): true residual %.6e (target %.3e)\n", restarts,
+                           cycle_it, looks_converged ? "converged" : broke ? "breakdown" : stagnated ? "stagnation" : "budget",
+                           rt, target);
+        if (!(rt == rt) || std::isinf(rt)) { set_error("sparse solver: Krylov breakdown (solution is not finite)"); return RS_ESINGULAR; }
+        if (rt <= target) { rtrue = rt; done = true; break; }
+        fruitless = (rt > 0.5 * rtrue) ? fruitless + 1 : 0;
+        rtrue = rt;
+        if (fruitless >= 6) break;   // six cycles in a row without halving the residual: give up, report what we have
+        restarts++;
+        cycle_it = 0; best = rt; since_best = 0;
     }
     RS_CUDA(cudaGetLastError());
-    *relres = rnorm / bnorm;
+    *relres = rtrue / bnorm;
+    if (!done && debug) fprintf(stderr, "[krylov] not converged: relres %.3e after %d its\n", *relres, total);
     return RS_OK;
 }
 

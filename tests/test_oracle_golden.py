@@ -1,0 +1,161 @@
+"""Pins the CPU oracle (oracle/stodes_oracle.c) to everything the reference holds for this path
+(SURVEY.md 8(c)): the frozen vignette output in inst/doc/rootSolve.pdf p.16, the closed-form
+nonzero counts implied by src/sparsecoeff.f, the group counts of JGROUP, and an independent
+sparse direct solve for the Yale LDU chain.  CPU only."""
+import ctypes as C
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_pdf_p16_golden(oracle):
+    """nnz=6400, ngp=12, work length 82366, precis = 1.105000e+01 3.917674e-07 2.751792e-16"""
+    g = json.load(open(os.path.join(GOLD, "rootsolve_pdf_p16.json")))
+    n = g["n"]
+    r = oracle.stsparse(np.full(n ** 3, g["y0"]), oracle.model("diff3d", g["parms"]), sparsetype="3D",
+                        nnz=[1, n, n, n, 0, 0, 0], atol=g["tol"], rtol=g["tol"], ctol=g["tol"], lrw=g["lrw_given"],
+                        positive=True, ipar=[1, n, n, n, 1])
+    assert r["steady"] is True
+    assert r["dims"] == {"nnz": g["nnz"], "ngp": g["ngp"], "lrw": g["lrw_used"]}
+    assert len(r["precis"]) == 3
+    # the PDF prints 7 significant digits
+    for got, want in zip(r["precis"], g["precis"]):
+        assert float("%.6e" % got) == want
+    # R-side estimates printed by verbose=TRUE (R/stodes.R:139,143,182-183)
+    Type, nnzv, ngp, lrw, itol = oracle.stodes_args(n ** 3, "3D", [1, n, n, n, 0, 0, 0])
+    assert (Type, int(nnzv[0]), ngp, itol) == (4, g["nnz_estimated_by_R"], g["function_calls_estimated_by_R"], 1)
+
+
+def test_structure_hash_fixture(oracle):
+    for e in json.load(open(os.path.join(GOLD, "structure_hashes.json"))):
+        ian, jan = oracle.sparse_structure(e["kind"], e["nspec"], e["dims"], e["cyclic"])
+        ngp, igp, jgp = oracle.jgroup(ian, jan)
+        sha = lambda a: hashlib.sha256(np.ascontiguousarray(a, dtype=np.int32).tobytes()).hexdigest()
+        assert (len(jan), ngp) == (e["nnz"], e["ngp"])
+        assert (sha(ian), sha(jan), sha(igp), sha(jgp)) == (e["ian"], e["jan"], e["igp"], e["jgp"])
+
+
+@pytest.mark.parametrize("nspec,nb", [(1, 10), (3, 40), (5, 1000)])
+def test_nnz_closed_form_1d(oracle, nspec, nb):
+    n = nspec * nb
+    ian, jan = oracle.sparse_structure("1D", nspec, [nb], [0])
+    assert len(jan) == n * (2 + nspec) - 2 * nspec                     # R/stodes.R:104
+    ianc, janc = oracle.sparse_structure("1D", nspec, [nb], [1])
+    assert len(janc) == n * (2 + nspec)                               # + 2*nspec when cyclic, R/stodes.R:106-108
+    ngp, igp, jgp = oracle.jgroup(ian, jan)
+    assert ngp == 3 * nspec                                            # SURVEY 8(c) closed form
+    assert sorted(jgp.tolist()) == list(range(1, n + 1))
+
+
+@pytest.mark.parametrize("nspec,d", [(1, (50, 50)), (1, (100, 100)), (2, (17, 9)), (1, (50, 100))])
+def test_nnz_closed_form_2d(oracle, nspec, d):
+    n = nspec * d[0] * d[1]
+    ian, jan = oracle.sparse_structure("2D", nspec, d, [0, 0])
+    assert len(jan) == n * (4 + nspec) - 2 * nspec * (d[0] + d[1])     # R/stodes.R:116-117
+    ngp, _, _ = oracle.jgroup(ian, jan)
+    if nspec == 1:
+        assert ngp == 7
+
+
+@pytest.mark.parametrize("nspec,d", [(1, (10, 10, 10)), (2, (6, 7, 8)), (1, (16, 16, 16))])
+def test_nnz_closed_form_3d(oracle, nspec, d):
+    n = nspec * d[0] * d[1] * d[2]
+    ian, jan = oracle.sparse_structure("3D", nspec, d, [0, 0, 0])
+    assert len(jan) == n * (6 + nspec) - 2 * nspec * (d[1] * d[2] + d[0] * d[2] + d[0] * d[1])
+    # every column's first entry is its own diagonal (src/sparsecoeff.f:247)
+    assert np.array_equal(jan[ian[:-1] - 1], np.arange(1, n + 1))
+
+
+def test_grouping_is_a_valid_partition(oracle):
+    """columns of one group never share a row (what makes the grouped FD Jacobian exact)"""
+    ian, jan = oracle.sparse_structure("3D", 2, (5, 6, 7), (1, 0, 1))
+    ngp, igp, jgp = oracle.jgroup(ian, jan)
+    n = len(ian) - 1
+    for g in range(ngp):
+        rows = np.concatenate([jan[ian[j - 1] - 1: ian[j] - 1] for j in jgp[igp[g] - 1: igp[g + 1] - 1]])
+        assert len(rows) == len(set(rows.tolist()))
+    assert igp[0] == 1 and igp[-1] == n + 1
+
+
+def test_perturb_rule(oracle):
+    L = oracle.lib()
+    for v in [0.0, 1e-12, -3.0, 10.0, 1e9]:
+        x = C.c_double(v)
+        d = L.orc_perturb(C.byref(x))
+        assert d == max(abs(v) * 1e-8, 1e-8) and x.value == v + d
+
+
+def test_yale_solve_against_scipy(oracle):
+    """odrv + cdrv(path 1) solve M x = b and cdrv(path 4) solves M' x = b (src/sparse.f:136-149)"""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+    rng = np.random.default_rng(20260101)
+    L = oracle.lib()
+    for kind, nspec, dims in [("2D", 1, (15, 12)), ("3D", 2, (5, 6, 4)), ("1D", 4, (60,))]:
+        ian, jan = oracle.sparse_structure(kind, nspec, dims, [0] * len(dims))
+        n = len(ian) - 1
+        a = rng.uniform(-1, 1, len(jan))
+        a[ian[:-1] - 1] = 5.0 + rng.uniform(0, 1, n)
+        b = rng.standard_normal(n)
+        M = sp.csr_matrix((a.copy(), jan - 1, ian - 1), shape=(n, n))   # (ian,jan,a) read by rows is M
+        nsp = 40 * len(jan)
+        isp = np.zeros(2 * nsp, dtype=np.int32)
+        rsp = np.zeros(nsp)
+        r = np.zeros(n, dtype=np.int32)
+        ic = np.zeros(n, dtype=np.int32)
+        ianw, janw, aw = ian.copy(), jan.copy(), a.copy()
+        assert L.orc_odrv(n, H.ip(ianw), H.ip(janw), H.ip(r), H.ip(ic), nsp, H.ip(isp), 1) == 0
+        assert sorted(r.tolist()) == list(range(1, n + 1))
+        c = np.zeros(n, dtype=np.int32)
+        c[ic - 1] = np.arange(1, n + 1)
+        x = np.zeros(n)
+        esp = C.c_int(0)
+        assert L.orc_cdrv(n, H.ip(r), H.ip(c), H.ip(ic), H.ip(ianw), H.ip(janw), H.dp(aw), H.dp(b), H.dp(x), nsp,
+                          H.ip(isp), H.dp(rsp), C.byref(esp), 1) == 0
+        assert np.allclose(x, spla.spsolve(M.tocsc(), b), rtol=1e-10, atol=1e-12)
+        xt = np.zeros(n)
+        assert L.orc_cdrv(n, H.ip(r), H.ip(c), H.ip(ic), H.ip(ianw), H.ip(janw), H.dp(aw), H.dp(b), H.dp(xt), nsp,
+                          H.ip(isp), H.dp(rsp), C.byref(esp), 4) == 0
+        assert np.allclose(xt, spla.spsolve(M.T.tocsc(), b), rtol=1e-10, atol=1e-12)
+        assert esp.value > 0
+
+
+def test_oracle_newton_on_nonlinear_cases(oracle):
+    """C1 (2-D Monod) and the two-species 3-D case converge, stay positive, and satisfy the residual test"""
+    d = (50, 50)
+    r = oracle.stsparse(np.full(d[0] * d[1], 10.0), oracle.model("diff2d", H.P_DIFF2D_MONOD), sparsetype="2D",
+                        nnz=[1, d[0], d[1], 0, 0], ipar=[1, d[0], d[1], 1, 1], lrw=600000, positive=True, **H.TOL)
+    assert r["steady"] and r["dims"]["nnz"] == 12300 and r["dims"]["ngp"] == 7
+    assert r["y"].min() > 0 and r["y"].max() < 1.0
+    # the transposed-first-step quirk does not move the root
+    r2 = oracle.stsparse(np.full(d[0] * d[1], 10.0), oracle.model("diff2d", H.P_DIFF2D_MONOD), sparsetype="2D",
+                         nnz=[1, d[0], d[1], 0, 0], ipar=[1, d[0], d[1], 1, 1], lrw=600000, positive=True,
+                         quirk_first_step_transposed=False, **H.TOL)
+    ok, worst = H.within_tol(r2["y"], r["y"])
+    assert ok, worst
+    sd = (6, 7, 8)
+    nc = int(np.prod(sd))
+    y0 = np.concatenate([np.full(nc, 10.0), np.full(nc, 1.0)])
+    q = oracle.stsparse(y0, oracle.model("rd3d", H.P_RD3D), sparsetype="3D", nnz=[2, *sd, 0, 0, 0], ipar=[2, *sd, 0],
+                        lrw=2000000, positive=True, **H.TOL)
+    q2 = oracle.stsparse(y0, oracle.model("rd3d", H.P_RD3D), sparsetype="3D", nnz=[2, *sd, 0, 0, 0], ipar=[2, *sd, 0],
+                         lrw=2000000, positive=True, quirk_first_step_transposed=False, **H.TOL)
+    assert q["steady"] and q2["steady"]
+    ok, worst = H.within_tol(q2["y"], q["y"], factor=2.0)
+    assert ok, worst
+
+
+def test_oracle_error_paths(oracle):
+    with pytest.raises(RuntimeError, match="lrw"):
+        oracle.stsparse(np.full(1000, 10.0), oracle.model("diff3d", H.P_DIFF3D), sparsetype="3D",
+                        nnz=[1, 10, 10, 10, 0, 0, 0], ipar=[1, 10, 10, 10, 0], lrw=20000, **H.TOL)
+    with pytest.raises(RuntimeError, match="not compatible"):
+        oracle.stsparse(np.full(1001, 10.0), oracle.model("diff3d", H.P_DIFF3D), sparsetype="3D",
+                        nnz=[2, 10, 10, 10, 0, 0, 0], ipar=[1, 10, 10, 10, 0], lrw=200000, **H.TOL)
