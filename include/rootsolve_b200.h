@@ -169,6 +169,10 @@ int rs_linsolve(int neq, const int *ian, const int *jan, const double *a, const 
 /* y = J x with J given by columns as (ian, jan, a) -- the SpMV kernel on its own. */
 int rs_spmv(int neq, const int *ian, const int *jan, const double *a, const double *x, double *y);
 
+/* Convergence test 1 of the Newton loop (src/sparse.f:122-133): out2[0] = sum |beta_k| (precis is this / neq),
+ * out2[1] = max |beta_k / ewt_k| (steady when <= 1). */
+int rs_convergence_test(int neq, const double *beta, const double *ewt, double *out2);
+
 /* errset (src/sparse.f:264-293) */
 int rs_errset(int neq, int itol, const double *rtol, const double *atol, const double *y, double *ewt);
 

@@ -742,6 +742,23 @@ extern "C" int rs_errset(int neq, int itol, const double *rtol, const double *at
     return RS_OK;
 }
 
+extern "C" int rs_convergence_test(int neq, const double *beta, const double *ewt, double *out2)
+{
+    if (!beta || !ewt || !out2 || neq <= 0) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    Ctx c;
+    DevBuf<double> d_b, d_e, partials, red;
+    DevBuf<unsigned> ticket;
+    RS_TRY(d_b.alloc(neq)); RS_TRY(d_e.alloc(neq)); RS_TRY(partials.alloc(2 * 148 * 8)); RS_TRY(red.alloc(2)); RS_TRY(ticket.alloc(1));
+    RS_TRY(d_b.upload(beta, neq, c.stream)); RS_TRY(d_e.upload(ewt, neq, c.stream));
+    RS_TRY(ticket.zero(c.stream));
+    test1_kernel<<<grid_for(neq, 256, 148 * 8), 256, 0, c.stream>>>(neq, d_b.p, d_e.p, partials.p, ticket.p, red.p);
+    RS_CUDA(cudaGetLastError());
+    RS_TRY(red.download(out2, 2, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    return RS_OK;
+}
+
 extern "C" const char *rs_last_error(void) { return g_err; }
 extern "C" int rs_abi_version(void) { return RS_ABI_VERSION; }
 extern "C" int rs_device_count(void)

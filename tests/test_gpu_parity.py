@@ -253,6 +253,19 @@ def test_errset_bit_exact(built, oracle):
         assert np.array_equal(e, er)
 
 
+def test_convergence_test_kernel(built):
+    """sum |beta| and max |beta/ewt| (src/sparse.f:122-133); the sum is order-dependent -> 1e-13 relative"""
+    from rootsolve_b200 import _capi
+    rng = np.random.default_rng(11)
+    for n in (1, 255, 4096, 1000003):
+        beta = rng.standard_normal(n) * 1e-3
+        ewt = rng.uniform(1e-9, 1e-6, n)
+        out = np.zeros(2)
+        _capi.check(built.rs_convergence_test(n, H.dp(beta), H.dp(ewt), H.dp(out)))
+        assert abs(out[0] - np.abs(beta).sum()) <= 1e-13 * np.abs(beta).sum()
+        assert out[1] == np.max(np.abs(beta / ewt))
+
+
 SOLVES = [
     # (case, R dimens, oracle lrw)
     ("diff2d_lin", (30, 20), 400000),
