@@ -173,6 +173,19 @@ int rs_spmv(int neq, const int *ian, const int *jan, const double *a, const doub
  * out2[1] = max |beta_k / ewt_k| (steady when <= 1). */
 int rs_convergence_test(int neq, const double *beta, const double *ewt, double *out2);
 
+/* No counterpart in the reference.  The same test as rs_convergence_test for callers that cannot allocate
+ * device memory while they run (applications that gave the GPU heap to their own pool, in-situ / real-time
+ * coupling loops where cudaMalloc would stall the device, plugins barred from allocating after start-up):
+ * d_beta, d_ewt (neq doubles each) and d_out2 (2 doubles) are DEVICE pointers the caller owns; the kernel is
+ * queued on `stream` (a cudaStream_t, NULL = default stream) and the call returns without synchronising.
+ * Scratch comes from a 64 KiB static device array inside the library, hence the limit: neq must not exceed
+ * RS_CONVERGENCE_TEST_NOALLOC_MAX_NEQ (RS_ETOOBIG otherwise).  No cudaMalloc/cudaFree is ever called.
+ * The array is shared by all calls on a device: calls that may overlap on the GPU race and must be ordered
+ * by the caller.  The first call on each device resolves the array's address; make it before any stream
+ * capture begins. */
+#define RS_CONVERGENCE_TEST_NOALLOC_MAX_NEQ 8355840
+int rs_convergence_test_noalloc(int neq, const double *d_beta, const double *d_ewt, double *d_out2, void *stream);
+
 /* errset (src/sparse.f:264-293) */
 int rs_errset(int neq, int itol, const double *rtol, const double *atol, const double *y, double *ewt);
 
