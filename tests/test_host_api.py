@@ -1,0 +1,139 @@
+"""CPU-side tests: the host mirror of the R front end, and that the C-ABI library loads and exports every
+symbol include/rootsolve_b200.h declares.  No compute call needs a GPU here."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import helpers as H
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_functions():
+    src = open(os.path.join(ROOT, "include", "rootsolve_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(rs_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(built):
+    names = declared_functions()
+    assert "rs_stsparse" in names and "rs_convergence_test_noalloc" in names and len(names) >= 25
+    for nm in names:
+        assert hasattr(built, nm), f"{nm} is declared in rootsolve_b200.h but not exported"
+    assert built.rs_abi_version() == 1
+
+
+def test_model_library_descriptors(built):
+    from rootsolve_b200 import _capi
+
+    class Desc(C.Structure):
+        _fields_ = [("abi", C.c_int), ("name", C.c_char_p), ("nparms", C.c_int), ("launch", C.c_void_p),
+                    ("initfunc", C.c_void_p), ("initforc", C.c_void_p)]
+    for name, npar in [("diff2d", 7), ("diff3d", 8), ("rd3d", 10), ("rt1d", 7)]:
+        d = C.cast(_capi.model_symbol(name), C.POINTER(Desc)).contents
+        assert d.abi == 1 and d.name.decode() == name and d.nparms == npar and d.launch and d.initfunc
+    with pytest.raises(ValueError, match="dyn function not loaded"):
+        _capi.model_symbol("no_such_model")
+
+
+def test_no_cpu_fallback(built):
+    """without a GPU every compute entry point fails loudly with RS_ENODEVICE"""
+    if built.rs_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    import rootsolve_b200 as rs
+    with pytest.raises(rs.RootSolveError) as e:
+        rs.steady_2D(np.full((5, 5), 10.0), func="diff2d", parms=H.P_DIFF2D_LIN, dimens=[5, 5], ipar=[1, 5, 5, 1, 0])
+    assert e.value.code == -2 and "no CPU path" in str(e.value)
+    ian = np.array([1, 2], dtype=np.int32)
+    jan = np.array([1], dtype=np.int32)
+    ngp = C.c_int(0)
+    assert built.rs_jgroup(1, H.ip(ian), H.ip(jan), 2, None, C.byref(ngp), None, None) == -2
+
+
+@pytest.mark.parametrize("st,nnz,n", [("1D", [5, 200, 0], 1000), ("1D", [2, 30, 1], 60), ("2D", [1, 50, 50, 0, 0], 2500),
+                                      ("2D", [2, 17, 9, 1, 0], 306), ("2D", [1, 100, 50, 1, 1], 5000),
+                                      ("3D", [1, 10, 10, 10, 0, 0, 0], 1000), ("3D", [2, 4, 5, 6, 1, 0, 1], 240)])
+def test_sparse_args_match_independent_restatement(oracle, st, nnz, n):
+    """Type / nnz vector / ngp / lrw of R/stodes.R:101-160: host mirror vs the oracle's own restatement"""
+    from rootsolve_b200.stodes import sparse_args
+    Type, v, ngp, lrw, ian, jan = sparse_args(n, st, nnz)
+    rType, rv, rngp, rlrw, _ = oracle.stodes_args(n, st, nnz)
+    assert (Type, ngp, lrw) == (rType, rngp, rlrw) and np.array_equal(v, rv) and ian is None and jan is None
+
+
+def test_sparse_args_known_values():
+    from rootsolve_b200.stodes import sparse_args
+    # the verbose print-out of the reference's 10^3 example: "6910" nonzeros, "1001" function calls (pdf p.16)
+    Type, v, ngp, lrw, _, _ = sparse_args(1000, "3D", [1, 10, 10, 10, 0, 0, 0])
+    assert (Type, int(v[0]), ngp, lrw) == (4, 6910, 1001, 3 * 1000 + 4 * 6910)
+    Type, v, ngp, _, _, _ = sparse_args(1000, "1D", [5, 200, 1])
+    assert (Type, int(v[0]), ngp) == (2, 1000 * 7 - 10 + 10, 17)
+    # sparseusr: (row, col) pairs sorted by column -> ian/jan
+    inz = np.array([[1, 1], [2, 1], [1, 2], [2, 2], [3, 3]])
+    Type, v, _, _, ian, jan = sparse_args(3, "sparseusr", inz=inz)
+    assert Type == 0 and list(ian) == [1, 3, 5, 6] and list(jan) == [1, 2, 1, 2, 3] and int(v[0]) == 5
+    with pytest.raises(ValueError, match="should be sorted"):
+        sparse_args(3, "sparseusr", inz=inz[::-1])
+    with pytest.raises(ValueError, match="sparsetype not known"):
+        sparse_args(3, "4D", [1])
+
+
+def test_argument_checks_mirror_the_r_front_end(built):
+    import rootsolve_b200 as rs
+    y = np.full(25, 1.0)
+    kw = dict(func="diff2d", parms=H.P_DIFF2D_LIN, ipar=[1, 5, 5, 1, 0])
+    with pytest.raises(ValueError, match="dimens should be specified"):
+        rs.steady_2D(y, dimens=None, **kw)
+    with pytest.raises(ValueError, match="should contain 2 values"):
+        rs.steady_2D(y, dimens=[5, 5, 1], **kw)
+    with pytest.raises(ValueError, match="not an integer fraction"):
+        rs.steady_2D(y, dimens=[4, 4], **kw)
+    with pytest.raises(ValueError, match="should contain 3 values"):
+        rs.steady_3D(y, dimens=[5, 5], **kw)
+    with pytest.raises(ValueError, match="either nspec or dimens"):
+        rs.steady_1D(y, **kw)
+    with pytest.raises(ValueError, match="cyclicBnd should be a vector or number not exceeding 2"):
+        rs.steady_2D(y, dimens=[5, 5], cyclicBnd=3, **kw)
+    with pytest.raises(ValueError, match="`atol' must either be a scalar"):
+        rs.stodes(y, sparsetype="2D", nnz=[1, 5, 5, 0, 0], atol=[1e-8, 1e-8], **kw)
+    with pytest.raises(ValueError, match="maxiter must be >=1"):
+        rs.stodes(y, sparsetype="2D", nnz=[1, 5, 5, 0, 0], maxiter=0, **kw)
+    with pytest.raises(ValueError, match="should be < the number of state variables"):
+        rs.stodes(y, sparsetype="2D", nnz=[1, 5, 5, 0, 0], positive=[1, 26], **kw)
+    with pytest.raises(TypeError, match="compiled device model"):
+        rs.stodes(y, func=lambda t, y, p: y, sparsetype="2D", nnz=[1, 5, 5, 0, 0])
+    with pytest.raises(ValueError, match="spmethod"):
+        rs.stodes(y, sparsetype="2D", nnz=[1, 5, 5, 0, 0], spmethod="ilut", **kw)
+    with pytest.raises(NotImplementedError):
+        rs.steady_2D(y, dimens=[5, 5], method="runsteady", **kw)
+
+
+def test_pack_args_layout(built):
+    """the POD block handed to rs_stsparse: R's column-major flattening, itol, Pos/positive, rev(dimens)"""
+    import importlib
+    host = importlib.import_module("rootsolve_b200.stodes")
+    y = np.arange(6.0).reshape(2, 3)           # R: matrix(nrow=2, ncol=3)
+    P = host.pack_args(y, 0.0, "diff2d", H.P_DIFF2D_LIN, [1e-6] * 6, 1e-8, 1e-8, "2D", False, [1, 3, 2, 0, 0], None,
+                       None, None, [1, 2], 100, None, "rs_models", H.P_DIFF2D_LIN, None, [1, 3, 2, 1, 0], 0, "yale",
+                       {"precond": "jacobi", "lin_rtol": 1e-12})
+    a = P.args
+    assert [a.y[i] for i in range(6)] == [0.0, 3.0, 1.0, 4.0, 2.0, 5.0]
+    assert a.neq == 6 and a.itol == 3 and a.Pos == 0 and a.npositive == 2 and a.Type == 3 and a.imethod == 1
+    assert [a.nnz[i] for i in range(a.nnnz)] == [6 * 5 - 2 * (3 + 2), 1, 3, 2, 0, 0]
+    assert a.ngp == 7 and a.control.contents.precond == 1 and a.control.contents.lin_rtol == 1e-12
+
+
+def test_slab_bounds(built):
+    for d1, nr in [(256, 8), (10, 3), (7, 7), (5, 8), (128, 2)]:
+        j0, j1 = C.c_int(0), C.c_int(0)
+        edges = []
+        for r in range(nr):
+            built.rs_slab_bounds(d1, nr, r, C.byref(j0), C.byref(j1))
+            edges.append((j0.value, j1.value))
+        assert edges[0][0] == 0 and edges[-1][1] == d1
+        assert all(edges[r][1] == edges[r + 1][0] for r in range(nr - 1))
+        sizes = [b - a for a, b in edges]
+        assert max(sizes) - min(sizes) <= 1
