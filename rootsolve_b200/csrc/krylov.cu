@@ -16,7 +16,9 @@
 // kernels recompute them from the raw dot products in `scal`, so one step is
 // five launches and the host only reads ||r||^2 to decide when to stop.
 #include <cmath>
+#include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 #include "solver.cuh"
 
@@ -98,6 +100,141 @@ int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const
     spmv_dispatch<0>(c.stream, lanes, spmv_blocks(n, lanes), n, rowptr, col, val, x, y, nullptr, nullptr, nullptr, nullptr);
     RS_CUDA(cudaGetLastError());
     return RS_OK;
+}
+
+// ---- SpMV, TMA-staged variant ---------------------------------------------------------
+// Persistent CTAs walk tiles of TMA_ROWS consecutive rows.  The tile's slice of (val, col) is one
+// contiguous byte range of each array, so an elected thread streams it into shared memory with two
+// 1-D bulk copies (cp.async.bulk -> UBLKCP, completion counted on an mbarrier) TMA_STAGES tiles ahead
+// of the consumers; the matrix never passes through the LSU/L1 path.  Consumers are one thread per
+// row: with ascending columns the k-th entry of consecutive rows addresses consecutive x, so the x
+// gathers are coalesced and mostly L1/L2 hits (the stencil bands are re-read by neighbouring rows).
+constexpr int TMA_ROWS = 256;      // rows per tile = threads per CTA
+constexpr int TMA_STAGES = 4;
+constexpr int TMA_CAP = 2304;      // nonzeros a stage can hold (avg 9 per row); larger tiles -> sub-warp kernel
+constexpr int TMA_STAGE_BYTES = TMA_CAP * 12;
+constexpr int TMA_SMEM_BYTES = TMA_STAGES * TMA_STAGE_BYTES;
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// issues the two bulk copies of tile `tile` into stage buffers; a0 = first staged nonzero (multiple of 4)
+__device__ __forceinline__ void tma_issue_tile(int tile, int n, const int *__restrict__ rowptr, const int *__restrict__ col,
+                                               const double *__restrict__ val, unsigned char *stage,
+                                               unsigned long long *bar, int *a0_slot)
+{
+    const int r0 = tile * TMA_ROWS;
+    const int r1 = min(n, r0 + TMA_ROWS);
+    const int p0 = rowptr[r0], p1 = rowptr[r1];
+    const int a0 = p0 & ~3;
+    const int cnt = ((p1 + 3) & ~3) - a0;   // multiple of 4 -> 16-byte multiples for both arrays
+    *a0_slot = a0;
+    if (cnt > 0) {
+        mbar_expect_tx(bar, (unsigned)cnt * 12u);
+        bulk_g2s(stage, val + a0, (unsigned)cnt * 8u, bar);
+        bulk_g2s(stage + TMA_CAP * 8, col + a0, (unsigned)cnt * 4u, bar);
+    } else {
+        mbar_expect_tx(bar, 0u);
+    }
+}
+
+template <int NDOT>
+__global__ void __launch_bounds__(TMA_ROWS) spmv_tma_kernel(int n, int ntiles, const int *__restrict__ rowptr,
+                                                            const int *__restrict__ col, const double *__restrict__ val,
+                                                            const double *__restrict__ x, double *__restrict__ y,
+                                                            const double *__restrict__ w, double *partials,
+                                                            unsigned *ticket, double *out)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) unsigned long long full[TMA_STAGES];
+    __shared__ int a0s[TMA_STAGES];
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        for (int s = 0; s < TMA_STAGES; s++) mbar_init(&full[s], 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int my_tiles = (ntiles > (int)blockIdx.x) ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    if (tid == 0) {
+        for (int i = 0; i < TMA_STAGES && i < my_tiles; i++)
+            tma_issue_tile(blockIdx.x + i * gridDim.x, n, rowptr, col, val, smem + i * TMA_STAGE_BYTES, &full[i], &a0s[i]);
+    }
+    double acc[NDOT > 0 ? NDOT : 1] = {0.0};
+    for (int i = 0; i < my_tiles; i++) {
+        const int s = i % TMA_STAGES;
+        const unsigned parity = (unsigned)(i / TMA_STAGES) & 1u;
+        const int tile = blockIdx.x + i * gridDim.x;
+        const int r = tile * TMA_ROWS + tid;
+        int pb = 0, pe = 0;
+        if (r < n) { pb = rowptr[r]; pe = rowptr[r + 1]; }
+        mbar_wait(&full[s], parity);
+        const int a0 = a0s[s];
+        const double *sval = reinterpret_cast<const double *>(smem + s * TMA_STAGE_BYTES) - a0;
+        const int *scol = reinterpret_cast<const int *>(smem + s * TMA_STAGE_BYTES + TMA_CAP * 8) - a0;
+        if (r < n) {
+            double sum0 = 0.0, sum1 = 0.0;
+            int p = pb;
+            for (; p + 3 < pe; p += 4) {
+                const int c0 = scol[p], c1 = scol[p + 1], c2 = scol[p + 2], c3 = scol[p + 3];
+                const double x0 = __ldg(&x[c0]), x1 = __ldg(&x[c1]), x2 = __ldg(&x[c2]), x3 = __ldg(&x[c3]);
+                sum0 += sval[p] * x0; sum1 += sval[p + 1] * x1; sum0 += sval[p + 2] * x2; sum1 += sval[p + 3] * x3;
+            }
+            for (; p < pe; p++) sum0 += sval[p] * __ldg(&x[scol[p]]);
+            const double sum = sum0 + sum1;
+            y[r] = sum;
+            if (NDOT == 1) acc[0] += w[r] * sum;
+            if (NDOT == 2) { acc[0] += sum * w[r]; acc[1] += sum * sum; }
+        }
+        __syncthreads();   // every consumer is done with stage s
+        if (tid == 0 && i + TMA_STAGES < my_tiles) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            tma_issue_tile(blockIdx.x + (i + TMA_STAGES) * gridDim.x, n, rowptr, col, val, smem + s * TMA_STAGE_BYTES, &full[s], &a0s[s]);
+        }
+    }
+    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out);
+}
+
+// largest number of staged nonzeros any tile needs
+__global__ void tma_tile_max_kernel(int n, int ntiles, const int *__restrict__ rowptr, int *__restrict__ out)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntiles) return;
+    const int r0 = t * TMA_ROWS, r1 = min(n, r0 + TMA_ROWS);
+    const int need = ((rowptr[r1] + 3) & ~3) - (rowptr[r0] & ~3);
+    atomicMax(out, need);
+}
+
+template <int NDOT>
+static void spmv_run(const Krylov &k, cudaStream_t st, int sb, const double *x, double *y, const double *w, double *out)
+{
+    if (k.tma_tiles > 0) {
+        spmv_tma_kernel<NDOT><<<k.tma_grid, TMA_ROWS, TMA_SMEM_BYTES, st>>>(k.n, k.tma_tiles, k.rowptr, k.col, k.val, x, y, w,
+                                                                            k.partials.p, k.ticket.p, out);
+    } else {
+        spmv_dispatch<NDOT>(st, k.lanes, sb, k.n, k.rowptr, k.col, k.val, x, y, w, k.partials.p, k.ticket.p, out);
+    }
 }
 
 // ---- preconditioner set-up ----------------------------------------------------------
@@ -324,6 +461,35 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
         if (ctl->check_every > 0) k.check_every = ctl->check_every;
     }
     k.lanes = pick_lanes(n, nnz);
+    // TMA-staged SpMV when every tile's slice fits one stage (RS_SPMV=subwarp forces the other kernel)
+    k.tma_tiles = 0;
+    {
+        const char *force = getenv("RS_SPMV");
+        const int ntiles = (n + TMA_ROWS - 1) / TMA_ROWS;
+        if (!(force && strcmp(force, "subwarp") == 0) && ntiles > 0) {
+            DevBuf<int> mx;
+            RS_TRY(mx.alloc(1));
+            RS_TRY(mx.zero(c.stream));
+            tma_tile_max_kernel<<<(ntiles + 255) / 256, 256, 0, c.stream>>>(n, ntiles, rowptr, mx.p);
+            c.launches++;
+            int need = 0;
+            RS_TRY(mx.download(&need, 1, c.stream));
+            RS_CUDA(cudaStreamSynchronize(c.stream));
+            if (need <= TMA_CAP) {
+                RS_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TMA_SMEM_BYTES));
+                RS_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TMA_SMEM_BYTES));
+                RS_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TMA_SMEM_BYTES));
+                int dev = 0, sms = 0, per_sm = 0;
+                RS_CUDA(cudaGetDevice(&dev));
+                RS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+                RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmv_tma_kernel<2>, TMA_ROWS, TMA_SMEM_BYTES));
+                if (per_sm >= 1) {
+                    k.tma_tiles = ntiles;
+                    k.tma_grid = std::min(ntiles, sms * per_sm);
+                }
+            }
+        }
+    }
     RS_TRY(k.r.alloc(n)); RS_TRY(k.r0.alloc(n)); RS_TRY(k.p.alloc(n)); RS_TRY(k.v.alloc(n));
     RS_TRY(k.s.alloc(n)); RS_TRY(k.t.alloc(n)); RS_TRY(k.ph.alloc(n)); RS_TRY(k.sh.alloc(n));
     if (precond == RS_PRECOND_JACOBI) RS_TRY(k.dinv.alloc(n));
@@ -369,7 +535,7 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first, int v
     }
     {
         Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
-        spmv_dispatch<1>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, k.ph.p, k.v.p, k.r0.p, k.partials.p, k.ticket.p, slot + S_R0V);
+        spmv_run<1>(k, st, sb, k.ph.p, k.v.p, k.r0.p, slot + S_R0V);
     }
     if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
     {
@@ -385,7 +551,7 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first, int v
     }
     {
         Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
-        spmv_dispatch<2>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, k.sh.p, k.t.p, k.s.p, k.partials.p, k.ticket.p, slot + S_TS);
+        spmv_run<2>(k, st, sb, k.sh.p, k.t.p, k.s.p, slot + S_TS);
     }
     if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
     {
@@ -403,7 +569,7 @@ static int true_residual_restart(Ctx &c, Krylov &k, const double *b, const doubl
     cudaStream_t st = c.stream;
     {
         Launch L(c, K_SPMV, spmv_bytes(n, k.nnz));
-        spmv_dispatch<0>(st, k.lanes, sb, n, k.rowptr, k.col, k.val, x, k.v.p, nullptr, nullptr, nullptr, nullptr);
+        spmv_run<0>(k, st, sb, x, k.v.p, nullptr, nullptr);
     }
     {
         Launch L(c, K_VEC, 32.0 * n);

@@ -82,7 +82,8 @@ struct DevBuf {
     {
         release();
         if (count == 0) count = 1;
-        cudaError_t e = cudaMalloc((void **)&p, count * sizeof(T));
+        // 64 bytes of slack: bulk (TMA) copies round their byte ranges up to 16-byte multiples
+        cudaError_t e = cudaMalloc((void **)&p, count * sizeof(T) + 64);
         if (e != cudaSuccess) {
             p = nullptr;
             set_error("cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e));

@@ -58,7 +58,8 @@ struct Krylov {
     DevBuf<double> partials, scal;
     DevBuf<unsigned> ticket;
     double *h_scal = nullptr;  // pinned mirror
-    int lanes = 8;             // lanes per row of the SpMV
+    int lanes = 8;             // lanes per row of the sub-warp SpMV
+    int tma_tiles = 0, tma_grid = 0;  // > 0: the TMA-staged SpMV is used (every tile fits a stage)
     int max_iter = 10000, check_every = 1;
     double lin_rtol = 1e-10, lin_ewt_factor = 0.05;
     ~Krylov();
