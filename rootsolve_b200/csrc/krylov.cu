@@ -111,6 +111,8 @@ int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const
 // gathers are coalesced and mostly L1/L2 hits (the stencil bands are re-read by neighbouring rows).
 constexpr int TMA_ROWS = 256;      // rows per tile = threads per CTA
 constexpr int TMA_STAGES = 4;
+constexpr int TMA_CONSUMER_WARPS = TMA_ROWS / 32;
+constexpr int TMA_THREADS = TMA_ROWS + 32;   // + one producer warp
 constexpr int TMA_CAP = 2304;      // nonzeros a stage can hold (avg 9 per row); larger tiles -> sub-warp kernel
 constexpr int TMA_STAGE_BYTES = TMA_CAP * 12;
 constexpr int TMA_SMEM_BYTES = TMA_STAGES * TMA_STAGE_BYTES;
@@ -123,6 +125,10 @@ __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned coun
 __device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes)
 {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
 {
@@ -161,56 +167,85 @@ __device__ __forceinline__ void tma_issue_tile(int tile, int n, const int *__res
 }
 
 template <int NDOT>
-__global__ void __launch_bounds__(TMA_ROWS) spmv_tma_kernel(int n, int ntiles, const int *__restrict__ rowptr,
+__global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int n, int ntiles, const int *__restrict__ rowptr,
                                                             const int *__restrict__ col, const double *__restrict__ val,
                                                             const double *__restrict__ x, double *__restrict__ y,
                                                             const double *__restrict__ w, double *partials,
                                                             unsigned *ticket, double *out)
 {
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ __align__(8) unsigned long long full[TMA_STAGES];
+    __shared__ __align__(8) unsigned long long full[TMA_STAGES], empty[TMA_STAGES];
     __shared__ int a0s[TMA_STAGES];
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
-        for (int s = 0; s < TMA_STAGES; s++) mbar_init(&full[s], 1u);
+        for (int s = 0; s < TMA_STAGES; s++) { mbar_init(&full[s], 1u); mbar_init(&empty[s], TMA_CONSUMER_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     const int my_tiles = (ntiles > (int)blockIdx.x) ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-    if (tid == 0) {
-        for (int i = 0; i < TMA_STAGES && i < my_tiles; i++)
-            tma_issue_tile(blockIdx.x + i * gridDim.x, n, rowptr, col, val, smem + i * TMA_STAGE_BYTES, &full[i], &a0s[i]);
-    }
     double acc[NDOT > 0 ? NDOT : 1] = {0.0};
-    for (int i = 0; i < my_tiles; i++) {
-        const int s = i % TMA_STAGES;
-        const unsigned parity = (unsigned)(i / TMA_STAGES) & 1u;
-        const int tile = blockIdx.x + i * gridDim.x;
-        const int r = tile * TMA_ROWS + tid;
-        int pb = 0, pe = 0;
-        if (r < n) { pb = rowptr[r]; pe = rowptr[r + 1]; }
-        mbar_wait(&full[s], parity);
-        const int a0 = a0s[s];
-        const double *sval = reinterpret_cast<const double *>(smem + s * TMA_STAGE_BYTES) - a0;
-        const int *scol = reinterpret_cast<const int *>(smem + s * TMA_STAGE_BYTES + TMA_CAP * 8) - a0;
-        if (r < n) {
-            double sum0 = 0.0, sum1 = 0.0;
-            int p = pb;
-            for (; p + 3 < pe; p += 4) {
-                const int c0 = scol[p], c1 = scol[p + 1], c2 = scol[p + 2], c3 = scol[p + 3];
-                const double x0 = __ldg(&x[c0]), x1 = __ldg(&x[c1]), x2 = __ldg(&x[c2]), x3 = __ldg(&x[c3]);
-                sum0 += sval[p] * x0; sum1 += sval[p + 1] * x1; sum0 += sval[p + 2] * x2; sum1 += sval[p + 3] * x3;
+    if (warp == TMA_CONSUMER_WARPS) {
+        // ---- producer warp: one lane keeps TMA_STAGES tiles in flight ----
+        if (lane == 0) {
+            for (int i = 0; i < my_tiles; i++) {
+                const int s = i % TMA_STAGES;
+                if (i >= TMA_STAGES) {
+                    mbar_wait(&empty[s], (unsigned)(i / TMA_STAGES - 1) & 1u);   // all consumer warps left stage s
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                }
+                tma_issue_tile(blockIdx.x + i * gridDim.x, n, rowptr, col, val, smem + s * TMA_STAGE_BYTES, &full[s], &a0s[s]);
             }
-            for (; p < pe; p++) sum0 += sval[p] * __ldg(&x[scol[p]]);
-            const double sum = sum0 + sum1;
-            y[r] = sum;
-            if (NDOT == 1) acc[0] += w[r] * sum;
-            if (NDOT == 2) { acc[0] += sum * w[r]; acc[1] += sum * sum; }
         }
-        __syncthreads();   // every consumer is done with stage s
-        if (tid == 0 && i + TMA_STAGES < my_tiles) {
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            tma_issue_tile(blockIdx.x + (i + TMA_STAGES) * gridDim.x, n, rowptr, col, val, smem + s * TMA_STAGE_BYTES, &full[s], &a0s[s]);
+    } else {
+        // ---- consumer warps: 32 rows of every tile each, no block-wide barrier ----
+        int r = (int)blockIdx.x * TMA_ROWS + tid;
+        int pb = 0, pe = 0;
+        if (my_tiles > 0 && r < n) { pb = rowptr[r]; pe = rowptr[r + 1]; }
+        for (int i = 0; i < my_tiles; i++) {
+            const int s = i % TMA_STAGES;
+            const unsigned parity = (unsigned)(i / TMA_STAGES) & 1u;
+            // row pointers of the next tile are fetched while this one is processed
+            const int rn = r + (int)gridDim.x * TMA_ROWS;
+            int pbn = 0, pen = 0;
+            if (i + 1 < my_tiles && rn < n) { pbn = rowptr[rn]; pen = rowptr[rn + 1]; }
+            mbar_wait(&full[s], parity);
+            const int a0 = a0s[s];
+            const double *sval = reinterpret_cast<const double *>(smem + s * TMA_STAGE_BYTES) - a0;
+            const int *scol = reinterpret_cast<const int *>(smem + s * TMA_STAGE_BYTES + TMA_CAP * 8) - a0;
+            // The row's (col, val) go from shared memory to registers first; the stage is handed back
+            // to the producer as soon as the whole warp holds its entries, BEFORE the x gathers, so a
+            // stage is busy for a TMA round trip plus a few shared-memory reads, not a gather latency.
+            // Eight predicated slots per trip issue all gathers of a 5..8-entry row back to back.
+            const int len = pe - pb;
+            const int wtrips = __reduce_max_sync(0xffffffffu, (len + 7) >> 3);
+            double sum = 0.0;
+            if (wtrips == 0) {
+                if (lane == 0) mbar_arrive(&empty[s]);
+            }
+            for (int tq = 0; tq < wtrips; tq++) {
+                const int p = pb + 8 * tq;
+                int c[8];
+                double v[8];
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const bool ok = p + q < pe;
+                    c[q] = ok ? scol[p + q] : -1;
+                    v[q] = ok ? sval[p + q] : 0.0;
+                }
+                if (tq == wtrips - 1) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&empty[s]);   // this warp no longer reads stage s
+                }
+#pragma unroll
+                for (int q = 0; q < 8; q++)
+                    if (c[q] >= 0) sum += v[q] * __ldg(&x[c[q]]);
+            }
+            if (r < n) {
+                y[r] = sum;
+                if (NDOT == 1) acc[0] += w[r] * sum;
+                if (NDOT == 2) { acc[0] += sum * w[r]; acc[1] += sum * sum; }
+            }
+            r = rn; pb = pbn; pe = pen;
         }
     }
     if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out);
@@ -230,7 +265,7 @@ template <int NDOT>
 static void spmv_run(const Krylov &k, cudaStream_t st, int sb, const double *x, double *y, const double *w, double *out)
 {
     if (k.tma_tiles > 0) {
-        spmv_tma_kernel<NDOT><<<k.tma_grid, TMA_ROWS, TMA_SMEM_BYTES, st>>>(k.n, k.tma_tiles, k.rowptr, k.col, k.val, x, y, w,
+        spmv_tma_kernel<NDOT><<<k.tma_grid, TMA_THREADS, TMA_SMEM_BYTES, st>>>(k.n, k.tma_tiles, k.rowptr, k.col, k.val, x, y, w,
                                                                             k.partials.p, k.ticket.p, out);
     } else {
         spmv_dispatch<NDOT>(st, k.lanes, sb, k.n, k.rowptr, k.col, k.val, x, y, w, k.partials.p, k.ticket.p, out);
@@ -340,7 +375,25 @@ __global__ void __launch_bounds__(256) update_p_kernel(int n, int nspec, int nce
             }
         }
     } else {
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        // 16-byte accesses: two unknowns per thread and trip (all vectors are 256-byte aligned)
+        const long long n2 = n >> 1;
+        const double2 *r2 = reinterpret_cast<const double2 *>(r), *v2 = reinterpret_cast<const double2 *>(v);
+        const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
+        double2 *p2 = reinterpret_cast<double2 *>(p), *ph2 = reinterpret_cast<double2 *>(ph);
+#pragma unroll 2
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
+            double2 pn = r2[i];
+            if (!first) {
+                const double2 po = p2[i], vo = v2[i];
+                pn.x += beta * (po.x - omega * vo.x);
+                pn.y += beta * (po.y - omega * vo.y);
+            }
+            p2[i] = pn;
+            if (PRE == 1) { const double2 d = d2[i]; pn.x *= d.x; pn.y *= d.y; }
+            ph2[i] = pn;
+        }
+        if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+            const long long i = n - 1;
             const double pn = first ? r[i] : r[i] + beta * (p[i] - omega * v[i]);
             p[i] = pn;
             ph[i] = (PRE == 1) ? dinv[i] * pn : pn;
@@ -374,7 +427,22 @@ __global__ void __launch_bounds__(256) update_s_kernel(int n, int nspec, int nce
             }
         }
     } else {
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const long long n2 = n >> 1;
+        const double2 *r2 = reinterpret_cast<const double2 *>(r), *v2 = reinterpret_cast<const double2 *>(v);
+        const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
+        double2 *s2 = reinterpret_cast<double2 *>(s_), *sh2 = reinterpret_cast<double2 *>(sh);
+#pragma unroll 2
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
+            const double2 ro = r2[i], vo = v2[i];
+            double2 sn;
+            sn.x = ro.x - alpha * vo.x;
+            sn.y = ro.y - alpha * vo.y;
+            s2[i] = sn;
+            if (PRE == 1) { const double2 d = d2[i]; sn.x *= d.x; sn.y *= d.y; }
+            sh2[i] = sn;
+        }
+        if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+            const long long i = n - 1;
             const double sn = r[i] - alpha * v[i];
             s_[i] = sn;
             sh[i] = (PRE == 1) ? dinv[i] * sn : sn;
@@ -399,7 +467,26 @@ __global__ void __launch_bounds__(256) update_xr_kernel(int n, double *scal, int
     if (bad) { alpha = 0.0; omega = 0.0; }
     if (blockIdx.x == 0 && threadIdx.x == 0) slot[S_BAD] = bad ? 1.0 : 0.0;
     double acc[2] = {0.0, 0.0};
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long n2 = n >> 1;
+    const double2 *ph2 = reinterpret_cast<const double2 *>(ph), *sh2 = reinterpret_cast<const double2 *>(sh);
+    const double2 *s2 = reinterpret_cast<const double2 *>(s_), *t2 = reinterpret_cast<const double2 *>(t);
+    const double2 *r02 = reinterpret_cast<const double2 *>(r0);
+    double2 *x2 = reinterpret_cast<double2 *>(x), *r2 = reinterpret_cast<double2 *>(r);
+#pragma unroll 2
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (long long)gridDim.x * blockDim.x) {
+        const double2 a = ph2[i], b = sh2[i], sv = s2[i], tv = t2[i], q = r02[i];
+        double2 xv = x2[i], rn;
+        xv.x += alpha * a.x + omega * b.x;
+        xv.y += alpha * a.y + omega * b.y;
+        x2[i] = xv;
+        rn.x = sv.x - omega * tv.x;
+        rn.y = sv.y - omega * tv.y;
+        r2[i] = rn;
+        acc[0] += rn.x * rn.x + rn.y * rn.y;
+        acc[1] += q.x * rn.x + q.y * rn.y;
+    }
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+        const long long i = n - 1;
         x[i] += alpha * ph[i] + omega * sh[i];
         const double rn = s_[i] - omega * t[i];
         r[i] = rn;
@@ -482,7 +569,7 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
                 int dev = 0, sms = 0, per_sm = 0;
                 RS_CUDA(cudaGetDevice(&dev));
                 RS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-                RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmv_tma_kernel<2>, TMA_ROWS, TMA_SMEM_BYTES));
+                RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmv_tma_kernel<2>, TMA_THREADS, TMA_SMEM_BYTES));
                 if (per_sm >= 1) {
                     k.tma_tiles = ntiles;
                     k.tma_grid = std::min(ntiles, sms * per_sm);

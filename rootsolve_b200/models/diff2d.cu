@@ -10,10 +10,11 @@ __device__ void diff2d(int *neq, double *t, double *y, double *ydot, double *you
     const int d1 = ip[4], d2 = ip[5], variant = ip[7];
     int j0 = 0, j1 = d1;
     if (RS_SLAB_J1(ip) >= 0) { j0 = RS_SLAB_J0(ip); j1 = RS_SLAB_J1(ip); }
-    const long long first = (long long)j0 * d2, count = (long long)(j1 - j0) * d2;
-    RS_FOR_EACH(q, count) {
-        const long long idx = first + q;
-        const int j = (int)(idx / d2), k = (int)(idx - (long long)j * d2);
+    const int first = j0 * d2, count = (j1 - j0) * d2;
+    const int nthreads = (int)RS_THREAD_COUNT;
+    for (int q = (int)RS_THREAD_ID; q < count; q += nthreads) {
+        const int idx = first + q;
+        const int j = idx / d2, k = idx - j * d2;
         ydot[idx] = rsm_diff2d_point(y, j, k, d1, d2, parms, variant);
     }
 }

@@ -11,12 +11,14 @@ __device__ void diff3d(int *neq, double *t, double *y, double *ydot, double *you
     const int d1 = ip[4], d2 = ip[5], d3 = ip[6], variant = ip[7];
     int j0 = 0, j1 = d1;
     if (RS_SLAB_J1(ip) >= 0) { j0 = RS_SLAB_J0(ip); j1 = RS_SLAB_J1(ip); }
-    const long long plane = (long long)d2 * d3;
-    const long long first = j0 * plane, count = (j1 - j0) * plane;
-    RS_FOR_EACH(q, count) {
-        const long long idx = first + q;
-        const int j = (int)(idx / plane);
-        const int rem = (int)(idx - j * plane);
+    // 32-bit index arithmetic: neq < 2^31, and 64-bit divisions would dominate this kernel
+    const int plane = d2 * d3;
+    const int first = j0 * plane, count = (j1 - j0) * plane;
+    const int nthreads = (int)RS_THREAD_COUNT;
+    for (int q = (int)RS_THREAD_ID; q < count; q += nthreads) {
+        const int idx = first + q;
+        const int j = idx / plane;
+        const int rem = idx - j * plane;
         const int k = rem / d3, l = rem - k * d3;
         ydot[idx] = rsm_diff3d_point(y, j, k, l, d1, d2, d3, parms, variant);
     }
