@@ -26,7 +26,7 @@ LIB_MODELS = os.path.join(HERE, "librs_models.so")
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ARCH + ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets",
-                 "-I", INCLUDE, "-I", CSRC, "-I", MODELS]
+                 "-I", INCLUDE, "-I", CSRC, "-I", MODELS] + os.environ.get("RS_NVCC_DEFS", "").split()
 # Translation units whose floating-point results are compared bit-for-bit with the
 # oracle (residuals, FD quotients, error weights) must not contract a*b+c into FMA.
 NO_FMA = {"fdjac.cu", "api.cu"}

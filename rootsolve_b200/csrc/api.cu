@@ -398,7 +398,10 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
         RS_TRY(krylov_precond_update(c, s.kry));
         int kit = 0;
         double relres = 0.0;
-        RS_TRY(krylov_solve(c, s.kry, s.beta.p, s.x.p, s.kry.lin_ewt_factor * s.min_atol, &kit, &relres));
+        // Absolute floor of the linear residual: once its RMS is a small fraction of the smallest error
+        // weight, the next residual test (max |f/ewt| <= 1) passes and further Krylov work is wasted.
+        RS_TRY(krylov_solve(c, s.kry, s.beta.p, s.x.p, s.kry.lin_ewt_factor * s.min_atol * std::sqrt((double)n), &kit,
+                            &relres));
         s.krylov_iters += kit;
         if (s.verbose) fprintf(stderr, "[rootsolve_b200] newton %d: mean|f|=%.6e  krylov its=%d relres=%.3e\n", it, s.precis[it - 1], kit, relres);
         {

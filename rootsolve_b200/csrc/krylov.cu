@@ -109,11 +109,25 @@ int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const
 // of the consumers; the matrix never passes through the LSU/L1 path.  Consumers are one thread per
 // row: with ascending columns the k-th entry of consecutive rows addresses consecutive x, so the x
 // gathers are coalesced and mostly L1/L2 hits (the stencil bands are re-read by neighbouring rows).
-constexpr int TMA_ROWS = 256;      // rows per tile = threads per CTA
-constexpr int TMA_STAGES = 4;
+// Tile shape from a sweep on B200 at 256^3 (scratch/tune_spmv.sh; ms per SpMV launch):
+//   rows x stages: 256x4 0.384, 256x3 0.386, 128x4 0.384, 128x6 0.680, 256x6 0.682, 128x8 0.680, 512x2 0.282.
+// What matters is consumer warps per SM (the x gathers are latency bound): 512 rows x 2 stages is
+// 110 KB per CTA, so two CTAs = 32 consumer warps fit an SM; deeper pipelines that leave room for
+// only one CTA lose.
+#ifndef RS_TMA_ROWS
+#define RS_TMA_ROWS 512
+#endif
+#ifndef RS_TMA_STAGES
+#define RS_TMA_STAGES 2
+#endif
+#ifndef RS_TMA_CAP
+#define RS_TMA_CAP (RS_TMA_ROWS * 9)
+#endif
+constexpr int TMA_ROWS = RS_TMA_ROWS;      // rows per tile = consumer threads per CTA
+constexpr int TMA_STAGES = RS_TMA_STAGES;
 constexpr int TMA_CONSUMER_WARPS = TMA_ROWS / 32;
 constexpr int TMA_THREADS = TMA_ROWS + 32;   // + one producer warp
-constexpr int TMA_CAP = 2304;      // nonzeros a stage can hold (avg 9 per row); larger tiles -> sub-warp kernel
+constexpr int TMA_CAP = RS_TMA_CAP;      // nonzeros a stage can hold (avg 9 per row); larger tiles -> sub-warp kernel
 constexpr int TMA_STAGE_BYTES = TMA_CAP * 12;
 constexpr int TMA_SMEM_BYTES = TMA_STAGES * TMA_STAGE_BYTES;
 

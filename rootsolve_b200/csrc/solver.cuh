@@ -61,7 +61,7 @@ struct Krylov {
     int lanes = 8;             // lanes per row of the sub-warp SpMV
     int tma_tiles = 0, tma_grid = 0;  // > 0: the TMA-staged SpMV is used (every tile fits a stage)
     int max_iter = 10000, check_every = 1;
-    double lin_rtol = 1e-10, lin_ewt_factor = 0.05;
+    double lin_rtol = 1e-10, lin_ewt_factor = 5e-4;
     ~Krylov();
 };
 int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int *col, const double *val,
