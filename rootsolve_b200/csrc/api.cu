@@ -98,34 +98,37 @@ __device__ __forceinline__ double ewt_of(int itol, const double *__restrict__ rt
     return rt * fabs(yi) + at;
 }
 
-__global__ void errset_kernel(int n, int itol, const double *__restrict__ rtol, const double *__restrict__ atol,
+// All Newton kernels work on an index range [b, e) of global-index vectors (one range on a single GPU,
+// one per species of the slab when sharded); `accumulate` chains the reductions of several ranges.
+__global__ void errset_kernel(int b, int e, int itol, const double *__restrict__ rtol, const double *__restrict__ atol,
                               const double *__restrict__ y, double *__restrict__ ewt)
 {
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x)
         ewt[i] = ewt_of(itol, rtol, atol, i, y[i]);
 }
 
 // test 1 (src/sparse.f:122-133): out = { sum |beta|, max |beta/ewt| }
-__global__ void __launch_bounds__(256) test1_kernel(int n, const double *__restrict__ beta, const double *__restrict__ ewt,
-                                                    double *partials, unsigned *ticket, double *out)
+__global__ void __launch_bounds__(256) test1_kernel(int b, int e, const double *__restrict__ beta,
+                                                    const double *__restrict__ ewt, double *partials, unsigned *ticket,
+                                                    double *out, int accumulate)
 {
     double acc[2] = {0.0, 0.0};
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const double b = beta[i];
-        acc[0] += fabs(b);
-        acc[1] = fmax(acc[1], fabs(b / ewt[i]));
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
+        const double bi = beta[i];
+        acc[0] += fabs(bi);
+        acc[1] = fmax(acc[1], fabs(bi / ewt[i]));
     }
-    grid_reduce<2>(acc, 2u, partials, ticket, out);
+    grid_reduce<2>(acc, 2u, partials, ticket, out, accumulate != 0);
 }
 
 // update (src/sparse.f:152-163, 185): out = { max |x| } ; y += x ; clamp ; ewt(y)
-__global__ void __launch_bounds__(256) update_kernel(int n, int positivity, int itol, const double *__restrict__ rtol,
+__global__ void __launch_bounds__(256) update_kernel(int b, int e, int positivity, int itol, const double *__restrict__ rtol,
                                                      const double *__restrict__ atol, const double *__restrict__ x,
                                                      double *__restrict__ y, double *__restrict__ ewt, double *partials,
-                                                     unsigned *ticket, double *out)
+                                                     unsigned *ticket, double *out, int accumulate)
 {
     double acc[1] = {0.0};
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
         const double xi = x[i];
         acc[0] = fmax(acc[0], fabs(xi));
         double yn = y[i] + xi;
@@ -133,29 +136,31 @@ __global__ void __launch_bounds__(256) update_kernel(int n, int positivity, int 
         y[i] = yn;
         ewt[i] = ewt_of(itol, rtol, atol, i, yn);
     }
-    grid_reduce<1>(acc, 1u, partials, ticket, out);
+    grid_reduce<1>(acc, 1u, partials, ticket, out, accumulate != 0);
 }
 
-// index-vector form of `positive` (src/sparse.f:159-163)
-__global__ void clamp_indices_kernel(int npos, const int *__restrict__ pos, int itol, const double *__restrict__ rtol,
-                                     const double *__restrict__ atol, double *__restrict__ y, double *__restrict__ ewt)
+// index-vector form of `positive` (src/sparse.f:159-163); only indices inside [b, e) are touched
+__global__ void clamp_indices_kernel(int b, int e, int npos, const int *__restrict__ pos, int itol,
+                                     const double *__restrict__ rtol, const double *__restrict__ atol,
+                                     double *__restrict__ y, double *__restrict__ ewt)
 {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= npos) return;
     const int i = pos[q] - 1;
+    if (i < b || i >= e) return;
     const double yn = fmax(0.0, y[i]);
     y[i] = yn;
     ewt[i] = ewt_of(itol, rtol, atol, i, yn);
 }
 
 // test 2's extra evaluation (src/sparse.f:165-183): out = { sum |f| }
-__global__ void __launch_bounds__(256) sumabs_kernel(int n, const double *__restrict__ f, double *partials,
-                                                     unsigned *ticket, double *out)
+__global__ void __launch_bounds__(256) sumabs_kernel(int b, int e, const double *__restrict__ f, double *partials,
+                                                     unsigned *ticket, double *out, int accumulate)
 {
     double acc[1] = {0.0};
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x)
         acc[0] += fabs(f[i]);
-    grid_reduce<1>(acc, 0u, partials, ticket, out);
+    grid_reduce<1>(acc, 0u, partials, ticket, out, accumulate != 0);
 }
 
 }  // namespace rs
@@ -179,6 +184,9 @@ struct rs_solver {
     double *h_red = nullptr;
     FdWork fd;
     Krylov kry;
+    Ranges own, touch;          // rows this rank solves for / unknowns it reads (own + halo planes)
+    HaloPlan halo;
+    int slab_j0 = 0, slab_j1 = -1, plane = 0;   // slab of the slowest grid index (j1 < 0: not sharded)
     bool structure_only = false;
     std::vector<double> precis;
     int niter = 0, steady = 0, krylov_iters = 0;
@@ -317,9 +325,31 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         RS_TRY(s.ticket.alloc(4));
         RS_TRY(s.ticket.zero(c.stream));
         RS_CUDA(cudaMallocHost((void **)&s.h_red, 8 * sizeof(double)));
-        RS_TRY(fd_setup(c, s.fd, n, s.ngp, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, 0, -1));
+        // who owns what: one range [0, n) on a single GPU; planes [j0, j1) of every species when sharded
+        s.own.n = 1; s.own.b[0] = 0; s.own.e[0] = n;
+        s.touch = s.own;
+        if (comm_active()) {
+            const GridDesc &g = s.grid;
+            const int nr = comm_nranks(), rk = comm_rank();
+            if (!g.type) { set_error("a sharded solve needs a grid sparsity type (1D/2D/3D)"); return RS_EINVAL; }
+            if (g.cyc[0]) { set_error("a cyclic boundary in the sharded (slowest) dimension is not supported"); return RS_EINVAL; }
+            if (nr > g.d[0]) { set_error("more ranks (%d) than planes (%d) in the sharded dimension", nr, g.d[0]); return RS_EINVAL; }
+            if (g.nspec > MAXR) { set_error("more than %d species in a sharded solve", MAXR); return RS_ETOOBIG; }
+            s.plane = g.ncell / g.d[0];
+            rs_slab_bounds(g.d[0], nr, rk, &s.slab_j0, &s.slab_j1);
+            const int jl = std::max(s.slab_j0 - 1, 0), jh = std::min(s.slab_j1 + 1, g.d[0]);
+            s.own.n = s.touch.n = g.nspec;
+            for (int q = 0; q < g.nspec; q++) {
+                s.own.b[q] = q * g.ncell + s.slab_j0 * s.plane;   s.own.e[q] = q * g.ncell + s.slab_j1 * s.plane;
+                s.touch.b[q] = q * g.ncell + jl * s.plane;        s.touch.e[q] = q * g.ncell + jh * s.plane;
+            }
+            s.halo.nspec = g.nspec; s.halo.ncell = g.ncell; s.halo.plane = s.plane;
+            s.halo.j0 = s.slab_j0; s.halo.j1 = s.slab_j1;
+            s.halo.has_lo = rk > 0; s.halo.has_hi = rk < nr - 1;
+        }
+        RS_TRY(fd_setup(c, s.fd, n, s.ngp, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, s.slab_j0, s.slab_j1));
         RS_TRY(krylov_setup(c, s.kry, n, s.nnz, s.rowptr.p, s.col.p, s.val.p, s.ctl.precond, s.grid.type ? s.grid.nspec : 1,
-                            s.grid.type ? s.grid.ncell : n, &s.ctl));
+                            s.grid.type ? s.grid.ncell : n, &s.ctl, &s.own, comm_active() ? &s.halo : nullptr));
         RS_TRY(s.y.upload(a->y, n, c.stream));
     } else {
         RS_TRY(s.y.alloc(n));
@@ -350,6 +380,8 @@ extern "C" double *rs_solver_state_device(rs_solver *s) { return s ? s->y.p : nu
 extern "C" int rs_solver_get_state(rs_solver *s, double *y_host)
 {
     if (!s || !y_host) return RS_EINVAL;
+    if (comm_active() && !s->structure_only)
+        RS_TRY(comm_gather_slabs(s->ctx, s->y.p, s->grid.nspec, s->grid.ncell, s->plane, s->grid.d[0]));
     RS_TRY(s->y.download(y_host, s->n, s->ctx.stream));
     RS_CUDA(cudaStreamSynchronize(s->ctx.stream));
     return RS_OK;
@@ -369,7 +401,9 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
     rs_solver &s = *sp;
     Ctx &c = s.ctx;
     if (s.structure_only) { s.niter = 1; s.steady = 0; s.precis.assign(1, 0.0); return RS_OK; }
-    const int n = s.n, vb = grid_for(n, 256, 148 * 8);
+    const int n = s.n;
+    const Ranges &own = s.own;
+    const double rows = (double)own.total();
     cudaStream_t st = c.stream;
     cudaEvent_t e0, e1;
     RS_CUDA(cudaEventCreate(&e0));
@@ -379,17 +413,23 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
     s.niter = 0; s.steady = 0; s.krylov_iters = 0;
     const long long launches0 = c.launches;
     {
-        Launch L(c, K_NEWTON, 16.0 * n);
-        errset_kernel<<<vb, 256, 0, st>>>(n, s.itol, s.rtol.p, s.atol.p, s.y.p, s.ewt.p);
+        Launch L(c, K_NEWTON, 16.0 * rows);
+        for (int q = 0; q < own.n; q++)
+            errset_kernel<<<grid_for(own.e[q] - own.b[q], 256), 256, 0, st>>>(own.b[q], own.e[q], s.itol, s.rtol.p, s.atol.p, s.y.p, s.ewt.p);
     }
     for (int it = 1; it <= s.maxiter; it++) {
         s.niter = it;
+        RS_TRY(comm_halo_exchange(c, s.y.p, s.halo));   // the residual reads one plane beyond the slab
         RS_TRY(fd_jacobian(c, s.model, s.fd, n, s.nnz, s.ngp, s.time, s.y.p, s.group_of.p, s.rowptr.p, s.col.p, s.val.p,
-                           s.beta.p, n, 0, n));
+                           s.beta.p, own, s.touch));
         {
-            Launch L(c, K_NEWTON, 16.0 * n);
-            test1_kernel<<<vb, 256, 0, st>>>(n, s.beta.p, s.ewt.p, s.partials.p, s.ticket.p, s.red.p);
+            Launch L(c, K_NEWTON, 16.0 * rows);
+            for (int q = 0; q < own.n; q++)
+                test1_kernel<<<grid_for(own.e[q] - own.b[q], 256), 256, 0, st>>>(own.b[q], own.e[q], s.beta.p, s.ewt.p, s.partials.p,
+                                                                                 s.ticket.p, s.red.p, q > 0);
         }
+        RS_TRY(comm_allreduce_sum(c, s.red.p, 1));
+        RS_TRY(comm_allreduce_max(c, s.red.p + 1, 1));
         RS_TRY(read_red(s, 2));
         s.precis[it - 1] = s.h_red[0] / n;
         if (!(s.h_red[0] == s.h_red[0])) { set_error("model returned NaN in the rate of change"); return RS_ESINGULAR; }
@@ -403,25 +443,35 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
         RS_TRY(krylov_solve(c, s.kry, s.beta.p, s.x.p, s.kry.lin_ewt_factor * s.min_atol * std::sqrt((double)n), &kit,
                             &relres));
         s.krylov_iters += kit;
-        if (s.verbose) fprintf(stderr, "[rootsolve_b200] newton %d: mean|f|=%.6e  krylov its=%d relres=%.3e\n", it, s.precis[it - 1], kit, relres);
+        if (s.verbose && comm_rank() == 0)
+            fprintf(stderr, "[rootsolve_b200] newton %d: mean|f|=%.6e  krylov its=%d relres=%.3e\n", it, s.precis[it - 1], kit, relres);
         {
-            Launch L(c, K_NEWTON, 48.0 * n);
-            update_kernel<<<vb, 256, 0, st>>>(n, s.Pos > 0 ? 1 : 0, s.itol, s.rtol.p, s.atol.p, s.x.p, s.y.p, s.ewt.p,
-                                              s.partials.p, s.ticket.p, s.red.p);
+            Launch L(c, K_NEWTON, 48.0 * rows);
+            for (int q = 0; q < own.n; q++)
+                update_kernel<<<grid_for(own.e[q] - own.b[q], 256), 256, 0, st>>>(own.b[q], own.e[q], s.Pos > 0 ? 1 : 0, s.itol, s.rtol.p,
+                                                                                  s.atol.p, s.x.p, s.y.p, s.ewt.p, s.partials.p,
+                                                                                  s.ticket.p, s.red.p, q > 0);
         }
         if (s.Pos <= 0 && s.npos > 1) {
             Launch L(c, K_NEWTON, 28.0 * s.npos);
-            clamp_indices_kernel<<<(s.npos + 255) / 256, 256, 0, st>>>(s.npos, s.pos.p, s.itol, s.rtol.p, s.atol.p, s.y.p, s.ewt.p);
+            for (int q = 0; q < own.n; q++)
+                clamp_indices_kernel<<<(s.npos + 255) / 256, 256, 0, st>>>(own.b[q], own.e[q], s.npos, s.pos.p, s.itol, s.rtol.p,
+                                                                           s.atol.p, s.y.p, s.ewt.p);
         }
+        RS_TRY(comm_allreduce_max(c, s.red.p, 1));
         RS_TRY(read_red(s, 1));
         const double relchange = s.h_red[0];
         if (relchange <= s.ctol) {
             if (it < s.maxiter) {
-                RS_TRY(residual_only(c, s.model, s.fd, n, s.time, s.y.p, s.ftmp.p, n));
+                RS_TRY(comm_halo_exchange(c, s.y.p, s.halo));
+                RS_TRY(residual_only(c, s.model, s.fd, n, s.time, s.y.p, s.ftmp.p, own.total()));
                 {
-                    Launch L(c, K_NEWTON, 8.0 * n);
-                    sumabs_kernel<<<vb, 256, 0, st>>>(n, s.ftmp.p, s.partials.p, s.ticket.p, s.red.p);
+                    Launch L(c, K_NEWTON, 8.0 * rows);
+                    for (int q = 0; q < own.n; q++)
+                        sumabs_kernel<<<grid_for(own.e[q] - own.b[q], 256), 256, 0, st>>>(own.b[q], own.e[q], s.ftmp.p, s.partials.p,
+                                                                                          s.ticket.p, s.red.p, q > 0);
                 }
+                RS_TRY(comm_allreduce_sum(c, s.red.p, 1));
                 RS_TRY(read_red(s, 1));
                 s.precis[it] = s.h_red[0];  // a sum, not a mean: src/sparse.f:177
                 s.niter = it + 1;
@@ -484,9 +534,11 @@ static int pack_result(rs_solver &s, const rs_stsparse_args *a, rs_stsparse_resu
     Ctx &c = s.ctx;
     const int n = s.n;
     if (r->y) {
+        if (comm_active() && !s.structure_only)   // every rank returns the whole state, as the R call does
+            RS_TRY(comm_gather_slabs(c, s.y.p, s.grid.nspec, s.grid.ncell, s.plane, s.grid.d[0]));
         RS_TRY(s.y.download(r->y, n, c.stream));
         if (a->nout > 0 && !s.structure_only) {  // one more derivs call for the outputs, src/call_stsparse.c:281-286
-            RS_TRY(residual_only(c, s.model, s.fd, n, s.time, s.y.p, s.ftmp.p, n));
+            RS_TRY(residual_only(c, s.model, s.fd, n, s.time, s.y.p, s.ftmp.p, s.own.total()));
             RS_CUDA(cudaMemcpyAsync(r->y + n, s.fd.yout.p, sizeof(double) * a->nout, cudaMemcpyDeviceToHost, c.stream));
         }
     }
@@ -612,7 +664,9 @@ extern "C" int rs_fd_jacobian(const rs_model_desc *func, const double *initpar, 
     RS_TRY(build_csr_pattern(c, neq, nnz, d_ian.p, d_jan.p, rowptr, col));
     FdWork w;
     RS_TRY(fd_setup(c, w, neq, ngp, 0, rpar, nrpar, ipar, nipar, 0, -1));
-    RS_TRY(fd_jacobian(c, func, w, neq, nnz, ngp, time, d_y.p, group_of.p, rowptr.p, col.p, d_val.p, d_beta.p, neq, 0, neq));
+    Ranges all;
+    all.n = 1; all.b[0] = 0; all.e[0] = neq;
+    RS_TRY(fd_jacobian(c, func, w, neq, nnz, ngp, time, d_y.p, group_of.p, rowptr.p, col.p, d_val.p, d_beta.p, all, all));
     RS_TRY(gather_csc_values(c, neq, nnz, d_ian.p, d_jan.p, rowptr.p, col.p, d_val.p, d_a.p));
     if (beta) RS_TRY(d_beta.download(beta, neq, c.stream));
     if (a) RS_TRY(d_a.download(a, (size_t)nnz, c.stream));
@@ -718,7 +772,7 @@ extern "C" int rs_linsolve(int neq, const int *ian, const int *jan, const double
     Krylov k;
     const int nspec = nspec_block > 1 ? nspec_block : 1;
     RS_TRY(krylov_setup(c, k, neq, nnz, rowptr.p, col.p, val.p, control ? control->precond : RS_PRECOND_AUTO, nspec,
-                        nspec > 1 ? neq / nspec : neq, control));
+                        nspec > 1 ? neq / nspec : neq, control, nullptr, nullptr));
     RS_TRY(krylov_precond_update(c, k));
     int it = 0;
     double rr = 0.0;
@@ -739,7 +793,7 @@ extern "C" int rs_errset(int neq, int itol, const double *rtol, const double *at
     DevBuf<double> d_r, d_a, d_y, d_e;
     RS_TRY(d_r.alloc(nr)); RS_TRY(d_a.alloc(na)); RS_TRY(d_y.alloc(neq)); RS_TRY(d_e.alloc(neq));
     RS_TRY(d_r.upload(rtol, nr, c.stream)); RS_TRY(d_a.upload(atol, na, c.stream)); RS_TRY(d_y.upload(y, neq, c.stream));
-    errset_kernel<<<grid_for(neq, 256), 256, 0, c.stream>>>(neq, itol, d_r.p, d_a.p, d_y.p, d_e.p);
+    errset_kernel<<<grid_for(neq, 256), 256, 0, c.stream>>>(0, neq, itol, d_r.p, d_a.p, d_y.p, d_e.p);
     RS_TRY(d_e.download(ewt, neq, c.stream));
     RS_CUDA(cudaStreamSynchronize(c.stream));
     return RS_OK;
@@ -755,7 +809,7 @@ extern "C" int rs_convergence_test(int neq, const double *beta, const double *ew
     RS_TRY(d_b.alloc(neq)); RS_TRY(d_e.alloc(neq)); RS_TRY(partials.alloc(2 * 148 * 8)); RS_TRY(red.alloc(2)); RS_TRY(ticket.alloc(1));
     RS_TRY(d_b.upload(beta, neq, c.stream)); RS_TRY(d_e.upload(ewt, neq, c.stream));
     RS_TRY(ticket.zero(c.stream));
-    test1_kernel<<<grid_for(neq, 256, 148 * 8), 256, 0, c.stream>>>(neq, d_b.p, d_e.p, partials.p, ticket.p, red.p);
+    test1_kernel<<<grid_for(neq, 256, 148 * 8), 256, 0, c.stream>>>(0, neq, d_b.p, d_e.p, partials.p, ticket.p, red.p, 0);
     RS_CUDA(cudaGetLastError());
     RS_TRY(red.download(out2, 2, c.stream));
     RS_CUDA(cudaStreamSynchronize(c.stream));

@@ -25,12 +25,12 @@ __device__ __forceinline__ double perturbed(double v)
     return v + d;
 }
 
-// Y[0] = y ; Y[g+1][i] = y[i] (+delta_i when column i belongs to group g), rows [r0,r1) only... all rows here.
-__global__ void __launch_bounds__(256) perturb_kernel(int n, int ngp, const double *__restrict__ y,
+// Y[0] = y ; Y[g+1][i] = y[i] (+delta_i when column i belongs to group g), for i in [b, e)
+__global__ void __launch_bounds__(256) perturb_kernel(int b, int e, int ngp, const double *__restrict__ y,
                                                       const int *__restrict__ group_of, double *__restrict__ Y,
                                                       long long ld)
 {
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
         const double v = y[i];
         const double vp = perturbed(v);
         const int g = group_of[i];
@@ -92,11 +92,16 @@ int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, in
 
 int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
                 const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
-                long long work, int row0, int row1)
+                const Ranges &own, const Ranges &touch)
 {
+    const long long work = own.total();
+    const double frac = (double)work / (double)n;
     {
-        Launch L(c, K_PERTURB, 12.0 * n + 8.0 * n * (ngp + 1));
-        perturb_kernel<<<grid_for(n, 256), 256, 0, c.stream>>>(n, ngp, d_y, d_group_of, w.Y.p, w.ld);
+        const double nt = (double)touch.total();
+        Launch L(c, K_PERTURB, 12.0 * nt + 8.0 * nt * (ngp + 1));
+        for (int q = 0; q < touch.n; q++)
+            perturb_kernel<<<grid_for(touch.e[q] - touch.b[q], 256), 256, 0, c.stream>>>(touch.b[q], touch.e[q], ngp, d_y, d_group_of,
+                                                                                       w.Y.p, w.ld);
     }
     {
         Launch L(c, K_RESIDUAL, 16.0 * work * (ngp + 1));
@@ -104,10 +109,12 @@ int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int n
         if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
     }
     {
-        const long long rows = row1 - row0;
-        Launch L(c, K_ASSEMBLE, 20.0 * nnz + 20.0 * n);
-        assemble_kernel<8><<<grid_for(rows * 8, 256, 148 * 16), 256, 0, c.stream>>>(row0, row1, d_rowptr, d_col, d_group_of,
-                                                                                  d_y, w.F.p, w.ld, d_val, d_beta);
+        Launch L(c, K_ASSEMBLE, (20.0 * nnz + 20.0 * n) * frac);
+        for (int q = 0; q < own.n; q++) {
+            const long long rows = own.e[q] - own.b[q];
+            assemble_kernel<8><<<grid_for(rows * 8, 256, 148 * 16), 256, 0, c.stream>>>(own.b[q], own.e[q], d_rowptr, d_col,
+                                                                                      d_group_of, d_y, w.F.p, w.ld, d_val, d_beta);
+        }
     }
     RS_CUDA(cudaGetLastError());
     return RS_OK;

@@ -4,10 +4,11 @@
 // matrix symbolically and numerically on every Newton iteration.
 //
 // Kernels (all FP64, all bandwidth bound; algorithmic bytes in DESIGN.md):
-//   K_SPMV   y = A x, LANES threads per row, shuffle reduction inside the
-//            sub-warp, with the dot products that follow the product in
-//            BiCGStab fused into the same pass (block reduce -> per-block
-//            partials -> last block folds them in fixed order);
+//   K_SPMV   y = A x with the dot products that follow the product in BiCGStab fused
+//            into the same pass.  Main variant: persistent CTAs, the matrix streamed
+//            into shared memory by TMA bulk copies (one producer warp, mbarrier
+//            pipeline), one consumer thread per row.  Fallback for matrices whose
+//            tiles do not fit a stage: LANES threads per row + shuffle reduction.
 //   K_VEC    the three fused vector updates of one BiCGStab step (direction,
 //            intermediate residual, solution + residual), each also applying
 //            the (block-)Jacobi preconditioner and producing its dots;
@@ -15,8 +16,13 @@
 // Every scalar of the recurrence (rho, alpha, omega, beta) stays on the device:
 // kernels recompute them from the raw dot products in `scal`, so one step is
 // five launches and the host only reads ||r||^2 to decide when to stop.
-#include <cmath>
+//
+// Multi-GPU: a rank works on its own index ranges (Ranges, one per species of its
+// slab) of global-index vectors; every kernel takes [b, e) and a reduction that
+// spans several ranges accumulates into the same slot (stream order).  The SpMV
+// input gets its halo planes by ncclSend/Recv first; dots go through ncclAllReduce.
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 
@@ -25,7 +31,7 @@
 namespace rs {
 
 constexpr int MAXS = 8;        // largest species count handled by the block preconditioner
-constexpr int SLOT = 8;        // doubles per parity slot: r0v, ts, tt, rr, rhonext
+constexpr int SLOT = 8;        // doubles per parity slot: r0v, ts, tt, rr, rhonext, bad
 constexpr int S_R0V = 0, S_TS = 1, S_TT = 2, S_RR = 3, S_RHONEXT = 4, S_BAD = 5;
 constexpr int S_BNORM = 2 * SLOT, S_RTRUE = 2 * SLOT + 1;
 constexpr int NSCAL = 2 * SLOT + 8;
@@ -44,60 +50,63 @@ int pick_lanes(int n, int nnz)
     return 32;
 }
 
-// ---- SpMV ------------------------------------------------------------------------
+// ---- SpMV, sub-warp variant --------------------------------------------------------
 // NDOT = 0: plain product.  NDOT = 1: out[0] = <w, y>.  NDOT = 2: out[0] = <y, w>, out[1] = <y, y>.
 template <int LANES, int NDOT>
-__global__ void __launch_bounds__(256) spmv_kernel(int n, const int *__restrict__ rowptr, const int *__restrict__ col,
-                                                   const double *__restrict__ val, const double *__restrict__ x,
-                                                   double *__restrict__ y, const double *__restrict__ w,
-                                                   double *partials, unsigned *ticket, double *out)
+__global__ void __launch_bounds__(256) spmv_kernel(int row0, int row1, const int *__restrict__ rowptr,
+                                                   const int *__restrict__ col, const double *__restrict__ val,
+                                                   const double *__restrict__ x, double *__restrict__ y,
+                                                   const double *__restrict__ w, double *partials, unsigned *ticket,
+                                                   double *out, int accumulate)
 {
     const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x % LANES;
     const long long stride = ((long long)gridDim.x * blockDim.x) / LANES;
+    const long long n = row1 - row0;
     double acc[NDOT > 0 ? NDOT : 1] = {0.0};
     // every thread runs the same number of trips so the shuffles stay converged
     const long long trips = (n + stride - 1) / stride;
-    long long r = gt / LANES;
-    for (long long it = 0; it < trips; it++, r += stride) {
+    long long q = gt / LANES;
+    for (long long it = 0; it < trips; it++, q += stride) {
         double sum = 0.0;
-        if (r < n) {
+        const long long r = row0 + q;
+        if (q < n) {
             const int e = rowptr[r + 1];
             for (int p = rowptr[r] + lane; p < e; p += LANES) sum += val[p] * __ldg(&x[col[p]]);
         }
 #pragma unroll
         for (int o = LANES / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        if (r < n && lane == 0) {
+        if (q < n && lane == 0) {
             y[r] = sum;
             if (NDOT == 1) acc[0] += w[r] * sum;
             if (NDOT == 2) { acc[0] += sum * w[r]; acc[1] += sum * sum; }
         }
     }
-    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out);
+    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out, accumulate != 0);
 }
 
 template <int NDOT>
-static void spmv_dispatch(cudaStream_t st, int lanes, int blocks, int n, const int *rowptr, const int *col,
+static void spmv_dispatch(cudaStream_t st, int lanes, int row0, int row1, const int *rowptr, const int *col,
                           const double *val, const double *x, double *y, const double *w, double *partials,
-                          unsigned *ticket, double *out)
+                          unsigned *ticket, double *out, int accumulate)
 {
+    const int blocks = grid_for((long long)(row1 - row0) * lanes, 256, 148 * 8);
     switch (lanes) {
-    case 4: spmv_kernel<4, NDOT><<<blocks, 256, 0, st>>>(n, rowptr, col, val, x, y, w, partials, ticket, out); break;
-    case 8: spmv_kernel<8, NDOT><<<blocks, 256, 0, st>>>(n, rowptr, col, val, x, y, w, partials, ticket, out); break;
-    case 16: spmv_kernel<16, NDOT><<<blocks, 256, 0, st>>>(n, rowptr, col, val, x, y, w, partials, ticket, out); break;
-    default: spmv_kernel<32, NDOT><<<blocks, 256, 0, st>>>(n, rowptr, col, val, x, y, w, partials, ticket, out); break;
+    case 4: spmv_kernel<4, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate); break;
+    case 8: spmv_kernel<8, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate); break;
+    case 16: spmv_kernel<16, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate); break;
+    default: spmv_kernel<32, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate); break;
     }
 }
 
-static inline double spmv_bytes(int n, int nnz) { return 12.0 * nnz + 4.0 * (n + 1) + 16.0 * n; }
-
-static inline int spmv_blocks(int n, int lanes) { return grid_for((long long)n * lanes, 256, 148 * 8); }
+// algorithmic bytes of one product over `rows` rows holding `nz` nonzeros
+static inline double spmv_bytes(double rows, double nz) { return 12.0 * nz + 4.0 * (rows + 1) + 16.0 * rows; }
 
 int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const double *val, const double *x,
                 double *y, int lanes)
 {
     Launch L(c, K_SPMV, spmv_bytes(n, nnz));
-    spmv_dispatch<0>(c.stream, lanes, spmv_blocks(n, lanes), n, rowptr, col, val, x, y, nullptr, nullptr, nullptr, nullptr);
+    spmv_dispatch<0>(c.stream, lanes, 0, n, rowptr, col, val, x, y, nullptr, nullptr, nullptr, nullptr, 0);
     RS_CUDA(cudaGetLastError());
     return RS_OK;
 }
@@ -109,6 +118,7 @@ int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const
 // of the consumers; the matrix never passes through the LSU/L1 path.  Consumers are one thread per
 // row: with ascending columns the k-th entry of consecutive rows addresses consecutive x, so the x
 // gathers are coalesced and mostly L1/L2 hits (the stencil bands are re-read by neighbouring rows).
+//
 // Tile shape from a sweep on B200 at 256^3 (scratch/tune_spmv.sh; ms per SpMV launch):
 //   rows x stages: 256x4 0.384, 256x3 0.386, 128x4 0.384, 128x6 0.680, 256x6 0.682, 128x8 0.680, 512x2 0.282.
 // What matters is consumer warps per SM (the x gathers are latency bound): 512 rows x 2 stages is
@@ -160,13 +170,13 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// issues the two bulk copies of tile `tile` into stage buffers; a0 = first staged nonzero (multiple of 4)
-__device__ __forceinline__ void tma_issue_tile(int tile, int n, const int *__restrict__ rowptr, const int *__restrict__ col,
-                                               const double *__restrict__ val, unsigned char *stage,
-                                               unsigned long long *bar, int *a0_slot)
+// issues the two bulk copies of tile `tile` into a stage; a0 = first staged nonzero (multiple of 4)
+__device__ __forceinline__ void tma_issue_tile(int tile, int row0, int row1, const int *__restrict__ rowptr,
+                                               const int *__restrict__ col, const double *__restrict__ val,
+                                               unsigned char *stage, unsigned long long *bar, int *a0_slot)
 {
-    const int r0 = tile * TMA_ROWS;
-    const int r1 = min(n, r0 + TMA_ROWS);
+    const int r0 = row0 + tile * TMA_ROWS;
+    const int r1 = min(row1, r0 + TMA_ROWS);
     const int p0 = rowptr[r0], p1 = rowptr[r1];
     const int a0 = p0 & ~3;
     const int cnt = ((p1 + 3) & ~3) - a0;   // multiple of 4 -> 16-byte multiples for both arrays
@@ -181,11 +191,11 @@ __device__ __forceinline__ void tma_issue_tile(int tile, int n, const int *__res
 }
 
 template <int NDOT>
-__global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int n, int ntiles, const int *__restrict__ rowptr,
-                                                            const int *__restrict__ col, const double *__restrict__ val,
-                                                            const double *__restrict__ x, double *__restrict__ y,
-                                                            const double *__restrict__ w, double *partials,
-                                                            unsigned *ticket, double *out)
+__global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int row0, int row1, int ntiles, const int *__restrict__ rowptr,
+                                                               const int *__restrict__ col, const double *__restrict__ val,
+                                                               const double *__restrict__ x, double *__restrict__ y,
+                                                               const double *__restrict__ w, double *partials,
+                                                               unsigned *ticket, double *out, int accumulate)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) unsigned long long full[TMA_STAGES], empty[TMA_STAGES];
@@ -207,21 +217,21 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int n, int ntiles
                     mbar_wait(&empty[s], (unsigned)(i / TMA_STAGES - 1) & 1u);   // all consumer warps left stage s
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 }
-                tma_issue_tile(blockIdx.x + i * gridDim.x, n, rowptr, col, val, smem + s * TMA_STAGE_BYTES, &full[s], &a0s[s]);
+                tma_issue_tile(blockIdx.x + i * gridDim.x, row0, row1, rowptr, col, val, smem + s * TMA_STAGE_BYTES, &full[s], &a0s[s]);
             }
         }
     } else {
         // ---- consumer warps: 32 rows of every tile each, no block-wide barrier ----
-        int r = (int)blockIdx.x * TMA_ROWS + tid;
+        int r = row0 + (int)blockIdx.x * TMA_ROWS + tid;
         int pb = 0, pe = 0;
-        if (my_tiles > 0 && r < n) { pb = rowptr[r]; pe = rowptr[r + 1]; }
+        if (my_tiles > 0 && r < row1) { pb = rowptr[r]; pe = rowptr[r + 1]; }
         for (int i = 0; i < my_tiles; i++) {
             const int s = i % TMA_STAGES;
             const unsigned parity = (unsigned)(i / TMA_STAGES) & 1u;
             // row pointers of the next tile are fetched while this one is processed
             const int rn = r + (int)gridDim.x * TMA_ROWS;
             int pbn = 0, pen = 0;
-            if (i + 1 < my_tiles && rn < n) { pbn = rowptr[rn]; pen = rowptr[rn + 1]; }
+            if (i + 1 < my_tiles && rn < row1) { pbn = rowptr[rn]; pen = rowptr[rn + 1]; }
             mbar_wait(&full[s], parity);
             const int a0 = a0s[s];
             const double *sval = reinterpret_cast<const double *>(smem + s * TMA_STAGE_BYTES) - a0;
@@ -254,7 +264,7 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int n, int ntiles
                 for (int q = 0; q < 8; q++)
                     if (c[q] >= 0) sum += v[q] * __ldg(&x[c[q]]);
             }
-            if (r < n) {
+            if (r < row1) {
                 y[r] = sum;
                 if (NDOT == 1) acc[0] += w[r] * sum;
                 if (NDOT == 2) { acc[0] += sum * w[r]; acc[1] += sum * sum; }
@@ -262,27 +272,34 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int n, int ntiles
             r = rn; pb = pbn; pe = pen;
         }
     }
-    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out);
+    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out, accumulate != 0);
 }
 
-// largest number of staged nonzeros any tile needs
-__global__ void tma_tile_max_kernel(int n, int ntiles, const int *__restrict__ rowptr, int *__restrict__ out)
+// largest number of staged nonzeros any tile of [row0, row1) needs
+__global__ void tma_tile_max_kernel(int row0, int row1, int ntiles, const int *__restrict__ rowptr, int *__restrict__ out)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= ntiles) return;
-    const int r0 = t * TMA_ROWS, r1 = min(n, r0 + TMA_ROWS);
+    const int r0 = row0 + t * TMA_ROWS, r1 = min(row1, r0 + TMA_ROWS);
     const int need = ((rowptr[r1] + 3) & ~3) - (rowptr[r0] & ~3);
     atomicMax(out, need);
 }
 
+// y = A x over the rank's rows, with NDOT fused dots (accumulated over the ranges into out[])
 template <int NDOT>
-static void spmv_run(const Krylov &k, cudaStream_t st, int sb, const double *x, double *y, const double *w, double *out)
+static void spmv_run(const Krylov &k, cudaStream_t st, const double *x, double *y, const double *w, double *out)
 {
-    if (k.tma_tiles > 0) {
-        spmv_tma_kernel<NDOT><<<k.tma_grid, TMA_THREADS, TMA_SMEM_BYTES, st>>>(k.n, k.tma_tiles, k.rowptr, k.col, k.val, x, y, w,
-                                                                            k.partials.p, k.ticket.p, out);
-    } else {
-        spmv_dispatch<NDOT>(st, k.lanes, sb, k.n, k.rowptr, k.col, k.val, x, y, w, k.partials.p, k.ticket.p, out);
+    for (int q = 0; q < k.own.n; q++) {
+        const int row0 = k.own.b[q], row1 = k.own.e[q];
+        if (row1 <= row0) continue;
+        if (k.tma_ok) {
+            const int ntiles = (row1 - row0 + TMA_ROWS - 1) / TMA_ROWS;
+            const int grid = std::min(ntiles, k.tma_sms * k.tma_per_sm);
+            spmv_tma_kernel<NDOT><<<grid, TMA_THREADS, TMA_SMEM_BYTES, st>>>(row0, row1, ntiles, k.rowptr, k.col, k.val, x, y, w,
+                                                                             k.partials.p, k.ticket.p, out, q > 0);
+        } else {
+            spmv_dispatch<NDOT>(st, k.lanes, row0, row1, k.rowptr, k.col, k.val, x, y, w, k.partials.p, k.ticket.p, out, q > 0);
+        }
     }
 }
 
@@ -300,11 +317,11 @@ __device__ __forceinline__ double csr_entry(const int *__restrict__ rowptr, cons
     return 0.0;
 }
 
-__global__ void jacobi_setup_kernel(int n, const int *__restrict__ rowptr, const int *__restrict__ col,
+__global__ void jacobi_setup_kernel(int row0, int row1, const int *__restrict__ rowptr, const int *__restrict__ col,
                                     const double *__restrict__ val, double *__restrict__ dinv)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    const int i = row0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= row1) return;
     const double d = csr_entry(rowptr, col, val, i, i);
     dinv[i] = (d != 0.0) ? 1.0 / d : 1.0;
 }
@@ -313,11 +330,11 @@ __global__ void jacobi_setup_kernel(int n, const int *__restrict__ rowptr, const
 // cell (the "other species in the same box" entries of src/sparsecoeff.f:70-75,
 // 162-166, 296-302 plus the diagonal) and inverts it by Gauss-Jordan with
 // partial pivoting.  binv is stored [s][s'][cell] so that applying it is coalesced.
-__global__ void block_setup_kernel(int nspec, int ncell, const int *__restrict__ rowptr, const int *__restrict__ col,
-                                   const double *__restrict__ val, double *__restrict__ binv)
+__global__ void block_setup_kernel(int nspec, int ncell, int cell0, int cell1, const int *__restrict__ rowptr,
+                                   const int *__restrict__ col, const double *__restrict__ val, double *__restrict__ binv)
 {
-    const int cidx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (cidx >= ncell) return;
+    const int cidx = cell0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (cidx >= cell1) return;
     double A[MAXS][MAXS], B[MAXS][MAXS];
     for (int s = 0; s < nspec; s++)
         for (int q = 0; q < nspec; q++) {
@@ -353,12 +370,31 @@ __global__ void block_setup_kernel(int nspec, int ncell, const int *__restrict__
 }
 
 // ---- fused vector updates --------------------------------------------------------------
-// Work item = one cell (PRE == BLOCK: all its species) or one unknown.
-// PRE: 0 none, 1 Jacobi, 2 block-Jacobi.
+// Element loops run over an index range [b, e) with 16-byte accesses: the even-aligned interior goes
+// two unknowns per thread and trip (every vector base is 256-byte aligned, so index parity decides
+// alignment); a possible odd first / last element is handled by one thread.
+#define RS_RANGE_LOOP(b, e, ONE, TWO)                                                                  \
+    do {                                                                                               \
+        const long long b_al_ = ((long long)(b) + 1) & ~1LL, e_al_ = (long long)(e) & ~1LL;            \
+        const long long stride_ = (long long)gridDim.x * blockDim.x;                                   \
+        if (b_al_ < e_al_) {                                                                           \
+            _Pragma("unroll 2")                                                                        \
+            for (long long i2 = (b_al_ >> 1) + (long long)blockIdx.x * blockDim.x + threadIdx.x;       \
+                 i2 < (e_al_ >> 1); i2 += stride_) { TWO(i2); }                                        \
+            if (blockIdx.x == 0 && threadIdx.x == 0) {                                                 \
+                if ((b) < b_al_) { ONE((long long)(b)); }                                              \
+                if (e_al_ < (e)) { ONE(e_al_); }                                                       \
+            }                                                                                          \
+        } else if (blockIdx.x == 0 && threadIdx.x == 0) {                                              \
+            for (long long i1 = (b); i1 < (e); i1++) { ONE(i1); }                                      \
+        }                                                                                              \
+    } while (0)
+
+// PRE: 0 none, 1 Jacobi, 2 block-Jacobi (work item = one cell, all its species).
 
 // p = r + beta (p - omega v)  [first step: p = r] ; ph = M^-1 p
 template <int PRE>
-__global__ void __launch_bounds__(256) update_p_kernel(int n, int nspec, int ncell, int first, const double *scal,
+__global__ void __launch_bounds__(256) update_p_kernel(int b, int e, int nspec, int ncell, int first, const double *scal,
                                                        int cur, const double *__restrict__ r, const double *__restrict__ v,
                                                        double *__restrict__ p, double *__restrict__ ph,
                                                        const double *__restrict__ dinv, const double *__restrict__ binv)
@@ -372,9 +408,9 @@ __global__ void __launch_bounds__(256) update_p_kernel(int n, int nspec, int nce
         beta = (rho_k / rho_km1) * (alpha / omega);
         if (!isfinite(beta)) { beta = 0.0; omega = 0.0; }
     }
-    const long long stride = (long long)gridDim.x * blockDim.x;
     if (PRE == 2) {
-        for (long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < ncell; c += stride) {
+        const long long stride = (long long)gridDim.x * blockDim.x;
+        for (long long c = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; c < e; c += stride) {
             double pv[MAXS];
             for (int s = 0; s < nspec; s++) {
                 const long long i = (long long)s * ncell + c;
@@ -389,35 +425,21 @@ __global__ void __launch_bounds__(256) update_p_kernel(int n, int nspec, int nce
             }
         }
     } else {
-        // 16-byte accesses: two unknowns per thread and trip (all vectors are 256-byte aligned)
-        const long long n2 = n >> 1;
         const double2 *r2 = reinterpret_cast<const double2 *>(r), *v2 = reinterpret_cast<const double2 *>(v);
         const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
         double2 *p2 = reinterpret_cast<double2 *>(p), *ph2 = reinterpret_cast<double2 *>(ph);
-#pragma unroll 2
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
-            double2 pn = r2[i];
-            if (!first) {
-                const double2 po = p2[i], vo = v2[i];
-                pn.x += beta * (po.x - omega * vo.x);
-                pn.y += beta * (po.y - omega * vo.y);
-            }
-            p2[i] = pn;
-            if (PRE == 1) { const double2 d = d2[i]; pn.x *= d.x; pn.y *= d.y; }
-            ph2[i] = pn;
-        }
-        if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-            const long long i = n - 1;
-            const double pn = first ? r[i] : r[i] + beta * (p[i] - omega * v[i]);
-            p[i] = pn;
-            ph[i] = (PRE == 1) ? dinv[i] * pn : pn;
-        }
+#define P_ONE(i) { const double pn = first ? r[i] : r[i] + beta * (p[i] - omega * v[i]); p[i] = pn; ph[i] = (PRE == 1) ? dinv[i] * pn : pn; }
+#define P_TWO(i) { double2 pn = r2[i]; if (!first) { const double2 po = p2[i], vo = v2[i]; pn.x += beta * (po.x - omega * vo.x); pn.y += beta * (po.y - omega * vo.y); } \
+                   p2[i] = pn; if (PRE == 1) { const double2 d = d2[i]; pn.x *= d.x; pn.y *= d.y; } ph2[i] = pn; }
+        RS_RANGE_LOOP(b, e, P_ONE, P_TWO);
+#undef P_ONE
+#undef P_TWO
     }
 }
 
 // s = r - alpha v ; sh = M^-1 s
 template <int PRE>
-__global__ void __launch_bounds__(256) update_s_kernel(int n, int nspec, int ncell, const double *scal, int cur,
+__global__ void __launch_bounds__(256) update_s_kernel(int b, int e, int nspec, int ncell, const double *scal, int cur,
                                                        const double *__restrict__ r, const double *__restrict__ v,
                                                        double *__restrict__ s_, double *__restrict__ sh,
                                                        const double *__restrict__ dinv, const double *__restrict__ binv)
@@ -425,9 +447,9 @@ __global__ void __launch_bounds__(256) update_s_kernel(int n, int nspec, int nce
     const double rho = scal[SLOT * (cur ^ 1) + S_RHONEXT];
     double alpha = rho / scal[SLOT * cur + S_R0V];
     if (!isfinite(alpha)) alpha = 0.0;  // breakdown: flagged by update_xr_kernel, host restarts
-    const long long stride = (long long)gridDim.x * blockDim.x;
     if (PRE == 2) {
-        for (long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < ncell; c += stride) {
+        const long long stride = (long long)gridDim.x * blockDim.x;
+        for (long long c = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; c < e; c += stride) {
             double sv[MAXS];
             for (int s = 0; s < nspec; s++) {
                 const long long i = (long long)s * ncell + c;
@@ -441,35 +463,24 @@ __global__ void __launch_bounds__(256) update_s_kernel(int n, int nspec, int nce
             }
         }
     } else {
-        const long long n2 = n >> 1;
         const double2 *r2 = reinterpret_cast<const double2 *>(r), *v2 = reinterpret_cast<const double2 *>(v);
         const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
         double2 *s2 = reinterpret_cast<double2 *>(s_), *sh2 = reinterpret_cast<double2 *>(sh);
-#pragma unroll 2
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
-            const double2 ro = r2[i], vo = v2[i];
-            double2 sn;
-            sn.x = ro.x - alpha * vo.x;
-            sn.y = ro.y - alpha * vo.y;
-            s2[i] = sn;
-            if (PRE == 1) { const double2 d = d2[i]; sn.x *= d.x; sn.y *= d.y; }
-            sh2[i] = sn;
-        }
-        if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-            const long long i = n - 1;
-            const double sn = r[i] - alpha * v[i];
-            s_[i] = sn;
-            sh[i] = (PRE == 1) ? dinv[i] * sn : sn;
-        }
+#define S_ONE(i) { const double sn = r[i] - alpha * v[i]; s_[i] = sn; sh[i] = (PRE == 1) ? dinv[i] * sn : sn; }
+#define S_TWO(i) { const double2 ro = r2[i], vo = v2[i]; double2 sn; sn.x = ro.x - alpha * vo.x; sn.y = ro.y - alpha * vo.y; s2[i] = sn; \
+                   if (PRE == 1) { const double2 d = d2[i]; sn.x *= d.x; sn.y *= d.y; } sh2[i] = sn; }
+        RS_RANGE_LOOP(b, e, S_ONE, S_TWO);
+#undef S_ONE
+#undef S_TWO
     }
 }
 
 // x += alpha ph + omega sh ; r = s - omega t ; out = { <r,r>, <r0,r> }
-__global__ void __launch_bounds__(256) update_xr_kernel(int n, double *scal, int cur, const double *__restrict__ ph,
+__global__ void __launch_bounds__(256) update_xr_kernel(int b, int e, double *scal, int cur, const double *__restrict__ ph,
                                                         const double *__restrict__ sh, const double *__restrict__ s_,
                                                         const double *__restrict__ t, const double *__restrict__ r0,
                                                         double *__restrict__ x, double *__restrict__ r,
-                                                        double *partials, unsigned *ticket)
+                                                        double *partials, unsigned *ticket, int accumulate)
 {
     double *slot = scal + SLOT * cur;
     const double rho = scal[SLOT * (cur ^ 1) + S_RHONEXT];
@@ -481,62 +492,48 @@ __global__ void __launch_bounds__(256) update_xr_kernel(int n, double *scal, int
     if (bad) { alpha = 0.0; omega = 0.0; }
     if (blockIdx.x == 0 && threadIdx.x == 0) slot[S_BAD] = bad ? 1.0 : 0.0;
     double acc[2] = {0.0, 0.0};
-    const long long n2 = n >> 1;
     const double2 *ph2 = reinterpret_cast<const double2 *>(ph), *sh2 = reinterpret_cast<const double2 *>(sh);
     const double2 *s2 = reinterpret_cast<const double2 *>(s_), *t2 = reinterpret_cast<const double2 *>(t);
     const double2 *r02 = reinterpret_cast<const double2 *>(r0);
     double2 *x2 = reinterpret_cast<double2 *>(x), *r2 = reinterpret_cast<double2 *>(r);
-#pragma unroll 2
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (long long)gridDim.x * blockDim.x) {
-        const double2 a = ph2[i], b = sh2[i], sv = s2[i], tv = t2[i], q = r02[i];
-        double2 xv = x2[i], rn;
-        xv.x += alpha * a.x + omega * b.x;
-        xv.y += alpha * a.y + omega * b.y;
-        x2[i] = xv;
-        rn.x = sv.x - omega * tv.x;
-        rn.y = sv.y - omega * tv.y;
-        r2[i] = rn;
-        acc[0] += rn.x * rn.x + rn.y * rn.y;
-        acc[1] += q.x * rn.x + q.y * rn.y;
-    }
-    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-        const long long i = n - 1;
-        x[i] += alpha * ph[i] + omega * sh[i];
-        const double rn = s_[i] - omega * t[i];
-        r[i] = rn;
-        acc[0] += rn * rn;
-        acc[1] += r0[i] * rn;
-    }
-    grid_reduce<2>(acc, 0u, partials, ticket, slot + S_RR);
+#define X_ONE(i) { x[i] += alpha * ph[i] + omega * sh[i]; const double rn = s_[i] - omega * t[i]; r[i] = rn; acc[0] += rn * rn; acc[1] += r0[i] * rn; }
+#define X_TWO(i) { const double2 a = ph2[i], bb = sh2[i], sv = s2[i], tv = t2[i], q = r02[i]; double2 xv = x2[i], rn; \
+                   xv.x += alpha * a.x + omega * bb.x; xv.y += alpha * a.y + omega * bb.y; x2[i] = xv; \
+                   rn.x = sv.x - omega * tv.x; rn.y = sv.y - omega * tv.y; r2[i] = rn; \
+                   acc[0] += rn.x * rn.x + rn.y * rn.y; acc[1] += q.x * rn.x + q.y * rn.y; }
+    RS_RANGE_LOOP(b, e, X_ONE, X_TWO);
+#undef X_ONE
+#undef X_TWO
+    grid_reduce<2>(acc, 0u, partials, ticket, slot + S_RR, accumulate != 0);
 }
 
-// r = r0 = b ; x = 0 ; out = <b,b> into both the bnorm slot and slot(1).rhonext
-__global__ void __launch_bounds__(256) krylov_init_kernel(int n, const double *__restrict__ b, double *__restrict__ r,
+// r = r0 = b ; x = 0 ; out = <b,b>
+__global__ void __launch_bounds__(256) krylov_init_kernel(int b, int e, const double *__restrict__ rhs, double *__restrict__ r,
                                                           double *__restrict__ r0, double *__restrict__ x,
-                                                          double *partials, unsigned *ticket, double *scal)
+                                                          double *partials, unsigned *ticket, double *scal, int accumulate)
 {
     double acc[1] = {0.0};
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const double bi = b[i];
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
+        const double bi = rhs[i];
         r[i] = bi; r0[i] = bi; x[i] = 0.0;
         acc[0] += bi * bi;
     }
-    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_BNORM);
+    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_BNORM, accumulate != 0);
 }
 
 // restart: r = r0 = b - Ax (Ax given) ; out = <r,r> (the true residual)
-__global__ void __launch_bounds__(256) krylov_restart_kernel(int n, const double *__restrict__ b,
+__global__ void __launch_bounds__(256) krylov_restart_kernel(int b, int e, const double *__restrict__ rhs,
                                                              const double *__restrict__ ax, double *__restrict__ r,
                                                              double *__restrict__ r0, double *partials,
-                                                             unsigned *ticket, double *scal)
+                                                             unsigned *ticket, double *scal, int accumulate)
 {
     double acc[1] = {0.0};
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const double ri = b[i] - ax[i];
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
+        const double ri = rhs[i] - ax[i];
         r[i] = ri; r0[i] = ri;
         acc[0] += ri * ri;
     }
-    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_RTRUE);
+    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_RTRUE, accumulate != 0);
 }
 
 // rho_0 = <r0, r> = ||r||^2 goes where step 0 looks for "rho of the previous step"
@@ -547,10 +544,15 @@ __global__ void krylov_seed_kernel(double *scal, int src)
 
 // ---- host driver ------------------------------------------------------------------------
 int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int *col, const double *val,
-                 int precond, int nspec, int ncell, const rs_krylov_control *ctl)
+                 int precond, int nspec, int ncell, const rs_krylov_control *ctl, const Ranges *own,
+                 const HaloPlan *halo)
 {
     k.n = n; k.nnz = nnz; k.rowptr = rowptr; k.col = col; k.val = val;
     k.nspec = nspec; k.ncell = ncell;
+    if (own) k.own = *own; else { k.own.n = 1; k.own.b[0] = 0; k.own.e[0] = n; }
+    if (halo) k.halo = *halo; else k.halo = HaloPlan();
+    k.cell0 = 0; k.cell1 = ncell;
+    if (halo && halo->nspec > 0) { k.cell0 = halo->j0 * halo->plane; k.cell1 = halo->j1 * halo->plane; }
     if (precond == RS_PRECOND_AUTO) precond = (nspec > 1 && nspec <= MAXS && ncell > 0) ? RS_PRECOND_BLOCK_JACOBI : RS_PRECOND_JACOBI;
     if (precond == RS_PRECOND_BLOCK_JACOBI && !(nspec > 1 && nspec <= MAXS && ncell > 0 && (long long)nspec * ncell == n))
         precond = RS_PRECOND_JACOBI;
@@ -563,16 +565,20 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
     }
     k.lanes = pick_lanes(n, nnz);
     // TMA-staged SpMV when every tile's slice fits one stage (RS_SPMV=subwarp forces the other kernel)
-    k.tma_tiles = 0;
+    k.tma_ok = 0;
     {
         const char *force = getenv("RS_SPMV");
-        const int ntiles = (n + TMA_ROWS - 1) / TMA_ROWS;
-        if (!(force && strcmp(force, "subwarp") == 0) && ntiles > 0) {
+        if (!(force && strcmp(force, "subwarp") == 0)) {
             DevBuf<int> mx;
             RS_TRY(mx.alloc(1));
             RS_TRY(mx.zero(c.stream));
-            tma_tile_max_kernel<<<(ntiles + 255) / 256, 256, 0, c.stream>>>(n, ntiles, rowptr, mx.p);
-            c.launches++;
+            for (int q = 0; q < k.own.n; q++) {
+                const int rows = k.own.e[q] - k.own.b[q];
+                if (rows <= 0) continue;
+                const int ntiles = (rows + TMA_ROWS - 1) / TMA_ROWS;
+                tma_tile_max_kernel<<<(ntiles + 255) / 256, 256, 0, c.stream>>>(k.own.b[q], k.own.e[q], ntiles, rowptr, mx.p);
+                c.launches++;
+            }
             int need = 0;
             RS_TRY(mx.download(&need, 1, c.stream));
             RS_CUDA(cudaStreamSynchronize(c.stream));
@@ -580,19 +586,19 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
                 RS_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TMA_SMEM_BYTES));
                 RS_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TMA_SMEM_BYTES));
                 RS_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TMA_SMEM_BYTES));
-                int dev = 0, sms = 0, per_sm = 0;
+                int dev = 0;
                 RS_CUDA(cudaGetDevice(&dev));
-                RS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-                RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmv_tma_kernel<2>, TMA_THREADS, TMA_SMEM_BYTES));
-                if (per_sm >= 1) {
-                    k.tma_tiles = ntiles;
-                    k.tma_grid = std::min(ntiles, sms * per_sm);
-                }
+                RS_CUDA(cudaDeviceGetAttribute(&k.tma_sms, cudaDevAttrMultiProcessorCount, dev));
+                RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k.tma_per_sm, spmv_tma_kernel<2>, TMA_THREADS, TMA_SMEM_BYTES));
+                if (k.tma_per_sm >= 1) k.tma_ok = 1;
             }
         }
     }
     RS_TRY(k.r.alloc(n)); RS_TRY(k.r0.alloc(n)); RS_TRY(k.p.alloc(n)); RS_TRY(k.v.alloc(n));
     RS_TRY(k.s.alloc(n)); RS_TRY(k.t.alloc(n)); RS_TRY(k.ph.alloc(n)); RS_TRY(k.sh.alloc(n));
+    if (comm_active()) {  // halo planes are read before they are first received only if left uninitialised
+        RS_TRY(k.ph.zero(c.stream)); RS_TRY(k.sh.zero(c.stream));
+    }
     if (precond == RS_PRECOND_JACOBI) RS_TRY(k.dinv.alloc(n));
     if (precond == RS_PRECOND_BLOCK_JACOBI) RS_TRY(k.binv.alloc((size_t)nspec * nspec * ncell));
     RS_TRY(k.partials.alloc(4 * 148 * 16));
@@ -607,76 +613,99 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
 int krylov_precond_update(Ctx &c, Krylov &k)
 {
     if (k.precond == RS_PRECOND_JACOBI) {
-        Launch L(c, K_PRECOND_SETUP, 20.0 * k.n);
-        jacobi_setup_kernel<<<(k.n + 255) / 256, 256, 0, c.stream>>>(k.n, k.rowptr, k.col, k.val, k.dinv.p);
+        for (int q = 0; q < k.own.n; q++) {
+            const int rows = k.own.e[q] - k.own.b[q];
+            if (rows <= 0) continue;
+            Launch L(c, K_PRECOND_SETUP, 20.0 * rows);
+            jacobi_setup_kernel<<<(rows + 255) / 256, 256, 0, c.stream>>>(k.own.b[q], k.own.e[q], k.rowptr, k.col, k.val, k.dinv.p);
+        }
     } else if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
-        Launch L(c, K_PRECOND_SETUP, 20.0 * k.nspec * k.n);
-        block_setup_kernel<<<(k.ncell + 127) / 128, 128, 0, c.stream>>>(k.nspec, k.ncell, k.rowptr, k.col, k.val, k.binv.p);
+        const int cells = k.cell1 - k.cell0;
+        if (cells > 0) {
+            Launch L(c, K_PRECOND_SETUP, 20.0 * k.nspec * k.nspec * cells);
+            block_setup_kernel<<<(cells + 127) / 128, 128, 0, c.stream>>>(k.nspec, k.ncell, k.cell0, k.cell1, k.rowptr, k.col, k.val, k.binv.p);
+        }
     }
     RS_CUDA(cudaGetLastError());
     return RS_OK;
 }
 
-// One BiCGStab step (five launches); the raw dot products land in slot(cur).
-static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first, int vb, int cb, int sb, double pre_bytes)
+static inline double own_nnz_estimate(const Krylov &k) { return (double)k.nnz * (double)k.own.total() / (double)k.n; }
+
+// One BiCGStab step; the raw dot products land in slot(cur).
+static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
 {
-    const int n = k.n;
     cudaStream_t st = c.stream;
     double *slot = k.scal.p + SLOT * cur;
+    const double rows = (double)k.own.total();
+    const double pre_bytes = (k.precond == RS_PRECOND_BLOCK_JACOBI) ? 8.0 * k.nspec * rows : (k.precond == RS_PRECOND_JACOBI ? 8.0 * rows : 0.0);
     {
-        Launch L(c, K_VEC, (first ? 24.0 : 40.0) * n + pre_bytes);
-        switch (k.precond) {
-        case RS_PRECOND_BLOCK_JACOBI:
-            update_p_kernel<2><<<cb, 256, 0, st>>>(n, k.nspec, k.ncell, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, k.binv.p); break;
-        case RS_PRECOND_JACOBI:
-            update_p_kernel<1><<<cb, 256, 0, st>>>(n, 1, n, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, k.dinv.p, nullptr); break;
-        default:
-            update_p_kernel<0><<<cb, 256, 0, st>>>(n, 1, n, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, nullptr); break;
+        Launch L(c, K_VEC, (first ? 24.0 : 40.0) * rows + pre_bytes);
+        if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
+            update_p_kernel<2><<<grid_for(k.cell1 - k.cell0, 256), 256, 0, st>>>(k.cell0, k.cell1, k.nspec, k.ncell, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, k.binv.p);
+        } else {
+            for (int q = 0; q < k.own.n; q++) {
+                const int b = k.own.b[q], e = k.own.e[q];
+                if (k.precond == RS_PRECOND_JACOBI)
+                    update_p_kernel<1><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, k.dinv.p, nullptr);
+                else
+                    update_p_kernel<0><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, nullptr);
+            }
         }
     }
+    RS_TRY(comm_halo_exchange(c, k.ph.p, k.halo));
     {
-        Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
-        spmv_run<1>(k, st, sb, k.ph.p, k.v.p, k.r0.p, slot + S_R0V);
+        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)) + 8.0 * rows);
+        spmv_run<1>(k, st, k.ph.p, k.v.p, k.r0.p, slot + S_R0V);
     }
-    if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
+    RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
     {
-        Launch L(c, K_VEC, 32.0 * n + pre_bytes);
-        switch (k.precond) {
-        case RS_PRECOND_BLOCK_JACOBI:
-            update_s_kernel<2><<<cb, 256, 0, st>>>(n, k.nspec, k.ncell, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, k.binv.p); break;
-        case RS_PRECOND_JACOBI:
-            update_s_kernel<1><<<cb, 256, 0, st>>>(n, 1, n, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, k.dinv.p, nullptr); break;
-        default:
-            update_s_kernel<0><<<cb, 256, 0, st>>>(n, 1, n, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, nullptr); break;
+        Launch L(c, K_VEC, 32.0 * rows + pre_bytes);
+        if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
+            update_s_kernel<2><<<grid_for(k.cell1 - k.cell0, 256), 256, 0, st>>>(k.cell0, k.cell1, k.nspec, k.ncell, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, k.binv.p);
+        } else {
+            for (int q = 0; q < k.own.n; q++) {
+                const int b = k.own.b[q], e = k.own.e[q];
+                if (k.precond == RS_PRECOND_JACOBI)
+                    update_s_kernel<1><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, k.dinv.p, nullptr);
+                else
+                    update_s_kernel<0><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, nullptr);
+            }
         }
     }
+    RS_TRY(comm_halo_exchange(c, k.sh.p, k.halo));
     {
-        Launch L(c, K_SPMV, spmv_bytes(n, k.nnz) + 8.0 * n);
-        spmv_run<2>(k, st, sb, k.sh.p, k.t.p, k.s.p, slot + S_TS);
+        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)) + 8.0 * rows);
+        spmv_run<2>(k, st, k.sh.p, k.t.p, k.s.p, slot + S_TS);
     }
-    if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
+    RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
     {
-        Launch L(c, K_VEC, 64.0 * n);
-        update_xr_kernel<<<vb, 256, 0, st>>>(n, k.scal.p, cur, k.ph.p, k.sh.p, k.s.p, k.t.p, k.r0.p, x, k.r.p, k.partials.p, k.ticket.p);
+        Launch L(c, K_VEC, 64.0 * rows);
+        for (int q = 0; q < k.own.n; q++) {
+            const int b = k.own.b[q], e = k.own.e[q];
+            update_xr_kernel<<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph.p, k.sh.p, k.s.p, k.t.p, k.r0.p, x, k.r.p, k.partials.p, k.ticket.p, q > 0);
+        }
     }
-    if (comm_active()) RS_TRY(comm_allreduce_sum(c, slot + S_RR, 2));
+    RS_TRY(comm_allreduce_sum(c, slot + S_RR, 2));
     return RS_OK;
 }
 
 // r = r0 = b - A x explicitly; returns ||r||_2.  Restarts the recurrence (new shadow residual).
-static int true_residual_restart(Ctx &c, Krylov &k, const double *b, const double *x, int vb, int sb, double *rnorm)
+static int true_residual_restart(Ctx &c, Krylov &k, const double *b, double *x, double *rnorm)
 {
-    const int n = k.n;
     cudaStream_t st = c.stream;
+    const double rows = (double)k.own.total();
+    RS_TRY(comm_halo_exchange(c, x, k.halo));
     {
-        Launch L(c, K_SPMV, spmv_bytes(n, k.nnz));
-        spmv_run<0>(k, st, sb, x, k.v.p, nullptr, nullptr);
+        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)));
+        spmv_run<0>(k, st, x, k.v.p, nullptr, nullptr);
     }
     {
-        Launch L(c, K_VEC, 32.0 * n);
-        krylov_restart_kernel<<<vb, 256, 0, st>>>(n, b, k.v.p, k.r.p, k.r0.p, k.partials.p, k.ticket.p, k.scal.p);
+        Launch L(c, K_VEC, 32.0 * rows);
+        for (int q = 0; q < k.own.n; q++)
+            krylov_restart_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, k.v.p, k.r.p, k.r0.p, k.partials.p, k.ticket.p, k.scal.p, q > 0);
     }
-    if (comm_active()) RS_TRY(comm_allreduce_sum(c, k.scal.p + S_RTRUE, 1));
+    RS_TRY(comm_allreduce_sum(c, k.scal.p + S_RTRUE, 1));
     krylov_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, S_RTRUE);
     c.launches++;
     RS_CUDA(cudaMemcpyAsync(k.h_scal + S_RTRUE, k.scal.p + S_RTRUE, sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -689,20 +718,17 @@ static int true_residual_restart(Ctx &c, Krylov &k, const double *b, const doubl
 // stagnate, or break down (a recurrence scalar hits zero); each of those ends the current cycle:
 // the true residual is recomputed, becomes the new shadow residual, and the recurrence restarts
 // from the x reached so far.  Convergence is only ever declared on the true residual.
+// All ranks take the same decisions: every number they are based on has been all-reduced.
 int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres)
 {
-    const int n = k.n;
     cudaStream_t st = c.stream;
-    const int vb = grid_for(n, 256, 148 * 8);
-    const int cb = grid_for(k.precond == RS_PRECOND_BLOCK_JACOBI ? k.ncell : n, 256, 148 * 8);
-    const int sb = spmv_blocks(n, k.lanes);
-    const double pre_bytes = (k.precond == RS_PRECOND_BLOCK_JACOBI) ? 8.0 * k.nspec * n : (k.precond == RS_PRECOND_JACOBI ? 8.0 * n : 0.0);
     static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
     {
-        Launch L(c, K_VEC, 32.0 * n);
-        krylov_init_kernel<<<vb, 256, 0, st>>>(n, b, k.r.p, k.r0.p, x, k.partials.p, k.ticket.p, k.scal.p);
+        Launch L(c, K_VEC, 32.0 * (double)k.own.total());
+        for (int q = 0; q < k.own.n; q++)
+            krylov_init_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, k.r.p, k.r0.p, x, k.partials.p, k.ticket.p, k.scal.p, q > 0);
     }
-    if (comm_active()) RS_TRY(comm_allreduce_sum(c, k.scal.p + S_BNORM, 1));
+    RS_TRY(comm_allreduce_sum(c, k.scal.p + S_BNORM, 1));
     krylov_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, S_BNORM);
     c.launches++;
     RS_CUDA(cudaMemcpyAsync(k.h_scal + S_BNORM, k.scal.p + S_BNORM, sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -720,7 +746,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     bool done = false;
     while (!done && total < k.max_iter) {
         const int cur = cycle_it & 1;
-        RS_TRY(bicgstab_step(c, k, x, cur, cycle_it == 0, vb, cb, sb, pre_bytes));
+        RS_TRY(bicgstab_step(c, k, x, cur, cycle_it == 0));
         total++; cycle_it++;
         *iters = total;
         if (total % k.check_every != 0 && total != k.max_iter) continue;
@@ -741,7 +767,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
         if (!(looks_converged || broke || stagnated || total >= k.max_iter)) continue;
         // end of cycle: what did it really achieve?
         double rt = 0.0;
-        RS_TRY(true_residual_restart(c, k, b, x, vb, sb, &rt));
+        RS_TRY(true_residual_restart(c, k, b, x, &rt));
         if (debug) fprintf(stderr, "[krylov] cycle %d ends after %d its (%s): true residual %.6e (target %.3e)\n", restarts,
                            cycle_it, looks_converged ? "converged" : broke ? "breakdown" : stagnated ? "stagnation" : "budget",
                            rt, target);

@@ -126,7 +126,7 @@ __device__ __forceinline__ double warp_max(double v)
 // block.  Every thread of the block must call this.
 template <int K>
 __device__ __forceinline__ void grid_reduce(double (&v)[K], unsigned max_mask, double *partials,
-                                            unsigned *ticket, double *out)
+                                            unsigned *ticket, double *out, bool accumulate = false)
 {
     __shared__ double sh[K][32];
     __shared__ bool is_last;
@@ -165,7 +165,8 @@ __device__ __forceinline__ void grid_reduce(double (&v)[K], unsigned max_mask, d
                     r = mx ? fmax(r, q) : r + q;
                 }
                 r = mx ? warp_max(r) : warp_sum(r);
-                if (lane == 0) out[k] = r;
+                // accumulate: a launch per index range of the same reduction (stream order makes it safe)
+                if (lane == 0) out[k] = accumulate ? (mx ? fmax(out[k], r) : out[k] + r) : r;
             }
             if (lane == 0) *ticket = 0;
         }

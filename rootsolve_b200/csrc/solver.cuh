@@ -14,6 +14,21 @@ struct GridDesc {
     int ncell = 0;
 };
 
+// The unknowns a rank works on: up to MAXR disjoint index ranges (one per species of its slab;
+// a single range [0, N) on one GPU).  Vectors keep GLOBAL indices on every rank.
+constexpr int MAXR = 16;
+struct Ranges {
+    int n = 0;
+    int b[MAXR], e[MAXR];
+    long long total() const { long long t = 0; for (int q = 0; q < n; q++) t += e[q] - b[q]; return t; }
+};
+
+// One halo exchange: plane j0 / j1-1 of every species go to the slab neighbours, planes j0-1 / j1 come back.
+struct HaloPlan {
+    int nspec = 0, ncell = 0, plane = 0, j0 = 0, j1 = 0;
+    bool has_lo = false, has_hi = false;
+};
+
 // structure.cu
 int exclusive_scan(Ctx &c, const int *in, int *out, int n, int base, bool write_total);
 int build_grid_structure(Ctx &c, const GridDesc &g, int n, DevBuf<int> &d_ian, DevBuf<int> &d_jan, int *nnz);
@@ -35,10 +50,11 @@ struct FdWork {
 };
 int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, int nrpar, const int *ipar,
              int nipar, int slab_j0, int slab_j1);
-// beta = -f(y); val[] (CSR order) = FD Jacobian; dinv (optional) = 1/diag
+// beta = -f(y); val[] (row-wise) = FD Jacobian.  `own`: rows this rank assembles; `touch`: the
+// unknowns whose perturbed copies it needs (own + halo planes).
 int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
                 const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
-                long long work, int row0, int row1);
+                const Ranges &own, const Ranges &touch);
 int residual_only(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, const double *d_y, double *d_f,
                   long long work);
 // a_csc[k] = val[position of (jan[k], column of k)] -- for returning the Jacobian in jan order
@@ -48,24 +64,27 @@ int scatter_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_ja
                        const int *d_col, const double *d_a, double *d_val);
 
 // krylov.cu
-struct RowRange { int n_ranges = 1; int begin[8]; int end[8]; };  // owned rows (species-major slabs)
 struct Krylov {
     int n = 0, nnz = 0;
     const int *rowptr = nullptr, *col = nullptr;
     const double *val = nullptr;
     int precond = RS_PRECOND_JACOBI, nspec = 1, ncell = 0;
+    Ranges own;                 // rows of this rank
+    int cell0 = 0, cell1 = 0;   // cells of this rank (block preconditioner)
+    HaloPlan halo;
     DevBuf<double> r, r0, p, v, s, t, ph, sh, dinv, binv;
     DevBuf<double> partials, scal;
     DevBuf<unsigned> ticket;
     double *h_scal = nullptr;  // pinned mirror
     int lanes = 8;             // lanes per row of the sub-warp SpMV
-    int tma_tiles = 0, tma_grid = 0;  // > 0: the TMA-staged SpMV is used (every tile fits a stage)
+    int tma_ok = 0, tma_sms = 0, tma_per_sm = 0;  // the TMA-staged SpMV is usable (every tile fits a stage)
     int max_iter = 10000, check_every = 1;
     double lin_rtol = 1e-10, lin_ewt_factor = 5e-4;
     ~Krylov();
 };
 int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int *col, const double *val,
-                 int precond, int nspec, int ncell, const rs_krylov_control *ctl);
+                 int precond, int nspec, int ncell, const rs_krylov_control *ctl, const Ranges *own,
+                 const HaloPlan *halo);
 int krylov_precond_update(Ctx &c, Krylov &k);
 // solves A x = b (x overwritten, starts from 0); abs_floor: absolute 2-norm stop
 int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres);
@@ -75,7 +94,11 @@ int pick_lanes(int n, int nnz);
 
 // comm.cu
 bool comm_active();
+int comm_nranks();
+int comm_rank();
 int comm_allreduce_sum(Ctx &c, double *d_buf, int count);
 int comm_allreduce_max(Ctx &c, double *d_buf, int count);
+int comm_halo_exchange(Ctx &c, double *v, const HaloPlan &h);
+int comm_gather_slabs(Ctx &c, double *v, int nspec, int ncell, int plane, int d1);
 
 }  // namespace rs
