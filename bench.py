@@ -194,7 +194,9 @@ def run_ours(args):
     R = new_result(False)
     for _ in range(args.warmup):
         step(R)
-    _capi.check(L.rs_solver_set_profiling(h, 1))
+    # per-kernel CUDA events over the timed region (N = 1: the roofline line).  Sharded runs replay
+    # captured CUDA graphs, which cannot carry per-launch events, so their kernel table is left empty.
+    _capi.check(L.rs_solver_set_profiling(h, 1 if world == 1 else 0))
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()

@@ -69,10 +69,18 @@ void Ctx::reset_stats()
     for (int i = 0; i < K_COUNT; i++) { ms[i] = 0; count[i] = 0; }
     launches = 0;
 }
+Ctx::Ctx()
+{
+    if (cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking) != cudaSuccess) {
+        stream = nullptr;   // no device: every entry point reports RS_ENODEVICE before launching anything
+        cudaGetLastError();
+    }
+}
 Ctx::~Ctx()
 {
     resolve();
     for (auto e : pool) cudaEventDestroy(e);
+    if (stream) cudaStreamDestroy(stream);
 }
 
 int ensure_device()

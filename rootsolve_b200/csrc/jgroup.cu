@@ -21,6 +21,7 @@
 #include <cooperative_groups.h>
 
 #include "solver.cuh"
+#include "grid_rows.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -66,24 +67,35 @@ __global__ void jg_commit_kernel(int n, unsigned char *__restrict__ state, int *
     if ((threadIdx.x & 31) == 0 && m) atomicAdd(accepted, __popc(m));
 }
 
-// One group of the wavefront variant.  covered[] must be zero on entry.
-__global__ void __launch_bounds__(256) jg_wave_kernel(GridDesc g, int S, int nlevels, const int *__restrict__ ian,
-                                                      const int *__restrict__ jan, unsigned char *done,
-                                                      unsigned char *covered, int *__restrict__ group_of,
-                                                      int gidx, int *__restrict__ accepted)
+// The wavefront variant, software-pipelined over the groups.  Group g+1's verdict on a column only
+// needs (i) group g's verdict on the same column and (ii) its own verdicts on lower levels, so group
+// slot g can sweep level (step - g) while slot g+1 sweeps level (step - g - 1): WAVE_SLOTS groups
+// advance together, one grid-wide barrier per step, nlevels + WAVE_SLOTS - 1 steps per pass instead
+// of nlevels per group.  covered[row] holds one bit per slot.  Rows of a column come from
+// emit_column (same order and content as ian/jan), so no structure array is read.
+// group_of[c] < 0 on entry marks the columns still to be grouped; a pass assigns base .. base+SLOTS-1.
+constexpr int WAVE_SLOTS = 16;
+
+__global__ void __launch_bounds__(256) jg_wave_kernel(GridDesc g, int S, int nlevels, unsigned *covered,
+                                                      int *__restrict__ group_of, int base, int *__restrict__ stats)
 {
     cg::grid_group grid = cg::this_grid();
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long nthreads = (long long)gridDim.x * blockDim.x;
     const int d1 = g.d[0], d2 = g.d[1], d3 = g.d[2];
     const bool three = (g.type == RS_TYPE_3D);
-    // candidate lines: (species, j, k) in 3-D, (species, j) in 2-D; the last
-    // coordinate follows from the level
+    // candidate lines: (species, j, k) in 3-D, (species, j) in 2-D; the last coordinate follows from the level
     const long long nlines = three ? (long long)g.nspec * d1 * d2 : (long long)g.nspec * d1;
     const int dl = three ? d3 : d2;
-    int count = 0;
-    for (int t = 0; t < nlevels; t++) {
-        for (long long q = tid; q < nlines; q += nthreads) {
+    int count = 0, top = -1;
+    const int nsteps = nlevels + WAVE_SLOTS - 1;
+    for (int step = 0; step < nsteps; step++) {
+        const int slot_lo = max(0, step - nlevels + 1), slot_hi = min(WAVE_SLOTS - 1, step);
+        const long long work = (long long)(slot_hi - slot_lo + 1) * nlines;
+        for (long long wq = tid; wq < work; wq += nthreads) {
+            const int slot = slot_lo + (int)(wq / nlines);
+            const long long q = wq % nlines;
+            const int t = step - slot;
             int s, last;
             long long c;
             if (three) {
@@ -100,20 +112,24 @@ __global__ void __launch_bounds__(256) jg_wave_kernel(GridDesc g, int S, int nle
                 c = q * d2 + last;
             }
             if (last < 0 || last >= dl) continue;
-            if (done[c]) continue;
-            const int k0 = ian[c] - 1, k1 = ian[c + 1] - 1;
+            if (group_of[c] >= 0) continue;          // taken by an earlier group (earlier step or pass)
+            const unsigned bit = 1u << slot;
             bool clash = false;
-            for (int k = k0; k < k1; k++)
-                if (covered[jan[k] - 1]) { clash = true; break; }
+            emit_column(g, (int)c + 1, [&](int row) { clash = clash || (covered[row - 1] & bit); });
             if (clash) continue;
-            done[c] = 1;
-            group_of[c] = gidx;
-            for (int k = k0; k < k1; k++) covered[jan[k] - 1] = 1;
+            group_of[c] = base + slot;
+            emit_column(g, (int)c + 1, [&](int row) { atomicOr(&covered[row - 1], bit); });
             count++;
+            top = max(top, base + slot);
         }
         grid.sync();
     }
-    if (count) atomicAdd(accepted, count);
+    if (count) { atomicAdd(&stats[0], count); atomicMax(&stats[1], top); }
+}
+
+__global__ void fill_int_kernel(int n, int *__restrict__ p, int v)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) p[i] = v;
 }
 
 static bool wave_applicable(const GridDesc &g)
@@ -136,7 +152,7 @@ int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, c
     int total = 0, groups = 0;
 
     if (wave_applicable(g)) {
-        DevBuf<unsigned char> covered;
+        DevBuf<unsigned> covered;   // one bit per group slot of the current pass
         RS_TRY(covered.alloc(n));
         const bool three = g.type == RS_TYPE_3D;
         const int S = three ? 5 : 3;
@@ -147,32 +163,41 @@ int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, c
         RS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jg_wave_kernel, 256, 0));
         const long long nlines = three ? (long long)g.nspec * g.d[0] * g.d[1] : (long long)g.nspec * g.d[0];
-        long long want = (nlines + 255) / 256;
-        long long cap = (long long)sms * (per_sm > 2 ? 2 : per_sm);
+        long long want = (nlines * WAVE_SLOTS + 255) / 256;
+        long long cap = (long long)sms * (per_sm > 4 ? 4 : per_sm);
         int blocks = (int)(want < cap ? want : cap);
         if (blocks < 1) blocks = 1;
+        fill_int_kernel<<<grid_for(n, 256), 256, 0, c.stream>>>(n, group_of.p, -1);
+        c.launches++;
+        int base = 0;
         while (total < n) {
-            if (groups >= maxg) {
+            if (base >= maxg) {
                 set_error("error during grouping: NGP too small (should be more than %d)", maxg);
                 return RS_EGROUP;
             }
             RS_TRY(covered.zero(c.stream));
-            RS_CUDA(cudaMemsetAsync(counters.p, 0, 2 * sizeof(int), c.stream));
+            const int init[2] = {0, -1};
+            RS_CUDA(cudaMemcpyAsync(counters.p, init, 2 * sizeof(int), cudaMemcpyHostToDevice, c.stream));
             GridDesc gg = g;
-            int Sx = S, nl = nlevels, gi = groups;
-            unsigned char *dn = state.p, *cv = covered.p;
-            int *go = group_of.p, *acc = counters.p + 1;
-            void *args[] = {&gg, &Sx, &nl, (void *)&d_ian, (void *)&d_jan, &dn, &cv, &go, &gi, &acc};
+            int Sx = S, nl = nlevels, bs = base;
+            unsigned *cv = covered.p;
+            int *go = group_of.p, *st = counters.p;
+            void *args[] = {&gg, &Sx, &nl, &cv, &go, &bs, &st};
             {
-                Launch L(c, K_JGROUP, 9.0 * n + 4.0 * nnz);
+                Launch L(c, K_JGROUP, (double)WAVE_SLOTS * 4.0 * n);
                 RS_CUDA(cudaLaunchCooperativeKernel((void *)jg_wave_kernel, dim3(blocks), dim3(256), args, 0, c.stream));
             }
-            int acc_h = 0;
-            RS_CUDA(cudaMemcpyAsync(&acc_h, counters.p + 1, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+            int st_h[2] = {0, -1};
+            RS_CUDA(cudaMemcpyAsync(st_h, counters.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, c.stream));
             RS_CUDA(cudaStreamSynchronize(c.stream));
-            if (acc_h == 0) break;  // cannot happen while columns remain; guards against a hang
-            total += acc_h;
-            groups++;
+            if (st_h[0] == 0) break;  // cannot happen while columns remain; guards against a hang
+            total += st_h[0];
+            groups = st_h[1] + 1;
+            base += WAVE_SLOTS;
+        }
+        if (groups > maxg) {
+            set_error("error during grouping: NGP too small (should be at least %d, while it is %d)", groups, maxg);
+            return RS_EGROUP;
         }
     } else {
         const int blocks = (n + 255) / 256;

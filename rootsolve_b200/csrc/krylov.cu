@@ -39,6 +39,7 @@ constexpr int NSCAL = 2 * SLOT + 8;
 Krylov::~Krylov()
 {
     if (h_scal) cudaFreeHost(h_scal);
+    if (pair_exec) cudaGraphExecDestroy(pair_exec);
 }
 
 int pick_lanes(int n, int nnz)
@@ -744,10 +745,38 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     double best = bnorm;      // smallest recursive residual of the current cycle
     int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
     bool done = false;
+    // Sharded solves are bound by launch + NCCL enqueue latency, not bandwidth: after the first two
+    // steps of a cycle, steps run in pairs (slot parities 0, 1) from one captured CUDA graph -- ten
+    // kernels, four halo exchanges and six all-reduces per host call.  (Not while profiling: the
+    // per-launch events cannot live inside a graph.)
+    static const bool no_graph = getenv("RS_NO_GRAPH") != nullptr;
+    const bool use_graph = comm_active() && !c.profile && !no_graph;
     while (!done && total < k.max_iter) {
-        const int cur = cycle_it & 1;
-        RS_TRY(bicgstab_step(c, k, x, cur, cycle_it == 0));
-        total++; cycle_it++;
+        int cur = cycle_it & 1;
+        if (use_graph && cycle_it >= 2 && cur == 0 && total + 2 <= k.max_iter) {
+            if (!k.pair_exec || k.pair_x != x) {
+                if (k.pair_exec) { cudaGraphExecDestroy(k.pair_exec); k.pair_exec = nullptr; }
+                cudaGraph_t g = nullptr;
+                const long long l0 = c.launches;
+                RS_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+                int rc = bicgstab_step(c, k, x, 0, 0);
+                if (rc == RS_OK) rc = bicgstab_step(c, k, x, 1, 0);
+                cudaError_t ce = cudaStreamEndCapture(st, &g);
+                c.launches = l0;
+                if (rc != RS_OK) { if (g) cudaGraphDestroy(g); return rc; }
+                RS_CUDA(ce);
+                RS_CUDA(cudaGraphInstantiate(&k.pair_exec, g, 0));
+                cudaGraphDestroy(g);
+                k.pair_x = x;
+            }
+            RS_CUDA(cudaGraphLaunch(k.pair_exec, st));
+            c.launches += 10;
+            total += 2; cycle_it += 2;
+            cur = 1;
+        } else {
+            RS_TRY(bicgstab_step(c, k, x, cur, cycle_it == 0));
+            total++; cycle_it++;
+        }
         *iters = total;
         if (total % k.check_every != 0 && total != k.max_iter) continue;
         double *slot = k.scal.p + SLOT * cur;

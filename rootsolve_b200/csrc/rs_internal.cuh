@@ -57,6 +57,9 @@ struct Ctx {
     void end(int id);
     void resolve();  // synchronises and folds pending events into ms[]
     void reset_stats();
+    Ctx();           // owns a non-blocking stream (capturable into CUDA graphs, unlike the legacy default stream)
+    Ctx(const Ctx &) = delete;
+    Ctx &operator=(const Ctx &) = delete;
     ~Ctx();
 };
 

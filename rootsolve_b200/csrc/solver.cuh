@@ -78,6 +78,8 @@ struct Krylov {
     double *h_scal = nullptr;  // pinned mirror
     int lanes = 8;             // lanes per row of the sub-warp SpMV
     int tma_ok = 0, tma_sms = 0, tma_per_sm = 0;  // the TMA-staged SpMV is usable (every tile fits a stage)
+    cudaGraphExec_t pair_exec = nullptr;   // two BiCGStab steps (slot parities 0 and 1) captured once, replayed
+    const double *pair_x = nullptr;        // the solution vector the captured graph updates
     int max_iter = 10000, check_every = 1;
     double lin_rtol = 1e-10, lin_ewt_factor = 5e-4;
     ~Krylov();
