@@ -451,6 +451,14 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
         RS_TRY(krylov_solve(c, s.kry, s.beta.p, s.x.p, s.kry.lin_ewt_factor * s.min_atol * std::sqrt((double)n), &kit,
                             &relres));
         s.krylov_iters += kit;
+        // An inexact Newton step is fine; no step at all is not: a solve that barely reduced the residual
+        // would otherwise look like convergence to test 2 (max|x| <= ctol).  The reference's direct solve
+        // cannot fail this way -- it stops with "zero pivot" instead (src/sparse.f:2376).
+        if (!(relres <= 0.1)) {
+            set_error("sparse solver: the Krylov solve of Newton iteration %d stalled at relative residual %.3e after %d "
+                      "iterations (matrix too ill-conditioned or indefinite for the chosen preconditioner)", it, relres, kit);
+            return RS_ESINGULAR;
+        }
         if (s.verbose && comm_rank() == 0)
             fprintf(stderr, "[rootsolve_b200] newton %d: mean|f|=%.6e  krylov its=%d relres=%.3e\n", it, s.precis[it - 1], kit, relres);
         {

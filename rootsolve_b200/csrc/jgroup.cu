@@ -7,13 +7,14 @@
 // shares a row with j has joined g -- the lexicographically first maximal
 // independent set of the column-intersection graph.  Two exact device variants:
 //
-//  * wavefront (regular non-cyclic 2-D/3-D grids): with the level function
-//    phi = S*species + 4*j + 2*k + l (3-D) or S*species + 2*j + k (2-D) every
-//    pair of conflicting columns lies on different levels and the lower index
-//    is always on the lower level, so sweeping the levels in order with a
-//    "row covered" bitmap is the sequential algorithm, run one hyperplane at a
-//    time by a cooperative kernel (grid-wide barrier between levels);
-//  * rounds (any structure, used for 1-D, cyclic and user patterns): each
+//  * wavefront (regular non-cyclic 1-D/2-D/3-D grids): with the level function
+//    phi = S*species + 4*j + 2*k + l (3-D), S*species + 2*j + k (2-D) or
+//    S*species + j (1-D) every pair of conflicting columns lies on different
+//    levels and the lower index is always on the lower level, so sweeping the
+//    levels in order with a "row covered" bitmap is the sequential algorithm,
+//    run one hyperplane at a time by a cooperative kernel (grid-wide barrier
+//    between levels) and pipelined over 16 groups at once (see jg_wave_kernel);
+//  * rounds (any structure, used for cyclic and user patterns): each
 //    undecided column looks at the lower-index columns it conflicts with;
 //    one of them in the group -> rejected; all of them rejected or grouped
 //    earlier -> accepted; otherwise it waits for the next round.  Decisions are
@@ -83,10 +84,11 @@ __global__ void __launch_bounds__(256) jg_wave_kernel(GridDesc g, int S, int nle
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long nthreads = (long long)gridDim.x * blockDim.x;
     const int d1 = g.d[0], d2 = g.d[1], d3 = g.d[2];
-    const bool three = (g.type == RS_TYPE_3D);
-    // candidate lines: (species, j, k) in 3-D, (species, j) in 2-D; the last coordinate follows from the level
-    const long long nlines = three ? (long long)g.nspec * d1 * d2 : (long long)g.nspec * d1;
-    const int dl = three ? d3 : d2;
+    const bool three = (g.type == RS_TYPE_3D), one = (g.type == RS_TYPE_1D);
+    // candidate lines: (species, j, k) in 3-D, (species, j) in 2-D, (species) in 1-D; the last coordinate
+    // follows from the level
+    const long long nlines = three ? (long long)g.nspec * d1 * d2 : one ? (long long)g.nspec : (long long)g.nspec * d1;
+    const int dl = three ? d3 : one ? d1 : d2;
     int count = 0, top = -1;
     const int nsteps = nlevels + WAVE_SLOTS - 1;
     for (int step = 0; step < nsteps; step++) {
@@ -105,6 +107,10 @@ __global__ void __launch_bounds__(256) jg_wave_kernel(GridDesc g, int S, int nle
                 s = (int)(r / d1);
                 last = t - S * s - 4 * j - 2 * k;
                 c = q * d3 + last;
+            } else if (one) {
+                s = (int)q;
+                last = t - S * s;
+                c = q * d1 + last;
             } else {
                 const int j = (int)(q % d1);
                 s = (int)(q / d1);
@@ -134,7 +140,7 @@ __global__ void fill_int_kernel(int n, int *__restrict__ p, int v)
 
 static bool wave_applicable(const GridDesc &g)
 {
-    if (g.type != RS_TYPE_2D && g.type != RS_TYPE_3D) return false;
+    if (g.type != RS_TYPE_1D && g.type != RS_TYPE_2D && g.type != RS_TYPE_3D) return false;
     for (int q = 0; q < 3; q++) if (g.cyc[q]) return false;
     return true;
 }
@@ -155,14 +161,17 @@ int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, c
         DevBuf<unsigned> covered;   // one bit per group slot of the current pass
         RS_TRY(covered.alloc(n));
         const bool three = g.type == RS_TYPE_3D;
-        const int S = three ? 5 : 3;
+        const bool one = g.type == RS_TYPE_1D;
+        // species weight S: larger than the biggest level difference between neighbouring cells
+        const int S = three ? 5 : one ? 2 : 3;
         const int nlevels = three ? S * (g.nspec - 1) + 4 * (g.d[0] - 1) + 2 * (g.d[1] - 1) + g.d[2]
+                            : one ? S * (g.nspec - 1) + g.d[0]
                                   : S * (g.nspec - 1) + 2 * (g.d[0] - 1) + g.d[1];
         int dev = 0, sms = 0, per_sm = 0;
         RS_CUDA(cudaGetDevice(&dev));
         RS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jg_wave_kernel, 256, 0));
-        const long long nlines = three ? (long long)g.nspec * g.d[0] * g.d[1] : (long long)g.nspec * g.d[0];
+        const long long nlines = three ? (long long)g.nspec * g.d[0] * g.d[1] : one ? (long long)g.nspec : (long long)g.nspec * g.d[0];
         long long want = (nlines * WAVE_SLOTS + 255) / 256;
         long long cap = (long long)sms * (per_sm > 4 ? 4 : per_sm);
         int blocks = (int)(want < cap ? want : cap);

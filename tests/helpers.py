@@ -9,7 +9,8 @@ TOL = dict(atol=1e-10, rtol=1e-10, ctol=1e-10)
 P_DIFF2D_LIN = [1.0, 1.0, 1.0, 1.0, 0.025, 1.0, 1.0]
 P_DIFF2D_MONOD = [1.0, 1.0, 1.0, 1.0, 0.25, 1.0, 1.0]
 P_DIFF3D = [1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 0.025, 1.0]
-P_RD3D = [1.0, 0.5, 1.0, 1.0, 1.0, 0.01, 0.05, 10.0, 1.0, 0.0]
+# D1 D2 dx dy dz k m BNDu BNDv -- m > k*BNDu keeps dv/dv < 0 everywhere (a decaying, not a growing, species v)
+P_RD3D = [1.0, 0.5, 1.0, 1.0, 1.0, 0.01, 0.2, 10.0, 1.0, 0.0]
 P_RT1D = [1.0, 1.0, 1.0, 0.5, 0.5, 1.0, 0.1]
 
 

@@ -78,8 +78,15 @@ def _jg_case(built, oracle, kind, nspec, dims, cyc, hint):
 
 
 @pytest.mark.parametrize("nspec,nb,cyc", GRIDS_1D)
-def test_jgroup_1d_bit_exact(built, oracle, nspec, nb, cyc):
-    _jg_case(built, oracle, "1D", nspec, [nb], [cyc], None)
+@pytest.mark.parametrize("wave", [False, True])
+def test_jgroup_1d_bit_exact(built, oracle, nspec, nb, cyc, wave):
+    hint = [2, nspec, nb, 1, 1, cyc, 0, 0] if wave else None
+    _jg_case(built, oracle, "1D", nspec, [nb], [cyc], hint)
+
+
+def test_jgroup_1d_long_column(built, oracle):
+    """config C2's shape at a tenth of its length: 5 species x 20 000 boxes through the pipelined wavefront"""
+    _jg_case(built, oracle, "1D", 5, [20000], [0], [2, 5, 20000, 1, 1, 0, 0, 0])
 
 
 @pytest.mark.parametrize("nspec,dims,cyc", GRIDS_2D)
@@ -388,6 +395,78 @@ def _full_inz(n):
     from oracle import oracle as O
     ian, jan = O.sparse_structure("2D", 1, (n, n), (0, 0))
     return np.concatenate([ian, jan])
+
+
+def _host_residual(oracle, model, parms, ipar, y):
+    """f(y) evaluated by the oracle's host model (independent of every CUDA kernel)"""
+    func = C.cast(oracle.model(model, parms), oracle.DERIV)
+    n = len(y)
+    f = np.zeros(n)
+    ipfull = np.concatenate([[0, 0, 3 + len(ipar)], ipar]).astype(np.int32)
+    neq, t = C.c_int(n), C.c_double(0.0)
+    func(C.byref(neq), C.byref(t), H.dp(np.ascontiguousarray(y)), H.dp(f), H.dp(np.zeros(1)), H.ip(ipfull))
+    return f
+
+
+def _accept(y, f, atol=1e-10, rtol=1e-10):
+    """the reference's own acceptance test (src/sparse.f:126-129): max |f / ewt| with ewt = rtol|y| + atol"""
+    return float(np.max(np.abs(f) / (rtol * np.abs(y) + atol)))
+
+
+def test_config_c2_full_size(built, oracle):
+    """BASELINE config C2: steady.1D, nspec=5, 200 000 boxes (N = 10^6) -- beyond what the oracle's Yale solve does in
+    seconds.  Checked: closed-form nnz, ngp = 3*nspec, steady, and the state passes the reference's residual test when
+    f is evaluated by the oracle's host model; a one-Newton-step-accuracy bound follows from ctol."""
+    import rootsolve_b200 as rs
+    nb, ns = 200000, 5
+    ipar = [ns, nb, 1, 1, 0]
+    out = rs.steady_1D(np.full(ns * nb, 1.0), nspec=ns, method="stodes", func="rt1d", parms=H.P_RT1D, positive=True,
+                       ipar=ipar, **H.TOL)
+    A = out.attributes
+    n = ns * nb
+    assert A["steady"] and A["dims"]["nnz"] == n * (2 + ns) - 2 * ns and A["dims"]["ngp"] == 3 * ns
+    f = _host_residual(oracle, "rt1d", H.P_RT1D, ipar, out["y"])
+    assert _accept(out["y"], f) <= 1.0 or np.abs(f).max() <= 1e-8
+    assert out["y"].min() >= 0 and out["y"].max() <= 1.0 + 1e-9
+    # far downstream the column no longer changes: the last boxes of every species agree with their neighbours
+    Y = out["y"].reshape(ns, nb)
+    assert np.allclose(Y[:, -1], Y[:, -2], rtol=0, atol=1e-9)
+
+
+def test_config_c4_full_size(built, oracle):
+    """BASELINE config C4: steady.3D 128^3, two species (N = 4.19 M) -- infeasible for the reference (32-bit work array).
+    Checked: closed-form nnz, steady, the reference's residual test with the host model, positivity, and the mirror
+    symmetries of the cube."""
+    import rootsolve_b200 as rs
+    d = 128
+    nc = d ** 3
+    ipar = [2, d, d, d, 0]
+    y0 = np.concatenate([np.full(nc, 10.0), np.full(nc, 1.0)])
+    out = rs.steady_3D(y0, func="rd3d", parms=H.P_RD3D, nspec=2, dimens=[d, d, d], positive=True, ipar=ipar, **H.TOL)
+    A = out.attributes
+    n = 2 * nc
+    assert A["steady"] and A["dims"]["nnz"] == n * (6 + 2) - 2 * 2 * 3 * d * d
+    assert 16 <= A["dims"]["ngp"] <= 24
+    f = _host_residual(oracle, "rd3d", H.P_RD3D, ipar, out["y"])
+    assert _accept(out["y"], f) <= 1.0 or np.abs(f).max() <= 1e-8
+    assert out["y"].min() >= 0
+    U = out["y"][:nc].reshape(d, d, d)
+    assert np.allclose(U, U[::-1], rtol=0, atol=1e-7) and np.allclose(U, U.transpose(1, 0, 2), rtol=0, atol=1e-7)
+
+
+def test_config_c3_full_size(built, oracle):
+    """BASELINE config C3: steady.2D 2048 x 2048 Monod (N = 4.19 M)."""
+    import rootsolve_b200 as rs
+    d = 2048
+    ipar = [1, d, d, 1, 1]
+    out = rs.steady_2D(np.full(d * d, 10.0), func="diff2d", parms=H.P_DIFF2D_MONOD, dimens=[d, d], positive=True,
+                       ipar=ipar, **H.TOL)
+    A = out.attributes
+    assert A["steady"] and A["dims"]["nnz"] == d * d * 5 - 4 * d and A["dims"]["ngp"] == 7
+    f = _host_residual(oracle, "diff2d", H.P_DIFF2D_MONOD, ipar, out["y"])
+    assert _accept(out["y"], f) <= 1.0 or np.abs(f).max() <= 1e-8
+    Y = out["y"].reshape(d, d)
+    assert np.allclose(Y, Y[::-1, :], rtol=0, atol=1e-8) and np.allclose(Y, Y.T, rtol=0, atol=1e-8)
 
 
 def test_full_size_properties(built):
