@@ -8,6 +8,9 @@
 // Messages are small (a 256^2 plane is 512 KiB), so the cost is latency, not bandwidth: all sends
 // and receives of one exchange go into a single NCCL group, on the solver's stream, with no host
 // synchronisation.
+#include <cstdlib>
+#include <vector>
+
 #include "solver.cuh"
 
 #ifdef RS_WITH_NCCL
@@ -32,6 +35,157 @@ static int g_nranks = 1, g_rank = 0;
 bool comm_active() { return g_comm != nullptr && g_nranks > 1; }
 int comm_nranks() { return g_nranks; }
 int comm_rank() { return g_rank; }
+
+// ---- NVLink peer mailboxes (see PeerRed in rs_internal.cuh) -------------------------------------
+static double *g_mail_local = nullptr;
+static double *g_mail[PEER_MAX] = {nullptr};
+static bool g_peer_ok = false;
+static unsigned g_seq = 0;
+
+bool comm_peer_enabled() { return g_peer_ok && comm_active(); }
+
+PeerRed comm_next_peer_red()
+{
+    PeerRed pr;
+    if (!comm_peer_enabled()) return pr;
+    pr.nranks = g_nranks;
+    pr.rank = g_rank;
+    pr.seq = ++g_seq;
+    for (int p = 0; p < g_nranks; p++) pr.mail[p] = g_mail[p];
+    return pr;
+}
+
+// Maps every rank's mailbox into every process (CUDA IPC over NVLink P2P).  Any failure simply leaves
+// the NCCL all-reduce path in charge.
+static void peer_setup()
+{
+    g_peer_ok = false;
+    if (g_nranks > PEER_MAX || getenv("RS_NO_PEER")) return;
+    const size_t bytes = sizeof(double) * (2 * PEER_MAX * PEER_SLOT + 8);   // reduction slots + halo flag words
+    if (cudaMalloc((void **)&g_mail_local, bytes) != cudaSuccess) { cudaGetLastError(); return; }
+    cudaMemset(g_mail_local, 0, bytes);
+    cudaIpcMemHandle_t mine;
+    if (cudaIpcGetMemHandle(&mine, g_mail_local) != cudaSuccess) { cudaGetLastError(); return; }
+    char *d_h = nullptr;
+    const size_t hs = sizeof(cudaIpcMemHandle_t);
+    if (cudaMalloc((void **)&d_h, hs * g_nranks) != cudaSuccess) { cudaGetLastError(); return; }
+    cudaMemcpy(d_h + hs * g_rank, &mine, hs, cudaMemcpyHostToDevice);
+    std::vector<cudaIpcMemHandle_t> all(g_nranks);
+    int ok = 1;
+    if (ncclAllGather(d_h + hs * g_rank, d_h, hs, ncclChar, g_comm, nullptr) != ncclSuccess) ok = 0;
+    if (ok && cudaStreamSynchronize(nullptr) != cudaSuccess) ok = 0;
+    if (ok) cudaMemcpy(all.data(), d_h, hs * g_nranks, cudaMemcpyDeviceToHost);
+    for (int p = 0; ok && p < g_nranks; p++) {
+        if (p == g_rank) { g_mail[p] = g_mail_local; continue; }
+        void *ptr = nullptr;
+        if (cudaIpcOpenMemHandle(&ptr, all[p], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+        g_mail[p] = (double *)ptr;
+    }
+    // everybody must agree, and nobody may use a mailbox before all of them are mapped
+    int *d_ok = (int *)d_h;
+    cudaMemcpy(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice);
+    if (ncclAllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, g_comm, nullptr) == ncclSuccess && cudaStreamSynchronize(nullptr) == cudaSuccess)
+        cudaMemcpy(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost);
+    else
+        ok = 0;
+    cudaFree(d_h);
+    g_peer_ok = ok != 0;
+    g_seq = 0;
+}
+
+// ---- halo push: neighbours' vectors mapped for direct stores --------------------------------------
+static unsigned g_halo_seq = 0;
+
+// Maps the slab neighbours' copies of `count` vectors (allocation bases) into this process.
+// lo[i] / hi[i] receive the lower / upper neighbour's pointer for vector i (nullptr at the ends).
+// Collective over all ranks.  Returns false (and leaves the NCCL halo exchange in charge) on any failure.
+bool comm_share_vectors(void *const *mine, int count, void **lo, void **hi)
+{
+    for (int i = 0; i < count; i++) { lo[i] = nullptr; hi[i] = nullptr; }
+    if (!comm_peer_enabled() || count > 4) return false;
+    const size_t hs = sizeof(cudaIpcMemHandle_t);
+    std::vector<cudaIpcMemHandle_t> own(count), all((size_t)count * g_nranks);
+    int ok = 1;
+    for (int i = 0; i < count; i++)
+        if (cudaIpcGetMemHandle(&own[i], mine[i]) != cudaSuccess) { cudaGetLastError(); ok = 0; }
+    char *d_h = nullptr;
+    if (cudaMalloc((void **)&d_h, hs * count * g_nranks + 64) != cudaSuccess) { cudaGetLastError(); return false; }
+    cudaMemcpy(d_h + hs * count * g_rank, own.data(), hs * count, cudaMemcpyHostToDevice);
+    if (ncclAllGather(d_h + hs * count * g_rank, d_h, hs * count, ncclChar, g_comm, nullptr) != ncclSuccess) ok = 0;
+    if (cudaStreamSynchronize(nullptr) != cudaSuccess) ok = 0;
+    if (ok) cudaMemcpy(all.data(), d_h, hs * count * g_nranks, cudaMemcpyDeviceToHost);
+    for (int i = 0; ok && i < count; i++) {
+        if (g_rank > 0 && cudaIpcOpenMemHandle(&lo[i], all[(size_t)(g_rank - 1) * count + i], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); lo[i] = nullptr; ok = 0; }
+        if (g_rank < g_nranks - 1 && cudaIpcOpenMemHandle(&hi[i], all[(size_t)(g_rank + 1) * count + i], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); hi[i] = nullptr; ok = 0; }
+    }
+    int *d_ok = (int *)d_h;
+    cudaMemcpy(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice);
+    if (ncclAllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, g_comm, nullptr) == ncclSuccess && cudaStreamSynchronize(nullptr) == cudaSuccess)
+        cudaMemcpy(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost);
+    else
+        ok = 0;
+    cudaFree(d_h);
+    if (!ok) comm_unshare_vectors(count, lo, hi);
+    return ok != 0;
+}
+
+void comm_unshare_vectors(int count, void **lo, void **hi)
+{
+    for (int i = 0; i < count; i++) {
+        if (lo[i]) cudaIpcCloseMemHandle(lo[i]);
+        if (hi[i]) cudaIpcCloseMemHandle(hi[i]);
+        lo[i] = hi[i] = nullptr;
+    }
+}
+
+// Pool of two peer-mapped vectors, grown on demand, released with the communicator.
+static size_t g_pool_n = 0;
+static double *g_pool_mine[2] = {nullptr, nullptr};
+static void *g_pool_lo[2] = {nullptr, nullptr}, *g_pool_hi[2] = {nullptr, nullptr};
+static bool g_pool_ok = false;
+
+static void pool_release()
+{
+    if (g_pool_ok) comm_unshare_vectors(2, g_pool_lo, g_pool_hi);
+    for (int i = 0; i < 2; i++) { if (g_pool_mine[i]) cudaFree(g_pool_mine[i]); g_pool_mine[i] = nullptr; }
+    g_pool_n = 0;
+    g_pool_ok = false;
+}
+
+bool comm_pooled_vectors(size_t n, double **mine, void **lo, void **hi)
+{
+    if (!comm_peer_enabled()) return false;
+    if (!g_pool_ok || g_pool_n < n) {   // every rank asks for the same n in the same order: the branch is collective
+        cudaDeviceSynchronize();
+        pool_release();
+        int ok = 1;
+        for (int i = 0; i < 2; i++)
+            if (cudaMalloc((void **)&g_pool_mine[i], (n + 8) * sizeof(double)) != cudaSuccess) { cudaGetLastError(); g_pool_mine[i] = nullptr; ok = 0; }
+        for (int i = 0; ok && i < 2; i++) cudaMemset(g_pool_mine[i], 0, (n + 8) * sizeof(double));
+        void *m[2] = {g_pool_mine[0], g_pool_mine[1]};
+        // the share is collective even if this rank failed to allocate: pass what we have, it reports failure for all
+        g_pool_ok = (g_pool_mine[0] && g_pool_mine[1]) ? comm_share_vectors(m, 2, g_pool_lo, g_pool_hi) : false;
+        if (!g_pool_ok) { pool_release(); return false; }
+        g_pool_n = n;
+    }
+    for (int i = 0; i < 2; i++) { mine[i] = g_pool_mine[i]; lo[i] = g_pool_lo[i]; hi[i] = g_pool_hi[i]; }
+    return true;
+}
+
+// flag words of the halo handshake live behind the reduction slots of every mailbox:
+//   [HALO_FROM_LO] is written by rank-1, [HALO_FROM_HI] by rank+1
+HaloSignal comm_next_halo_signal()
+{
+    HaloSignal hs;
+    if (!comm_peer_enabled()) return hs;
+    hs.seq = ++g_halo_seq;
+    const size_t off = (size_t)2 * PEER_MAX * PEER_SLOT;
+    hs.wait_lo = g_rank > 0 ? g_mail_local + off + 0 : nullptr;
+    hs.wait_hi = g_rank < g_nranks - 1 ? g_mail_local + off + 1 : nullptr;
+    hs.tell_lo = g_rank > 0 ? g_mail[g_rank - 1] + off + 1 : nullptr;              // I am their upper neighbour
+    hs.tell_hi = g_rank < g_nranks - 1 ? g_mail[g_rank + 1] + off + 0 : nullptr;   // I am their lower neighbour
+    return hs;
+}
 
 int comm_allreduce_sum(Ctx &c, double *d_buf, int count)
 {
@@ -86,6 +240,12 @@ int comm_gather_slabs(Ctx &c, double *v, int nspec, int ncell, int plane, int d1
 }
 #else
 bool comm_active() { return false; }
+bool comm_peer_enabled() { return false; }
+PeerRed comm_next_peer_red() { return PeerRed(); }
+bool comm_share_vectors(void *const *, int count, void **lo, void **hi) { for (int i = 0; i < count; i++) lo[i] = hi[i] = nullptr; return false; }
+bool comm_pooled_vectors(size_t, double **, void **, void **) { return false; }
+void comm_unshare_vectors(int, void **, void **) {}
+HaloSignal comm_next_halo_signal() { return HaloSignal(); }
 int comm_nranks() { return 1; }
 int comm_rank() { return 0; }
 int comm_allreduce_sum(Ctx &, double *, int) { return RS_OK; }
@@ -125,6 +285,7 @@ extern "C" int rs_comm_init(int nranks, int rank, const char id[128])
     if (r != ncclSuccess) { g_comm = nullptr; set_error("ncclCommInitRank failed: %s", ncclGetErrorString(r)); return RS_ECOMM; }
     g_nranks = nranks;
     g_rank = rank;
+    peer_setup();
     return RS_OK;
 #else
     (void)nranks; (void)rank; (void)id;
@@ -139,7 +300,18 @@ extern "C" int rs_comm_rank(void) { return rs::comm_rank(); }
 extern "C" void rs_comm_finalize(void)
 {
 #ifdef RS_WITH_NCCL
-    if (rs::g_comm) { ncclCommDestroy(rs::g_comm); rs::g_comm = nullptr; rs::g_nranks = 1; rs::g_rank = 0; }
+    if (rs::g_comm) {
+        cudaDeviceSynchronize();
+        for (int p = 0; p < rs::PEER_MAX; p++) {
+            if (rs::g_mail[p] && rs::g_mail[p] != rs::g_mail_local) cudaIpcCloseMemHandle(rs::g_mail[p]);
+            rs::g_mail[p] = nullptr;
+        }
+        rs::pool_release();
+        if (rs::g_mail_local) { cudaFree(rs::g_mail_local); rs::g_mail_local = nullptr; }
+        rs::g_peer_ok = false;
+        ncclCommDestroy(rs::g_comm);
+        rs::g_comm = nullptr; rs::g_nranks = 1; rs::g_rank = 0;
+    }
 #endif
 }
 

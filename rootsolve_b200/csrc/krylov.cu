@@ -58,8 +58,9 @@ __global__ void __launch_bounds__(256) spmv_kernel(int row0, int row1, const int
                                                    const int *__restrict__ col, const double *__restrict__ val,
                                                    const double *__restrict__ x, double *__restrict__ y,
                                                    const double *__restrict__ w, double *partials, unsigned *ticket,
-                                                   double *out, int accumulate)
+                                                   double *out, int accumulate, PeerRed pr, HaloSignal hw)
 {
+    halo_wait(hw);
     const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x % LANES;
     const long long stride = ((long long)gridDim.x * blockDim.x) / LANES;
@@ -83,20 +84,20 @@ __global__ void __launch_bounds__(256) spmv_kernel(int row0, int row1, const int
             if (NDOT == 2) { acc[0] += sum * w[r]; acc[1] += sum * sum; }
         }
     }
-    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out, accumulate != 0);
+    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out, accumulate != 0, &pr);
 }
 
 template <int NDOT>
 static void spmv_dispatch(cudaStream_t st, int lanes, int row0, int row1, const int *rowptr, const int *col,
                           const double *val, const double *x, double *y, const double *w, double *partials,
-                          unsigned *ticket, double *out, int accumulate)
+                          unsigned *ticket, double *out, int accumulate, const PeerRed &pr, const HaloSignal &hw)
 {
     const int blocks = grid_for((long long)(row1 - row0) * lanes, 256, 148 * 8);
     switch (lanes) {
-    case 4: spmv_kernel<4, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate); break;
-    case 8: spmv_kernel<8, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate); break;
-    case 16: spmv_kernel<16, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate); break;
-    default: spmv_kernel<32, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate); break;
+    case 4: spmv_kernel<4, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate, pr, hw); break;
+    case 8: spmv_kernel<8, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate, pr, hw); break;
+    case 16: spmv_kernel<16, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate, pr, hw); break;
+    default: spmv_kernel<32, NDOT><<<blocks, 256, 0, st>>>(row0, row1, rowptr, col, val, x, y, w, partials, ticket, out, accumulate, pr, hw); break;
     }
 }
 
@@ -107,7 +108,7 @@ int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const
                 double *y, int lanes)
 {
     Launch L(c, K_SPMV, spmv_bytes(n, nnz));
-    spmv_dispatch<0>(c.stream, lanes, 0, n, rowptr, col, val, x, y, nullptr, nullptr, nullptr, nullptr, 0);
+    spmv_dispatch<0>(c.stream, lanes, 0, n, rowptr, col, val, x, y, nullptr, nullptr, nullptr, nullptr, 0, PeerRed(), HaloSignal());
     RS_CUDA(cudaGetLastError());
     return RS_OK;
 }
@@ -196,7 +197,7 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int row0, int row
                                                                const int *__restrict__ col, const double *__restrict__ val,
                                                                const double *__restrict__ x, double *__restrict__ y,
                                                                const double *__restrict__ w, double *partials,
-                                                               unsigned *ticket, double *out, int accumulate)
+                                                               unsigned *ticket, double *out, int accumulate, PeerRed pr, HaloSignal hw)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(8) unsigned long long full[TMA_STAGES], empty[TMA_STAGES];
@@ -207,6 +208,7 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int row0, int row
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    halo_wait(hw);   // the halo planes of x have been pushed by both neighbours
     const int my_tiles = (ntiles > (int)blockIdx.x) ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
     double acc[NDOT > 0 ? NDOT : 1] = {0.0};
     if (warp == TMA_CONSUMER_WARPS) {
@@ -273,7 +275,7 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int row0, int row
             r = rn; pb = pbn; pe = pen;
         }
     }
-    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out, accumulate != 0);
+    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out, accumulate != 0, &pr);
 }
 
 // largest number of staged nonzeros any tile of [row0, row1) needs
@@ -288,18 +290,20 @@ __global__ void tma_tile_max_kernel(int row0, int row1, int ntiles, const int *_
 
 // y = A x over the rank's rows, with NDOT fused dots (accumulated over the ranges into out[])
 template <int NDOT>
-static void spmv_run(const Krylov &k, cudaStream_t st, const double *x, double *y, const double *w, double *out)
+static void spmv_run(const Krylov &k, cudaStream_t st, const double *x, double *y, const double *w, double *out,
+                     const PeerRed &peer, const HaloSignal &hw)
 {
     for (int q = 0; q < k.own.n; q++) {
         const int row0 = k.own.b[q], row1 = k.own.e[q];
         if (row1 <= row0) continue;
+        const PeerRed pr = (q == k.own.n - 1) ? peer : PeerRed();   // the ranks meet once, after the last range
         if (k.tma_ok) {
             const int ntiles = (row1 - row0 + TMA_ROWS - 1) / TMA_ROWS;
             const int grid = std::min(ntiles, k.tma_sms * k.tma_per_sm);
             spmv_tma_kernel<NDOT><<<grid, TMA_THREADS, TMA_SMEM_BYTES, st>>>(row0, row1, ntiles, k.rowptr, k.col, k.val, x, y, w,
-                                                                             k.partials.p, k.ticket.p, out, q > 0);
+                                                                             k.partials.p, k.ticket.p, out, q > 0, pr, hw);
         } else {
-            spmv_dispatch<NDOT>(st, k.lanes, row0, row1, k.rowptr, k.col, k.val, x, y, w, k.partials.p, k.ticket.p, out, q > 0);
+            spmv_dispatch<NDOT>(st, k.lanes, row0, row1, k.rowptr, k.col, k.val, x, y, w, k.partials.p, k.ticket.p, out, q > 0, pr, hw);
         }
     }
 }
@@ -398,7 +402,8 @@ template <int PRE>
 __global__ void __launch_bounds__(256) update_p_kernel(int b, int e, int nspec, int ncell, int first, const double *scal,
                                                        int cur, const double *__restrict__ r, const double *__restrict__ v,
                                                        double *__restrict__ p, double *__restrict__ ph,
-                                                       const double *__restrict__ dinv, const double *__restrict__ binv)
+                                                       const double *__restrict__ dinv, const double *__restrict__ binv,
+                                                       HaloPush hp, unsigned *hticket)
 {
     double beta = 0.0, omega = 0.0;
     if (!first) {
@@ -423,19 +428,24 @@ __global__ void __launch_bounds__(256) update_p_kernel(int b, int e, int nspec, 
                 double a = 0.0;
                 for (int q = 0; q < nspec; q++) a += binv[((long long)s * nspec + q) * ncell + c] * pv[q];
                 ph[(long long)s * ncell + c] = a;
+                if (hp.lo != nullptr && c < b + hp.plane) hp.lo[(long long)s * ncell + c] = a;
+                if (hp.hi != nullptr && c >= e - hp.plane) hp.hi[(long long)s * ncell + c] = a;
             }
         }
     } else {
         const double2 *r2 = reinterpret_cast<const double2 *>(r), *v2 = reinterpret_cast<const double2 *>(v);
         const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
         double2 *p2 = reinterpret_cast<double2 *>(p), *ph2 = reinterpret_cast<double2 *>(ph);
-#define P_ONE(i) { const double pn = first ? r[i] : r[i] + beta * (p[i] - omega * v[i]); p[i] = pn; ph[i] = (PRE == 1) ? dinv[i] * pn : pn; }
+#define P_ONE(i) { const double pn = first ? r[i] : r[i] + beta * (p[i] - omega * v[i]); p[i] = pn; const double ph_ = (PRE == 1) ? dinv[i] * pn : pn; \
+                   ph[i] = ph_; halo_store(hp, b, e, i, ph_); }
 #define P_TWO(i) { double2 pn = r2[i]; if (!first) { const double2 po = p2[i], vo = v2[i]; pn.x += beta * (po.x - omega * vo.x); pn.y += beta * (po.y - omega * vo.y); } \
-                   p2[i] = pn; if (PRE == 1) { const double2 d = d2[i]; pn.x *= d.x; pn.y *= d.y; } ph2[i] = pn; }
+                   p2[i] = pn; if (PRE == 1) { const double2 d = d2[i]; pn.x *= d.x; pn.y *= d.y; } ph2[i] = pn; \
+                   halo_store(hp, b, e, 2 * (i), pn.x); halo_store(hp, b, e, 2 * (i) + 1, pn.y); }
         RS_RANGE_LOOP(b, e, P_ONE, P_TWO);
 #undef P_ONE
 #undef P_TWO
     }
+    halo_signal_done(hp, hticket);
 }
 
 // s = r - alpha v ; sh = M^-1 s
@@ -443,7 +453,8 @@ template <int PRE>
 __global__ void __launch_bounds__(256) update_s_kernel(int b, int e, int nspec, int ncell, const double *scal, int cur,
                                                        const double *__restrict__ r, const double *__restrict__ v,
                                                        double *__restrict__ s_, double *__restrict__ sh,
-                                                       const double *__restrict__ dinv, const double *__restrict__ binv)
+                                                       const double *__restrict__ dinv, const double *__restrict__ binv,
+                                                       HaloPush hp, unsigned *hticket)
 {
     const double rho = scal[SLOT * (cur ^ 1) + S_RHONEXT];
     double alpha = rho / scal[SLOT * cur + S_R0V];
@@ -461,19 +472,23 @@ __global__ void __launch_bounds__(256) update_s_kernel(int b, int e, int nspec, 
                 double a = 0.0;
                 for (int q = 0; q < nspec; q++) a += binv[((long long)s * nspec + q) * ncell + c] * sv[q];
                 sh[(long long)s * ncell + c] = a;
+                if (hp.lo != nullptr && c < b + hp.plane) hp.lo[(long long)s * ncell + c] = a;
+                if (hp.hi != nullptr && c >= e - hp.plane) hp.hi[(long long)s * ncell + c] = a;
             }
         }
     } else {
         const double2 *r2 = reinterpret_cast<const double2 *>(r), *v2 = reinterpret_cast<const double2 *>(v);
         const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
         double2 *s2 = reinterpret_cast<double2 *>(s_), *sh2 = reinterpret_cast<double2 *>(sh);
-#define S_ONE(i) { const double sn = r[i] - alpha * v[i]; s_[i] = sn; sh[i] = (PRE == 1) ? dinv[i] * sn : sn; }
+#define S_ONE(i) { const double sn = r[i] - alpha * v[i]; s_[i] = sn; const double sh_ = (PRE == 1) ? dinv[i] * sn : sn; sh[i] = sh_; halo_store(hp, b, e, i, sh_); }
 #define S_TWO(i) { const double2 ro = r2[i], vo = v2[i]; double2 sn; sn.x = ro.x - alpha * vo.x; sn.y = ro.y - alpha * vo.y; s2[i] = sn; \
-                   if (PRE == 1) { const double2 d = d2[i]; sn.x *= d.x; sn.y *= d.y; } sh2[i] = sn; }
+                   if (PRE == 1) { const double2 d = d2[i]; sn.x *= d.x; sn.y *= d.y; } sh2[i] = sn; \
+                   halo_store(hp, b, e, 2 * (i), sn.x); halo_store(hp, b, e, 2 * (i) + 1, sn.y); }
         RS_RANGE_LOOP(b, e, S_ONE, S_TWO);
 #undef S_ONE
 #undef S_TWO
     }
+    halo_signal_done(hp, hticket);
 }
 
 // x += alpha ph + omega sh ; r = s - omega t ; out = { <r,r>, <r0,r> }
@@ -481,7 +496,7 @@ __global__ void __launch_bounds__(256) update_xr_kernel(int b, int e, double *sc
                                                         const double *__restrict__ sh, const double *__restrict__ s_,
                                                         const double *__restrict__ t, const double *__restrict__ r0,
                                                         double *__restrict__ x, double *__restrict__ r,
-                                                        double *partials, unsigned *ticket, int accumulate)
+                                                        double *partials, unsigned *ticket, int accumulate, PeerRed pr)
 {
     double *slot = scal + SLOT * cur;
     const double rho = scal[SLOT * (cur ^ 1) + S_RHONEXT];
@@ -505,13 +520,13 @@ __global__ void __launch_bounds__(256) update_xr_kernel(int b, int e, double *sc
     RS_RANGE_LOOP(b, e, X_ONE, X_TWO);
 #undef X_ONE
 #undef X_TWO
-    grid_reduce<2>(acc, 0u, partials, ticket, slot + S_RR, accumulate != 0);
+    grid_reduce<2>(acc, 0u, partials, ticket, slot + S_RR, accumulate != 0, &pr);
 }
 
 // r = r0 = b ; x = 0 ; out = <b,b>
 __global__ void __launch_bounds__(256) krylov_init_kernel(int b, int e, const double *__restrict__ rhs, double *__restrict__ r,
                                                           double *__restrict__ r0, double *__restrict__ x,
-                                                          double *partials, unsigned *ticket, double *scal, int accumulate)
+                                                          double *partials, unsigned *ticket, double *scal, int accumulate, PeerRed pr)
 {
     double acc[1] = {0.0};
     for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
@@ -519,14 +534,14 @@ __global__ void __launch_bounds__(256) krylov_init_kernel(int b, int e, const do
         r[i] = bi; r0[i] = bi; x[i] = 0.0;
         acc[0] += bi * bi;
     }
-    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_BNORM, accumulate != 0);
+    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_BNORM, accumulate != 0, &pr);
 }
 
 // restart: r = r0 = b - Ax (Ax given) ; out = <r,r> (the true residual)
 __global__ void __launch_bounds__(256) krylov_restart_kernel(int b, int e, const double *__restrict__ rhs,
                                                              const double *__restrict__ ax, double *__restrict__ r,
                                                              double *__restrict__ r0, double *partials,
-                                                             unsigned *ticket, double *scal, int accumulate)
+                                                             unsigned *ticket, double *scal, int accumulate, PeerRed pr)
 {
     double acc[1] = {0.0};
     for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
@@ -534,7 +549,7 @@ __global__ void __launch_bounds__(256) krylov_restart_kernel(int b, int e, const
         r[i] = ri; r0[i] = ri;
         acc[0] += ri * ri;
     }
-    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_RTRUE, accumulate != 0);
+    grid_reduce<1>(acc, 0u, partials, ticket, scal + S_RTRUE, accumulate != 0, &pr);
 }
 
 // rho_0 = <r0, r> = ||r||^2 goes where step 0 looks for "rho of the previous step"
@@ -596,9 +611,20 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
         }
     }
     RS_TRY(k.r.alloc(n)); RS_TRY(k.r0.alloc(n)); RS_TRY(k.p.alloc(n)); RS_TRY(k.v.alloc(n));
-    RS_TRY(k.s.alloc(n)); RS_TRY(k.t.alloc(n)); RS_TRY(k.ph.alloc(n)); RS_TRY(k.sh.alloc(n));
-    if (comm_active()) {  // halo planes are read before they are first received only if left uninitialised
-        RS_TRY(k.ph.zero(c.stream)); RS_TRY(k.sh.zero(c.stream));
+    RS_TRY(k.s.alloc(n)); RS_TRY(k.t.alloc(n));
+    // ph / sh are the SpMV inputs, i.e. the vectors whose halo planes travel.  With NVLink halo push they
+    // come from a process-wide pool that stays mapped into the neighbours (mapping per solve would cost
+    // far more than the solve); otherwise they are ordinary buffers filled by ncclSend/Recv.
+    k.push_ok = false;
+    if (comm_peer_enabled() && k.halo.nspec > 0 && !getenv("RS_NO_PUSH")) {
+        double *mine[2] = {nullptr, nullptr};
+        k.push_ok = comm_pooled_vectors((size_t)n, mine, k.nb_lo, k.nb_hi);
+        if (k.push_ok) { k.ph_v = mine[0]; k.sh_v = mine[1]; }
+    }
+    if (!k.push_ok) {
+        RS_TRY(k.ph.alloc(n)); RS_TRY(k.sh.alloc(n));
+        if (comm_active()) { RS_TRY(k.ph.zero(c.stream)); RS_TRY(k.sh.zero(c.stream)); }
+        k.ph_v = k.ph.p; k.sh_v = k.sh.p;
     }
     if (precond == RS_PRECOND_JACOBI) RS_TRY(k.dinv.alloc(n));
     if (precond == RS_PRECOND_BLOCK_JACOBI) RS_TRY(k.binv.alloc((size_t)nspec * nspec * ncell));
@@ -633,6 +659,19 @@ int krylov_precond_update(Ctx &c, Krylov &k)
 
 static inline double own_nnz_estimate(const Krylov &k) { return (double)k.nnz * (double)k.own.total() / (double)k.n; }
 
+// descriptor for pushing the first / last owned plane of vector `vi` (0: ph, 1: sh) to the slab neighbours
+static HaloPush make_push(const Krylov &k, int vi, const HaloSignal &sig, bool last_launch)
+{
+    HaloPush hp;
+    if (!k.push_ok) return hp;
+    hp.lo = (double *)k.nb_lo[vi];
+    hp.hi = (double *)k.nb_hi[vi];
+    hp.plane = k.halo.plane;
+    hp.signal = last_launch ? 1 : 0;
+    hp.sig = sig;
+    return hp;
+}
+
 // One BiCGStab step; the raw dot products land in slot(cur).
 static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
 {
@@ -640,54 +679,65 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     double *slot = k.scal.p + SLOT * cur;
     const double rows = (double)k.own.total();
     const double pre_bytes = (k.precond == RS_PRECOND_BLOCK_JACOBI) ? 8.0 * k.nspec * rows : (k.precond == RS_PRECOND_JACOBI ? 8.0 * rows : 0.0);
+    // halo handshakes of this step (sequence numbers advance identically on every rank)
+    const HaloSignal sig_p = k.push_ok ? comm_next_halo_signal() : HaloSignal();
+    const HaloSignal sig_s = k.push_ok ? comm_next_halo_signal() : HaloSignal();
     {
         Launch L(c, K_VEC, (first ? 24.0 : 40.0) * rows + pre_bytes);
         if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
-            update_p_kernel<2><<<grid_for(k.cell1 - k.cell0, 256), 256, 0, st>>>(k.cell0, k.cell1, k.nspec, k.ncell, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, k.binv.p);
+            update_p_kernel<2><<<grid_for(k.cell1 - k.cell0, 256), 256, 0, st>>>(k.cell0, k.cell1, k.nspec, k.ncell, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph_v, nullptr, k.binv.p,
+                                                                                 make_push(k, 0, sig_p, true), k.ticket.p + 1);
         } else {
             for (int q = 0; q < k.own.n; q++) {
                 const int b = k.own.b[q], e = k.own.e[q];
                 if (k.precond == RS_PRECOND_JACOBI)
-                    update_p_kernel<1><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, k.dinv.p, nullptr);
+                    update_p_kernel<1><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph_v, k.dinv.p, nullptr,
+                                                                                   make_push(k, 0, sig_p, q == k.own.n - 1), k.ticket.p + 1);
                 else
-                    update_p_kernel<0><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph.p, nullptr, nullptr);
+                    update_p_kernel<0><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph_v, nullptr, nullptr,
+                                                                                   make_push(k, 0, sig_p, q == k.own.n - 1), k.ticket.p + 1);
             }
         }
     }
-    RS_TRY(comm_halo_exchange(c, k.ph.p, k.halo));
+    if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.ph_v, k.halo));
     {
         Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)) + 8.0 * rows);
-        spmv_run<1>(k, st, k.ph.p, k.v.p, k.r0.p, slot + S_R0V);
+        spmv_run<1>(k, st, k.ph_v, k.v.p, k.r0.p, slot + S_R0V, comm_next_peer_red(), sig_p);
     }
-    RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
+    if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
     {
         Launch L(c, K_VEC, 32.0 * rows + pre_bytes);
         if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
-            update_s_kernel<2><<<grid_for(k.cell1 - k.cell0, 256), 256, 0, st>>>(k.cell0, k.cell1, k.nspec, k.ncell, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, k.binv.p);
+            update_s_kernel<2><<<grid_for(k.cell1 - k.cell0, 256), 256, 0, st>>>(k.cell0, k.cell1, k.nspec, k.ncell, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh_v, nullptr, k.binv.p,
+                                                                                 make_push(k, 1, sig_s, true), k.ticket.p + 1);
         } else {
             for (int q = 0; q < k.own.n; q++) {
                 const int b = k.own.b[q], e = k.own.e[q];
                 if (k.precond == RS_PRECOND_JACOBI)
-                    update_s_kernel<1><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, k.dinv.p, nullptr);
+                    update_s_kernel<1><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh_v, k.dinv.p, nullptr,
+                                                                                   make_push(k, 1, sig_s, q == k.own.n - 1), k.ticket.p + 1);
                 else
-                    update_s_kernel<0><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh.p, nullptr, nullptr);
+                    update_s_kernel<0><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh_v, nullptr, nullptr,
+                                                                                   make_push(k, 1, sig_s, q == k.own.n - 1), k.ticket.p + 1);
             }
         }
     }
-    RS_TRY(comm_halo_exchange(c, k.sh.p, k.halo));
+    if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.sh_v, k.halo));
     {
         Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)) + 8.0 * rows);
-        spmv_run<2>(k, st, k.sh.p, k.t.p, k.s.p, slot + S_TS);
+        spmv_run<2>(k, st, k.sh_v, k.t.p, k.s.p, slot + S_TS, comm_next_peer_red(), sig_s);
     }
-    RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
+    if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
     {
         Launch L(c, K_VEC, 64.0 * rows);
+        const PeerRed peer = comm_next_peer_red();
         for (int q = 0; q < k.own.n; q++) {
             const int b = k.own.b[q], e = k.own.e[q];
-            update_xr_kernel<<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph.p, k.sh.p, k.s.p, k.t.p, k.r0.p, x, k.r.p, k.partials.p, k.ticket.p, q > 0);
+            update_xr_kernel<<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph_v, k.sh_v, k.s.p, k.t.p, k.r0.p, x, k.r.p, k.partials.p, k.ticket.p, q > 0,
+                                                                         q == k.own.n - 1 ? peer : PeerRed());
         }
     }
-    RS_TRY(comm_allreduce_sum(c, slot + S_RR, 2));
+    if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + S_RR, 2));
     return RS_OK;
 }
 
@@ -699,14 +749,16 @@ static int true_residual_restart(Ctx &c, Krylov &k, const double *b, double *x, 
     RS_TRY(comm_halo_exchange(c, x, k.halo));
     {
         Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)));
-        spmv_run<0>(k, st, x, k.v.p, nullptr, nullptr);
+        spmv_run<0>(k, st, x, k.v.p, nullptr, nullptr, PeerRed(), HaloSignal());
     }
     {
         Launch L(c, K_VEC, 32.0 * rows);
+        const PeerRed peer = comm_next_peer_red();
         for (int q = 0; q < k.own.n; q++)
-            krylov_restart_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, k.v.p, k.r.p, k.r0.p, k.partials.p, k.ticket.p, k.scal.p, q > 0);
+            krylov_restart_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, k.v.p, k.r.p, k.r0.p, k.partials.p, k.ticket.p, k.scal.p, q > 0,
+                                                                                      q == k.own.n - 1 ? peer : PeerRed());
     }
-    RS_TRY(comm_allreduce_sum(c, k.scal.p + S_RTRUE, 1));
+    if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, k.scal.p + S_RTRUE, 1));
     krylov_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, S_RTRUE);
     c.launches++;
     RS_CUDA(cudaMemcpyAsync(k.h_scal + S_RTRUE, k.scal.p + S_RTRUE, sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -726,10 +778,12 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
     {
         Launch L(c, K_VEC, 32.0 * (double)k.own.total());
+        const PeerRed peer = comm_next_peer_red();
         for (int q = 0; q < k.own.n; q++)
-            krylov_init_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, k.r.p, k.r0.p, x, k.partials.p, k.ticket.p, k.scal.p, q > 0);
+            krylov_init_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, k.r.p, k.r0.p, x, k.partials.p, k.ticket.p, k.scal.p, q > 0,
+                                                                                   q == k.own.n - 1 ? peer : PeerRed());
     }
-    RS_TRY(comm_allreduce_sum(c, k.scal.p + S_BNORM, 1));
+    if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, k.scal.p + S_BNORM, 1));
     krylov_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, S_BNORM);
     c.launches++;
     RS_CUDA(cudaMemcpyAsync(k.h_scal + S_BNORM, k.scal.p + S_BNORM, sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -750,7 +804,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     // kernels, four halo exchanges and six all-reduces per host call.  (Not while profiling: the
     // per-launch events cannot live inside a graph.)
     static const bool no_graph = getenv("RS_NO_GRAPH") != nullptr;
-    const bool use_graph = comm_active() && !c.profile && !no_graph;
+    const bool use_graph = comm_active() && !comm_peer_enabled() && !c.profile && !no_graph;   // peer reductions carry a per-launch sequence number
     while (!done && total < k.max_iter) {
         int cur = cycle_it & 1;
         if (use_graph && cycle_it >= 2 && cur == 0 && total + 2 <= k.max_iter) {

@@ -122,14 +122,125 @@ __device__ __forceinline__ double warp_max(double v)
     return v;
 }
 
+// ---- all-reduce over NVLink peer memory, fused into the reducing kernel ------------------------
+// Every rank owns a small mailbox in device memory that all peers have mapped (CUDA IPC).  The last
+// block of a reducing kernel stores its rank's partial results straight into every peer's mailbox
+// (remote stores over NVLink), then waits until all peers' contributions for the same sequence
+// number have landed in its own mailbox and adds them in rank order -- so every rank computes a
+// bitwise identical sum, inside the kernel that produced the partial, with no extra launch.
+// Slots are double-buffered by sequence parity: an all-reduce is a barrier, so a peer can run at
+// most one reduction ahead.  A bounded spin turns a lost peer into NaNs (caught by the host)
+// instead of a hung GPU.
+constexpr int PEER_MAX = 8;
+constexpr int PEER_SLOT = 4;   // doubles per (parity, source rank): two values, the sequence flag, padding
+struct PeerRed {
+    int nranks = 1, rank = 0;
+    unsigned seq = 0;                // sequence number of this reduction (same on every rank)
+    double *mail[PEER_MAX] = {nullptr};   // mail[p]: rank p's mailbox as mapped into this process
+};
+
+// ---- halo push over NVLink --------------------------------------------------------------------
+// The kernel that produces a vector also stores its first / last owned plane straight into the slab
+// neighbours' copies (peer pointers), then the last block tells the neighbours "sequence seq is
+// complete"; the consuming SpMV waits for both neighbours' flags before it touches the halo.  No NCCL
+// call, no extra launch.  Flags only ever grow, so the wait is `flag >= seq`.
+struct HaloSignal {
+    unsigned seq = 0;
+    double *tell_lo = nullptr, *tell_hi = nullptr;         // flag words inside the neighbours' mailboxes
+    const double *wait_lo = nullptr, *wait_hi = nullptr;   // flag words inside my own mailbox
+};
+struct HaloPush {
+    double *lo = nullptr, *hi = nullptr;   // the neighbours' copies of the vector being written (same global indexing)
+    int plane = 0;                         // unknowns per plane
+    int signal = 0;                        // this launch is the last one writing the vector: raise the flags
+    HaloSignal sig;
+};
+
+// store v at global index i into the neighbours' halo if i lies in the first / last plane of [b, e)
+__device__ __forceinline__ void halo_store(const HaloPush &hp, long long b, long long e, long long i, double v)
+{
+    if (hp.lo != nullptr && i < b + hp.plane) hp.lo[i] = v;
+    if (hp.hi != nullptr && i >= e - hp.plane) hp.hi[i] = v;
+}
+
+// end of a producing kernel: once every block's remote stores are out, the last block raises the flags
+__device__ __forceinline__ void halo_signal_done(const HaloPush &hp, unsigned *ticket)
+{
+    if (!hp.signal) return;
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(ticket, 1u);
+        if (t == gridDim.x - 1) {
+            *ticket = 0;
+            __threadfence_system();
+            if (hp.sig.tell_lo) *(volatile double *)hp.sig.tell_lo = (double)hp.sig.seq;
+            if (hp.sig.tell_hi) *(volatile double *)hp.sig.tell_hi = (double)hp.sig.seq;
+        }
+    }
+}
+
+// start of a consuming kernel: every block waits until both neighbours have delivered sequence seq
+__device__ __forceinline__ void halo_wait(const HaloSignal &hs)
+{
+    if (hs.seq == 0) return;
+    if (threadIdx.x == 0) {
+        const double want = (double)hs.seq;
+        const long long t0 = clock64();
+        if (hs.wait_lo) while (*(volatile const double *)hs.wait_lo < want) { if (clock64() - t0 > 4000000000LL) break; }
+        if (hs.wait_hi) while (*(volatile const double *)hs.wait_hi < want) { if (clock64() - t0 > 4000000000LL) break; }
+        __threadfence_system();
+    }
+    __syncthreads();
+}
+
+template <int K>
+__device__ __forceinline__ void peer_allreduce_warp(double (&r)[K], const PeerRed &pr, int lane)
+{
+    static_assert(K <= 2, "mailbox slots carry two values");
+    const int parity = pr.seq & 1u;
+    const double flag = (double)pr.seq;
+    if (lane < pr.nranks) {
+        volatile double *dst = pr.mail[lane] + (size_t)(parity * PEER_MAX + pr.rank) * PEER_SLOT;
+        dst[0] = r[0];
+        if (K > 1) dst[1] = r[K > 1 ? 1 : 0];
+        __threadfence_system();
+        dst[2] = flag;
+    }
+    double got[K];
+#pragma unroll
+    for (int k = 0; k < K; k++) got[k] = 0.0;
+    if (lane < pr.nranks) {
+        volatile double *src = pr.mail[pr.rank] + (size_t)(parity * PEER_MAX + lane) * PEER_SLOT;
+        const long long t0 = clock64();
+        bool ok = true;
+        while (src[2] != flag) {
+            if (clock64() - t0 > 4000000000LL) { ok = false; break; }   // ~2 s: a peer is gone
+        }
+        __threadfence_system();
+        const double nan = __longlong_as_double(0x7ff8000000000000LL);
+        got[0] = ok ? src[0] : nan;
+        if (K > 1) got[K > 1 ? 1 : 0] = ok ? src[1] : nan;
+    }
+    // sum in rank order on every lane -> the same bits on every rank
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        double s = 0.0;
+        for (int p = 0; p < pr.nranks; p++) s += __shfl_sync(0xffffffffu, got[k], p);
+        r[k] = s;
+    }
+}
+
 // Reduces K per-thread values over the block and, across blocks, through
 // per-block partials: the last block to arrive adds the partials in block order
 // (deterministic) and stores the K results in out[0..K).  is_max[k] selects max
 // instead of sum.  `ticket` must be zero on entry and is reset by the last
-// block.  Every thread of the block must call this.
+// block.  Every thread of the block must call this.  With `peer` (sum reductions
+// only) the result is additionally all-reduced over the ranks before it is stored.
 template <int K>
 __device__ __forceinline__ void grid_reduce(double (&v)[K], unsigned max_mask, double *partials,
-                                            unsigned *ticket, double *out, bool accumulate = false)
+                                            unsigned *ticket, double *out, bool accumulate = false,
+                                            const PeerRed *peer = nullptr)
 {
     __shared__ double sh[K][32];
     __shared__ bool is_last;
@@ -158,6 +269,7 @@ __device__ __forceinline__ void grid_reduce(double (&v)[K], unsigned max_mask, d
     if (is_last) {
         __threadfence();
         if (wid == 0) {
+            double res[K];
 #pragma unroll
             for (int k = 0; k < K; k++) {
                 const bool mx = max_mask >> k & 1u;
@@ -169,9 +281,16 @@ __device__ __forceinline__ void grid_reduce(double (&v)[K], unsigned max_mask, d
                 }
                 r = mx ? warp_max(r) : warp_sum(r);
                 // accumulate: a launch per index range of the same reduction (stream order makes it safe)
-                if (lane == 0) out[k] = accumulate ? (mx ? fmax(out[k], r) : out[k] + r) : r;
+                res[k] = accumulate ? (mx ? fmax(out[k], r) : out[k] + r) : r;
             }
-            if (lane == 0) *ticket = 0;
+            if (peer != nullptr && peer->nranks > 1) {
+                if constexpr (K <= 2) peer_allreduce_warp<K>(res, *peer, lane);
+            }
+            if (lane == 0) {
+#pragma unroll
+                for (int k = 0; k < K; k++) out[k] = res[k];
+                *ticket = 0;
+            }
         }
     }
 }

@@ -78,6 +78,9 @@ struct Krylov {
     double *h_scal = nullptr;  // pinned mirror
     int lanes = 8;             // lanes per row of the sub-warp SpMV
     int tma_ok = 0, tma_sms = 0, tma_per_sm = 0;  // the TMA-staged SpMV is usable (every tile fits a stage)
+    double *ph_v = nullptr, *sh_v = nullptr;   // the preconditioned directions (SpMV inputs): own buffers or pooled, peer-mapped ones
+    bool push_ok = false;                  // halos of ph / sh are pushed into the neighbours' vectors over NVLink
+    void *nb_lo[2] = {nullptr, nullptr}, *nb_hi[2] = {nullptr, nullptr};   // neighbours' ph (0) and sh (1)
     cudaGraphExec_t pair_exec = nullptr;   // two BiCGStab steps (slot parities 0 and 1) captured once, replayed
     const double *pair_x = nullptr;        // the solution vector the captured graph updates
     int max_iter = 10000, check_every = 1;
@@ -98,6 +101,15 @@ int pick_lanes(int n, int nnz);
 bool comm_active();
 int comm_nranks();
 int comm_rank();
+// NVLink peer-memory all-reduce fused into the reducing kernels (rs_internal.cuh); falls back to NCCL when off
+bool comm_peer_enabled();
+PeerRed comm_next_peer_red();   // descriptor with the next sequence number (nranks = 1 when disabled)
+// halo push: map the slab neighbours' copies of vectors (collective); handshake flags with the next sequence number
+bool comm_share_vectors(void *const *mine, int count, void **lo, void **hi);
+void comm_unshare_vectors(int count, void **lo, void **hi);
+// two n-vectors from a pool that stays mapped into the slab neighbours for the life of the communicator
+bool comm_pooled_vectors(size_t n, double **mine, void **lo, void **hi);
+HaloSignal comm_next_halo_signal();
 int comm_allreduce_sum(Ctx &c, double *d_buf, int count);
 int comm_allreduce_max(Ctx &c, double *d_buf, int count);
 int comm_halo_exchange(Ctx &c, double *v, const HaloPlan &h);
