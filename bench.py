@@ -252,6 +252,23 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     pk, pk_src = peaks()
+    # DRAM traffic of the SpMV kernel per launch from the committed `ncu --set full` capture (256^3 only)
+    traffic = None
+    prof = os.path.join(ROOT, "profiles", "r01_ncu_spmv_tma_full.json")
+    if S == 256 and world == 1 and os.path.exists(prof):
+        try:
+            unit = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+            rows = json.load(open(prof))
+            tot = []
+            for r_ in rows:
+                t_ = 0.0
+                for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    v_, u_ = r_[key].split()
+                    t_ += float(v_) * unit[u_]
+                tot.append(t_)
+            traffic = sum(tot) / len(tot)
+        except Exception:
+            traffic = None
     sp = kstats.get("spmv_csr", {"ms": 0.0, "launches": 0, "bytes_per_launch": 0.0})
     ach = (sp["bytes_per_launch"] * sp["launches"] / (sp["ms"] * 1e-3) / 1e9) if sp["ms"] > 0 else 0.0
     ms_per_step = ms_total / args.steps
@@ -267,7 +284,8 @@ def run_ours(args):
         "time_to_steady_state_s": ms_per_step * 1e-3, "newton_iters_per_s": newton / (ms_per_step * 1e-3),
         "setup_s": setup_s,
         "roofline": {"bound": "hbm", "kernel": "spmv_csr (+fused dots)", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                     "frac": ach / pk["hbm_gbs"] if pk["hbm_gbs"] else None, "traffic": None, "peak_source": pk_src,
+                     "frac": ach / pk["hbm_gbs"] if pk["hbm_gbs"] else None, "traffic": traffic, "algorithmic_bytes": sp["bytes_per_launch"],
+                     "peak_source": pk_src,
                      "avg_launch_ms": sp["ms"] / sp["launches"] if sp["launches"] else None},
         "kernels": {k: {"ms_per_step": v["ms"] / args.steps, "launches_per_step": v["launches"] / args.steps,
                         "GBps": (v["bytes_per_launch"] * v["launches"] / (v["ms"] * 1e-3) / 1e9) if v["ms"] > 0 else None}

@@ -64,7 +64,7 @@ typedef struct {
     double lin_rtol;        /* ||J x - beta||_2 <= lin_rtol * ||beta||_2 (1e-10) */
     double lin_ewt_factor;  /* ... or rms(J x - beta) <= lin_ewt_factor * min(atol) (5e-4): far below the error
                              * weights, because the error of the state is up to ||J^-1|| times this residual */
-    int check_every;        /* host convergence check period in Krylov iterations (1) */
+    int check_every;        /* host convergence check period in Krylov iterations (4) */
 } rs_krylov_control;
 
 /* POD mirror of the 27 .Call arguments (src/call_stsparse.c:60-64). */

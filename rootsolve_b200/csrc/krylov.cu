@@ -846,7 +846,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
         const double rnorm = finite ? std::sqrt(rr) : best;
         if (finite && rnorm < 0.9 * best) { best = rnorm; since_best = 0; } else since_best++;
         const bool looks_converged = finite && !broke && rnorm <= target;
-        const bool stagnated = since_best >= 25;
+        const bool stagnated = since_best * k.check_every >= 40;   // ~40 steps without a 10 % gain
         if (!(looks_converged || broke || stagnated || total >= k.max_iter)) continue;
         // end of cycle: what did it really achieve?
         double rt = 0.0;

@@ -83,7 +83,10 @@ struct Krylov {
     void *nb_lo[2] = {nullptr, nullptr}, *nb_hi[2] = {nullptr, nullptr};   // neighbours' ph (0) and sh (1)
     cudaGraphExec_t pair_exec = nullptr;   // two BiCGStab steps (slot parities 0 and 1) captured once, replayed
     const double *pair_x = nullptr;        // the solution vector the captured graph updates
-    int max_iter = 10000, check_every = 1;
+    // The host looks at ||r|| every check_every steps: each look drains the stream (a ~20 us bubble, as
+    // long as a whole step on 8 GPUs or on a small grid).  Steps taken after convergence are harmless --
+    // a breakdown there leaves x untouched (update_xr_kernel) -- and cost at most check_every-1 steps.
+    int max_iter = 10000, check_every = 4;
     double lin_rtol = 1e-10, lin_ewt_factor = 5e-4;
     ~Krylov();
 };
