@@ -33,7 +33,11 @@ namespace rs {
 constexpr int MAXS = 8;        // largest species count handled by the block preconditioner
 constexpr int SLOT = 8;        // doubles per parity slot: r0v, ts, tt, rr, rhonext, bad
 constexpr int S_R0V = 0, S_TS = 1, S_TT = 2, S_RR = 3, S_RHONEXT = 4, S_BAD = 5;
-constexpr int S_BNORM = 2 * SLOT, S_RTRUE = 2 * SLOT + 1;
+constexpr int S_BNORM = 2 * SLOT, S_RTRUE = 2 * SLOT + 1, S_SYM = 2 * SLOT + 2;   // S_SYM: two doubles
+// slots of the CG recurrence (same parity scheme): <p,Ap>, <r,r>, <r,z> of the step, breakdown flag
+constexpr int C_PQ = 0, C_RR = 1, C_RZ = 2, C_BAD = 5;
+struct Krylov;
+static inline double own_nnz_estimate(const Krylov &k);
 constexpr int NSCAL = 2 * SLOT + 8;
 
 Krylov::~Krylov()
@@ -637,14 +641,50 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
     return RS_OK;
 }
 
+// out = { max |a_ij - a_ji| , max |a_ij| } over the entries whose row and column both lie in [row0, row1);
+// a missing transposed entry counts with its full size.
+__global__ void __launch_bounds__(256) symmetry_kernel(int row0, int row1, const int *__restrict__ rowptr,
+                                                       const int *__restrict__ col, const double *__restrict__ val,
+                                                       double *partials, unsigned *ticket, double *out, int accumulate)
+{
+    double acc[2] = {0.0, 0.0};
+    for (long long i = row0 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < row1; i += (long long)gridDim.x * blockDim.x) {
+        for (int p = rowptr[i]; p < rowptr[i + 1]; p++) {
+            const int j = col[p];
+            const double a = val[p];
+            acc[1] = fmax(acc[1], fabs(a));
+            if (j > i && j < row1) acc[0] = fmax(acc[0], fabs(a - csr_entry(rowptr, col, val, j, (int)i)));
+            else if (j < i && j >= row0 && csr_entry(rowptr, col, val, j, (int)i) == 0.0) acc[0] = fmax(acc[0], fabs(a));
+        }
+    }
+    grid_reduce<2>(acc, 3u, partials, ticket, out, accumulate != 0);
+}
+
 int krylov_precond_update(Ctx &c, Krylov &k)
 {
+    k.use_cg = false;
     if (k.precond == RS_PRECOND_JACOBI) {
         for (int q = 0; q < k.own.n; q++) {
             const int rows = k.own.e[q] - k.own.b[q];
             if (rows <= 0) continue;
             Launch L(c, K_PRECOND_SETUP, 20.0 * rows);
             jacobi_setup_kernel<<<(rows + 255) / 256, 256, 0, c.stream>>>(k.own.b[q], k.own.e[q], k.rowptr, k.col, k.val, k.dinv.p);
+        }
+        // A Jacobian that is symmetric up to finite-difference noise (single-species diffusion-reaction: the
+        // reference's own examples) is solved by preconditioned CG: one SpMV per step instead of two.
+        static const bool no_cg = getenv("RS_NO_CG") != nullptr;
+        if (!no_cg && k.own.n == 1) {
+            {
+                Launch L(c, K_PRECOND_SETUP, 24.0 * own_nnz_estimate(k));
+                symmetry_kernel<<<grid_for(k.own.e[0] - k.own.b[0], 256), 256, 0, c.stream>>>(k.own.b[0], k.own.e[0], k.rowptr, k.col, k.val,
+                                                                                            k.partials.p, k.ticket.p, k.scal.p + S_SYM, 0);
+            }
+            RS_TRY(comm_allreduce_max(c, k.scal.p + S_SYM, 2));
+            RS_CUDA(cudaMemcpyAsync(k.h_scal + S_SYM, k.scal.p + S_SYM, 2 * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+            RS_CUDA(cudaStreamSynchronize(c.stream));
+            const double da = k.h_scal[S_SYM], amax = k.h_scal[S_SYM + 1];
+            k.asym = amax > 0.0 ? da / amax : 1.0;
+            k.use_cg = (k.asym == k.asym) && k.asym <= 1.0e-6;
         }
     } else if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
         const int cells = k.cell1 - k.cell0;
@@ -767,6 +807,202 @@ static int true_residual_restart(Ctx &c, Krylov &k, const double *b, double *x, 
     return RS_OK;
 }
 
+// ---- preconditioned CG (Jacobi) for Jacobians that are symmetric to FD noise -----------------------
+// Two fused vector kernels + one SpMV per step (BiCGStab: three + two).  p lives in ph_v (the SpMV
+// input whose halo planes travel), q = A p in v.  z = dinv r is never stored.
+
+// p = z + beta p  [first: p = z],  z = dinv r
+__global__ void __launch_bounds__(256) cg_update_p_kernel(int b, int e, int first, const double *scal, int cur,
+                                                          const double *__restrict__ r, const double *__restrict__ dinv,
+                                                          double *__restrict__ p, HaloPush hp, unsigned *hticket)
+{
+    double beta = 0.0;
+    if (!first) {
+        beta = scal[SLOT * (cur ^ 1) + C_RZ] / scal[SLOT * cur + C_RZ];   // rho_k / rho_{k-1}
+        if (!isfinite(beta)) beta = 0.0;
+    }
+    const double2 *r2 = reinterpret_cast<const double2 *>(r), *d2 = reinterpret_cast<const double2 *>(dinv);
+    double2 *p2 = reinterpret_cast<double2 *>(p);
+#define CP_ONE(i) { const double pn = dinv[i] * r[i] + (first ? 0.0 : beta * p[i]); p[i] = pn; halo_store(hp, b, e, i, pn); }
+#define CP_TWO(i) { const double2 rv = r2[i], dv = d2[i]; double2 pn; pn.x = dv.x * rv.x; pn.y = dv.y * rv.y; \
+                    if (!first) { const double2 po = p2[i]; pn.x += beta * po.x; pn.y += beta * po.y; } p2[i] = pn; \
+                    halo_store(hp, b, e, 2 * (i), pn.x); halo_store(hp, b, e, 2 * (i) + 1, pn.y); }
+    RS_RANGE_LOOP(b, e, CP_ONE, CP_TWO);
+#undef CP_ONE
+#undef CP_TWO
+    halo_signal_done(hp, hticket);
+}
+
+// alpha = rho / <p,q> ; x += alpha p ; r -= alpha q ; out = { <r,r>, <r, dinv r> }
+__global__ void __launch_bounds__(256) cg_update_xr_kernel(int b, int e, double *scal, int cur, const double *__restrict__ p,
+                                                           const double *__restrict__ q, const double *__restrict__ dinv,
+                                                           double *__restrict__ x, double *__restrict__ r,
+                                                           double *partials, unsigned *ticket, int accumulate, PeerRed pr)
+{
+    double *slot = scal + SLOT * cur;
+    const double rho = scal[SLOT * (cur ^ 1) + C_RZ];
+    double alpha = rho / slot[C_PQ];
+    // alpha must be positive for a definite matrix (rho and <p,Ap> share the sign of A): anything else means the
+    // matrix is indefinite or the recurrence broke down -- keep x, tell the host.
+    const bool bad = !isfinite(alpha) || !(alpha > 0.0);
+    if (bad) alpha = 0.0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) slot[C_BAD] = bad ? 1.0 : 0.0;
+    double acc[2] = {0.0, 0.0};
+    const double2 *p2 = reinterpret_cast<const double2 *>(p), *q2 = reinterpret_cast<const double2 *>(q);
+    const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
+    double2 *x2 = reinterpret_cast<double2 *>(x), *r2 = reinterpret_cast<double2 *>(r);
+#define CX_ONE(i) { x[i] += alpha * p[i]; const double rn = r[i] - alpha * q[i]; r[i] = rn; acc[0] += rn * rn; acc[1] += rn * dinv[i] * rn; }
+#define CX_TWO(i) { const double2 pv = p2[i], qv = q2[i], dv = d2[i]; double2 xv = x2[i], rn = r2[i]; \
+                    xv.x += alpha * pv.x; xv.y += alpha * pv.y; x2[i] = xv; rn.x -= alpha * qv.x; rn.y -= alpha * qv.y; r2[i] = rn; \
+                    acc[0] += rn.x * rn.x + rn.y * rn.y; acc[1] += rn.x * dv.x * rn.x + rn.y * dv.y * rn.y; }
+    RS_RANGE_LOOP(b, e, CX_ONE, CX_TWO);
+#undef CX_ONE
+#undef CX_TWO
+    grid_reduce<2>(acc, 0u, partials, ticket, slot + C_RR, accumulate != 0, &pr);
+}
+
+// start of a cycle: r = b - ax (ax = nullptr: r = b, x = 0) ; out[0] = <r,r> (into scal[dst]) , out[1] = <r, dinv r>
+__global__ void __launch_bounds__(256) cg_start_kernel(int b, int e, const double *__restrict__ rhs, const double *__restrict__ ax,
+                                                       const double *__restrict__ dinv, double *__restrict__ r,
+                                                       double *__restrict__ x, double *partials, unsigned *ticket,
+                                                       double *out2, int accumulate, PeerRed pr)
+{
+    double acc[2] = {0.0, 0.0};
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
+        double ri = rhs[i];
+        if (ax != nullptr) ri -= ax[i]; else x[i] = 0.0;
+        r[i] = ri;
+        acc[0] += ri * ri;
+        acc[1] += ri * dinv[i] * ri;
+    }
+    grid_reduce<2>(acc, 0u, partials, ticket, out2, accumulate != 0, &pr);
+}
+
+// <r,r> -> where the caller reads it, <r,z> -> slot(1).rz (the "rho of the previous step" of step 0)
+__global__ void cg_seed_kernel(double *scal, int dst_rr)
+{
+    scal[dst_rr] = scal[SLOT * 0 + 6];
+    scal[SLOT * 1 + C_RZ] = scal[SLOT * 0 + 7];
+}
+
+static int cg_start(Ctx &c, Krylov &k, const double *b, double *x, bool restart, int dst_rr, double *rnorm)
+{
+    cudaStream_t st = c.stream;
+    const double rows = (double)k.own.total();
+    if (restart) {
+        RS_TRY(comm_halo_exchange(c, x, k.halo));
+        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)));
+        spmv_run<0>(k, st, x, k.v.p, nullptr, nullptr, PeerRed(), HaloSignal());
+    }
+    {
+        Launch L(c, K_VEC, 40.0 * rows);
+        const PeerRed peer = comm_next_peer_red();
+        for (int q = 0; q < k.own.n; q++)
+            cg_start_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, restart ? k.v.p : nullptr, k.dinv.p,
+                                                                                k.r.p, x, k.partials.p, k.ticket.p, k.scal.p + 6, q > 0,
+                                                                                q == k.own.n - 1 ? peer : PeerRed());
+    }
+    if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, k.scal.p + 6, 2));
+    cg_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, dst_rr);
+    c.launches++;
+    RS_CUDA(cudaMemcpyAsync(k.h_scal + dst_rr, k.scal.p + dst_rr, sizeof(double), cudaMemcpyDeviceToHost, st));
+    RS_CUDA(cudaStreamSynchronize(st));
+    *rnorm = std::sqrt(k.h_scal[dst_rr]);
+    return RS_OK;
+}
+
+static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
+{
+    cudaStream_t st = c.stream;
+    double *slot = k.scal.p + SLOT * cur;
+    const double rows = (double)k.own.total();
+    const HaloSignal sig = k.push_ok ? comm_next_halo_signal() : HaloSignal();
+    {
+        Launch L(c, K_VEC, (first ? 24.0 : 32.0) * rows);
+        for (int q = 0; q < k.own.n; q++) {
+            const int b = k.own.b[q], e = k.own.e[q];
+            cg_update_p_kernel<<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, k.dinv.p, k.ph_v,
+                                                                           make_push(k, 0, sig, q == k.own.n - 1), k.ticket.p + 1);
+        }
+    }
+    if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.ph_v, k.halo));
+    {
+        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)) + 8.0 * rows);
+        spmv_run<1>(k, st, k.ph_v, k.v.p, k.ph_v, slot + C_PQ, comm_next_peer_red(), sig);
+    }
+    if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_PQ, 1));
+    {
+        Launch L(c, K_VEC, 56.0 * rows);
+        const PeerRed peer = comm_next_peer_red();
+        for (int q = 0; q < k.own.n; q++) {
+            const int b = k.own.b[q], e = k.own.e[q];
+            cg_update_xr_kernel<<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph_v, k.v.p, k.dinv.p, x, k.r.p, k.partials.p,
+                                                                            k.ticket.p, q > 0, q == k.own.n - 1 ? peer : PeerRed());
+        }
+    }
+    if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_RR, 2));
+    return RS_OK;
+}
+
+// PCG with the same cycle logic as the BiCGStab driver below: convergence is declared on the true residual only.
+// *fallback is set when CG is not applicable after all (indefinite matrix / breakdown): the caller then runs BiCGStab.
+static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres, bool *fallback)
+{
+    cudaStream_t st = c.stream;
+    static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
+    *fallback = false;
+    *iters = 0;
+    *relres = 0.0;
+    double bnorm = 0.0;
+    RS_TRY(cg_start(c, k, b, x, false, S_BNORM, &bnorm));
+    if (!(bnorm == bnorm) || std::isinf(bnorm)) { set_error("sparse solver: right-hand side is not finite"); return RS_ESINGULAR; }
+    if (!(bnorm > 0.0)) return RS_OK;
+    double target = k.lin_rtol * bnorm;
+    if (abs_floor > target) target = abs_floor;
+    double rtrue = bnorm, best = bnorm;
+    int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
+    bool done = false;
+    while (!done && total < k.max_iter) {
+        const int cur = cycle_it & 1;
+        RS_TRY(cg_step(c, k, x, cur, cycle_it == 0));
+        total++; cycle_it++;
+        *iters = total;
+        if (total % k.check_every != 0 && total != k.max_iter) continue;
+        double *slot = k.scal.p + SLOT * cur;
+        RS_CUDA(cudaMemcpyAsync(k.h_scal + SLOT * cur, slot, sizeof(double) * 6, cudaMemcpyDeviceToHost, st));
+        RS_CUDA(cudaStreamSynchronize(st));
+        const double *h = k.h_scal + SLOT * cur;
+        const double rr = h[C_RR];
+        if (debug) fprintf(stderr, "[pcg] it %d rr %.6e pq %.6e rz %.6e bad %g\n", total, rr, h[C_PQ], h[C_RZ], h[C_BAD]);
+        const bool finite = (rr == rr) && !std::isinf(rr);
+        const bool broke = !finite || h[C_BAD] != 0.0;
+        if (broke) {   // not a matrix for CG: hand over to BiCGStab (which starts again from x = 0)
+            if (debug) fprintf(stderr, "[pcg] breakdown / indefinite after %d its: falling back to BiCGStab\n", total);
+            *fallback = true;
+            return RS_OK;
+        }
+        const double rnorm = std::sqrt(rr);
+        if (rnorm < 0.9 * best) { best = rnorm; since_best = 0; } else since_best++;
+        const bool looks_converged = rnorm <= target;
+        const bool stagnated = since_best * k.check_every >= 40;
+        if (!(looks_converged || stagnated || total >= k.max_iter)) continue;
+        double rt = 0.0;
+        RS_TRY(cg_start(c, k, b, x, true, S_RTRUE, &rt));
+        if (debug) fprintf(stderr, "[pcg] cycle %d ends after %d its (%s): true residual %.6e (target %.3e)\n", restarts, cycle_it,
+                           looks_converged ? "converged" : stagnated ? "stagnation" : "budget", rt, target);
+        if (!(rt == rt) || std::isinf(rt)) { set_error("sparse solver: Krylov breakdown (solution is not finite)"); return RS_ESINGULAR; }
+        if (rt <= target) { rtrue = rt; done = true; break; }
+        fruitless = (rt > 0.5 * rtrue) ? fruitless + 1 : 0;
+        rtrue = rt;
+        if (fruitless >= 3) { *fallback = true; return RS_OK; }
+        restarts++;
+        cycle_it = 0; best = rt; since_best = 0;
+    }
+    RS_CUDA(cudaGetLastError());
+    *relres = rtrue / bnorm;
+    return RS_OK;
+}
+
 // Solves A x = b from x = 0.  BiCGStab's recursively updated residual can drift away from b - A x,
 // stagnate, or break down (a recurrence scalar hits zero); each of those ends the current cycle:
 // the true residual is recomputed, becomes the new shadow residual, and the recurrence restarts
@@ -776,6 +1012,12 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
 {
     cudaStream_t st = c.stream;
     static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
+    if (k.use_cg) {
+        bool fallback = false;
+        RS_TRY(pcg_solve(c, k, b, x, abs_floor, iters, relres, &fallback));
+        if (!fallback) return RS_OK;
+        k.use_cg = false;   // not a CG matrix after all: BiCGStab below, from x = 0
+    }
     {
         Launch L(c, K_VEC, 32.0 * (double)k.own.total());
         const PeerRed peer = comm_next_peer_red();

@@ -79,6 +79,8 @@ struct Krylov {
     int lanes = 8;             // lanes per row of the sub-warp SpMV
     int tma_ok = 0, tma_sms = 0, tma_per_sm = 0;  // the TMA-staged SpMV is usable (every tile fits a stage)
     double *ph_v = nullptr, *sh_v = nullptr;   // the preconditioned directions (SpMV inputs): own buffers or pooled, peer-mapped ones
+    bool use_cg = false;                   // J is symmetric to FD noise: preconditioned CG (one SpMV per step) instead of BiCGStab
+    double asym = 0.0;                     // max |a_ij - a_ji| / max |a_ij| of the last Jacobian
     bool push_ok = false;                  // halos of ph / sh are pushed into the neighbours' vectors over NVLink
     void *nb_lo[2] = {nullptr, nullptr}, *nb_hi[2] = {nullptr, nullptr};   // neighbours' ph (0) and sh (1)
     cudaGraphExec_t pair_exec = nullptr;   // two BiCGStab steps (slot parities 0 and 1) captured once, replayed
