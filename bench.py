@@ -126,8 +126,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"steady.3D {args.size}^3 reaction-diffusion (C5); reference arm runs the bounded sample {S}^3",
-                   "newton_iters": iters},
+        "config": {"workload": f"steady.3D {args.size}^3 reaction-diffusion, nspec=1 (BASELINE config C5), stodes path",
+                   "bounded_sample": f"{S}^3 (the Yale direct solve cannot reach {args.size}^3: 32-bit work array, ~N^2 time)",
+                   "newton_iters": iters, "atol=rtol=ctol": TOL},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "time_to_steady_state_s": total / args.steps,

@@ -43,7 +43,7 @@ constexpr int NSCAL = 2 * SLOT + 8;
 Krylov::~Krylov()
 {
     if (h_scal) cudaFreeHost(h_scal);
-    if (pair_exec) cudaGraphExecDestroy(pair_exec);
+    for (int w = 0; w < 2; w++) if (g_exec[w]) cudaGraphExecDestroy(g_exec[w]);
 }
 
 int pick_lanes(int n, int nnz)
@@ -944,6 +944,47 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     return RS_OK;
 }
 
+// ---- CUDA-graph replay of Krylov steps ----------------------------------------------------------
+// Small grids and sharded solves are bound by launch latency, not bandwidth: after the first two steps
+// of a cycle an even number of steps (one check period; slot parities 0,1,0,1...) is captured once and
+// replayed with a single host call.  Not while profiling (per-launch events cannot live in a graph) and
+// not with the fused NVLink collectives (their sequence numbers are kernel arguments).
+static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first);
+static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first);
+
+static int graph_steps_per_launch(const Ctx &c, const Krylov &k)
+{
+    static const bool no_graph = getenv("RS_NO_GRAPH") != nullptr;
+    if (no_graph || c.profile || comm_peer_enabled()) return 0;
+    int g = k.check_every & ~1;
+    return g >= 2 ? g : 2;
+}
+
+static int launch_step_graph(Ctx &c, Krylov &k, double *x, bool cg, int nsteps)
+{
+    const int w = cg ? 1 : 0;
+    cudaStream_t st = c.stream;
+    if (!k.g_exec[w] || k.g_x[w] != x || k.g_n[w] != nsteps) {
+        if (k.g_exec[w]) { cudaGraphExecDestroy(k.g_exec[w]); k.g_exec[w] = nullptr; }
+        cudaGraph_t g = nullptr;
+        const long long l0 = c.launches;
+        RS_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        int rc = RS_OK;
+        for (int q = 0; q < nsteps && rc == RS_OK; q++) rc = cg ? cg_step(c, k, x, q & 1, 0) : bicgstab_step(c, k, x, q & 1, 0);
+        cudaError_t ce = cudaStreamEndCapture(st, &g);
+        k.g_launches[w] = (int)(c.launches - l0);
+        c.launches = l0;
+        if (rc != RS_OK) { if (g) cudaGraphDestroy(g); return rc; }
+        RS_CUDA(ce);
+        RS_CUDA(cudaGraphInstantiate(&k.g_exec[w], g, 0));
+        cudaGraphDestroy(g);
+        k.g_x[w] = x; k.g_n[w] = nsteps;
+    }
+    RS_CUDA(cudaGraphLaunch(k.g_exec[w], st));
+    c.launches += k.g_launches[w];
+    return RS_OK;
+}
+
 // PCG with the same cycle logic as the BiCGStab driver below: convergence is declared on the true residual only.
 // *fallback is set when CG is not applicable after all (indefinite matrix / breakdown): the caller then runs BiCGStab.
 static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres, bool *fallback)
@@ -962,12 +1003,21 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
     double rtrue = bnorm, best = bnorm;
     int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
     bool done = false;
+    const int gsteps = graph_steps_per_launch(c, k);
     while (!done && total < k.max_iter) {
-        const int cur = cycle_it & 1;
-        RS_TRY(cg_step(c, k, x, cur, cycle_it == 0));
-        total++; cycle_it++;
+        int cur = cycle_it & 1;
+        bool looked = false;
+        if (gsteps > 0 && cycle_it >= 2 && cur == 0 && total + gsteps <= k.max_iter) {
+            RS_TRY(launch_step_graph(c, k, x, true, gsteps));
+            total += gsteps; cycle_it += gsteps;
+            cur = 1;
+            looked = true;
+        } else {
+            RS_TRY(cg_step(c, k, x, cur, cycle_it == 0));
+            total++; cycle_it++;
+        }
         *iters = total;
-        if (total % k.check_every != 0 && total != k.max_iter) continue;
+        if (!looked && total % k.check_every != 0 && total != k.max_iter) continue;
         double *slot = k.scal.p + SLOT * cur;
         RS_CUDA(cudaMemcpyAsync(k.h_scal + SLOT * cur, slot, sizeof(double) * 6, cudaMemcpyDeviceToHost, st));
         RS_CUDA(cudaStreamSynchronize(st));
@@ -1041,40 +1091,21 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     double best = bnorm;      // smallest recursive residual of the current cycle
     int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
     bool done = false;
-    // Sharded solves are bound by launch + NCCL enqueue latency, not bandwidth: after the first two
-    // steps of a cycle, steps run in pairs (slot parities 0, 1) from one captured CUDA graph -- ten
-    // kernels, four halo exchanges and six all-reduces per host call.  (Not while profiling: the
-    // per-launch events cannot live inside a graph.)
-    static const bool no_graph = getenv("RS_NO_GRAPH") != nullptr;
-    const bool use_graph = comm_active() && !comm_peer_enabled() && !c.profile && !no_graph;   // peer reductions carry a per-launch sequence number
+    const int gsteps = graph_steps_per_launch(c, k);
     while (!done && total < k.max_iter) {
         int cur = cycle_it & 1;
-        if (use_graph && cycle_it >= 2 && cur == 0 && total + 2 <= k.max_iter) {
-            if (!k.pair_exec || k.pair_x != x) {
-                if (k.pair_exec) { cudaGraphExecDestroy(k.pair_exec); k.pair_exec = nullptr; }
-                cudaGraph_t g = nullptr;
-                const long long l0 = c.launches;
-                RS_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-                int rc = bicgstab_step(c, k, x, 0, 0);
-                if (rc == RS_OK) rc = bicgstab_step(c, k, x, 1, 0);
-                cudaError_t ce = cudaStreamEndCapture(st, &g);
-                c.launches = l0;
-                if (rc != RS_OK) { if (g) cudaGraphDestroy(g); return rc; }
-                RS_CUDA(ce);
-                RS_CUDA(cudaGraphInstantiate(&k.pair_exec, g, 0));
-                cudaGraphDestroy(g);
-                k.pair_x = x;
-            }
-            RS_CUDA(cudaGraphLaunch(k.pair_exec, st));
-            c.launches += 10;
-            total += 2; cycle_it += 2;
+        bool looked = false;
+        if (gsteps > 0 && cycle_it >= 2 && cur == 0 && total + gsteps <= k.max_iter) {
+            RS_TRY(launch_step_graph(c, k, x, false, gsteps));
+            total += gsteps; cycle_it += gsteps;
             cur = 1;
+            looked = true;   // always look after a graph: it spans a whole check period
         } else {
             RS_TRY(bicgstab_step(c, k, x, cur, cycle_it == 0));
             total++; cycle_it++;
         }
         *iters = total;
-        if (total % k.check_every != 0 && total != k.max_iter) continue;
+        if (!looked && total % k.check_every != 0 && total != k.max_iter) continue;
         double *slot = k.scal.p + SLOT * cur;
         RS_CUDA(cudaMemcpyAsync(k.h_scal + SLOT * cur, slot, sizeof(double) * SLOT, cudaMemcpyDeviceToHost, st));
         RS_CUDA(cudaStreamSynchronize(st));

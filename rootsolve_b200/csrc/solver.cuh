@@ -83,8 +83,10 @@ struct Krylov {
     double asym = 0.0;                     // max |a_ij - a_ji| / max |a_ij| of the last Jacobian
     bool push_ok = false;                  // halos of ph / sh are pushed into the neighbours' vectors over NVLink
     void *nb_lo[2] = {nullptr, nullptr}, *nb_hi[2] = {nullptr, nullptr};   // neighbours' ph (0) and sh (1)
-    cudaGraphExec_t pair_exec = nullptr;   // two BiCGStab steps (slot parities 0 and 1) captured once, replayed
-    const double *pair_x = nullptr;        // the solution vector the captured graph updates
+    // captured Krylov steps ([0] BiCGStab, [1] CG): graph, the solution vector it updates, steps and launches per replay
+    cudaGraphExec_t g_exec[2] = {nullptr, nullptr};
+    const double *g_x[2] = {nullptr, nullptr};
+    int g_n[2] = {0, 0}, g_launches[2] = {0, 0};
     // The host looks at ||r|| every check_every steps: each look drains the stream (a ~20 us bubble, as
     // long as a whole step on 8 GPUs or on a small grid).  Steps taken after convergence are harmless --
     // a breakdown there leaves x untouched (update_xr_kernel) -- and cost at most check_every-1 steps.
