@@ -40,7 +40,7 @@ int comm_rank() { return g_rank; }
 static double *g_mail_local = nullptr;
 static double *g_mail[PEER_MAX] = {nullptr};
 static bool g_peer_ok = false;
-static unsigned g_seq = 0;
+static unsigned *g_seq_dev = nullptr;   // [0] all-reduces, [1] halo pushes completed on this rank (device counters)
 
 bool comm_peer_enabled() { return g_peer_ok && comm_active(); }
 
@@ -50,7 +50,7 @@ PeerRed comm_next_peer_red()
     if (!comm_peer_enabled()) return pr;
     pr.nranks = g_nranks;
     pr.rank = g_rank;
-    pr.seq = ++g_seq;
+    pr.seq = g_seq_dev;
     for (int p = 0; p < g_nranks; p++) pr.mail[p] = g_mail[p];
     return pr;
 }
@@ -90,11 +90,11 @@ static void peer_setup()
         ok = 0;
     cudaFree(d_h);
     g_peer_ok = ok != 0;
-    g_seq = 0;
+    if (ok) { ok = cudaMalloc((void **)&g_seq_dev, 64) == cudaSuccess; if (ok) cudaMemset(g_seq_dev, 0, 64); else cudaGetLastError(); g_peer_ok = ok != 0; }
 }
 
 // ---- halo push: neighbours' vectors mapped for direct stores --------------------------------------
-static unsigned g_halo_seq = 0;
+
 
 // Maps the slab neighbours' copies of `count` vectors (allocation bases) into this process.
 // lo[i] / hi[i] receive the lower / upper neighbour's pointer for vector i (nullptr at the ends).
@@ -178,7 +178,7 @@ HaloSignal comm_next_halo_signal()
 {
     HaloSignal hs;
     if (!comm_peer_enabled()) return hs;
-    hs.seq = ++g_halo_seq;
+    hs.seq = g_seq_dev + 1;
     const size_t off = (size_t)2 * PEER_MAX * PEER_SLOT;
     hs.wait_lo = g_rank > 0 ? g_mail_local + off + 0 : nullptr;
     hs.wait_hi = g_rank < g_nranks - 1 ? g_mail_local + off + 1 : nullptr;
@@ -307,6 +307,7 @@ extern "C" void rs_comm_finalize(void)
             rs::g_mail[p] = nullptr;
         }
         rs::pool_release();
+        if (rs::g_seq_dev) { cudaFree(rs::g_seq_dev); rs::g_seq_dev = nullptr; }
         if (rs::g_mail_local) { cudaFree(rs::g_mail_local); rs::g_mail_local = nullptr; }
         rs::g_peer_ok = false;
         ncclCommDestroy(rs::g_comm);

@@ -955,7 +955,7 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first);
 static int graph_steps_per_launch(const Ctx &c, const Krylov &k)
 {
     static const bool no_graph = getenv("RS_NO_GRAPH") != nullptr;
-    if (no_graph || c.profile || comm_peer_enabled()) return 0;
+    if (no_graph || c.profile) return 0;
     int g = k.check_every & ~1;
     return g >= 2 ? g : 2;
 }

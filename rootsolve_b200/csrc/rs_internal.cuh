@@ -133,9 +133,13 @@ __device__ __forceinline__ double warp_max(double v)
 // instead of a hung GPU.
 constexpr int PEER_MAX = 8;
 constexpr int PEER_SLOT = 4;   // doubles per (parity, source rank): two values, the sequence flag, padding
+// Sequence numbers live in device memory and are advanced by the kernels themselves (only the last
+// block of a launch touches them), so a launch carries no per-call argument and whole Krylov steps can
+// be captured into CUDA graphs.  Every rank runs the same launches in the same order, hence the
+// counters agree across ranks without ever being communicated.
 struct PeerRed {
     int nranks = 1, rank = 0;
-    unsigned seq = 0;                // sequence number of this reduction (same on every rank)
+    unsigned *seq = nullptr;              // device counter: number of all-reduces completed on this rank
     double *mail[PEER_MAX] = {nullptr};   // mail[p]: rank p's mailbox as mapped into this process
 };
 
@@ -145,7 +149,7 @@ struct PeerRed {
 // complete"; the consuming SpMV waits for both neighbours' flags before it touches the halo.  No NCCL
 // call, no extra launch.  Flags only ever grow, so the wait is `flag >= seq`.
 struct HaloSignal {
-    unsigned seq = 0;
+    unsigned *seq = nullptr;                               // device counter: number of halo pushes completed on this rank
     double *tell_lo = nullptr, *tell_hi = nullptr;         // flag words inside the neighbours' mailboxes
     const double *wait_lo = nullptr, *wait_hi = nullptr;   // flag words inside my own mailbox
 };
@@ -173,19 +177,22 @@ __device__ __forceinline__ void halo_signal_done(const HaloPush &hp, unsigned *t
         const unsigned t = atomicAdd(ticket, 1u);
         if (t == gridDim.x - 1) {
             *ticket = 0;
+            const unsigned seq = *hp.sig.seq + 1u;   // this push's number; the consumer on this rank reads it back
             __threadfence_system();
-            if (hp.sig.tell_lo) *(volatile double *)hp.sig.tell_lo = (double)hp.sig.seq;
-            if (hp.sig.tell_hi) *(volatile double *)hp.sig.tell_hi = (double)hp.sig.seq;
+            if (hp.sig.tell_lo) *(volatile double *)hp.sig.tell_lo = (double)seq;
+            if (hp.sig.tell_hi) *(volatile double *)hp.sig.tell_hi = (double)seq;
+            *hp.sig.seq = seq;
         }
     }
 }
 
-// start of a consuming kernel: every block waits until both neighbours have delivered sequence seq
+// start of a consuming kernel: every block waits until both neighbours have delivered the push this
+// rank's own producer kernel just completed (the counter was advanced by that kernel, earlier in the stream)
 __device__ __forceinline__ void halo_wait(const HaloSignal &hs)
 {
-    if (hs.seq == 0) return;
+    if (hs.seq == nullptr) return;
     if (threadIdx.x == 0) {
-        const double want = (double)hs.seq;
+        const double want = (double)*(volatile const unsigned *)hs.seq;
         const long long t0 = clock64();
         if (hs.wait_lo) while (*(volatile const double *)hs.wait_lo < want) { if (clock64() - t0 > 4000000000LL) break; }
         if (hs.wait_hi) while (*(volatile const double *)hs.wait_hi < want) { if (clock64() - t0 > 4000000000LL) break; }
@@ -198,8 +205,9 @@ template <int K>
 __device__ __forceinline__ void peer_allreduce_warp(double (&r)[K], const PeerRed &pr, int lane)
 {
     static_assert(K <= 2, "mailbox slots carry two values");
-    const int parity = pr.seq & 1u;
-    const double flag = (double)pr.seq;
+    const unsigned seq = *(volatile const unsigned *)pr.seq + 1u;   // only the last block of a launch gets here
+    const int parity = seq & 1u;
+    const double flag = (double)seq;
     if (lane < pr.nranks) {
         volatile double *dst = pr.mail[lane] + (size_t)(parity * PEER_MAX + pr.rank) * PEER_SLOT;
         dst[0] = r[0];
@@ -229,6 +237,8 @@ __device__ __forceinline__ void peer_allreduce_warp(double (&r)[K], const PeerRe
         for (int p = 0; p < pr.nranks; p++) s += __shfl_sync(0xffffffffu, got[k], p);
         r[k] = s;
     }
+    __syncwarp();
+    if (lane == 0) *pr.seq = seq;
 }
 
 // Reduces K per-thread values over the block and, across blocks, through
