@@ -21,6 +21,8 @@
 //    only ever taken on final information, so the fixed point is the greedy's.
 #include <cooperative_groups.h>
 
+#include <cstdlib>
+
 #include "solver.cuh"
 #include "grid_rows.cuh"
 
@@ -81,28 +83,28 @@ __global__ void __launch_bounds__(256) jg_wave_kernel(GridDesc g, int S, int nle
                                                       int *__restrict__ group_of, int base, int *__restrict__ stats)
 {
     cg::grid_group grid = cg::this_grid();
-    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long nthreads = (long long)gridDim.x * blockDim.x;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;          // 32-bit index arithmetic throughout: columns < 2^31,
+    const int nthreads = gridDim.x * blockDim.x;                    // and 64-bit divisions would dominate a step
     const int d1 = g.d[0], d2 = g.d[1], d3 = g.d[2];
     const bool three = (g.type == RS_TYPE_3D), one = (g.type == RS_TYPE_1D);
     // candidate lines: (species, j, k) in 3-D, (species, j) in 2-D, (species) in 1-D; the last coordinate
     // follows from the level
-    const long long nlines = three ? (long long)g.nspec * d1 * d2 : one ? (long long)g.nspec : (long long)g.nspec * d1;
+    const int nlines = three ? g.nspec * d1 * d2 : one ? g.nspec : g.nspec * d1;
     const int dl = three ? d3 : one ? d1 : d2;
     int count = 0, top = -1;
     const int nsteps = nlevels + WAVE_SLOTS - 1;
     for (int step = 0; step < nsteps; step++) {
         const int slot_lo = max(0, step - nlevels + 1), slot_hi = min(WAVE_SLOTS - 1, step);
-        const long long work = (long long)(slot_hi - slot_lo + 1) * nlines;
-        for (long long wq = tid; wq < work; wq += nthreads) {
+        const int work = (slot_hi - slot_lo + 1) * nlines;
+        for (int wq = tid; wq < work; wq += nthreads) {
             const int slot = slot_lo + (int)(wq / nlines);
-            const long long q = wq % nlines;
+            const int q = wq % nlines;
             const int t = step - slot;
             int s, last;
-            long long c;
+            int c;
             if (three) {
                 const int k = (int)(q % d2);
-                const long long r = q / d2;
+                const int r = q / d2;
                 const int j = (int)(r % d1);
                 s = (int)(r / d1);
                 last = t - S * s - 4 * j - 2 * k;
@@ -173,7 +175,9 @@ int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, c
         RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jg_wave_kernel, 256, 0));
         const long long nlines = three ? (long long)g.nspec * g.d[0] * g.d[1] : one ? (long long)g.nspec : (long long)g.nspec * g.d[0];
         long long want = (nlines * WAVE_SLOTS + 255) / 256;
-        long long cap = (long long)sms * (per_sm > 4 ? 4 : per_sm);
+        const char *ctas_env = getenv("RS_WAVE_CTAS");
+        const int ctas = ctas_env ? atoi(ctas_env) : 4;
+        long long cap = (long long)sms * (per_sm > ctas ? ctas : per_sm);
         int blocks = (int)(want < cap ? want : cap);
         if (blocks < 1) blocks = 1;
         fill_int_kernel<<<grid_for(n, 256), 256, 0, c.stream>>>(n, group_of.p, -1);

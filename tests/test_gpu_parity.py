@@ -245,6 +245,45 @@ def test_linsolve_matches_direct(built, transposed):
         assert np.allclose(x, xr, rtol=1e-8, atol=1e-9), (kind, iters.value, rr.value)
 
 
+def test_linsolve_symmetric_paths(built):
+    """Symmetric matrices take the PCG path; a symmetric but INDEFINITE one must be caught (alpha <= 0) and handed
+    to BiCGStab.  Both are checked against a sparse direct solve."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+    from oracle import oracle as O
+    from rootsolve_b200 import _capi
+    rng = np.random.default_rng(5)
+    ian, jan = O.sparse_structure("2D", 1, (24, 24), (0, 0))
+    n = len(ian) - 1
+    for kind in ("definite", "indefinite"):
+        A = sp.lil_matrix((n, n))
+        for j in range(n):
+            for k in range(ian[j] - 1, ian[j + 1] - 1):
+                i = jan[k] - 1
+                if i != j:
+                    A[i, j] = A[j, i] = -1.0
+        shift = 4.5
+        if kind == "indefinite":   # a shift that puts part of the 5-point spectrum below zero but none of it near zero
+            m = 24
+            c = 2 * np.cos(np.arange(1, m + 1) * np.pi / (m + 1))
+            lam0 = -(c[:, None] + c[None, :]).ravel()
+            cands = np.linspace(1.0, 1.6, 121)
+            shift = float(cands[np.argmax([np.min(np.abs(lam0 + s_)) for s_ in cands])])
+        for j in range(n):
+            A[j, j] = shift
+        Ac = A.tocsc()
+        a = np.array([Ac[jan[k] - 1, j] for j in range(n) for k in range(ian[j] - 1, ian[j + 1] - 1)])
+        b = rng.standard_normal(n)
+        x = np.zeros(n)
+        iters, rr = C.c_int(0), C.c_double(0.0)
+        ctl = _capi.KrylovControl(precond=_capi.RS_PRECOND_JACOBI, max_krylov=20000)
+        _capi.check(built.rs_linsolve(n, H.ip(ian), H.ip(jan), H.dp(a), H.dp(b), 0, 1, C.byref(ctl), H.dp(x), C.byref(iters),
+                                      C.byref(rr)))
+        xr = spla.spsolve(Ac, b)
+        assert rr.value <= 1e-9, (kind, iters.value, rr.value)
+        assert np.allclose(x, xr, rtol=1e-6, atol=1e-7), kind
+
+
 def test_errset_bit_exact(built, oracle):
     from rootsolve_b200 import _capi
     rng = np.random.default_rng(7)
