@@ -46,7 +46,7 @@ enum {
 
 /* Sparsity types, the Type argument of R/stodes.R:66-158 / src/sparse.f:343-353.
  * A negative value means "return the structure only" (sparsetype="sparsereturn"). */
-enum { RS_TYPE_USER = 0, RS_TYPE_1D = 2, RS_TYPE_2D = 3, RS_TYPE_3D = 4 };
+enum { RS_TYPE_USER = 0, RS_TYPE_DETECT = 1, RS_TYPE_1D = 2, RS_TYPE_2D = 3, RS_TYPE_3D = 4 };
 
 /* Linear-solver selection: the reference's imethod (1 = yale, 10 = yale +
  * return ian/jan; R/stodes.R:316-329).  On the GPU "yale" is served by the

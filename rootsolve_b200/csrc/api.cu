@@ -263,7 +263,7 @@ static int check_args(const rs_stsparse_args *a)
     if (a->nrtol > 1 && a->nrtol != a->neq) { set_error("`rtol' must either be a scalar, or as long as `y'"); return RS_EINVAL; }
     if (a->imethod != 1 && a->imethod != 10) { set_error("`spmethod' must be `yale' on this path (imethod 1 or 10)"); return RS_EINVAL; }
     const int at = std::abs(a->Type);
-    if (at != RS_TYPE_USER && at != RS_TYPE_1D && at != RS_TYPE_2D && at != RS_TYPE_3D) {
+    if (at != RS_TYPE_USER && at != RS_TYPE_DETECT && at != RS_TYPE_1D && at != RS_TYPE_2D && at != RS_TYPE_3D) {
         set_error("cannot run stodes: sparsetype not known (Type %d is outside this path)", a->Type);
         return RS_EINVAL;
     }
@@ -298,8 +298,14 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
     RS_CUDA(cudaEventCreate(&e1));
     RS_CUDA(cudaEventRecord(e0, c.stream));
 
+    RS_TRY(s.y.alloc(n));
+    RS_TRY(s.y.upload(a->y, n, c.stream));
     // structure (xsparsestruct, src/sparse.f:300-455)
-    if (std::abs(a->Type) == RS_TYPE_USER) {
+    if (std::abs(a->Type) == RS_TYPE_DETECT) {
+        RS_TRY(init_model(a->func, a->initpar, a->ninitpar));
+        RS_TRY(detect_structure(c, a->func, n, a->time, s.y.p, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, a->nnz[0], s.ian,
+                                s.jan, &s.nnz));
+    } else if (std::abs(a->Type) == RS_TYPE_USER) {
         s.nnz = a->nnz[0];
         RS_TRY(s.ian.alloc((size_t)n + 1));
         RS_TRY(s.jan.alloc((size_t)s.nnz));
@@ -318,7 +324,7 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         RS_TRY(build_csr_pattern(c, n, s.nnz, s.ian.p, s.jan.p, s.rowptr, s.col));
         RS_TRY(jgroup_device(c, s.grid, n, s.nnz, s.ian.p, s.jan.p, s.rowptr.p, s.col.p, s.maxg, s.group_of, &s.ngp));
         RS_TRY(s.val.alloc((size_t)s.nnz));
-        RS_TRY(s.y.alloc(n)); RS_TRY(s.beta.alloc(n)); RS_TRY(s.ewt.alloc(n)); RS_TRY(s.x.alloc(n)); RS_TRY(s.ftmp.alloc(n));
+        RS_TRY(s.beta.alloc(n)); RS_TRY(s.ewt.alloc(n)); RS_TRY(s.x.alloc(n)); RS_TRY(s.ftmp.alloc(n));
         RS_TRY(s.atol.alloc(a->natol)); RS_TRY(s.rtol.alloc(a->nrtol));
         RS_TRY(s.atol.upload(a->atol, a->natol, c.stream));
         RS_TRY(s.rtol.upload(a->rtol, a->nrtol, c.stream));
@@ -358,10 +364,6 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         RS_TRY(fd_setup(c, s.fd, n, s.ngp, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, s.slab_j0, s.slab_j1));
         RS_TRY(krylov_setup(c, s.kry, n, s.nnz, s.rowptr.p, s.col.p, s.val.p, s.ctl.precond, s.grid.type ? s.grid.nspec : 1,
                             s.grid.type ? s.grid.ncell : n, &s.ctl, &s.own, comm_active() ? &s.halo : nullptr));
-        RS_TRY(s.y.upload(a->y, n, c.stream));
-    } else {
-        RS_TRY(s.y.alloc(n));
-        RS_TRY(s.y.upload(a->y, n, c.stream));
     }
     RS_CUDA(cudaEventRecord(e1, c.stream));
     RS_CUDA(cudaEventSynchronize(e1));

@@ -14,6 +14,8 @@
 // The arithmetic is ordered as in the reference and this file is compiled with
 // -fmad=false, so a[] is bit-identical to the reference's when the model's own
 // arithmetic is.
+#include <algorithm>
+
 #include "solver.cuh"
 
 namespace rs {
@@ -126,6 +128,117 @@ int residual_only(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, co
     Launch L(c, K_RESIDUAL, 16.0 * work);
     const int e = m->launch((void *)c.stream, n, t, d_y, d_f, w.ld, 1, w.yout.p, w.ldout, w.ip.p, work);
     if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
+    return RS_OK;
+}
+
+// ---- numeric structure detection (Type = +-1, sparsetype "sparseint"/"sparsereturn") -------------------
+// The reference perturbs one state variable at a time and records which rates of change move
+// (src/sparse.f:356-396): N+1 model calls.  Here the N perturbed states are evaluated in batches of B by
+// the batched residual kernel; a bit matrix (column j, row i) remembers the hits, so the model is not
+// called a second time to fill jan.  Same test as the reference: |(f_j[i] - f[i]) / delta_j| > 1e-30 with
+// delta_j the increment Perturb returns (not the rounded difference); rows come out ascending.
+
+// Y[b][i] = y[i] (+ delta when i == j0 + b), b in [0, nb)
+__global__ void __launch_bounds__(256) perturb_single_kernel(int n, int j0, int nb, const double *__restrict__ y,
+                                                             double *__restrict__ Y, long long ld)
+{
+    const long long total = (long long)n * nb;
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(q / n), i = (int)(q - (long long)b * n);
+        const double v = y[i];
+        Y[(long long)b * ld + i] = (i == j0 + b) ? perturbed(v) : v;
+    }
+}
+
+__global__ void __launch_bounds__(256) detect_kernel(int n, int j0, int nb, const double *__restrict__ y,
+                                                     const double *__restrict__ F0, const double *__restrict__ F,
+                                                     long long ld, unsigned *__restrict__ mask, int words,
+                                                     int *__restrict__ counts)
+{
+    const long long total = (long long)words * nb;
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(q / words), w = (int)(q - (long long)b * words);
+        const int j = j0 + b;
+        const double yj = y[j];
+        double delta = fabs(yj) * 1.0e-8;
+        if (delta < 1.0e-8) delta = 1.0e-8;
+        unsigned bits = 0;
+        for (int t = 0; t < 32; t++) {
+            const int i = w * 32 + t;
+            if (i < n && fabs((F[(long long)b * ld + i] - F0[i]) / delta) > 1.0e-30) bits |= 1u << t;
+        }
+        mask[(size_t)j * words + w] = bits;
+        if (bits) atomicAdd(&counts[j], __popc(bits));
+    }
+}
+
+__global__ void detect_fill_kernel(int n, const unsigned *__restrict__ mask, int words, const int *__restrict__ ian,
+                                   int *__restrict__ jan)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    int pos = ian[j] - 1;
+    for (int w = 0; w < words; w++) {
+        unsigned bits = mask[(size_t)j * words + w];
+        while (bits) {
+            const int t = __ffs(bits) - 1;
+            bits &= bits - 1;
+            jan[pos++] = w * 32 + t + 1;
+        }
+    }
+}
+
+int detect_structure(Ctx &c, const rs_model_desc *m, int n, double t, const double *d_y, int nout, const double *rpar,
+                     int nrpar, const int *ipar, int nipar, int nnz_cap, DevBuf<int> &ian, DevBuf<int> &jan, int *nnz)
+{
+    const long long ld = ((long long)n + 31) / 32 * 32;
+    long long B = (1LL << 27) / ld;   // <= 1 GiB per work array
+    if (B < 1) B = 1;
+    if (B > n) B = n;
+    FdWork w;
+    RS_TRY(fd_setup(c, w, n, (int)B - 1, nout, rpar, nrpar, ipar, nipar, 0, -1));
+    const int words = (n + 31) / 32;
+    DevBuf<double> F0;
+    DevBuf<unsigned> mask;
+    DevBuf<int> counts;
+    RS_TRY(F0.alloc(n));
+    RS_TRY(mask.alloc((size_t)n * words));
+    RS_TRY(counts.alloc(n));
+    RS_TRY(counts.zero(c.stream));
+    RS_TRY(residual_only(c, m, w, n, t, d_y, F0.p, n));
+    for (int j0 = 0; j0 < n; j0 += (int)B) {
+        const int nb = (int)std::min<long long>(B, n - j0);
+        {
+            Launch L(c, K_PERTURB, 8.0 * n * (nb + 1));
+            perturb_single_kernel<<<grid_for((long long)n * nb, 256), 256, 0, c.stream>>>(n, j0, nb, d_y, w.Y.p, w.ld);
+        }
+        {
+            Launch L(c, K_RESIDUAL, 16.0 * n * nb);
+            const int e = m->launch((void *)c.stream, n, t, w.Y.p, w.F.p, w.ld, nb, w.yout.p, w.ldout, w.ip.p, n);
+            if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
+        }
+        {
+            Launch L(c, K_STRUCT, 8.0 * n * nb);
+            detect_kernel<<<grid_for((long long)words * nb, 256), 256, 0, c.stream>>>(n, j0, nb, d_y, F0.p, w.F.p, w.ld, mask.p, words, counts.p);
+        }
+    }
+    RS_TRY(ian.alloc((size_t)n + 1));
+    RS_TRY(exclusive_scan(c, counts.p, ian.p, n, 1, true));
+    int last = 0;
+    RS_CUDA(cudaMemcpyAsync(&last, ian.p + n, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    *nnz = last - 1;
+    if (*nnz > nnz_cap) {   // src/sparse.f:374-393
+        set_error("error during determining sparsity: nnz too small; nnz should be at least %d", *nnz);
+        return RS_ESTRUCT;
+    }
+    RS_TRY(jan.alloc((size_t)std::max(*nnz, 1)));
+    {
+        Launch L(c, K_STRUCT, 4.0 * *nnz + 4.0 * (double)n * words);
+        detect_fill_kernel<<<(n + 255) / 256, 256, 0, c.stream>>>(n, mask.p, words, ian.p, jan.p);
+    }
+    RS_CUDA(cudaGetLastError());
+    RS_CUDA(cudaStreamSynchronize(c.stream));
     return RS_OK;
 }
 

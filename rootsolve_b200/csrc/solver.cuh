@@ -57,6 +57,9 @@ int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int n
                 const Ranges &own, const Ranges &touch);
 int residual_only(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, const double *d_y, double *d_f,
                   long long work);
+// numeric structure detection (Type +-1): ian/jan from N perturbed evaluations, bit-exact with src/sparse.f:356-396
+int detect_structure(Ctx &c, const rs_model_desc *m, int n, double t, const double *d_y, int nout, const double *rpar,
+                     int nrpar, const int *ipar, int nipar, int nnz_cap, DevBuf<int> &ian, DevBuf<int> &jan, int *nnz);
 // a_csc[k] = val[position of (jan[k], column of k)] -- for returning the Jacobian in jan order
 int gather_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, const int *d_rowptr,
                       const int *d_col, const double *d_val, double *d_a);

@@ -52,10 +52,10 @@ def sparse_args(n, sparsetype, nnz=None, inz=None, ngp=None, lrw=None):
     if ngp is None:
         ngp = n + 1
     if sparsetype in ("sparseint", "sparsereturn", "sparse"):
-        raise NotImplementedError(
-            "sparsetype %r (numeric structure detection, Type 1) is not on the GPU path yet; "
-            "use '1D', '2D', '3D', 'sparseusr' or 'sparsejan'" % sparsetype)
-    if sparsetype == "sparseusr":
+        # Type 1: sparsity estimated numerically by perturbation (R/stodes.R:71-78); nnz defaults to n*n
+        nz = n * n if (nnz is None or sparsetype == "sparse") else int(np.atleast_1d(nnz)[0])
+        nnzv = [min(nz, 2 ** 31 - 1)]
+    elif sparsetype == "sparseusr":
         if inz is None:
             raise ValueError("'inz' must be specified if 'sparsetype' = 'sparseusr'")
         inz = np.asarray(inz)
@@ -248,7 +248,9 @@ def stodes(y, time=0, func=None, parms=None, rtol=1e-6, atol=1e-8, ctol=1e-8, sp
     yout = np.zeros(n + int(nout))
     precis = np.zeros(int(maxiter))
     ian = np.zeros(n + 1, dtype=np.int32)
-    jan = np.zeros(P.nnz_cap, dtype=np.int32)
+    ret_only = sparsetype == "sparsereturn"
+    # jan is only handed back for sparsereturn / return_groups (nnz_cap is n*n for numerically detected structures)
+    jan = np.zeros(P.nnz_cap if (ret_only or return_groups) else 1, dtype=np.int32)
     R = _capi.StsparseResult()
     R.y, R.precis = _dp(yout), _dp(precis)
     ret_only = sparsetype == "sparsereturn"

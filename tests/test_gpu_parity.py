@@ -389,6 +389,34 @@ def test_sparsereturn_and_sparsejan_roundtrip(built, oracle):
     assert again.attributes["dims"]["ngp"] == full.attributes["dims"]["ngp"]
 
 
+def test_numeric_structure_detection(built, oracle):
+    """sparsetype='sparseint' / 'sparsereturn' (Type +-1, stodes' default): the structure found by perturbing one
+    state variable at a time (src/sparse.f:356-396) is bit-identical to the oracle's, and the solve built on it
+    reaches the same steady state."""
+    import rootsolve_b200 as rs
+    for model, parms, ipar, y0 in [("diff2d", H.P_DIFF2D_MONOD, [1, 9, 11, 1, 1], np.full(99, 10.0)),
+                                   ("rt1d", H.P_RT1D, [3, 40, 1, 1, 0], np.full(120, 1.0)),
+                                   ("rd3d", H.P_RD3D, [2, 4, 5, 6, 0], np.concatenate([np.full(120, 10.0), np.full(120, 1.0)]))]:
+        n = len(y0)
+        ref_s = oracle.stsparse(y0, oracle.model(model, parms), sparsetype="sparsereturn", nnz=None, ipar=ipar, **H.TOL)
+        got_s = rs.stodes(y0, func=model, parms=parms, sparsetype="sparsereturn", ipar=ipar, **H.TOL)
+        assert got_s.attributes["dims"]["nnz"] == ref_s["dims"]["nnz"]
+        assert np.array_equal(got_s.attributes["ian"], ref_s["ian"])
+        assert np.array_equal(got_s.attributes["jan"], ref_s["jan"])
+        ref = oracle.stsparse(y0, oracle.model(model, parms), sparsetype="sparseint", nnz=None, ipar=ipar, lrw=400000,
+                              positive=True, **H.TOL)
+        got = rs.stodes(y0, func=model, parms=parms, sparsetype="sparseint", ipar=ipar, positive=True,
+                        return_groups=True, **H.TOL)
+        assert got.attributes["steady"] and ref["steady"]
+        assert got.attributes["dims"]["nnz"] == ref["dims"]["nnz"] and got.attributes["dims"]["ngp"] == ref["dims"]["ngp"]
+        assert np.array_equal(got.attributes["igp"], ref["igp"]) and np.array_equal(got.attributes["jgp"], ref["jgp"])
+        ok, worst = H.within_tol(got["y"], ref["y"])
+        assert ok, (model, worst)
+    with pytest.raises(rs.RootSolveError, match="nnz should be at least"):
+        rs.stodes(np.full(99, 10.0), func="diff2d", parms=H.P_DIFF2D_MONOD, sparsetype="sparseint", nnz=50,
+                  ipar=[1, 9, 11, 1, 1])
+
+
 def test_positive_index_vector_and_vector_tolerances(built, oracle):
     """positive as an index vector (src/sparse.f:159-163) and itol=4 tolerances"""
     import rootsolve_b200 as rs
