@@ -38,7 +38,7 @@ class OrcArgs(C.Structure):
         ("ipar", C.POINTER(C.c_int)), ("nipar", C.c_int),
         ("type", C.c_int),
         ("ian_in", C.POINTER(C.c_int)), ("jan_in", C.POINTER(C.c_int)),
-        ("imethod", C.c_int), ("quirk_first_step_transposed", C.c_int),
+        ("imethod", C.c_int), ("quirk_first_step_transposed", C.c_int), ("quirk_unterminated_igp", C.c_int),
     ]
 
 
@@ -203,7 +203,7 @@ def model(name: str, parms):
 
 def stsparse(y, func, *, sparsetype, nnz, time=0.0, atol=1e-8, rtol=1e-6, ctol=1e-8, lrw=None,
              ngp=None, positive=False, maxiter=100, ipar=None, rpar=None, nout=0,
-             quirk_first_step_transposed=True, want_jacobian=False):
+             quirk_first_step_transposed=True, quirk_unterminated_igp=True, want_jacobian=False):
     """Run the oracle's whole solve; returns a dict shaped like stodes' result."""
     L = lib()
     y = np.ascontiguousarray(y, dtype=np.float64).ravel()
@@ -236,7 +236,8 @@ def stsparse(y, func, *, sparsetype, nnz, time=0.0, atol=1e-8, rtol=1e-6, ctol=1
                 lrw=lrw, ngp=maxg, maxiter=maxiter, posit=posit, pos=_ip(pos), ipos=len(pos), nout=nout,
                 rpar=_dp(rpar_a), nrpar=len(rpar_a), ipar=_ip(ipar_a), nipar=len(ipar_a), type=Type,
                 ian_in=None, jan_in=None, imethod=imethod,
-                quirk_first_step_transposed=int(quirk_first_step_transposed))
+                quirk_first_step_transposed=int(quirk_first_step_transposed),
+                quirk_unterminated_igp=int(quirk_unterminated_igp))
     R = OrcResult(y=_dp(yout), precis=_dp(precis), ian=_ip(ian), jan=_ip(jan), igp=_ip(igp), jgp=_ip(jgp),
                   a0=_dp(a0) if want_jacobian else None, beta0=_dp(beta0) if want_jacobian else None)
     rc = L.orc_stsparse(C.byref(A), C.byref(R))

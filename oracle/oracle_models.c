@@ -56,3 +56,12 @@ void rt1d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
     for (int s = 0; s < nspec; s++)
         for (int j = 0; j < nb; j++) ydot[(long)s * nb + j] = rsm_rt1d_point(y, s, j, nspec, nb, p_rt1);
 }
+
+/* the reference's compiled-code example, inst/dynload/anoxmodc.c (4 state variables, 1 output) */
+static double p_anox[RSM_ANOX_NPAR];
+void initanoxmod(void (*steadyparms)(int *, double *)) { int N = RSM_ANOX_NPAR; steadyparms(&N, p_anox); }
+void anoxmod(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)ip;
+    rsm_anox(y, ydot, yout, p_anox);
+}

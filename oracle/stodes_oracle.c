@@ -977,6 +977,10 @@ int orc_stsparse(const orc_args *A, orc_result *R)
         const int ier = orc_jgroup(n, ian, jan, maxg, &ngp, igp, jgp);
         if (ier == 1) { rc = fail(R, -12, "not enough memory for JGROUP"); goto done; }
         if (ier == 2) { rc = fail(R, -13, "error during grouping: NGP too small"); goto done; }
+        /* Reference quirk: with one column per group (ngp == n) JGROUP's loop ends before igp(ngp+1) is written
+         * (src/sparse.f:569-600), it stays 0, and xSparseJacob then skips the last group: the last column of the
+         * Jacobian is never filled.  quirk_unterminated_igp = 0 repairs the terminator instead. */
+        if (!A->quirk_unterminated_igp && ngp == n && igp[ngp] == 0) igp[ngp] = n + 1;
     }
     dims[0] = nnz;
     dims[1] = ngp;

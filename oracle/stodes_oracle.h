@@ -74,6 +74,7 @@ typedef struct {
     const int *ian_in; const int *jan_in;   /* type 0 only */
     int imethod;                   /* 1 yale, 10 sparsereturn */
     int quirk_first_step_transposed; /* 1 = as the reference (A.3-1), 0 = always solve J x = beta */
+    int quirk_unterminated_igp;      /* 1 = as the reference: igp(ngp+1) left at 0 when ngp == neq, last column of J skipped */
 } orc_args;
 
 typedef struct {

@@ -154,4 +154,25 @@ RSM_HD double rsm_rt1d_point(const double *y, int s, int j, int nspec, int nb, c
     return dY;
 }
 
+/* The 4-variable sediment model of the reference's vignette and of inst/dynload (organic matter OM, O2, SO4,
+ * HS; vignettes/rootSolve.Rnw:352-372): oxic and anoxic mineralisation with Monod limitation, re-oxidation of
+ * sulphide, exchange with the bottom water.  One output variable, SumS = SO4 + HS.
+ * p[0]=D p[1]=Flux p[2]=r p[3]=rox p[4]=ks p[5]=ks2 p[6]=BO2 p[7]=BSO4 p[8]=BHS */
+#define RSM_ANOX_NPAR 9
+RSM_HD void rsm_anox(const double *y, double *ydot, double *yout, const double *p)
+{
+    const double D = p[0], Flux = p[1], r = p[2], rox = p[3], ks = p[4], ks2 = p[5];
+    const double BO2 = p[6], BSO4 = p[7], BHS = p[8];
+    const double OM = y[0], O2 = y[1], SO4 = y[2], HS = y[3];
+    const double lim = O2 / (O2 + ks);
+    const double oxicmin = r * OM * lim;
+    const double anoxicmin = r * OM * (1.0 - lim) * SO4 / (SO4 + ks2);
+    const double reox = rox * HS * lim;
+    ydot[0] = Flux - oxicmin - anoxicmin;
+    ydot[1] = -oxicmin - 2.0 * reox + D * (BO2 - O2);
+    ydot[2] = -0.5 * anoxicmin + reox + D * (BSO4 - SO4);
+    ydot[3] = 0.5 * anoxicmin - reox + D * (BHS - HS);
+    yout[0] = SO4 + HS;
+}
+
 #endif /* RSM_MODEL_MATH_H */

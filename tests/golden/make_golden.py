@@ -30,6 +30,21 @@ PDF_P16 = {
     "steady": True,
 }
 
+# rootsolve_pdf_p8_anox.json -- transcribed by hand from inst/doc/rootSolve.pdf p.8-9: the 4-variable anoxic
+# sediment model (vignettes/rootSolve.Rnw:360-403) solved by the dense sibling `stode(y, fun, parms, pos=TRUE)`.
+# Same Newton skeleton (errset, Perturb, clamp, the two tests); stodes reaches the same root.
+PDF_P8_ANOX = {
+    "source": "rootSolve 1.8.2.4 inst/doc/rootSolve.pdf p.8-9; vignettes/rootSolve.Rnw:360-403",
+    "parms": [1.0, 100.0, 0.1, 1.0, 1.0, 1.0, 100.0, 10000.0, 0.0],
+    "parm_names": ["D", "Flux", "r", "rox", "ks", "ks2", "BO2", "BSO4", "BHS"],
+    "y0": [1.0, 1.0, 1.0, 1.0],
+    "y": [1000.012783, 6.825178, 9996.587411, 3.412589],
+    "SumS": 10000.0,
+    "precis": [2.549712e+03, 5.753884e+01, 2.039705e+01, 8.527476e+00, 2.168616e+00, 1.515096e-01, 7.266703e-04,
+               1.664189e-08],
+    "steady": True,
+}
+
 GRIDS = [
     ("1D", 1, [50], [0]), ("1D", 5, [1000], [0]), ("1D", 2, [30], [1]),
     ("2D", 1, [50, 50], [0, 0]), ("2D", 1, [100, 100], [0, 0]), ("2D", 2, [17, 9], [0, 0]), ("2D", 1, [50, 100], [0, 1]),
@@ -45,6 +60,7 @@ def sha(a):
 def main():
     from oracle import oracle as O
     json.dump(PDF_P16, open(os.path.join(HERE, "rootsolve_pdf_p16.json"), "w"), indent=1)
+    json.dump(PDF_P8_ANOX, open(os.path.join(HERE, "rootsolve_pdf_p8_anox.json"), "w"), indent=1)
     out = []
     for kind, nspec, dims, cyc in GRIDS:
         ian, jan = O.sparse_structure(kind, nspec, dims, cyc)

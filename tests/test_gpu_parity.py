@@ -371,6 +371,23 @@ def test_golden_pdf_example_on_gpu(built):
     assert A["precis"][1] < 1e-5 and A["precis"][2] < 1e-13
 
 
+def test_golden_anoxic_model_with_output_on_gpu(built):
+    """The reference's compiled-model example (inst/dynload/anoxmodc.c: 4 states, 1 output variable, parameters
+    through initfunc) run as the reference's README runs it -- steady(..., dllname, initfunc, nout = 1) -- but through
+    stodes: frozen y and SumS of inst/doc/rootSolve.pdf p.8-9."""
+    import json
+    import os
+    import rootsolve_b200 as rs
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "rootsolve_pdf_p8_anox.json")))
+    out = rs.steady(np.asarray(g["y0"]), func="anoxmod", parms=g["parms"], positive=True, nout=1, outnames=["SumS"])
+    assert out.attributes["steady"]
+    assert out.attributes["dims"]["nnz"] == 14 and out.attributes["dims"]["ngp"] == 4
+    for got, want in zip(out["y"], g["y"]):
+        assert abs(got - want) <= 1e-6 * abs(want) + 1e-6
+    assert out["SumS"][0] == pytest.approx(g["SumS"], rel=1e-9)
+    assert abs(out.attributes["precis"][0] - g["precis"][0]) <= 1e-6 * g["precis"][0]
+
+
 def test_sparsereturn_and_sparsejan_roundtrip(built, oracle):
     """sparsetype='sparsereturn' hands back ian/jan; feeding them back as 'sparsejan' solves the same problem
     (man/stodes.Rd:264-284)"""

@@ -33,6 +33,28 @@ def test_pdf_p16_golden(oracle):
     assert (Type, int(nnzv[0]), ngp, itol) == (4, g["nnz_estimated_by_R"], g["function_calls_estimated_by_R"], 1)
 
 
+def test_pdf_p8_anoxic_model_golden(oracle):
+    """The reference's compiled-code example (inst/dynload/anoxmodc.c) solved by its dense sibling stode: frozen y,
+    SumS and the eight precis values (pdf p.8-9).  The oracle's Newton skeleton reproduces all of them once it always
+    solves J x = beta (as stode does) and the igp terminator is repaired; run exactly as stodes would run it, the
+    reference's unterminated igp (every column its own group) leaves the last Jacobian column empty -> zero pivot."""
+    g = json.load(open(os.path.join(GOLD, "rootsolve_pdf_p8_anox.json")))
+    f = oracle.model("anoxmod", g["parms"])
+    r = oracle.stsparse(np.asarray(g["y0"]), f, sparsetype="sparseint", nnz=None, positive=True, nout=1, lrw=1000,
+                        quirk_first_step_transposed=False, quirk_unterminated_igp=False)
+    assert r["steady"] and r["dims"]["nnz"] == 14 and r["dims"]["ngp"] == 4
+    assert len(r["precis"]) == len(g["precis"])
+    # printed with 7 significant digits; the golden comes from the dense LINPACK sibling, so round-off differences
+    # grow as the quadratically converging iteration approaches 1e-8 (last two values: 1e-5 and 3e-3 relative)
+    for got, want, tol in zip(r["precis"], g["precis"], [2e-6] * 6 + [1e-4, 1e-2]):
+        assert abs(got - want) <= tol * abs(want)
+    for got, want in zip(r["y"], g["y"]):
+        assert float("%.10g" % got) == pytest.approx(want, rel=1e-9, abs=5e-7)
+    assert r["out"][0] == pytest.approx(g["SumS"], rel=1e-12)
+    with pytest.raises(RuntimeError, match="zero pivot"):
+        oracle.stsparse(np.asarray(g["y0"]), f, sparsetype="sparseint", nnz=None, positive=True, nout=1, lrw=1000)
+
+
 def test_structure_hash_fixture(oracle):
     for e in json.load(open(os.path.join(GOLD, "structure_hashes.json"))):
         ian, jan = oracle.sparse_structure(e["kind"], e["nspec"], e["dims"], e["cyclic"])
