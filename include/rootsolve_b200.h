@@ -46,7 +46,11 @@ enum {
 
 /* Sparsity types, the Type argument of R/stodes.R:66-158 / src/sparse.f:343-353.
  * A negative value means "return the structure only" (sparsetype="sparsereturn"). */
-enum { RS_TYPE_USER = 0, RS_TYPE_DETECT = 1, RS_TYPE_1D = 2, RS_TYPE_2D = 3, RS_TYPE_3D = 4 };
+enum { RS_TYPE_USER = 0, RS_TYPE_DETECT = 1, RS_TYPE_1D = 2, RS_TYPE_2D = 3, RS_TYPE_3D = 4,
+       /* 2-D / 3-D grid of which only the states listed in a map are unknowns (sparsetype "2Dmap"/"3Dmap",
+        * R/stodes.R:111-141, src/testMap.f); the nnz vector then continues after the cyclic flags with TotN =
+        * nspec*prod(dims) and the TotN map entries (src/call_stsparse.c:196-206) */
+       RS_TYPE_2DMAP = 30, RS_TYPE_3DMAP = 40 };
 
 /* Linear-solver selection: the reference's imethod (1 = yale, 10 = yale +
  * return ian/jan; R/stodes.R:316-329).  On the GPU "yale" is served by the
@@ -146,6 +150,13 @@ void rs_solver_destroy(rs_solver *s);
  * nnz: in = capacity of jan, out = number of nonzeros. */
 int rs_sparse_structure(int type, int neq, int nspec, const int *dims, const int *cyclic, int *nnz,
                         int *ian, int *jan);
+
+/* Replaces sparse2dmap/sparse3dmap (src/testMap.f:25-115, 119-227).  type = RS_TYPE_2DMAP/3DMAP; neq = number
+ * of states present; pres[totn], totn = nspec*prod(dims): new number (1..neq, in grid order) of each full-grid
+ * state, <= 0 if absent.  nnz: in = capacity, out = count; as in the reference the capacity must EXCEED the
+ * count (updatejan, src/testMap.f:17-20). */
+int rs_sparse_structure_map(int type, int neq, int nspec, const int *dims, const int *cyclic, const int *pres,
+                            int totn, int *nnz, int *ian, int *jan);
 
 /* Replaces JGROUP (src/sparse.f:531-616).  grid_hint: 0 = generic algorithm; otherwise
  * {type, nspec, d1,d2,d3, cyc1,cyc2,cyc3} lets the solver use the wavefront variant. */

@@ -110,6 +110,24 @@ def sparse_structure(kind: str, nspec: int, dims, cyclic=None):
     return ian, jan[: nnz.value].copy()
 
 
+def mapped_structure(kind: str, nspec: int, dims, pres, cyclic=None, cap=None):
+    """ian/jan (1-based, in the NEW numbering) of sparse2dmap / sparse3dmap; pres over the full grid."""
+    L = lib()
+    dims = np.atleast_1d(np.asarray(dims, dtype=np.int32))
+    cyc = np.zeros(len(dims), dtype=np.int32) if cyclic is None else np.asarray(cyclic, dtype=np.int32)
+    pres = np.ascontiguousarray(pres, dtype=np.int32).ravel()
+    n = int((pres > 0).sum())
+    cap = len(pres) * (2 * len(dims) + nspec) + 1 if cap is None else cap
+    ian = np.zeros(n + 1, dtype=np.int32)
+    jan = np.zeros(cap, dtype=np.int32)
+    nnz = C.c_int(cap)
+    fn = {"2Dmap": L.orc_sparse2dmap, "3Dmap": L.orc_sparse3dmap}[kind]
+    rc = fn(n, nspec, _ip(dims), _ip(cyc), C.byref(nnz), _ip(ian), _ip(jan), _ip(pres), len(pres))
+    if rc:
+        raise RuntimeError(f"oracle structure generator failed rc={rc}")
+    return ian, jan[: nnz.value].copy()
+
+
 def jgroup(ian, jan, maxg=None):
     L = lib()
     n = len(ian) - 1
@@ -146,22 +164,24 @@ def stodes_args(n, sparsetype, nnz=None, ngp=None, lrw=None, atol=1e-8, rtol=1e-
         if v[3] == 1:
             v[0] += 2 * nspec
             ngp += 1
-    elif sparsetype == "2D":
-        Type = 3
+    elif sparsetype in ("2D", "2Dmap"):
+        Type = 3 if sparsetype == "2D" else 30
         nspec = int(nnz[0])
         dimens = [int(q) for q in nnz[1:3]]
-        v = [n * (4 + nspec) - 2 * nspec * sum(dimens)] + [int(q) for q in nnz]
+        nstate = n if Type == 3 else nspec * dimens[0] * dimens[1]      # R/stodes.R:116-119
+        v = [nstate * (4 + nspec) - 2 * nspec * sum(dimens)] + [int(q) for q in nnz]
         dimmax = max(dimens)
         # "ngp < 4*nspec+1" in the reference is a comparison, not an assignment
         for slot in (4, 5):
             if v[slot] == 1:
                 v[0] += 2 * dimmax * nspec
                 ngp += 1
-    elif sparsetype == "3D":
-        Type = 4
+    elif sparsetype in ("3D", "3Dmap"):
+        Type = 4 if sparsetype == "3D" else 40
         nspec = int(nnz[0])
         dimens = [int(q) for q in nnz[1:4]]
-        v = [n * (6 + nspec) - 3 * nspec * sum(dimens)] + [int(q) for q in nnz]
+        nstate = n if Type == 4 else nspec * dimens[0] * dimens[1] * dimens[2]   # R/stodes.R:138-141
+        v = [nstate * (6 + nspec) - 3 * nspec * sum(dimens)] + [int(q) for q in nnz]
         if v[5] == 1:
             v[0] += 2 * dimens[1] * dimens[2] * nspec
             ngp += 1
@@ -203,8 +223,9 @@ def model(name: str, parms):
 
 def stsparse(y, func, *, sparsetype, nnz, time=0.0, atol=1e-8, rtol=1e-6, ctol=1e-8, lrw=None,
              ngp=None, positive=False, maxiter=100, ipar=None, rpar=None, nout=0,
-             quirk_first_step_transposed=True, quirk_unterminated_igp=True, want_jacobian=False):
-    """Run the oracle's whole solve; returns a dict shaped like stodes' result."""
+             quirk_first_step_transposed=True, quirk_unterminated_igp=True, want_jacobian=False, nnz_cap=None):
+    """Run the oracle's whole solve; returns a dict shaped like stodes' result.  nnz_cap overrides the nonzero
+    estimate R computes (tests only: the R-level stodes gives the user no such handle for grid types)."""
     L = lib()
     y = np.ascontiguousarray(y, dtype=np.float64).ravel()
     n = len(y)
@@ -213,6 +234,8 @@ def stsparse(y, func, *, sparsetype, nnz, time=0.0, atol=1e-8, rtol=1e-6, ctol=1
     imethod = 1
     if ret_only:
         imethod, Type = 10, -Type
+    if nnz_cap is not None:
+        nnzvec[0] = nnz_cap
     atol_a = np.atleast_1d(np.asarray(atol, dtype=np.float64))
     rtol_a = np.atleast_1d(np.asarray(rtol, dtype=np.float64))
     if isinstance(positive, (bool, np.bool_)):

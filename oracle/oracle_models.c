@@ -65,3 +65,14 @@ void anoxmod(int *neq, double *t, double *y, double *ydot, double *yout, int *ip
     (void)neq; (void)t; (void)ip;
     rsm_anox(y, ydot, yout, p_anox);
 }
+
+/* diffusion on a masked grid (sparsetype "2Dmap"/"3Dmap"); the map is in ipar, see model_math.h */
+static double p_dmap[RSM_DMAP_NPAR];
+void initdiffmap(void (*steadyparms)(int *, double *)) { int N = RSM_DMAP_NPAR; steadyparms(&N, p_dmap); }
+void diffmap(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)t; (void)yout;
+    const int d1 = ip[4], d2 = ip[5], d3 = ip[6];
+    for (int c = 0; c < *neq; c++)
+        ydot[c] = rsm_diffmap_point(y, c, RSM_DMAP_INV(ip), RSM_DMAP_PRES(ip), d1, d2, d3, p_dmap);
+}

@@ -142,6 +142,97 @@ int orc_sparse3d(int ntot, int nspec, const int *dimens, const int *cyclic, int 
     return 0;
 }
 
+/* src/testMap.f:5-23 (updatejan): append the NEW number of full-grid state ii when it is present.  The
+ * reference errors as soon as the write position passes the capacity, i.e. already when the capacity is used up
+ * exactly.  An index outside 1..totn (only the 2-D k==1 wrap of line 97 can produce one, when d1 > d2) reads
+ * beyond `pres` in the reference; here it counts as absent. */
+static int put_mapped(int *ij, int cap, int *jan, const int *pres, int totn, int ii)
+{
+    if (ii < 1 || ii > totn || pres[ii - 1] <= 0) return 0;
+    if (*ij > cap) return -2;           /* already failed: callers OR the codes and return afterwards */
+    jan[*ij - 1] = pres[ii - 1];
+    (*ij)++;
+    return (*ij > cap) ? -2 : 0;
+}
+
+/* src/testMap.f:25-115.  As sparse2d, on the states present in the map: pres[M-1] = new number (1..ntot, in
+ * grid order) of full-grid state M, <= 0 if absent.  Same entry order as sparse2d (incl. the line-97 wrap). */
+int orc_sparse2dmap(int ntot, int nspec, const int *dimens, const int *cyclic, int *nnz, int *ian, int *jan,
+                    const int *pres, int totn)
+{
+    if ((ntot / nspec) * nspec != ntot) return -1;
+    const int d1 = dimens[0], d2 = dimens[1], nb = d1 * d2, cap = *nnz;
+    int ij = 1, rc = 0;
+    ian[0] = 1;
+    for (int i = 1; i <= nspec; i++) {
+        const int isp = (i - 1) * nb;
+        for (int j = 1; j <= d1; j++)
+            for (int k = 1; k <= d2; k++) {
+                const int M = isp + (j - 1) * d2 + k;
+                const int Mnew = pres[M - 1];
+                if (Mnew <= 0) continue;
+                rc |= put_mapped(&ij, cap, jan, pres, totn, M);
+                if (k < d2) rc |= put_mapped(&ij, cap, jan, pres, totn, M + 1);
+                else if (cyclic[1] == 1) rc |= put_mapped(&ij, cap, jan, pres, totn, isp + (j - 1) * d2 + 1);
+                if (j < d1) rc |= put_mapped(&ij, cap, jan, pres, totn, M + d2);
+                else if (cyclic[0] == 1) rc |= put_mapped(&ij, cap, jan, pres, totn, isp + k);
+                if (j > 1) rc |= put_mapped(&ij, cap, jan, pres, totn, M - d2);
+                else if (cyclic[0] == 1) rc |= put_mapped(&ij, cap, jan, pres, totn, isp + (d1 - 1) * d2 + k);
+                if (k > 1) rc |= put_mapped(&ij, cap, jan, pres, totn, M - 1);
+                else if (cyclic[1] == 1) rc |= put_mapped(&ij, cap, jan, pres, totn, isp + j * d1);
+                for (int L = 1; L <= nspec; L++)
+                    if (L != i) rc |= put_mapped(&ij, cap, jan, pres, totn, (L - 1) * nb + (j - 1) * d2 + k);
+                if (rc) return -2;
+                ian[Mnew] = ij;
+            }
+    }
+    *nnz = ij - 1;
+    return 0;
+}
+
+/* src/testMap.f:119-227.  As sparse3d on the present states; no `interact` search here (the reference appends
+ * blindly; with wraps only for dimensions > 2 no duplicate can arise). */
+int orc_sparse3dmap(int ntot, int nspec, const int *dimens, const int *cyclic, int *nnz, int *ian, int *jan,
+                    const int *pres, int totn)
+{
+    if ((ntot / nspec) * nspec != ntot) return -1;
+    const int d1 = dimens[0], d2 = dimens[1], d3 = dimens[2];
+    const int nb = d1 * d2 * d3, cap = *nnz, s1 = d2 * d3;
+    int ij = 1, rc = 0;
+    ian[0] = 1;
+    for (int i = 1; i <= nspec; i++) {
+        const int isp = (i - 1) * nb;
+        for (int j = 1; j <= d1; j++)
+            for (int k = 1; k <= d2; k++)
+                for (int l = 1; l <= d3; l++) {
+                    const int line = isp + (j - 1) * s1 + (k - 1) * d3;
+                    const int M = line + l;
+                    const int Mnew = pres[M - 1];
+                    if (Mnew <= 0) continue;
+                    rc |= put_mapped(&ij, cap, jan, pres, totn, M);
+                    if (l < d3) rc |= put_mapped(&ij, cap, jan, pres, totn, M + 1);
+                    else if (cyclic[2] == 1 && d3 > 2) rc |= put_mapped(&ij, cap, jan, pres, totn, line + 1);
+                    if (l > 1) rc |= put_mapped(&ij, cap, jan, pres, totn, M - 1);
+                    else if (cyclic[2] == 1 && d3 > 2) rc |= put_mapped(&ij, cap, jan, pres, totn, line + d3);
+                    if (k < d2) rc |= put_mapped(&ij, cap, jan, pres, totn, M + d3);
+                    else if (cyclic[1] == 1 && d2 > 2) rc |= put_mapped(&ij, cap, jan, pres, totn, isp + (j - 1) * s1 + l);
+                    if (k > 1) rc |= put_mapped(&ij, cap, jan, pres, totn, M - d3);
+                    else if (cyclic[1] == 1 && d2 > 2) rc |= put_mapped(&ij, cap, jan, pres, totn, isp + j * s1 - d3 + l);
+                    if (j < d1) rc |= put_mapped(&ij, cap, jan, pres, totn, M + s1);
+                    else if (cyclic[0] == 1 && d1 > 2) rc |= put_mapped(&ij, cap, jan, pres, totn, isp + (k - 1) * d3 + l);
+                    if (j > 1) rc |= put_mapped(&ij, cap, jan, pres, totn, M - s1);
+                    else if (cyclic[0] == 1 && d1 > 2)
+                        rc |= put_mapped(&ij, cap, jan, pres, totn, isp + (d1 - 1) * s1 + (k - 1) * d3 + l);
+                    for (int L = 1; L <= nspec; L++)
+                        if (L != i) rc |= put_mapped(&ij, cap, jan, pres, totn, (L - 1) * nb + (j - 1) * s1 + (k - 1) * d3 + l);
+                    if (rc) return -2;
+                    ian[Mnew] = ij;
+                }
+    }
+    *nnz = ij - 1;
+    return 0;
+}
+
 /* ------------------------------------------------------------------------ */
 /* Column grouping                                                            */
 /* ------------------------------------------------------------------------ */
@@ -931,8 +1022,17 @@ int orc_stsparse(const orc_args *A, orc_result *R)
         memcpy(jan, A->jan_in, sizeof(int) * (size_t)nnz);
     }
     { /* src/call_stsparse.c:189-195 */
-        const int nd = (atype == 2) ? 3 : (atype == 3) ? 5 : (atype == 4) ? 7 : 0;
+        const int nd = (atype == 2) ? 3 : (atype == 3 || atype == 30) ? 5 : (atype == 4 || atype == 40) ? 7 : 0;
         for (int j = 0; j < nd && j + 1 < A->nnnz; j++) dims[j] = A->nnzvec[j + 1];
+    }
+    /* mapped grids, src/call_stsparse.c:196-206: after the cyclic flags come TotN and the map itself */
+    const int *pres = NULL;
+    int totn = 0;
+    if (atype == 30 || atype == 40) {
+        const int at = (atype == 30) ? 6 : 8;
+        if (A->nnnz < at + 1 || A->nnnz < at + 1 + A->nnzvec[at]) { rc = fail(R, -11, "nnz vector too short for a mapped grid"); goto done; }
+        totn = A->nnzvec[at];
+        pres = A->nnzvec + at + 1;
     }
     memset(igp, 0, sizeof(int) * ((size_t)maxg + 1));
     memset(jgp, 0, sizeof(int) * (size_t)n);
@@ -968,8 +1068,12 @@ int orc_stsparse(const orc_args *A, orc_result *R)
         rc = orc_sparse2d(n, dims[0], &dims[1], &dims[3], &nnz, ian, jan);
     } else if (atype == 4) {
         rc = orc_sparse3d(n, dims[0], &dims[1], &dims[4], &nnz, ian, jan);
+    } else if (atype == 30) {
+        rc = orc_sparse2dmap(n, dims[0], &dims[1], &dims[3], &nnz, ian, jan, pres, totn);
+    } else if (atype == 40) {
+        rc = orc_sparse3dmap(n, dims[0], &dims[1], &dims[4], &nnz, ian, jan, pres, totn);
     } else if (atype != 0) {
-        rc = fail(R, -11, "mapped sparsity types (30/40) are out of scope"); goto done;
+        rc = fail(R, -11, "cannot run stodes: sparsetype not known"); goto done;
     }
     if (rc == -1) { fail(R, rc, "cannot generate sparse jacobian - N and nspec not compatible"); goto done; }
     if (rc == -2) { fail(R, rc, "cannot generate sparse jacobian - not enough room for nonzeros"); goto done; }

@@ -32,6 +32,13 @@ int orc_sparse1d(int ntot, int nspec, int dim, int cyclic, int *nnz, int *ian, i
 int orc_sparse2d(int ntot, int nspec, const int *dimens, const int *cyclic, int *nnz, int *ian, int *jan);
 int orc_sparse3d(int ntot, int nspec, const int *dimens, const int *cyclic, int *nnz, int *ian, int *jan);
 
+/* mapped (masked) grids, src/testMap.f:25-115, 119-227.  pres[M-1] = new number of full-grid state M (1..ntot,
+ * increasing with M) or <= 0 if the state is absent; totn = nspec * prod(dimens) = length of pres. */
+int orc_sparse2dmap(int ntot, int nspec, const int *dimens, const int *cyclic, int *nnz, int *ian, int *jan,
+                    const int *pres, int totn);
+int orc_sparse3dmap(int ntot, int nspec, const int *dimens, const int *cyclic, int *nnz, int *ian, int *jan,
+                    const int *pres, int totn);
+
 /* column grouping, src/sparse.f:531-616.  igp has room for maxg+1 entries.
  * Returns 0, 1 (ier: not all columns chosen) or 2 (more than maxg groups). */
 int orc_jgroup(int n, const int *ia, const int *ja, int maxg, int *ngrp, int *igp, int *jgp);
@@ -70,7 +77,7 @@ typedef struct {
     int nout;
     const double *rpar; int nrpar;
     const int *ipar; int nipar;
-    int type;                      /* 0,+-1,+-2,+-3,+-4 */
+    int type;                      /* 0,+-1,+-2,+-3,+-4,+-30,+-40 */
     const int *ian_in; const int *jan_in;   /* type 0 only */
     int imethod;                   /* 1 yale, 10 sparsereturn */
     int quirk_first_step_transposed; /* 1 = as the reference (A.3-1), 0 = always solve J x = beta */

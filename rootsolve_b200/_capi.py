@@ -14,6 +14,7 @@ LIB_MODELS = os.path.join(HERE, "librs_models.so")
 
 RS_OK = 0
 RS_TYPE_USER, RS_TYPE_1D, RS_TYPE_2D, RS_TYPE_3D = 0, 2, 3, 4
+RS_TYPE_2DMAP, RS_TYPE_3DMAP = 30, 40
 RS_PRECOND_NONE, RS_PRECOND_JACOBI, RS_PRECOND_BLOCK_JACOBI, RS_PRECOND_AUTO = 0, 1, 2, -1
 ERROR_NAMES = {-1: "RS_EINVAL", -2: "RS_ENODEVICE", -3: "RS_ENOMEM", -4: "RS_ESTRUCT", -5: "RS_EGROUP",
                -6: "RS_EDUPLICATE", -7: "RS_ESINGULAR", -8: "RS_EMODEL", -9: "RS_ECOMM", -10: "RS_ETOOBIG"}
@@ -90,6 +91,8 @@ def lib():
         L.rs_solver_destroy.argtypes = [C.c_void_p]
         L.rs_solver_destroy.restype = None
         L.rs_sparse_structure.argtypes = [C.c_int, C.c_int, C.c_int, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p]
+        L.rs_sparse_structure_map.argtypes = [C.c_int, C.c_int, C.c_int, c_int_p, c_int_p, c_int_p, C.c_int, c_int_p,
+                                              c_int_p, c_int_p]
         L.rs_jgroup.argtypes = [C.c_int, c_int_p, c_int_p, C.c_int, c_int_p, c_int_p, c_int_p, c_int_p]
         L.rs_fd_jacobian.argtypes = [C.c_void_p, c_double_p, C.c_int, C.c_int, C.c_double, c_double_p, c_int_p, c_int_p,
                                      c_int_p, c_int_p, C.c_int, c_double_p, C.c_int, c_int_p, C.c_int, c_double_p,

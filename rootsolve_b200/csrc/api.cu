@@ -234,11 +234,16 @@ static int init_model(const rs_model_desc *m, const double *initpar, int ninitpa
 
 static int grid_from_nnz(int type, const int *nnzv, int nnnz, int n, GridDesc &g)
 {
-    const int at = std::abs(type);
+    int at = std::abs(type);
+    const bool mapped = at == RS_TYPE_2DMAP || at == RS_TYPE_3DMAP;
+    if (mapped) at = at == RS_TYPE_2DMAP ? RS_TYPE_2D : RS_TYPE_3D;
     g = GridDesc();
     g.type = at;
     const int need = at == RS_TYPE_1D ? 4 : at == RS_TYPE_2D ? 6 : 8;
-    if (nnnz < need) { set_error("nnz vector too short for sparsity type %d", type); return RS_EINVAL; }
+    if (nnnz < need + (mapped ? 1 : 0) || (mapped && (nnzv[need] < 0 || nnnz < need + 1 + nnzv[need]))) {
+        set_error("nnz vector too short for sparsity type %d", type);
+        return RS_EINVAL;
+    }
     g.nspec = nnzv[1];
     if (at == RS_TYPE_1D) { g.d[0] = nnzv[2]; g.cyc[0] = nnzv[3]; g.ncell = g.d[0]; }
     if (at == RS_TYPE_2D) { g.d[0] = nnzv[2]; g.d[1] = nnzv[3]; g.cyc[0] = nnzv[4]; g.cyc[1] = nnzv[5]; g.ncell = g.d[0] * g.d[1]; }
@@ -247,6 +252,7 @@ static int grid_from_nnz(int type, const int *nnzv, int nnnz, int n, GridDesc &g
         g.cyc[0] = nnzv[5]; g.cyc[1] = nnzv[6]; g.cyc[2] = nnzv[7];
         g.ncell = g.d[0] * g.d[1] * g.d[2];
     }
+    if (mapped) return RS_OK;   // build_mapped_structure checks the map against the grid
     if (g.nspec <= 0 || g.ncell <= 0 || (long long)g.nspec * g.ncell != n) {
         set_error("cannot generate sparse jacobian - N and nspec not compatible");
         return RS_ESTRUCT;
@@ -263,7 +269,8 @@ static int check_args(const rs_stsparse_args *a)
     if (a->nrtol > 1 && a->nrtol != a->neq) { set_error("`rtol' must either be a scalar, or as long as `y'"); return RS_EINVAL; }
     if (a->imethod != 1 && a->imethod != 10) { set_error("`spmethod' must be `yale' on this path (imethod 1 or 10)"); return RS_EINVAL; }
     const int at = std::abs(a->Type);
-    if (at != RS_TYPE_USER && at != RS_TYPE_DETECT && at != RS_TYPE_1D && at != RS_TYPE_2D && at != RS_TYPE_3D) {
+    if (at != RS_TYPE_USER && at != RS_TYPE_DETECT && at != RS_TYPE_1D && at != RS_TYPE_2D && at != RS_TYPE_3D &&
+        at != RS_TYPE_2DMAP && at != RS_TYPE_3DMAP) {
         set_error("cannot run stodes: sparsetype not known (Type %d is outside this path)", a->Type);
         return RS_EINVAL;
     }
@@ -311,6 +318,16 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         RS_TRY(s.jan.alloc((size_t)s.nnz));
         RS_TRY(s.ian.upload(a->ian, (size_t)n + 1, c.stream));
         RS_TRY(s.jan.upload(a->jan, (size_t)s.nnz, c.stream));
+    } else if (std::abs(a->Type) == RS_TYPE_2DMAP || std::abs(a->Type) == RS_TYPE_3DMAP) {
+        GridDesc full;
+        RS_TRY(grid_from_nnz(a->Type, a->nnz, a->nnnz, n, full));
+        const int at = std::abs(a->Type) == RS_TYPE_2DMAP ? 6 : 8;      // TotN, then the map (src/call_stsparse.c:196-206)
+        RS_TRY(build_mapped_structure(c, full, n, a->nnz[at], a->nnz + at + 1, s.ian, s.jan, &s.nnz));
+        if (s.nnz >= a->nnz[0]) {   // updatejan stops once the write position passes nnz, src/testMap.f:17-20
+            set_error("cannot generate sparse jacobian - not enough room for nonzeros");
+            return RS_ESTRUCT;
+        }
+        // s.grid stays "no grid knowledge": grouping, preconditioner and sharding take the general-structure routes
     } else {
         RS_TRY(grid_from_nnz(a->Type, a->nnz, a->nnnz, n, s.grid));
         RS_TRY(build_grid_structure(c, s.grid, n, s.ian, s.jan, &s.nnz));
@@ -611,6 +628,30 @@ extern "C" int rs_sparse_structure(int type, int neq, int nspec, const int *dims
     int z = 0;
     RS_TRY(build_grid_structure(c, g, neq, d_ian, d_jan, &z));
     if (z > *nnz) { set_error("cannot generate sparse jacobian - not enough room for nonzeros"); return RS_ESTRUCT; }
+    RS_TRY(d_ian.download(ian, (size_t)neq + 1, c.stream));
+    RS_TRY(d_jan.download(jan, (size_t)z, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    *nnz = z;
+    return RS_OK;
+}
+
+extern "C" int rs_sparse_structure_map(int type, int neq, int nspec, const int *dims, const int *cyclic, const int *pres,
+                                       int totn, int *nnz, int *ian, int *jan)
+{
+    if (!dims || !pres || !nnz || !ian || !jan) { set_error("null argument"); return RS_EINVAL; }
+    if (type != RS_TYPE_2DMAP && type != RS_TYPE_3DMAP) { set_error("type must be RS_TYPE_2DMAP or RS_TYPE_3DMAP"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    Ctx c;
+    GridDesc g;
+    g.type = type == RS_TYPE_2DMAP ? RS_TYPE_2D : RS_TYPE_3D; g.nspec = nspec;
+    const int nd = type == RS_TYPE_2DMAP ? 2 : 3;
+    long long cells = 1;
+    for (int q = 0; q < nd; q++) { g.d[q] = dims[q]; g.cyc[q] = cyclic ? cyclic[q] : 0; cells *= dims[q]; }
+    g.ncell = (int)cells;
+    DevBuf<int> d_ian, d_jan;
+    int z = 0;
+    RS_TRY(build_mapped_structure(c, g, neq, totn, pres, d_ian, d_jan, &z));
+    if (z >= *nnz) { set_error("cannot generate sparse jacobian - not enough room for nonzeros"); return RS_ESTRUCT; }
     RS_TRY(d_ian.download(ian, (size_t)neq + 1, c.stream));
     RS_TRY(d_jan.download(jan, (size_t)z, c.stream));
     RS_CUDA(cudaStreamSynchronize(c.stream));

@@ -32,6 +32,8 @@ struct HaloPlan {
 // structure.cu
 int exclusive_scan(Ctx &c, const int *in, int *out, int n, int base, bool write_total);
 int build_grid_structure(Ctx &c, const GridDesc &g, int n, DevBuf<int> &d_ian, DevBuf<int> &d_jan, int *nnz);
+int build_mapped_structure(Ctx &c, const GridDesc &g, int n, int totn, const int *h_pres, DevBuf<int> &d_ian,
+                           DevBuf<int> &d_jan, int *nnz);
 int build_csr_pattern(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, DevBuf<int> &rowptr,
                       DevBuf<int> &col);
 

@@ -148,6 +148,99 @@ int build_grid_structure(Ctx &c, const GridDesc &g, int n, DevBuf<int> &d_ian, D
     return RS_OK;
 }
 
+// ---- mapped (masked) grids: sparse2dmap / sparse3dmap, src/testMap.f:25-227 ----------
+// pres[M-1] = new number (1..n, increasing with M) of full-grid state M, <= 0 if absent.  The reference walks the
+// full grid and appends to column pres(M) the NEW numbers of the present neighbours, in sparse2d/sparse3d order.
+// Here: invert the map (inv[c] = M), then one thread per present column runs emit_column on its full-grid
+// position and keeps the present rows (count pass, prefix sum, fill pass as above).
+__global__ void map_invert_kernel(const int *__restrict__ pres, int totn, int n, int *__restrict__ inv, int *__restrict__ flag)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int p = (i < totn) ? pres[i] : 0;
+    if (p > n) atomicMax(&flag[0], 1);
+    else if (p > 0) inv[p - 1] = i + 1;
+    const unsigned present = __ballot_sync(0xffffffffu, p > 0);
+    if ((threadIdx.x & 31) == 0 && present) atomicAdd(&flag[1], __popc(present));
+}
+
+__global__ void map_check_kernel(const int *__restrict__ inv, int n, int *__restrict__ flag)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    if (inv[c] == 0 || (c + 1 < n && inv[c] >= inv[c + 1])) atomicMax(&flag[0], 2);
+}
+
+template <bool FILL>
+__global__ void structure_map_kernel(GridDesc g, int n, int totn, const int *__restrict__ pres, const int *__restrict__ inv,
+                                     const int *__restrict__ ian, int *__restrict__ out)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    int cnt = 0, pos = FILL ? ian[c] - 1 : 0;
+    emit_column(g, inv[c], [&](int row) {
+        // a row outside 1..totn can only come from the 2-D wrap of src/testMap.f:97 when d1 > d2 (the reference
+        // reads beyond `pres` there); it counts as absent
+        const int p = (row >= 1 && row <= totn) ? pres[row - 1] : 0;
+        if (p > 0) {
+            if (FILL) out[pos++] = p; else cnt++;
+        }
+    });
+    if (!FILL) out[c] = cnt;
+}
+
+// g describes the FULL grid (g.nspec * g.ncell = totn = length of h_pres); n = number of present states.
+int build_mapped_structure(Ctx &c, const GridDesc &g, int n, int totn, const int *h_pres, DevBuf<int> &d_ian,
+                           DevBuf<int> &d_jan, int *nnz)
+{
+    if (g.nspec <= 0 || (n / g.nspec) * g.nspec != n) {           // src/testMap.f:51-54, 141-144
+        set_error("cannot generate sparse jacobian - N and nspec not compatible");
+        return RS_ESTRUCT;
+    }
+    if (g.ncell <= 0 || (long long)g.nspec * g.ncell != totn) {
+        set_error("mapped grid: the map has %d entries, nspec*prod(dimens) = %lld", totn, (long long)g.nspec * g.ncell);
+        return RS_EINVAL;
+    }
+    DevBuf<int> pres, inv, flag, counts;
+    RS_TRY(pres.alloc(totn)); RS_TRY(inv.alloc(n)); RS_TRY(flag.alloc(2)); RS_TRY(counts.alloc(n));
+    RS_TRY(pres.upload(h_pres, totn, c.stream));
+    RS_TRY(inv.zero(c.stream));
+    RS_TRY(flag.zero(c.stream));
+    {
+        Launch L(c, K_STRUCT, 4.0 * totn + 4.0 * n);
+        map_invert_kernel<<<(totn + 255) / 256, 256, 0, c.stream>>>(pres.p, totn, n, inv.p, flag.p);
+    }
+    {
+        Launch L(c, K_STRUCT, 4.0 * n);
+        map_check_kernel<<<(n + 255) / 256, 256, 0, c.stream>>>(inv.p, n, flag.p);
+    }
+    int hflag[2] = {0, 0};
+    RS_CUDA(cudaMemcpyAsync(hflag, flag.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    if (hflag[0] || hflag[1] != n) {
+        set_error("mapped grid: the map must number the %d present states 1..%d in grid order (%d entries are present)", n, n,
+                  hflag[1]);
+        return RS_EINVAL;
+    }
+    RS_TRY(d_ian.alloc((size_t)n + 1));
+    {
+        Launch L(c, K_STRUCT, 8.0 * n);
+        structure_map_kernel<false><<<(n + 255) / 256, 256, 0, c.stream>>>(g, n, totn, pres.p, inv.p, nullptr, counts.p);
+    }
+    RS_TRY(exclusive_scan(c, counts.p, d_ian.p, n, 1, true));
+    int last = 0;
+    RS_CUDA(cudaMemcpyAsync(&last, d_ian.p + n, sizeof(int), cudaMemcpyDeviceToHost, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    *nnz = last - 1;
+    RS_TRY(d_jan.alloc((size_t)*nnz));
+    {
+        Launch L(c, K_STRUCT, 8.0 * n + 4.0 * *nnz);
+        structure_map_kernel<true><<<(n + 255) / 256, 256, 0, c.stream>>>(g, n, totn, pres.p, inv.p, d_ian.p, d_jan.p);
+    }
+    RS_CUDA(cudaGetLastError());
+    RS_CUDA(cudaStreamSynchronize(c.stream));  // pres/inv are released on return
+    return RS_OK;
+}
+
 // ---- CSC -> CSR pattern ------------------------------------------------------
 __global__ void row_hist_kernel(const int *__restrict__ jan, int nnz, int *__restrict__ cnt)
 {

@@ -175,4 +175,41 @@ RSM_HD void rsm_anox(const double *y, double *ydot, double *yout, const double *
     yout[0] = SO4 + HS;
 }
 
+/* Diffusion with first-order consumption on a MASKED 2-D or 3-D grid (sparsetype "2Dmap"/"3Dmap", src/testMap.f):
+ * the state vector holds only the cells present in the map, numbered in grid order; absent cells and the outside
+ * of the grid carry the imposed value BND.  A direction of extent 1 carries no flux (a 2-D map (a,b) is the 3-D
+ * layout (1,a,b)).  Parameters as diff3d.  The map travels in ipar:
+ *   ip[3]=1 ip[4]=d1 ip[5]=d2 ip[6]=d3 ip[7]=unused ip[8]=n, then inv[n] (full-grid number, 1-based, of unknown c)
+ *   and pres[d1*d2*d3] (new number of a full-grid cell, <= 0 if absent). */
+#define RSM_DMAP_NPAR 8
+#define RSM_DMAP_INV(ip) ((ip) + 9)
+#define RSM_DMAP_PRES(ip) ((ip) + 9 + (ip)[8])
+RSM_HD double rsm_dmap_value(const double *y, const int *pres, int inside, int cell, double bnd)
+{
+    if (!inside) return bnd;
+    const int p = pres[cell];
+    return (p > 0) ? y[p - 1] : bnd;
+}
+
+RSM_HD double rsm_diffmap_point(const double *y, int c, const int *inv, const int *pres, int d1, int d2, int d3,
+                                const double *p)
+{
+    const double Dx = p[0], Dy = p[1], Dz = p[2], dx = p[3], dy = p[4], dz = p[5], r = p[6], bnd = p[7];
+    const int s2 = d3, s1 = d2 * d3;
+    const int cell = inv[c] - 1;
+    const int j = cell / s1, rem = cell - j * s1, k = rem / s2, l = rem - k * s2;
+    const double yc = y[c];
+    double dY = -r * yc;
+    if (d3 > 1)
+        dY = dY - rsm_flux_div(rsm_dmap_value(y, pres, l > 0, cell - 1, bnd), yc,
+                               rsm_dmap_value(y, pres, l < d3 - 1, cell + 1, bnd), Dx, dx);
+    if (d2 > 1)
+        dY = dY - rsm_flux_div(rsm_dmap_value(y, pres, k > 0, cell - s2, bnd), yc,
+                               rsm_dmap_value(y, pres, k < d2 - 1, cell + s2, bnd), Dy, dy);
+    if (d1 > 1)
+        dY = dY - rsm_flux_div(rsm_dmap_value(y, pres, j > 0, cell - s1, bnd), yc,
+                               rsm_dmap_value(y, pres, j < d1 - 1, cell + s1, bnd), Dz, dz);
+    return dY;
+}
+
 #endif /* RSM_MODEL_MATH_H */

@@ -87,22 +87,25 @@ def sparse_args(n, sparsetype, nnz=None, inz=None, ngp=None, lrw=None):
         if nnzv[3] == 1:
             nnzv[0] += 2 * nspec
             ngp += 1
-    elif sparsetype == "2D":
-        Type = 3
+    elif sparsetype in ("2D", "2Dmap"):
+        # "2Dmap": nnz = (nspec, dimens, cyclic, TotN, map[TotN]) and y holds only the states present in the map
+        Type = 3 if sparsetype == "2D" else 30
         nspec = int(nnz[0])
         dimens = [int(v) for v in nnz[1:3]]
-        nnzv = [n * (4 + nspec) - 2 * nspec * sum(dimens)] + [int(v) for v in nnz]
+        nstate = n if Type == 3 else nspec * dimens[0] * dimens[1]     # R/stodes.R:116-119
+        nnzv = [nstate * (4 + nspec) - 2 * nspec * sum(dimens)] + [int(v) for v in nnz]
         # R/stodes.R:121 "ngp < 4*nspec+1" compares instead of assigning: ngp stays n+1
         dimmax = max(dimens)
         for slot in (4, 5):
             if nnzv[slot] == 1:
                 nnzv[0] += 2 * dimmax * nspec
                 ngp += 1
-    elif sparsetype == "3D":
-        Type = 4
+    elif sparsetype in ("3D", "3Dmap"):
+        Type = 4 if sparsetype == "3D" else 40
         nspec = int(nnz[0])
         dimens = [int(v) for v in nnz[1:4]]
-        nnzv = [n * (6 + nspec) - 3 * nspec * sum(dimens)] + [int(v) for v in nnz]
+        nstate = n if Type == 4 else nspec * dimens[0] * dimens[1] * dimens[2]   # R/stodes.R:138-141
+        nnzv = [nstate * (6 + nspec) - 3 * nspec * sum(dimens)] + [int(v) for v in nnz]
         if nnzv[5] == 1:
             nnzv[0] += 2 * dimens[1] * dimens[2] * nspec
             ngp += 1
@@ -112,8 +115,6 @@ def sparse_args(n, sparsetype, nnz=None, inz=None, ngp=None, lrw=None):
         if nnzv[7] == 1:
             nnzv[0] += 2 * dimens[0] * dimens[1] * nspec
             ngp += 1
-    elif sparsetype in ("2Dmap", "3Dmap"):
-        raise NotImplementedError("mapped grids (2Dmap/3Dmap) are outside this path (SURVEY.md 8(f))")
     else:
         raise ValueError("cannot run stodes: sparsetype not known ")
     if lrw is None:

@@ -22,6 +22,29 @@ def dp(a):
     return a.ctypes.data_as(C.POINTER(C.c_double))
 
 
+def make_map(mask, nspec=1):
+    """The presence map of sparsetype '2Dmap'/'3Dmap' (src/testMap.f): mask is a boolean array in stodes' dimension
+    order (last index fastest), the same for every species.  Returns (pres, inv): pres[M-1] = new number of
+    full-grid state M (0 if absent), inv[c] = full-grid number of unknown c (both 1-based values)."""
+    m = np.tile(np.asarray(mask, dtype=bool).ravel(), nspec)
+    pres = np.zeros(m.size, dtype=np.int32)
+    pres[m] = np.arange(1, int(m.sum()) + 1, dtype=np.int32)
+    inv = (np.nonzero(m)[0] + 1).astype(np.int32)
+    return pres, inv
+
+
+def ball_mask(dims, shrink=0.5):
+    """cells whose centre lies inside the ellipsoid inscribed in the grid (a lake, a sphere...)"""
+    axes = [(np.arange(d) + 0.5) / d - 0.5 for d in dims]
+    g = np.meshgrid(*axes, indexing="ij")
+    return sum(a * a for a in g) <= shrink * shrink
+
+
+def diffmap_ipar(dims3, pres, inv):
+    """ipar of the bundled `diffmap` model (model_math.h): nspec, d1, d2, d3, unused, n, inv[n], pres[ncell]"""
+    return np.concatenate([[1, dims3[0], dims3[1], dims3[2], 0, len(inv)], inv, pres]).astype(np.int32)
+
+
 def within_tol(y, yref, atol=1e-10, rtol=1e-10, factor=1.0):
     """The parity bound of BASELINE.json: |y - yref| <= atol + rtol*|yref| (times factor)."""
     err = np.abs(np.asarray(y) - np.asarray(yref))
