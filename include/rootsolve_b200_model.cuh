@@ -104,15 +104,31 @@ static int rs_launch_batched(void *stream, int neq, double t, const double *y, d
         cudaMemcpyToSymbol(parms, rs_parms_host_, sizeof(double) * N);           \
     }
 
-#define RS_MODEL_NAMED(NAME, FUNC, NPARMS, INITFN)                               \
+/* N forcing function values in __constant__ memory + the initialiser `initforc` of the reference's compiled
+ * models (deSolve's convention; R/stodes.R:222-237, src/steady_utils.c:62-77).  A steady-state solve sees the
+ * forcings at ONE time, so the values are constants of the solve. */
+#define RS_MODEL_FORCS(N)                                                        \
+    static __constant__ double forcs[N];                                         \
+    static double rs_forcs_host_[N];                                             \
+    static void rs_model_initforc_(void (*steadyforcs)(int *, double *))         \
+    {                                                                            \
+        int n_ = N;                                                              \
+        steadyforcs(&n_, rs_forcs_host_);                                        \
+        cudaMemcpyToSymbol(forcs, rs_forcs_host_, sizeof(double) * N);           \
+    }
+
+#define RS_MODEL_NAMED_F(NAME, FUNC, NPARMS, INITFN, FORCFN)                     \
     extern "C" const rs_model_desc *rs_model_##NAME(void)                        \
     {                                                                            \
-        static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched<FUNC>, INITFN, nullptr}; \
+        static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched<FUNC>, INITFN, FORCFN}; \
         return &d;                                                               \
     }
+#define RS_MODEL_NAMED(NAME, FUNC, NPARMS, INITFN) RS_MODEL_NAMED_F(NAME, FUNC, NPARMS, INITFN, nullptr)
 
 /* model with RS_MODEL_PARMS(NPARMS) declared earlier in the same file */
 #define RS_MODEL(FUNC, NPARMS) RS_MODEL_NAMED(FUNC, FUNC, NPARMS, rs_model_init_)
+/* model with RS_MODEL_PARMS(NPARMS) and RS_MODEL_FORCS(...) declared earlier in the same file */
+#define RS_MODEL_WITH_FORCS(FUNC, NPARMS) RS_MODEL_NAMED_F(FUNC, FUNC, NPARMS, rs_model_init_, rs_model_initforc_)
 /* model without parameters */
 #define RS_MODEL_NOPARMS(FUNC) RS_MODEL_NAMED(FUNC, FUNC, 0, nullptr)
 

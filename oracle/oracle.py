@@ -204,8 +204,8 @@ def stodes_args(n, sparsetype, nnz=None, ngp=None, lrw=None, atol=1e-8, rtol=1e-
 _KEEP = []  # keep ctypes callbacks alive
 
 
-def model(name: str, parms):
-    """Address of a bundled host model after running its initialiser with parms."""
+def model(name: str, parms, forcs=None):
+    """Address of a bundled host model after running its initialiser(s) with parms (and forcs)."""
     L = lib()
     p = np.ascontiguousarray(parms, dtype=np.float64)
 
@@ -218,6 +218,23 @@ def model(name: str, parms):
     cb = PARMS_CB(steadyparms)
     _KEEP.append(cb)
     getattr(L, "init" + name)(cb)
+    if forcs is not None:       # the forcing initialiser, src/call_stsparse.c:242-251
+        f = np.ascontiguousarray(forcs, dtype=np.float64)
+
+        bad = []
+
+        def steadyforcs(N, dst):
+            if N[0] != len(f):      # an exception cannot cross the C frame: note it, raise after the call
+                bad.append(N[0])
+                return
+            for i in range(N[0]):
+                dst[i] = f[i]
+
+        cbf = PARMS_CB(steadyforcs)
+        _KEEP.append(cbf)
+        getattr(L, "forc" + name)(cbf)
+        if bad:
+            raise ValueError("Confusion over the length of forcs.")
     return C.cast(getattr(L, name), C.c_void_p)
 
 

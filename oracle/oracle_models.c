@@ -66,6 +66,18 @@ void anoxmod(int *neq, double *t, double *y, double *ydot, double *yout, int *ip
     rsm_anox(y, ydot, yout, p_anox);
 }
 
+/* ... and with Flux and BO2 as forcing function values (initforc convention, src/steady_utils.c:62-77) */
+static double p_anoxf[RSM_ANOX_NPAR], f_anoxf[RSM_ANOXF_NFORC];
+void initanoxforc(void (*steadyparms)(int *, double *)) { int N = RSM_ANOX_NPAR; steadyparms(&N, p_anoxf); }
+void forcanoxforc(void (*steadyforcs)(int *, double *)) { int N = RSM_ANOXF_NFORC; steadyforcs(&N, f_anoxf); }
+void anoxforc(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)ip;
+    double p[RSM_ANOX_NPAR];
+    rsm_anox_forced_parms(p_anoxf, f_anoxf, p);
+    rsm_anox(y, ydot, yout, p);
+}
+
 /* diffusion on a masked grid (sparsetype "2Dmap"/"3Dmap"); the map is in ipar, see model_math.h */
 static double p_dmap[RSM_DMAP_NPAR];
 void initdiffmap(void (*steadyparms)(int *, double *)) { int N = RSM_DMAP_NPAR; steadyparms(&N, p_dmap); }

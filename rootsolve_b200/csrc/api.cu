@@ -216,7 +216,19 @@ static void steadyparms_cb(int *N, double *dst)
     for (int i = 0; i < *N; i++) dst[i] = tl_parms[i];
 }
 
-static int init_model(const rs_model_desc *m, const double *initpar, int ninitpar)
+// ... and the forcing function values through initforc, src/call_stsparse.c:242-251, src/steady_utils.c:62-77
+static void steadyforcs_cb(int *N, double *dst)
+{
+    if (*N != tl_nparms) {
+        set_error("Confusion over the length of forcs: passed to solver %d; in model %d", tl_nparms, *N);
+        tl_parm_err = 1;
+        return;
+    }
+    for (int i = 0; i < *N; i++) dst[i] = tl_parms[i];
+}
+
+static int init_model(const rs_model_desc *m, const double *initpar, int ninitpar, const double *forcs = nullptr,
+                      int nforcs = 0)
 {
     if (!m || m->abi != RS_MODEL_ABI || !m->launch) {
         set_error("`func' must be a compiled device model (rs_model_desc with ABI %d)", RS_MODEL_ABI);
@@ -228,6 +240,17 @@ static int init_model(const rs_model_desc *m, const double *initpar, int ninitpa
         if (tl_parm_err) return RS_EMODEL;
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("model initialiser failed: %s", cudaGetErrorString(e)); return RS_ENODEVICE; }
+    }
+    if (forcs && nforcs > 0) {
+        if (!m->initforc) {
+            set_error("forcings were given but the model exports no forcing initialiser (initforc)");
+            return RS_EMODEL;
+        }
+        tl_parms = forcs; tl_nparms = nforcs; tl_parm_err = 0;
+        m->initforc(steadyforcs_cb);
+        if (tl_parm_err) return RS_EMODEL;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("forcing initialiser failed: %s", cudaGetErrorString(e)); return RS_ENODEVICE; }
     }
     return RS_OK;
 }
@@ -309,7 +332,7 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
     RS_TRY(s.y.upload(a->y, n, c.stream));
     // structure (xsparsestruct, src/sparse.f:300-455)
     if (std::abs(a->Type) == RS_TYPE_DETECT) {
-        RS_TRY(init_model(a->func, a->initpar, a->ninitpar));
+        RS_TRY(init_model(a->func, a->initpar, a->ninitpar, a->forcs, a->nforcs));
         RS_TRY(detect_structure(c, a->func, n, a->time, s.y.p, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, a->nnz[0], s.ian,
                                 s.jan, &s.nnz));
     } else if (std::abs(a->Type) == RS_TYPE_USER) {
@@ -337,7 +360,7 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         }
     }
     if (!s.structure_only) {
-        RS_TRY(init_model(a->func, a->initpar, a->ninitpar));
+        RS_TRY(init_model(a->func, a->initpar, a->ninitpar, a->forcs, a->nforcs));
         RS_TRY(build_csr_pattern(c, n, s.nnz, s.ian.p, s.jan.p, s.rowptr, s.col));
         RS_TRY(jgroup_device(c, s.grid, n, s.nnz, s.ian.p, s.jan.p, s.rowptr.p, s.col.p, s.maxg, s.group_of, &s.ngp));
         RS_TRY(s.val.alloc((size_t)s.nnz));

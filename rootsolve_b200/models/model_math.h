@@ -175,6 +175,15 @@ RSM_HD void rsm_anox(const double *y, double *ydot, double *yout, const double *
     yout[0] = SO4 + HS;
 }
 
+/* the same model with Flux and BO2 taken from two forcing function values (anoxforc) */
+#define RSM_ANOXF_NFORC 2
+RSM_HD void rsm_anox_forced_parms(const double *p, const double *forcs, double *q)
+{
+    for (int i = 0; i < RSM_ANOX_NPAR; i++) q[i] = p[i];
+    q[1] = forcs[0];
+    q[6] = forcs[1];
+}
+
 /* Diffusion with first-order consumption on a MASKED 2-D or 3-D grid (sparsetype "2Dmap"/"3Dmap", src/testMap.f):
  * the state vector holds only the cells present in the map, numbered in grid order; absent cells and the outside
  * of the grid carry the imposed value BND.  A direction of extent 1 carries no flux (a 2-D map (a,b) is the 3-D

@@ -122,6 +122,49 @@ def sparse_args(n, sparsetype, nnz=None, inz=None, ngp=None, lrw=None):
     return Type, np.asarray(nnzv, dtype=np.int32), int(ngp), int(min(lrw, 2**31 - 1)), ian, jan
 
 
+def approx(xy, xout, method="linear", rule=1, f=0.0, ties="mean"):
+    """R's ``approx(x, y, xout, method, rule, f, ties)`` at ONE point, which is all ``stodes`` asks of it
+    (R/stodes.R:229-236).  rule 1: NaN outside the data range, 2: the value at the closest extreme."""
+    xy = np.asarray(xy, dtype=np.float64)
+    if xy.ndim != 2 or xy.shape[1] != 2:
+        raise ValueError("a forcing function data set must be a two-columned matrix (time, value)")
+    ok = ~(np.isnan(xy[:, 0]) | np.isnan(xy[:, 1]))
+    x, v = xy[ok, 0], xy[ok, 1]
+    order = np.argsort(x, kind="stable")
+    x, v = x[order], v[order]
+    ux, start = np.unique(x, return_index=True)
+    if len(ux) < len(x):                       # tied times
+        if ties not in ("mean", "ordered", "min", "max"):
+            raise ValueError("ties must be 'mean', 'ordered', 'min' or 'max'")
+        groups = np.split(v, start[1:])
+        pick = {"mean": np.mean, "min": np.min, "max": np.max, "ordered": lambda g: g[-1]}[ties]
+        x, v = ux, np.asarray([pick(g) for g in groups])
+    if len(x) == 0 or (method == "linear" and len(x) < 2):
+        raise ValueError("need at least two non-NA values to interpolate")
+    rules = (rule, rule) if np.ndim(rule) == 0 else tuple(rule)
+    if xout < x[0]:
+        return float(v[0]) if rules[0] == 2 else float("nan")
+    if xout > x[-1]:
+        return float(v[-1]) if rules[1] == 2 else float("nan")
+    hi = int(np.searchsorted(x, xout, side="left"))
+    if x[hi] == xout:
+        return float(v[hi])
+    lo = hi - 1
+    if method == "linear":
+        return float(v[lo] + (v[hi] - v[lo]) * ((xout - x[lo]) / (x[hi] - x[lo])))
+    if method == "constant":
+        return float(v[lo] * (1.0 - f) + v[hi] * f) if f != 0.0 else float(v[lo])
+    raise ValueError("approx: invalid interpolation method")
+
+
+def forcing_values(forcings, time, fcontrol=None):
+    """The ``Forc`` vector of R/stodes.R:229-236: a list of (time, value) data sets is interpolated at `time`;
+    anything else is taken as the vector of forcing function values itself."""
+    if isinstance(forcings, (list, tuple)) and len(forcings) > 0 and all(np.ndim(m) == 2 for m in forcings):
+        return np.asarray([approx(m, time, **(fcontrol or {})) for m in forcings], dtype=np.float64)
+    return np.ascontiguousarray(np.atleast_1d(np.asarray(forcings, dtype=np.float64)).ravel())
+
+
 def _itol(n, atol, rtol):
     itol = 1
     if len(atol) == n and len(rtol) == n:
@@ -241,10 +284,12 @@ def stodes(y, time=0, func=None, parms=None, rtol=1e-6, atol=1e-8, ctol=1e-8, sp
     if times is not None and np.size(times) > 1:
         warnings.warn("`times' should be one number - taking first value")
     time = 0.0 if times is None else float(np.atleast_1d(times)[0])
-    if forcings is not None or initforc is not None:
-        raise NotImplementedError("forcings/initforc are outside this path (SURVEY.md 8(f))")
     P = pack_args(y, time, func, parms, rtol, atol, ctol, sparsetype, verbose, nnz, inz, lrw, ngp, positive, maxiter,
                   dllname, initfunc, initpar, rpar, ipar, nout, spmethod, control)
+    if initforc is not None and forcings is not None:     # R/stodes.R:222-237: forcings without initforc are ignored
+        forc = forcing_values(forcings, time, fcontrol)
+        P.keep.append(forc)
+        P.args.forcs, P.args.nforcs = _dp(forc), len(forc)
     n = P.n
     yout = np.zeros(n + int(nout))
     precis = np.zeros(int(maxiter))

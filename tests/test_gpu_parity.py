@@ -388,6 +388,37 @@ def test_golden_anoxic_model_with_output_on_gpu(built):
     assert abs(out.attributes["precis"][0] - g["precis"][0]) <= 1e-6 * g["precis"][0]
 
 
+def test_forcings_through_initforc_on_gpu(built):
+    """forcings / initforc / fcontrol (R/stodes.R:222-237, src/steady_utils.c:62-77): Flux and BO2 of the anoxic model
+    arrive as forcing function values -- given directly, or as (time, value) data sets interpolated at `time` -- and
+    the solve lands on the reference's frozen state (pdf p.8-9)."""
+    import json
+    import os
+    import rootsolve_b200 as rs
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "rootsolve_pdf_p8_anox.json")))
+    parms = list(g["parms"])
+    flux, bo2 = parms[1], parms[6]
+    parms[1] = parms[6] = -1.0e30
+    kw = dict(func="anoxforc", parms=parms, positive=True, nout=1, outnames=["SumS"], initforc="forcanoxforc")
+    sets = [np.array([[0.0, 0.0], [10.0, 2.0 * flux]]), np.array([[0.0, bo2], [10.0, bo2]])]
+    for forcings, time, fcontrol in [([flux, bo2], 0.0, None), (sets, 5.0, None), (sets, 99.0, {"rule": 2})]:
+        if time == 99.0:
+            forcings = [np.array([[0.0, 0.0], [10.0, flux]]), sets[1]]
+        out = rs.stodes(np.asarray(g["y0"]), time=time, forcings=forcings, fcontrol=fcontrol, **kw)
+        assert out.attributes["steady"]
+        for got, want in zip(out["y"], g["y"]):
+            assert abs(got - want) <= 1e-6 * abs(want) + 1e-6
+        assert out["SumS"][0] == pytest.approx(g["SumS"], rel=1e-9)
+    with pytest.raises(rs.RootSolveError, match="Confusion over the length of forcs"):
+        rs.stodes(np.asarray(g["y0"]), forcings=[flux], **kw)
+    with pytest.raises(rs.RootSolveError, match="no forcing initialiser"):
+        rs.stodes(np.asarray(g["y0"]), func="anoxmod", parms=g["parms"], positive=True, nout=1, forcings=[flux, bo2],
+                  initforc="forcanoxmod")
+    # without initforc the forcings are ignored, as in R (R/stodes.R:222: Forc stays NULL)
+    out = rs.stodes(np.asarray(g["y0"]), func="anoxmod", parms=g["parms"], positive=True, nout=1, forcings=[1.0, 2.0, 3.0])
+    assert out.attributes["steady"] and abs(out["y"][0] - g["y"][0]) <= 1e-6 * g["y"][0]
+
+
 def test_sparsereturn_and_sparsejan_roundtrip(built, oracle):
     """sparsetype='sparsereturn' hands back ian/jan; feeding them back as 'sparsejan' solves the same problem
     (man/stodes.Rd:264-284)"""

@@ -32,9 +32,10 @@ def test_model_library_descriptors(built):
     class Desc(C.Structure):
         _fields_ = [("abi", C.c_int), ("name", C.c_char_p), ("nparms", C.c_int), ("launch", C.c_void_p),
                     ("initfunc", C.c_void_p), ("initforc", C.c_void_p)]
-    for name, npar in [("diff2d", 7), ("diff3d", 8), ("rd3d", 10), ("rt1d", 7)]:
+    for name, npar in [("diff2d", 7), ("diff3d", 8), ("rd3d", 10), ("rt1d", 7), ("anoxmod", 9), ("diffmap", 8), ("anoxforc", 9)]:
         d = C.cast(_capi.model_symbol(name), C.POINTER(Desc)).contents
         assert d.abi == 1 and d.name.decode() == name and d.nparms == npar and d.launch and d.initfunc
+        assert bool(d.initforc) == (name == "anoxforc")
     with pytest.raises(ValueError, match="dyn function not loaded"):
         _capi.model_symbol("no_such_model")
 
@@ -79,6 +80,44 @@ def test_sparse_args_known_values():
         sparse_args(3, "sparseusr", inz=inz[::-1])
     with pytest.raises(ValueError, match="sparsetype not known"):
         sparse_args(3, "4D", [1])
+
+
+def test_sparse_args_mapped_grids(oracle):
+    """2Dmap/3Dmap (R/stodes.R:111-141): Type 30/40, nnz estimate for the FULL grid, the map carried behind TotN"""
+    from rootsolve_b200.stodes import sparse_args
+    pres, inv = H.make_map(H.ball_mask((6, 7)))
+    nnz = [1, 6, 7, 0, 1, len(pres)] + pres.tolist()
+    Type, v, ngp, lrw, _, _ = sparse_args(len(inv), "2Dmap", nnz)
+    assert Type == 30 and int(v[0]) == 42 * 5 - 2 * 13 + 2 * 7 and ngp == len(inv) + 2
+    assert list(v[1:7]) == [1, 6, 7, 0, 1, 42] and np.array_equal(v[7:], pres)
+    rType, rv, rngp, rlrw, _ = oracle.stodes_args(len(inv), "2Dmap", nnz)
+    assert (Type, ngp, lrw) == (rType, rngp, rlrw) and np.array_equal(v, rv)
+    pres3, inv3 = H.make_map(H.ball_mask((4, 5, 6)))
+    nnz3 = [1, 4, 5, 6, 0, 0, 0, len(pres3)] + pres3.tolist()
+    Type, v, ngp, lrw, _, _ = sparse_args(len(inv3), "3Dmap", nnz3)
+    assert Type == 40 and int(v[0]) == 120 * 7 - 3 * 15 and int(v[8]) == 120
+    rType, rv, rngp, rlrw, _ = oracle.stodes_args(len(inv3), "3Dmap", nnz3)
+    assert (Type, ngp, lrw) == (rType, rngp, rlrw) and np.array_equal(v, rv)
+
+
+def test_forcing_values_follow_r_approx():
+    """forcings (R/stodes.R:229-236): a vector is used as is, a list of (time, value) data sets goes through approx()"""
+    from rootsolve_b200.stodes import approx, forcing_values
+    ds = np.array([[0.0, 10.0], [10.0, 20.0], [20.0, 0.0]])
+    assert approx(ds, 5.0) == 15.0 and approx(ds, 10.0) == 20.0 and approx(ds, 12.5) == 15.0
+    assert np.isnan(approx(ds, -1.0)) and np.isnan(approx(ds, 21.0))               # rule = 1
+    assert approx(ds, -1.0, rule=2) == 10.0 and approx(ds, 99.0, rule=2) == 0.0
+    assert approx(ds, 99.0, rule=(1, 2)) == 0.0 and np.isnan(approx(ds, -1.0, rule=(1, 2)))
+    assert approx(ds, 5.0, method="constant") == 10.0 and approx(ds, 5.0, method="constant", f=1.0) == 20.0
+    assert approx(ds, 5.0, method="constant", f=0.25) == 12.5
+    assert approx(ds[::-1], 5.0) == 15.0                                            # unsorted input
+    tied = np.array([[0.0, 1.0], [1.0, 2.0], [1.0, 4.0], [2.0, 5.0]])
+    assert approx(tied, 1.0) == 3.0 and approx(tied, 1.0, ties="ordered") == 4.0 and approx(tied, 1.0, ties="min") == 2.0
+    assert np.array_equal(forcing_values([100.0, 7.0], 3.0), [100.0, 7.0])
+    assert np.array_equal(forcing_values([ds, np.column_stack([ds[:, 0], 2.0 * ds[:, 1]])], 5.0), [15.0, 30.0])
+    assert np.array_equal(forcing_values([ds], 25.0, {"rule": 2}), [0.0])
+    with pytest.raises(ValueError, match="two-columned"):
+        approx(np.zeros((3, 3)), 0.0)
 
 
 def test_argument_checks_mirror_the_r_front_end(built):

@@ -55,6 +55,23 @@ def test_pdf_p8_anoxic_model_golden(oracle):
         oracle.stsparse(np.asarray(g["y0"]), f, sparsetype="sparseint", nnz=None, positive=True, nout=1, lrw=1000)
 
 
+def test_pdf_p8_golden_with_flux_and_bo2_as_forcings(oracle):
+    """The same model with Flux and BO2 handed over as forcing function values through the model's initforc
+    (src/call_stsparse.c:242-251, src/steady_utils.c:62-77): same golden state; wrong parameter slots are ignored."""
+    g = json.load(open(os.path.join(GOLD, "rootsolve_pdf_p8_anox.json")))
+    parms = list(g["parms"])
+    flux, bo2 = parms[1], parms[6]
+    parms[1] = parms[6] = -1.0e30          # must not be used
+    f = oracle.model("anoxforc", parms, forcs=[flux, bo2])
+    r = oracle.stsparse(np.asarray(g["y0"]), f, sparsetype="sparseint", nnz=None, positive=True, nout=1, lrw=1000,
+                        quirk_first_step_transposed=False, quirk_unterminated_igp=False)
+    assert r["steady"] and len(r["precis"]) == len(g["precis"])
+    for got, want in zip(r["y"], g["y"]):
+        assert float("%.10g" % got) == pytest.approx(want, rel=1e-9, abs=5e-7)
+    with pytest.raises(ValueError, match="Confusion over the length of forcs"):
+        oracle.model("anoxforc", parms, forcs=[flux])
+
+
 def test_structure_hash_fixture(oracle):
     for e in json.load(open(os.path.join(GOLD, "structure_hashes.json"))):
         ian, jan = oracle.sparse_structure(e["kind"], e["nspec"], e["dims"], e["cyclic"])
