@@ -118,6 +118,8 @@ typedef struct {
     int kernel_launches;    /* kernels launched by this call */
     double t_setup_s;       /* structure + grouping + CSR build (device events) */
     double t_newton_s;      /* Newton loop */
+    int spmv_kernel;        /* SpMV the Krylov solver ran: 0 sub-warp CSR, 1 TMA-staged CSR, 2 TMA-staged with
+                             * implicit columns (non-cyclic grid, <= 2 species) */
 } rs_stsparse_result;
 
 /* The path: replaces call_stsparse -> dsparse (src/call_stsparse.c:60-320, src/sparse.f:30-195). */

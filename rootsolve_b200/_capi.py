@@ -54,7 +54,7 @@ class StsparseResult(C.Structure):
         ("y", c_double_p), ("precis", c_double_p), ("niter", C.c_int), ("steady", C.c_int * 4),
         ("ian", c_int_p), ("jan", c_int_p), ("igp", c_int_p), ("jgp", c_int_p),
         ("krylov_iters", C.c_int), ("kernel_launches", C.c_int),
-        ("t_setup_s", C.c_double), ("t_newton_s", C.c_double),
+        ("t_setup_s", C.c_double), ("t_newton_s", C.c_double), ("spmv_kernel", C.c_int),
     ]
 
 

@@ -28,7 +28,7 @@ void set_error(const char *fmt, ...)
 
 const char *const kKernelNames[K_COUNT] = {"structure", "scan", "transpose", "jgroup", "perturb", "residual_batched",
                                            "fd_assemble", "spmv_csr", "krylov_vec", "precond_setup", "precond_apply",
-                                           "newton", "halo", "misc"};
+                                           "newton", "halo", "misc", "spmv_grid"};
 
 void Ctx::begin(int id, double algo_bytes)
 {
@@ -403,7 +403,8 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         }
         RS_TRY(fd_setup(c, s.fd, n, s.ngp, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, s.slab_j0, s.slab_j1));
         RS_TRY(krylov_setup(c, s.kry, n, s.nnz, s.rowptr.p, s.col.p, s.val.p, s.ctl.precond, s.grid.type ? s.grid.nspec : 1,
-                            s.grid.type ? s.grid.ncell : n, &s.ctl, &s.own, comm_active() ? &s.halo : nullptr));
+                            s.grid.type ? s.grid.ncell : n, &s.ctl, &s.own, comm_active() ? &s.halo : nullptr,
+                            s.grid.type ? &s.grid : nullptr));
     }
     RS_CUDA(cudaEventRecord(e1, c.stream));
     RS_CUDA(cudaEventSynchronize(e1));
@@ -554,6 +555,7 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
         meta->kernel_launches = (int)(c.launches - launches0);
         meta->t_setup_s = s.t_setup;
         meta->t_newton_s = s.t_newton;
+        meta->spmv_kernel = s.kry.gridcols ? 2 : s.kry.tma_ok ? 1 : 0;
         if (meta->precis) for (int q = 0; q < s.niter && q < s.maxiter; q++) meta->precis[q] = s.precis[q];
     }
     return RS_OK;

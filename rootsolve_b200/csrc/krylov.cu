@@ -107,6 +107,11 @@ static void spmv_dispatch(cudaStream_t st, int lanes, int row0, int row1, const 
 
 // algorithmic bytes of one product over `rows` rows holding `nz` nonzeros
 static inline double spmv_bytes(double rows, double nz) { return 12.0 * nz + 4.0 * (rows + 1) + 16.0 * rows; }
+// ... and of the kernel this solver actually runs: with implicit columns col[] (4 bytes per nonzero) is not read
+static inline double spmv_bytes(const Krylov &k, double rows, double nz)
+{
+    return k.gridcols ? 8.0 * nz + 4.0 * (rows + 1) + 16.0 * rows : spmv_bytes(rows, nz);
+}
 
 int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const double *val, const double *x,
                 double *y, int lanes)
@@ -282,6 +287,150 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int row0, int row
     if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out, accumulate != 0, &pr);
 }
 
+// ---- SpMV with implicit columns (non-cyclic regular grids) ----------------------------------------
+// On a non-cyclic 1-D/2-D/3-D grid the columns of row r are a pure function of r's grid position:
+// r -/+ d2*d3, r -/+ d3, r -/+ 1 where the neighbour exists, plus the same cell of the other species.
+// The kernel computes them instead of streaming col[] (4 of the 12 bytes per nonzero), and -- because
+// the addresses no longer depend on staged data -- issues the x gathers BEFORE it waits for the tile.
+// Algorithmic bytes: 8 Z + 4 (N+1) + 16 N.  The arithmetic (entry order, one FMA chain per row) is that
+// of the CSR kernels, so the result is bit-identical.  krylov_setup verifies the pattern row by row
+// (grid_cols_check_kernel) before this path is taken.
+struct GridCols { int d1, d2, d3, s1, ncell; };
+
+template <int NSPEC>
+struct GridRow {
+    static constexpr int NSLOT = NSPEC == 1 ? 7 : 9;
+    int c[NSLOT];
+    bool has[NSLOT];
+    // candidate columns of row r in ascending order; has[q]: the entry exists
+    __device__ __forceinline__ void set(const GridCols &g, int r, bool valid)
+    {
+        int sp = 0, cell = r;
+        if (NSPEC == 2 && r >= g.ncell) { sp = 1; cell = r - g.ncell; }
+        const int j = cell / g.s1, rem = cell - j * g.s1, k = rem / g.d3, l = rem - k * g.d3;
+        constexpr int o = NSPEC == 1 ? 0 : 1;
+        if (NSPEC == 2) {
+            has[0] = valid && sp == 1; c[0] = cell;                    // species 0 of the same cell
+            has[NSLOT - 1] = valid && sp == 0; c[NSLOT - 1] = cell + g.ncell;   // species 1 of the same cell
+        }
+        has[o + 0] = valid && j > 0;        c[o + 0] = r - g.s1;
+        has[o + 1] = valid && k > 0;        c[o + 1] = r - g.d3;
+        has[o + 2] = valid && l > 0;        c[o + 2] = r - 1;
+        has[o + 3] = valid;                 c[o + 3] = r;
+        has[o + 4] = valid && l < g.d3 - 1; c[o + 4] = r + 1;
+        has[o + 5] = valid && k < g.d2 - 1; c[o + 5] = r + g.d3;
+        has[o + 6] = valid && j < g.d1 - 1; c[o + 6] = r + g.s1;
+    }
+};
+
+template <int NSPEC>
+__global__ void grid_cols_check_kernel(GridCols g, int row0, int row1, const int *__restrict__ rowptr,
+                                       const int *__restrict__ col, int *__restrict__ bad)
+{
+    const int r = row0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= row1) return;
+    GridRow<NSPEC> gr;
+    gr.set(g, r, true);
+    int p = rowptr[r];
+    const int pe = rowptr[r + 1];
+    bool ok = true;
+#pragma unroll
+    for (int q = 0; q < GridRow<NSPEC>::NSLOT; q++)
+        if (gr.has[q]) {
+            if (p >= pe || col[p] != gr.c[q]) ok = false;
+            p++;
+        }
+    if (p != pe) ok = false;
+    if (!ok) *bad = 1;
+}
+
+#ifndef RS_GRID_STAGES
+#define RS_GRID_STAGES 2
+#endif
+#ifndef RS_GRID_MINB
+#define RS_GRID_MINB 2
+#endif
+constexpr int GRID_STAGES = RS_GRID_STAGES;
+constexpr int GRID_STAGE_BYTES = TMA_CAP * 8;
+constexpr int GRID_SMEM_BYTES = GRID_STAGES * GRID_STAGE_BYTES;
+
+template <int NDOT, int NSPEC>
+__global__ void __launch_bounds__(TMA_THREADS, RS_GRID_MINB)
+spmv_grid_kernel(GridCols g, int row0, int row1, int ntiles, const int *__restrict__ rowptr, const double *__restrict__ val,
+                 const double *__restrict__ x, double *__restrict__ y, const double *__restrict__ w, double *partials,
+                 unsigned *ticket, double *out, int accumulate, PeerRed pr, HaloSignal hw)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) unsigned long long full[GRID_STAGES], empty[GRID_STAGES];
+    __shared__ int a0s[GRID_STAGES];
+    constexpr int NSLOT = GridRow<NSPEC>::NSLOT;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < GRID_STAGES; s++) { mbar_init(&full[s], 1u); mbar_init(&empty[s], TMA_CONSUMER_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    halo_wait(hw);
+    const int my_tiles = (ntiles > (int)blockIdx.x) ? (ntiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    double acc[NDOT > 0 ? NDOT : 1] = {0.0};
+    if (warp == TMA_CONSUMER_WARPS) {
+        if (lane == 0) {
+            for (int i = 0; i < my_tiles; i++) {
+                const int s = i % GRID_STAGES;
+                if (i >= GRID_STAGES) {
+                    mbar_wait(&empty[s], (unsigned)(i / GRID_STAGES - 1) & 1u);
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                }
+                const int r0 = row0 + ((int)blockIdx.x + i * (int)gridDim.x) * TMA_ROWS;
+                const int r1 = min(row1, r0 + TMA_ROWS);
+                const int p0 = rowptr[r0], p1 = rowptr[r1];
+                const int a0 = p0 & ~1;                      // 16-byte aligned start of the value slice
+                const int cnt = ((p1 + 1) & ~1) - a0;
+                a0s[s] = a0;
+                mbar_expect_tx(&full[s], (unsigned)cnt * 8u);
+                if (cnt > 0) bulk_g2s(smem + s * GRID_STAGE_BYTES, val + a0, (unsigned)cnt * 8u, &full[s]);
+            }
+        }
+    } else {
+        int r = row0 + (int)blockIdx.x * TMA_ROWS + tid;
+        int pb = (my_tiles > 0 && r < row1) ? rowptr[r] : 0;
+        for (int i = 0; i < my_tiles; i++) {
+            const int s = i % GRID_STAGES;
+            const unsigned parity = (unsigned)(i / GRID_STAGES) & 1u;
+            const int rn = r + (int)gridDim.x * TMA_ROWS;
+            const int pbn = (i + 1 < my_tiles && rn < row1) ? rowptr[rn] : 0;
+            // the gathers need nothing from the staged tile: they are in flight while the tile arrives
+            GridRow<NSPEC> gr;
+            gr.set(g, r, r < row1);
+            double xv[NSLOT];
+#pragma unroll
+            for (int q = 0; q < NSLOT; q++) xv[q] = gr.has[q] ? __ldg(&x[gr.c[q]]) : 0.0;
+            mbar_wait(&full[s], parity);
+            const double *sval = reinterpret_cast<const double *>(smem + s * GRID_STAGE_BYTES) - a0s[s];
+            double v[NSLOT];
+            int p = pb;
+#pragma unroll
+            for (int q = 0; q < NSLOT; q++) {
+                v[q] = gr.has[q] ? sval[p] : 0.0;
+                p += gr.has[q] ? 1 : 0;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);   // the stage goes back before the gathers are waited for
+            double sum = 0.0;
+#pragma unroll
+            for (int q = 0; q < NSLOT; q++)
+                if (gr.has[q]) sum += v[q] * xv[q];
+            if (r < row1) {
+                y[r] = sum;
+                if (NDOT == 1) acc[0] += w[r] * sum;
+                if (NDOT == 2) { acc[0] += sum * w[r]; acc[1] += sum * sum; }
+            }
+            r = rn; pb = pbn;
+        }
+    }
+    if (NDOT > 0) grid_reduce<(NDOT > 0 ? NDOT : 1)>(acc, 0u, partials, ticket, out, accumulate != 0, &pr);
+}
+
 // largest number of staged nonzeros any tile of [row0, row1) needs
 __global__ void tma_tile_max_kernel(int row0, int row1, int ntiles, const int *__restrict__ rowptr, int *__restrict__ out)
 {
@@ -301,7 +450,17 @@ static void spmv_run(const Krylov &k, cudaStream_t st, const double *x, double *
         const int row0 = k.own.b[q], row1 = k.own.e[q];
         if (row1 <= row0) continue;
         const PeerRed pr = (q == k.own.n - 1) ? peer : PeerRed();   // the ranks meet once, after the last range
-        if (k.tma_ok) {
+        if (k.gridcols) {
+            const int ntiles = (row1 - row0 + TMA_ROWS - 1) / TMA_ROWS;
+            const int grid = std::min(ntiles, k.tma_sms * k.tma_per_sm_grid);
+            const GridCols g{k.gd1, k.gd2, k.gd3, k.gd2 * k.gd3, k.ncell};
+            if (k.gridcols == 1)
+                spmv_grid_kernel<NDOT, 1><<<grid, TMA_THREADS, GRID_SMEM_BYTES, st>>>(g, row0, row1, ntiles, k.rowptr, k.val, x, y, w,
+                                                                                     k.partials.p, k.ticket.p, out, q > 0, pr, hw);
+            else
+                spmv_grid_kernel<NDOT, 2><<<grid, TMA_THREADS, GRID_SMEM_BYTES, st>>>(g, row0, row1, ntiles, k.rowptr, k.val, x, y, w,
+                                                                                     k.partials.p, k.ticket.p, out, q > 0, pr, hw);
+        } else if (k.tma_ok) {
             const int ntiles = (row1 - row0 + TMA_ROWS - 1) / TMA_ROWS;
             const int grid = std::min(ntiles, k.tma_sms * k.tma_per_sm);
             spmv_tma_kernel<NDOT><<<grid, TMA_THREADS, TMA_SMEM_BYTES, st>>>(row0, row1, ntiles, k.rowptr, k.col, k.val, x, y, w,
@@ -565,7 +724,7 @@ __global__ void krylov_seed_kernel(double *scal, int src)
 // ---- host driver ------------------------------------------------------------------------
 int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int *col, const double *val,
                  int precond, int nspec, int ncell, const rs_krylov_control *ctl, const Ranges *own,
-                 const HaloPlan *halo)
+                 const HaloPlan *halo, const GridDesc *grid)
 {
     k.n = n; k.nnz = nnz; k.rowptr = rowptr; k.col = col; k.val = val;
     k.nspec = nspec; k.ncell = ncell;
@@ -612,6 +771,44 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
                 RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k.tma_per_sm, spmv_tma_kernel<2>, TMA_THREADS, TMA_SMEM_BYTES));
                 if (k.tma_per_sm >= 1) k.tma_ok = 1;
             }
+        }
+    }
+    // implicit columns: non-cyclic grid, 1 or 2 species, pattern verified row by row against the stencil
+    k.gridcols = 0;
+    if (k.tma_ok && grid && grid->type && !getenv("RS_NO_GRIDCOLS") && (grid->nspec == 1 || grid->nspec == 2) &&
+        !grid->cyc[0] && !grid->cyc[1] && !grid->cyc[2] && (long long)grid->nspec * grid->ncell == n) {
+        const int nd = grid->type == RS_TYPE_1D ? 1 : grid->type == RS_TYPE_2D ? 2 : 3;
+        k.gd1 = nd == 3 ? grid->d[0] : 1;
+        k.gd2 = nd == 3 ? grid->d[1] : nd == 2 ? grid->d[0] : 1;
+        k.gd3 = grid->d[nd - 1];
+        const GridCols g{k.gd1, k.gd2, k.gd3, k.gd2 * k.gd3, grid->ncell};
+        DevBuf<int> bad;
+        RS_TRY(bad.alloc(1));
+        RS_TRY(bad.zero(c.stream));
+        for (int q = 0; q < k.own.n; q++) {
+            const int rows = k.own.e[q] - k.own.b[q];
+            if (rows <= 0) continue;
+            Launch L(c, K_PRECOND_SETUP, 4.0 * nnz * rows / n + 8.0 * rows);
+            if (grid->nspec == 1) grid_cols_check_kernel<1><<<(rows + 255) / 256, 256, 0, c.stream>>>(g, k.own.b[q], k.own.e[q], rowptr, col, bad.p);
+            else grid_cols_check_kernel<2><<<(rows + 255) / 256, 256, 0, c.stream>>>(g, k.own.b[q], k.own.e[q], rowptr, col, bad.p);
+        }
+        int hbad = 1;
+        RS_TRY(bad.download(&hbad, 1, c.stream));
+        RS_CUDA(cudaStreamSynchronize(c.stream));
+        if (!hbad) {
+            int per_sm = 0;
+            if (grid->nspec == 1) {
+                RS_CUDA(cudaFuncSetAttribute(spmv_grid_kernel<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_SMEM_BYTES));
+                RS_CUDA(cudaFuncSetAttribute(spmv_grid_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_SMEM_BYTES));
+                RS_CUDA(cudaFuncSetAttribute(spmv_grid_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_SMEM_BYTES));
+                RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmv_grid_kernel<2, 1>, TMA_THREADS, GRID_SMEM_BYTES));
+            } else {
+                RS_CUDA(cudaFuncSetAttribute(spmv_grid_kernel<0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_SMEM_BYTES));
+                RS_CUDA(cudaFuncSetAttribute(spmv_grid_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_SMEM_BYTES));
+                RS_CUDA(cudaFuncSetAttribute(spmv_grid_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, GRID_SMEM_BYTES));
+                RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spmv_grid_kernel<2, 2>, TMA_THREADS, GRID_SMEM_BYTES));
+            }
+            if (per_sm >= 1) { k.tma_per_sm_grid = per_sm; k.gridcols = grid->nspec; }
         }
     }
     RS_TRY(k.r.alloc(n)); RS_TRY(k.r0.alloc(n)); RS_TRY(k.p.alloc(n)); RS_TRY(k.v.alloc(n));
@@ -741,7 +938,7 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     }
     if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.ph_v, k.halo));
     {
-        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)) + 8.0 * rows);
+        Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)) + 8.0 * rows);
         spmv_run<1>(k, st, k.ph_v, k.v.p, k.r0.p, slot + S_R0V, comm_next_peer_red(), sig_p);
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
@@ -764,7 +961,7 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     }
     if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.sh_v, k.halo));
     {
-        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)) + 8.0 * rows);
+        Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)) + 8.0 * rows);
         spmv_run<2>(k, st, k.sh_v, k.t.p, k.s.p, slot + S_TS, comm_next_peer_red(), sig_s);
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + S_TS, 2));
@@ -788,7 +985,7 @@ static int true_residual_restart(Ctx &c, Krylov &k, const double *b, double *x, 
     const double rows = (double)k.own.total();
     RS_TRY(comm_halo_exchange(c, x, k.halo));
     {
-        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)));
+        Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)));
         spmv_run<0>(k, st, x, k.v.p, nullptr, nullptr, PeerRed(), HaloSignal());
     }
     {
@@ -891,7 +1088,7 @@ static int cg_start(Ctx &c, Krylov &k, const double *b, double *x, bool restart,
     const double rows = (double)k.own.total();
     if (restart) {
         RS_TRY(comm_halo_exchange(c, x, k.halo));
-        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)));
+        Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)));
         spmv_run<0>(k, st, x, k.v.p, nullptr, nullptr, PeerRed(), HaloSignal());
     }
     {
@@ -927,7 +1124,7 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     }
     if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.ph_v, k.halo));
     {
-        Launch L(c, K_SPMV, spmv_bytes(rows, own_nnz_estimate(k)) + 8.0 * rows);
+        Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)) + 8.0 * rows);
         spmv_run<1>(k, st, k.ph_v, k.v.p, k.ph_v, slot + C_PQ, comm_next_peer_red(), sig);
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_PQ, 1));

@@ -83,6 +83,10 @@ struct Krylov {
     double *h_scal = nullptr;  // pinned mirror
     int lanes = 8;             // lanes per row of the sub-warp SpMV
     int tma_ok = 0, tma_sms = 0, tma_per_sm = 0;  // the TMA-staged SpMV is usable (every tile fits a stage)
+    // Non-cyclic 1-D/2-D/3-D grid with 1 or 2 species whose row-wise pattern was verified against the stencil:
+    // the SpMV then COMPUTES the column of every entry from the row's grid position and never reads col[]
+    // (gridcols = number of species, 0 = general CSR).  gd1..gd3: the grid as a 3-D box (leading extents 1).
+    int gridcols = 0, gd1 = 1, gd2 = 1, gd3 = 1, tma_per_sm_grid = 0;
     double *ph_v = nullptr, *sh_v = nullptr;   // the preconditioned directions (SpMV inputs): own buffers or pooled, peer-mapped ones
     bool use_cg = false;                   // J is symmetric to FD noise: preconditioned CG (one SpMV per step) instead of BiCGStab
     double asym = 0.0;                     // max |a_ij - a_ji| / max |a_ij| of the last Jacobian
@@ -101,7 +105,7 @@ struct Krylov {
 };
 int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int *col, const double *val,
                  int precond, int nspec, int ncell, const rs_krylov_control *ctl, const Ranges *own,
-                 const HaloPlan *halo);
+                 const HaloPlan *halo, const GridDesc *grid = nullptr);
 int krylov_precond_update(Ctx &c, Krylov &k);
 // solves A x = b (x overwritten, starts from 0); abs_floor: absolute 2-norm stop
 int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres);

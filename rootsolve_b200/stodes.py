@@ -336,6 +336,7 @@ def stodes(y, time=0, func=None, parms=None, rtol=1e-6, atol=1e-8, ctol=1e-8, sp
         out.attributes["jgp"] = jgp
     out.attributes["krylov_iters"] = R.krylov_iters
     out.attributes["kernel_launches"] = R.kernel_launches
+    out.attributes["spmv_kernel"] = {0: "csr-subwarp", 1: "csr-tma", 2: "grid-implicit-columns"}.get(R.spmv_kernel)
     out.attributes["timing"] = {"setup_s": R.t_setup_s, "newton_s": R.t_newton_s}
     if verbose:
         print("precision at each steady state step")

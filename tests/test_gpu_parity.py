@@ -388,6 +388,44 @@ def test_golden_anoxic_model_with_output_on_gpu(built):
     assert abs(out.attributes["precis"][0] - g["precis"][0]) <= 1e-6 * g["precis"][0]
 
 
+@pytest.mark.parametrize("name,rdims", [("diff2d_monod", (37, 23)), ("diff3d", (13, 9, 17)), ("rd3d", (8, 9, 10)), ("rt1d2", (600,)),
+                                        ("diff2d_lin", (1, 40)), ("diff3d", (2, 2, 30))])
+def test_implicit_column_spmv_is_bit_identical(built, name, rdims):
+    """On non-cyclic grids with 1 or 2 species the Krylov SpMV computes its column indices from the grid position
+    instead of reading them (spmv_grid_kernel): same entry order, same FMA chain, so the whole solve -- state,
+    iteration counts, precis -- must be bitwise what the general CSR kernel gives (RS_NO_GRIDCOLS=1)."""
+    import os
+    import rootsolve_b200 as rs
+    d = tuple(rdims)
+    if name.startswith("diff2d"):
+        kw = dict(func="diff2d", parms=H.P_DIFF2D_MONOD if name.endswith("monod") else H.P_DIFF2D_LIN, sparsetype="2D",
+                  nnz=[1, d[0], d[1], 0, 0], ipar=[1, d[0], d[1], 1, int(name.endswith("monod"))])
+        y0 = np.full(d[0] * d[1], 10.0)
+    elif name == "diff3d":
+        kw = dict(func="diff3d", parms=H.P_DIFF3D, sparsetype="3D", nnz=[1, d[0], d[1], d[2], 0, 0, 0], ipar=[1, d[0], d[1], d[2], 0])
+        y0 = np.full(d[0] * d[1] * d[2], 10.0)
+    elif name == "rd3d":
+        kw = dict(func="rd3d", parms=H.P_RD3D, sparsetype="3D", nnz=[2, d[0], d[1], d[2], 0, 0, 0], ipar=[2, d[0], d[1], d[2], 0])
+        nc = d[0] * d[1] * d[2]
+        y0 = np.concatenate([np.full(nc, 10.0), np.full(nc, 1.0)])
+    else:
+        kw = dict(func="rt1d", parms=H.P_RT1D, sparsetype="1D", nnz=[2, d[0], 0], ipar=[2, d[0], 1, 1, 0])
+        y0 = np.full(2 * d[0], 1.0)
+    outs = []
+    for off in (False, True):
+        if off:
+            os.environ["RS_NO_GRIDCOLS"] = "1"
+        try:
+            outs.append(rs.stodes(y0, positive=True, **kw, **H.TOL))
+        finally:
+            os.environ.pop("RS_NO_GRIDCOLS", None)
+    a, b = outs
+    assert a.attributes["steady"] and b.attributes["steady"]
+    assert a.attributes["spmv_kernel"] == "grid-implicit-columns" and b.attributes["spmv_kernel"] == "csr-tma"
+    assert a.attributes["krylov_iters"] == b.attributes["krylov_iters"]
+    assert np.array_equal(a["y"], b["y"]) and np.array_equal(a.attributes["precis"], b.attributes["precis"])
+
+
 def test_forcings_through_initforc_on_gpu(built):
     """forcings / initforc / fcontrol (R/stodes.R:222-237, src/steady_utils.c:62-77): Flux and BO2 of the anoxic model
     arrive as forcing function values -- given directly, or as (time, value) data sets interpolated at `time` -- and
