@@ -65,7 +65,7 @@ struct rs_model_desc;  /* device residual plug-in, see rootsolve_b200_model.cuh 
 typedef struct {
     int precond;            /* RS_PRECOND_* (AUTO: block-Jacobi on multi-species grids, else Jacobi) */
     int max_krylov;         /* per Newton step (10000) */
-    double lin_rtol;        /* ||J x - beta||_2 <= lin_rtol * ||beta||_2 (1e-10) */
+    double lin_rtol;        /* ||J x - beta||_2 <= lin_rtol * ||beta||_2 (1e-8: the accuracy of the FD Jacobian) */
     double lin_ewt_factor;  /* ... or rms(J x - beta) <= lin_ewt_factor * min(atol) (5e-4): far below the error
                              * weights, because the error of the state is up to ||J^-1|| times this residual */
     int check_every;        /* host convergence check period in Krylov iterations (4) */

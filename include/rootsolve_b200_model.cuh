@@ -85,9 +85,23 @@ static int rs_launch_batched(void *stream, int neq, double t, const double *y, d
     if (work <= 0 || nbatch <= 0) return 0;
     const int threads = 256;
     long long blocks = (work + threads - 1) / threads;
-    /* enough CTAs to fill 148 SMs x 8 resident CTAs even when nbatch is small */
-    const long long cap = (148LL * 8 + nbatch - 1) / nbatch;
-    if (blocks > cap) blocks = cap < 1 ? 1 : cap;
+    /* One wave: the whole (blocks x nbatch) grid is resident at once -- SMs x the CTAs of THIS model's kernel an SM
+     * holds (its register count decides) -- and every thread strides over its share; a grid that is a fraction of
+     * a wave larger leaves the SMs idle for most of a second wave. */
+    static int resident = 0;
+    if (resident == 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rs_residual_batched_kernel<F>, threads, 0) == cudaSuccess &&
+            sms > 0 && per_sm > 0)
+            resident = sms * per_sm;
+        else
+            resident = 148 * 4;
+    }
+    long long cap = resident / nbatch;
+    if (cap < 1) cap = 1;
+    if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks, (unsigned)nbatch);
     rs_residual_batched_kernel<F><<<grid, threads, 0, (cudaStream_t)stream>>>(neq, t, y, ydot, ld, yout, ldout, ip);
     return (int)cudaGetLastError();

@@ -100,7 +100,10 @@ struct Krylov {
     // long as a whole step on 8 GPUs or on a small grid).  Steps taken after convergence are harmless --
     // a breakdown there leaves x untouched (update_xr_kernel) -- and cost at most check_every-1 steps.
     int max_iter = 10000, check_every = 4;
-    double lin_rtol = 1e-10, lin_ewt_factor = 5e-4;
+    // lin_rtol: the finite-difference Jacobian carries a relative error of a few 1e-8 (Perturb's increment), so a
+    // Newton step cannot gain from a linear solve more accurate than that; the residual left over is picked up by
+    // the next step, whose own solve stops at the absolute floor (lin_ewt_factor, see rs_solver_run).
+    double lin_rtol = 1e-8, lin_ewt_factor = 5e-4;
     ~Krylov();
 };
 int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int *col, const double *val,

@@ -237,7 +237,8 @@ def test_linsolve_matches_direct(built, transposed):
         b = rng.standard_normal(n)
         x = np.zeros(n)
         iters, rr = C.c_int(0), C.c_double(0.0)
-        _capi.check(built.rs_linsolve(n, H.ip(ian), H.ip(jan), H.dp(a), H.dp(b), transposed, nspec, None, H.dp(x),
+        ctl = _capi.KrylovControl(precond=_capi.RS_PRECOND_AUTO, lin_rtol=1e-10)   # the default (1e-8) is Newton's, not a direct solver's
+        _capi.check(built.rs_linsolve(n, H.ip(ian), H.ip(jan), H.dp(a), H.dp(b), transposed, nspec, C.byref(ctl), H.dp(x),
                                       C.byref(iters), C.byref(rr)))
         A = _dense_from_columns(ian, jan, a)
         xr = spla.spsolve((A.T if transposed else A).tocsc(), b)
@@ -276,7 +277,7 @@ def test_linsolve_symmetric_paths(built):
         b = rng.standard_normal(n)
         x = np.zeros(n)
         iters, rr = C.c_int(0), C.c_double(0.0)
-        ctl = _capi.KrylovControl(precond=_capi.RS_PRECOND_JACOBI, max_krylov=20000)
+        ctl = _capi.KrylovControl(precond=_capi.RS_PRECOND_JACOBI, max_krylov=20000, lin_rtol=1e-10)
         _capi.check(built.rs_linsolve(n, H.ip(ian), H.ip(jan), H.dp(a), H.dp(b), 0, 1, C.byref(ctl), H.dp(x), C.byref(iters),
                                       C.byref(rr)))
         xr = spla.spsolve(Ac, b)
