@@ -286,8 +286,8 @@ def run_ours(args):
                    "parallelism": f"slab{world}" if world > 1 else "single-gpu", "steady": steady},
         "time_to_steady_state_s": ms_per_step * 1e-3, "newton_iters_per_s": newton / (ms_per_step * 1e-3),
         "setup_s": setup_s,
-        "roofline": {"bound": "hbm", "kernel": spname + (" (implicit columns: 8Z+4(N+1)+16N bytes, +8N fused dot)" if spname == "spmv_grid"
-                                                        else " (12Z+4(N+1)+16N bytes, +8N fused dot)"), "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": spname + (" (implicit columns: 8Z+4(N+1)+16N bytes, <p,Ap> fused)" if spname == "spmv_grid"
+                                                        else " (12Z+4(N+1)+16N bytes, dots fused)"), "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
                      "frac": ach / pk["hbm_gbs"] if pk["hbm_gbs"] else None, "traffic": traffic, "algorithmic_bytes": sp["bytes_per_launch"],
                      "peak_source": pk_src,
                      "avg_launch_ms": sp["ms"] / sp["launches"] if sp["launches"] else None},

@@ -27,7 +27,8 @@ __device__ __forceinline__ double perturbed(double v)
     return v + d;
 }
 
-// Y[0] = y ; Y[g+1][i] = y[i] (+delta_i when column i belongs to group g), for i in [b, e)
+// Y[g+1][i] = y[i] (+delta_i when column i belongs to group g), for i in [b, e); plane 0 is not used (f(y) is
+// evaluated on y itself, fd_base)
 __global__ void __launch_bounds__(256) perturb_kernel(int b, int e, int ngp, const double *__restrict__ y,
                                                       const int *__restrict__ group_of, double *__restrict__ Y,
                                                       long long ld)
@@ -36,7 +37,6 @@ __global__ void __launch_bounds__(256) perturb_kernel(int b, int e, int ngp, con
         const double v = y[i];
         const double vp = perturbed(v);
         const int g = group_of[i];
-        Y[i] = v;
         for (int q = 0; q < ngp; q++) Y[(long long)(q + 1) * ld + i] = (q == g) ? vp : v;
     }
 }
@@ -92,22 +92,48 @@ int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, in
     return RS_OK;
 }
 
-int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
-                const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
-                const Ranges &own, const Ranges &touch)
+// beta = -f(y) alone (the first model call of xSparseJacob, src/sparse.f:487-491).  The Newton loop runs it first:
+// convergence test 1 (src/sparse.f:122-133) needs nothing else, and when the test passes the ngp perturbed
+// evaluations of that iteration -- whose Jacobian the reference computes and never uses -- are not made.
+__global__ void __launch_bounds__(256) negate_kernel(int b, int e, const double *__restrict__ f, double *__restrict__ beta)
+{
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) beta[i] = -f[i];
+}
+
+int fd_base(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, const double *d_y, double *d_beta, const Ranges &own)
+{
+    const long long work = own.total();
+    {
+        Launch L(c, K_RESIDUAL, 16.0 * work);
+        const int e = m->launch((void *)c.stream, n, t, d_y, w.F.p, w.ld, 1, w.yout.p, w.ldout, w.ip.p, work);
+        if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
+    }
+    {
+        Launch L(c, K_NEWTON, 16.0 * work);
+        for (int q = 0; q < own.n; q++)
+            negate_kernel<<<grid_for(own.e[q] - own.b[q], 256), 256, 0, c.stream>>>(own.b[q], own.e[q], w.F.p, d_beta);
+    }
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+// The ngp perturbed evaluations and the assembly; F[0] = f(y) is already there (fd_base).
+int fd_groups(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
+              const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
+              const Ranges &own, const Ranges &touch)
 {
     const long long work = own.total();
     const double frac = (double)work / (double)n;
     {
         const double nt = (double)touch.total();
-        Launch L(c, K_PERTURB, 12.0 * nt + 8.0 * nt * (ngp + 1));
+        Launch L(c, K_PERTURB, 12.0 * nt + 8.0 * nt * ngp);
         for (int q = 0; q < touch.n; q++)
             perturb_kernel<<<grid_for(touch.e[q] - touch.b[q], 256), 256, 0, c.stream>>>(touch.b[q], touch.e[q], ngp, d_y, d_group_of,
                                                                                        w.Y.p, w.ld);
     }
-    {
-        Launch L(c, K_RESIDUAL, 16.0 * work * (ngp + 1));
-        const int e = m->launch((void *)c.stream, n, t, w.Y.p, w.F.p, w.ld, ngp + 1, w.yout.p, w.ldout, w.ip.p, work);
+    if (ngp > 0) {
+        Launch L(c, K_RESIDUAL, 16.0 * work * ngp);
+        const int e = m->launch((void *)c.stream, n, t, w.Y.p + w.ld, w.F.p + w.ld, w.ld, ngp, w.yout.p + w.ldout, w.ldout, w.ip.p, work);
         if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
     }
     {
@@ -120,6 +146,14 @@ int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int n
     }
     RS_CUDA(cudaGetLastError());
     return RS_OK;
+}
+
+int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
+                const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
+                const Ranges &own, const Ranges &touch)
+{
+    RS_TRY(fd_base(c, m, w, n, t, d_y, d_beta, own));
+    return fd_groups(c, m, w, n, nnz, ngp, t, d_y, d_group_of, d_rowptr, d_col, d_val, d_beta, own, touch);
 }
 
 int residual_only(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, const double *d_y, double *d_f,

@@ -857,9 +857,35 @@ __global__ void __launch_bounds__(256) symmetry_kernel(int row0, int row1, const
     grid_reduce<2>(acc, 3u, partials, ticket, out, accumulate != 0);
 }
 
+static inline double own_nnz_estimate(const Krylov &k);
+// (defined with the CG kernels below)
+__global__ void __launch_bounds__(256) cg_scale_setup_kernel(int row0, int row1, const double *__restrict__ dinv,
+                                                             double *__restrict__ s, double *partials, unsigned *ticket,
+                                                             double *out);
+__global__ void __launch_bounds__(256) cg_scale_matrix_kernel(int row0, int row1, const int *__restrict__ rowptr,
+                                                              const int *__restrict__ col, const double *__restrict__ s,
+                                                              double sigma, int inverse, double *__restrict__ val);
+
+// scales (or, inverse, restores) the rank's rows of the matrix in place; s must be valid on the halo planes too
+static int cg_scale_matrix(Ctx &c, Krylov &k, bool inverse)
+{
+    for (int q = 0; q < k.own.n; q++) {
+        const long long rows = k.own.e[q] - k.own.b[q];
+        if (rows <= 0) continue;
+        Launch L(c, K_PRECOND_SETUP, 20.0 * own_nnz_estimate(k) + 12.0 * rows);
+        cg_scale_matrix_kernel<<<(unsigned)((rows * 8 + 255) / 256), 256, 0, c.stream>>>(k.own.b[q], k.own.e[q], k.rowptr, k.col, k.sc.p,
+                                                                                      k.sigma, inverse ? 1 : 0, const_cast<double *>(k.val));
+    }
+    if (inverse) k.scaled = false;
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
 int krylov_precond_update(Ctx &c, Krylov &k)
 {
     k.use_cg = false;
+    k.scaled = false;
+    k.norm_conv = 1.0;
     if (k.precond == RS_PRECOND_JACOBI) {
         for (int q = 0; q < k.own.n; q++) {
             const int rows = k.own.e[q] - k.own.b[q];
@@ -882,6 +908,28 @@ int krylov_precond_update(Ctx &c, Krylov &k)
             const double da = k.h_scal[S_SYM], amax = k.h_scal[S_SYM + 1];
             k.asym = amax > 0.0 ? da / amax : 1.0;
             k.use_cg = (k.asym == k.asym) && k.asym <= 1.0e-6;
+            // fold the Jacobi preconditioner into the system (see the CG kernels): needs one sign on the whole diagonal
+            static const bool no_scale = getenv("RS_NO_CG_SCALING") != nullptr;
+            if (k.use_cg && !no_scale) {
+                if (!k.sc.p) RS_TRY(k.sc.alloc(k.n));
+                {
+                    Launch L(c, K_PRECOND_SETUP, 16.0 * (double)(k.own.e[0] - k.own.b[0]));
+                    cg_scale_setup_kernel<<<grid_for(k.own.e[0] - k.own.b[0], 256), 256, 0, c.stream>>>(k.own.b[0], k.own.e[0], k.dinv.p, k.sc.p,
+                                                                                                      k.partials.p, k.ticket.p, k.scal.p + S_SYM);
+                }
+                RS_TRY(comm_allreduce_sum(c, k.scal.p + S_SYM, 3));
+                RS_CUDA(cudaMemcpyAsync(k.h_scal + S_SYM, k.scal.p + S_SYM, 3 * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+                RS_CUDA(cudaStreamSynchronize(c.stream));
+                const double npos = k.h_scal[S_SYM], nneg = k.h_scal[S_SYM + 1], nbad = k.h_scal[S_SYM + 2];
+                if (nbad == 0.0 && (npos == 0.0 || nneg == 0.0)) {
+                    k.sigma = nneg > 0.0 ? -1.0 : 1.0;
+                    RS_TRY(comm_halo_exchange(c, k.sc.p, k.halo));   // columns on the neighbours' planes
+                    k.scaled = true;
+                    RS_TRY(cg_scale_matrix(c, k, false));
+                } else {
+                    k.use_cg = false;   // a diagonal of mixed sign: not a definite matrix
+                }
+            }
         }
     } else if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
         const int cells = k.cell1 - k.cell0;
@@ -1008,7 +1056,53 @@ static int true_residual_restart(Ctx &c, Krylov &k, const double *b, double *x, 
 // Two fused vector kernels + one SpMV per step (BiCGStab: three + two).  p lives in ph_v (the SpMV
 // input whose halo planes travel), q = A p in v.  z = dinv r is never stored.
 
-// p = z + beta p  [first: p = z],  z = dinv r
+//
+// The Jacobi preconditioner is folded into the system once per Newton iteration instead of being applied in every
+// step: with s_i = |a_ii|^(-1/2) and sigma = sign(a_ii) (one sign for all rows, else the matrix is indefinite and
+// BiCGStab takes over) CG runs on  A^ = sigma S A S  (unit diagonal, positive definite when sigma A is),
+// b^ = sigma S b,  x = S x^ .  In exact arithmetic these are the iterates of Jacobi-preconditioned CG on A; the
+// vector kernels no longer read dinv (16 N bytes per step) and z is r.  The values are scaled in place -- the next
+// FD assembly rewrites them anyway -- and scaled back if the solve has to fall back to BiCGStab.
+
+// s = |diag|^(-1/2) over the rows [row0,row1); out = { #rows with a_ii > 0, #rows with a_ii < 0, #rows with a_ii == 0 or NaN }
+__global__ void __launch_bounds__(256) cg_scale_setup_kernel(int row0, int row1, const double *__restrict__ dinv,
+                                                             double *__restrict__ s, double *partials, unsigned *ticket,
+                                                             double *out)
+{
+    double acc[3] = {0.0, 0.0, 0.0};
+    for (long long i = row0 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < row1; i += (long long)gridDim.x * blockDim.x) {
+        const double d = dinv[i];                 // 1 / a_ii  (jacobi_setup_kernel; 1 where a_ii is 0 or missing)
+        const double a = fabs(d);
+        s[i] = sqrt(a);
+        if (d > 0.0 && isfinite(d)) acc[0] += 1.0; else if (d < 0.0 && isfinite(d)) acc[1] += 1.0; else acc[2] += 1.0;
+    }
+    grid_reduce<3>(acc, 0u, partials, ticket, out, false);
+}
+
+// val[p] *= sigma * s_i * s_col[p]   (inverse: val[p] = sigma * val[p] / (s_i * s_col[p]))
+__global__ void __launch_bounds__(256) cg_scale_matrix_kernel(int row0, int row1, const int *__restrict__ rowptr,
+                                                              const int *__restrict__ col, const double *__restrict__ s,
+                                                              double sigma, int inverse, double *__restrict__ val)
+{
+    // 8 lanes per row: a row's entries are contiguous
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long i = row0 + (t >> 3);
+    if (i >= row1) return;
+    const double si = s[i];
+    for (int p = rowptr[i] + (int)(t & 7); p < rowptr[i + 1]; p += 8) {
+        const double f = si * s[col[p]];
+        val[p] = inverse ? sigma * val[p] / f : sigma * f * val[p];
+    }
+}
+
+// x = s * x^   (end of a scaled solve)
+__global__ void __launch_bounds__(256) cg_unscale_x_kernel(int b, int e, const double *__restrict__ s, double *__restrict__ x)
+{
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) x[i] *= s[i];
+}
+
+// p = z + beta p  [first: p = z],  z = dinv r  (SCALED: z = r, dinv is not read)
+template <bool SCALED>
 __global__ void __launch_bounds__(256) cg_update_p_kernel(int b, int e, int first, const double *scal, int cur,
                                                           const double *__restrict__ r, const double *__restrict__ dinv,
                                                           double *__restrict__ p, HaloPush hp, unsigned *hticket)
@@ -1020,8 +1114,8 @@ __global__ void __launch_bounds__(256) cg_update_p_kernel(int b, int e, int firs
     }
     const double2 *r2 = reinterpret_cast<const double2 *>(r), *d2 = reinterpret_cast<const double2 *>(dinv);
     double2 *p2 = reinterpret_cast<double2 *>(p);
-#define CP_ONE(i) { const double pn = dinv[i] * r[i] + (first ? 0.0 : beta * p[i]); p[i] = pn; halo_store(hp, b, e, i, pn); }
-#define CP_TWO(i) { const double2 rv = r2[i], dv = d2[i]; double2 pn; pn.x = dv.x * rv.x; pn.y = dv.y * rv.y; \
+#define CP_ONE(i) { const double pn = (SCALED ? r[i] : dinv[i] * r[i]) + (first ? 0.0 : beta * p[i]); p[i] = pn; halo_store(hp, b, e, i, pn); }
+#define CP_TWO(i) { const double2 rv = r2[i]; double2 pn = rv; if (!SCALED) { const double2 dv = d2[i]; pn.x = dv.x * rv.x; pn.y = dv.y * rv.y; } \
                     if (!first) { const double2 po = p2[i]; pn.x += beta * po.x; pn.y += beta * po.y; } p2[i] = pn; \
                     halo_store(hp, b, e, 2 * (i), pn.x); halo_store(hp, b, e, 2 * (i) + 1, pn.y); }
     RS_RANGE_LOOP(b, e, CP_ONE, CP_TWO);
@@ -1030,7 +1124,8 @@ __global__ void __launch_bounds__(256) cg_update_p_kernel(int b, int e, int firs
     halo_signal_done(hp, hticket);
 }
 
-// alpha = rho / <p,q> ; x += alpha p ; r -= alpha q ; out = { <r,r>, <r, dinv r> }
+// alpha = rho / <p,q> ; x += alpha p ; r -= alpha q ; out = { <r,r>, <r, dinv r> }  (SCALED: both are <r,r>)
+template <bool SCALED>
 __global__ void __launch_bounds__(256) cg_update_xr_kernel(int b, int e, double *scal, int cur, const double *__restrict__ p,
                                                            const double *__restrict__ q, const double *__restrict__ dinv,
                                                            double *__restrict__ x, double *__restrict__ r,
@@ -1048,29 +1143,45 @@ __global__ void __launch_bounds__(256) cg_update_xr_kernel(int b, int e, double 
     const double2 *p2 = reinterpret_cast<const double2 *>(p), *q2 = reinterpret_cast<const double2 *>(q);
     const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
     double2 *x2 = reinterpret_cast<double2 *>(x), *r2 = reinterpret_cast<double2 *>(r);
-#define CX_ONE(i) { x[i] += alpha * p[i]; const double rn = r[i] - alpha * q[i]; r[i] = rn; acc[0] += rn * rn; acc[1] += rn * dinv[i] * rn; }
-#define CX_TWO(i) { const double2 pv = p2[i], qv = q2[i], dv = d2[i]; double2 xv = x2[i], rn = r2[i]; \
+#define CX_ONE(i) { x[i] += alpha * p[i]; const double rn = r[i] - alpha * q[i]; r[i] = rn; acc[0] += rn * rn; \
+                    if (!SCALED) acc[1] += rn * dinv[i] * rn; }
+#define CX_TWO(i) { const double2 pv = p2[i], qv = q2[i]; double2 xv = x2[i], rn = r2[i]; \
                     xv.x += alpha * pv.x; xv.y += alpha * pv.y; x2[i] = xv; rn.x -= alpha * qv.x; rn.y -= alpha * qv.y; r2[i] = rn; \
-                    acc[0] += rn.x * rn.x + rn.y * rn.y; acc[1] += rn.x * dv.x * rn.x + rn.y * dv.y * rn.y; }
+                    acc[0] += rn.x * rn.x + rn.y * rn.y; \
+                    if (!SCALED) { const double2 dv = d2[i]; acc[1] += rn.x * dv.x * rn.x + rn.y * dv.y * rn.y; } }
     RS_RANGE_LOOP(b, e, CX_ONE, CX_TWO);
 #undef CX_ONE
 #undef CX_TWO
+    if (SCALED) acc[1] = acc[0];
     grid_reduce<2>(acc, 0u, partials, ticket, slot + C_RR, accumulate != 0, &pr);
 }
 
 // start of a cycle: r = b - ax (ax = nullptr: r = b, x = 0) ; out[0] = <r,r> (into scal[dst]) , out[1] = <r, dinv r>
+// Scaled system (scale != nullptr): r = sigma s b - ax ; out[0] = ||r / s||^2, the residual norm of the ORIGINAL
+// system, which is what the stopping test is stated in ; out[1] = <r,r>, the rho of the scaled recurrence.
 __global__ void __launch_bounds__(256) cg_start_kernel(int b, int e, const double *__restrict__ rhs, const double *__restrict__ ax,
-                                                       const double *__restrict__ dinv, double *__restrict__ r,
+                                                       const double *__restrict__ dinv, const double *__restrict__ scale,
+                                                       double sigma, double *__restrict__ r,
                                                        double *__restrict__ x, double *partials, unsigned *ticket,
                                                        double *out2, int accumulate, PeerRed pr)
 {
     double acc[2] = {0.0, 0.0};
     for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) {
-        double ri = rhs[i];
-        if (ax != nullptr) ri -= ax[i]; else x[i] = 0.0;
-        r[i] = ri;
-        acc[0] += ri * ri;
-        acc[1] += ri * dinv[i] * ri;
+        if (scale != nullptr) {
+            const double si = scale[i];
+            double ri = sigma * si * rhs[i];
+            if (ax != nullptr) ri -= ax[i]; else x[i] = 0.0;
+            r[i] = ri;
+            const double ro = ri / si;
+            acc[0] += ro * ro;
+            acc[1] += ri * ri;
+        } else {
+            double ri = rhs[i];
+            if (ax != nullptr) ri -= ax[i]; else x[i] = 0.0;
+            r[i] = ri;
+            acc[0] += ri * ri;
+            acc[1] += ri * dinv[i] * ri;
+        }
     }
     grid_reduce<2>(acc, 0u, partials, ticket, out2, accumulate != 0, &pr);
 }
@@ -1096,15 +1207,18 @@ static int cg_start(Ctx &c, Krylov &k, const double *b, double *x, bool restart,
         const PeerRed peer = comm_next_peer_red();
         for (int q = 0; q < k.own.n; q++)
             cg_start_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, restart ? k.v.p : nullptr, k.dinv.p,
+                                                                                k.scaled ? k.sc.p : nullptr, k.sigma,
                                                                                 k.r.p, x, k.partials.p, k.ticket.p, k.scal.p + 6, q > 0,
                                                                                 q == k.own.n - 1 ? peer : PeerRed());
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, k.scal.p + 6, 2));
     cg_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, dst_rr);
     c.launches++;
-    RS_CUDA(cudaMemcpyAsync(k.h_scal + dst_rr, k.scal.p + dst_rr, sizeof(double), cudaMemcpyDeviceToHost, st));
+    RS_CUDA(cudaMemcpyAsync(k.h_scal + 6, k.scal.p + 6, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
     RS_CUDA(cudaStreamSynchronize(st));
-    *rnorm = std::sqrt(k.h_scal[dst_rr]);
+    *rnorm = std::sqrt(k.h_scal[6]);
+    // what the recurrence's own <r,r> has to be multiplied by to read as a norm of the original system
+    k.norm_conv = (k.scaled && k.h_scal[7] > 0.0) ? std::sqrt(k.h_scal[6] / k.h_scal[7]) : 1.0;
     return RS_OK;
 }
 
@@ -1115,26 +1229,37 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     const double rows = (double)k.own.total();
     const HaloSignal sig = k.push_ok ? comm_next_halo_signal() : HaloSignal();
     {
-        Launch L(c, K_VEC, (first ? 24.0 : 32.0) * rows);
+        Launch L(c, K_VEC, ((first ? 24.0 : 32.0) - (k.scaled ? 8.0 : 0.0)) * rows);
         for (int q = 0; q < k.own.n; q++) {
             const int b = k.own.b[q], e = k.own.e[q];
-            cg_update_p_kernel<<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, k.dinv.p, k.ph_v,
-                                                                           make_push(k, 0, sig, q == k.own.n - 1), k.ticket.p + 1);
+            if (k.scaled)
+                cg_update_p_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, nullptr, k.ph_v,
+                                                                                     make_push(k, 0, sig, q == k.own.n - 1), k.ticket.p + 1);
+            else
+                cg_update_p_kernel<false><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, k.dinv.p, k.ph_v,
+                                                                                      make_push(k, 0, sig, q == k.own.n - 1), k.ticket.p + 1);
         }
     }
     if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.ph_v, k.halo));
     {
-        Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)) + 8.0 * rows);
+        // <p, Ap>: the dot's second operand is the SpMV input itself -- no bytes of its own
+        Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)));
         spmv_run<1>(k, st, k.ph_v, k.v.p, k.ph_v, slot + C_PQ, comm_next_peer_red(), sig);
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_PQ, 1));
     {
-        Launch L(c, K_VEC, 56.0 * rows);
+        Launch L(c, K_VEC, (k.scaled ? 48.0 : 56.0) * rows);
         const PeerRed peer = comm_next_peer_red();
         for (int q = 0; q < k.own.n; q++) {
             const int b = k.own.b[q], e = k.own.e[q];
-            cg_update_xr_kernel<<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph_v, k.v.p, k.dinv.p, x, k.r.p, k.partials.p,
-                                                                            k.ticket.p, q > 0, q == k.own.n - 1 ? peer : PeerRed());
+            if (k.scaled)
+                cg_update_xr_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph_v, k.v.p, nullptr, x, k.r.p,
+                                                                                      k.partials.p, k.ticket.p, q > 0,
+                                                                                      q == k.own.n - 1 ? peer : PeerRed());
+            else
+                cg_update_xr_kernel<false><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph_v, k.v.p, k.dinv.p, x, k.r.p,
+                                                                                       k.partials.p, k.ticket.p, q > 0,
+                                                                                       q == k.own.n - 1 ? peer : PeerRed());
         }
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_RR, 2));
@@ -1161,7 +1286,8 @@ static int launch_step_graph(Ctx &c, Krylov &k, double *x, bool cg, int nsteps)
 {
     const int w = cg ? 1 : 0;
     cudaStream_t st = c.stream;
-    if (!k.g_exec[w] || k.g_x[w] != x || k.g_n[w] != nsteps) {
+    if (!k.g_exec[w] || k.g_x[w] != x || k.g_n[w] != nsteps || k.g_scaled[w] != k.scaled) {
+        k.g_scaled[w] = k.scaled;
         if (k.g_exec[w]) { cudaGraphExecDestroy(k.g_exec[w]); k.g_exec[w] = nullptr; }
         cudaGraph_t g = nullptr;
         const long long l0 = c.launches;
@@ -1228,7 +1354,7 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
             *fallback = true;
             return RS_OK;
         }
-        const double rnorm = std::sqrt(rr);
+        const double rnorm = std::sqrt(rr) * k.norm_conv;   // scaled solve: estimate of the original system's residual norm
         if (rnorm < 0.9 * best) { best = rnorm; since_best = 0; } else since_best++;
         const bool looks_converged = rnorm <= target;
         const bool stagnated = since_best * k.check_every >= 40;
@@ -1244,6 +1370,11 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
         if (fruitless >= 3) { *fallback = true; return RS_OK; }
         restarts++;
         cycle_it = 0; best = rt; since_best = 0;
+    }
+    if (k.scaled) {   // back to the unknowns of the original system
+        Launch L(c, K_VEC, 24.0 * (double)k.own.total());
+        for (int q = 0; q < k.own.n; q++)
+            cg_unscale_x_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], k.sc.p, x);
     }
     RS_CUDA(cudaGetLastError());
     *relres = rtrue / bnorm;
@@ -1264,6 +1395,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
         RS_TRY(pcg_solve(c, k, b, x, abs_floor, iters, relres, &fallback));
         if (!fallback) return RS_OK;
         k.use_cg = false;   // not a CG matrix after all: BiCGStab below, from x = 0
+        if (k.scaled) RS_TRY(cg_scale_matrix(c, k, true));   // ... on the matrix as assembled
     }
     {
         Launch L(c, K_VEC, 32.0 * (double)k.own.total());

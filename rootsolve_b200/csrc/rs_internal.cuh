@@ -48,7 +48,7 @@ struct Ctx {
     bool profile = false;  // record CUDA events around every launch
     double ms[K_COUNT] = {0};
     long long count[K_COUNT] = {0};
-    double bytes[K_COUNT] = {0};  // algorithmic bytes of the last launch of the class
+    double bytes[K_COUNT] = {0};  // algorithmic bytes of all launches of the class since the last reset
     struct Pending { int id; cudaEvent_t a, b; };
     std::vector<Pending> pending;
     std::vector<cudaEvent_t> pool;
@@ -66,7 +66,7 @@ struct Ctx {
 // RAII guard: counts the launch and (when profiling) times it on the stream.
 struct Launch {
     Ctx &c; int id;
-    Launch(Ctx &ctx, int kid, double algo_bytes = 0.0) : c(ctx), id(kid) { c.launches++; c.count[id]++; if (c.profile) c.begin(id, algo_bytes); else c.bytes[id] = algo_bytes; }
+    Launch(Ctx &ctx, int kid, double algo_bytes = 0.0) : c(ctx), id(kid) { c.launches++; c.count[id]++; if (c.profile) c.begin(id, algo_bytes); else c.bytes[id] += algo_bytes; }
     ~Launch() { if (c.profile) c.end(id); }
 };
 

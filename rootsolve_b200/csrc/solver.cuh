@@ -57,6 +57,12 @@ int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, in
 int fd_jacobian(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
                 const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
                 const Ranges &own, const Ranges &touch);
+// the same in the two halves the Newton loop uses: beta = -f(y) first (enough for convergence test 1), then the
+// ngp perturbed evaluations + assembly only when a step is actually taken
+int fd_base(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, const double *d_y, double *d_beta, const Ranges &own);
+int fd_groups(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp, double t, const double *d_y,
+              const int *d_group_of, const int *d_rowptr, const int *d_col, double *d_val, double *d_beta,
+              const Ranges &own, const Ranges &touch);
 int residual_only(Ctx &c, const rs_model_desc *m, FdWork &w, int n, double t, const double *d_y, double *d_f,
                   long long work);
 // numeric structure detection (Type +-1): ian/jan from N perturbed evaluations, bit-exact with src/sparse.f:356-396
@@ -90,6 +96,12 @@ struct Krylov {
     double *ph_v = nullptr, *sh_v = nullptr;   // the preconditioned directions (SpMV inputs): own buffers or pooled, peer-mapped ones
     bool use_cg = false;                   // J is symmetric to FD noise: preconditioned CG (one SpMV per step) instead of BiCGStab
     double asym = 0.0;                     // max |a_ij - a_ji| / max |a_ij| of the last Jacobian
+    // CG on the symmetrically Jacobi-scaled system sigma S A S (values scaled in place): s, the common sign of the
+    // diagonal, and the factor that turns the recurrence's ||r^|| into a residual norm of the original system
+    DevBuf<double> sc;
+    bool scaled = false;
+    double sigma = 1.0, norm_conv = 1.0;
+    bool g_scaled[2] = {false, false};
     bool push_ok = false;                  // halos of ph / sh are pushed into the neighbours' vectors over NVLink
     void *nb_lo[2] = {nullptr, nullptr}, *nb_hi[2] = {nullptr, nullptr};   // neighbours' ph (0) and sh (1)
     // captured Krylov steps ([0] BiCGStab, [1] CG): graph, the solution vector it updates, steps and launches per replay
