@@ -207,6 +207,10 @@ const char *rs_last_error(void);
 int rs_abi_version(void);
 /* number of visible CUDA devices (0 when there is none); never fails */
 int rs_device_count(void);
+/* Device work arrays are cached between calls (the reference gets the same effect from R_alloc'ing out of R's own
+ * heap, src/call_stsparse.c:108-225: no system allocation per call).  Returns the cached bytes to the driver and
+ * reports how many there were; RS_POOL_MAX_BYTES in the environment caps the cache (0: none). */
+long long rs_release_cached_memory(void);
 
 /* ---- multi-GPU (one process per GPU; slabs over the slowest grid index) ---- */
 /* 128-byte NCCL unique id: rank 0 calls rs_comm_unique_id and ships the bytes to the other ranks

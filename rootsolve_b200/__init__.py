@@ -7,4 +7,12 @@ The package is a thin host mirror of the R API over a C-ABI CUDA library
 from .stodes import stodes, steady, steady_1D, steady_2D, steady_3D, SteadyResult  # noqa: F401
 from ._capi import RootSolveError  # noqa: F401
 
-__all__ = ["stodes", "steady", "steady_1D", "steady_2D", "steady_3D", "SteadyResult", "RootSolveError"]
+
+def release_cached_memory():
+    """Returns the device work arrays cached between solves to the CUDA driver; the number of bytes released."""
+    from . import _capi
+    return int(_capi.lib().rs_release_cached_memory())
+
+
+__all__ = ["stodes", "steady", "steady_1D", "steady_2D", "steady_3D", "SteadyResult", "RootSolveError",
+           "release_cached_memory"]

@@ -105,6 +105,7 @@ def lib():
         L.rs_errset.argtypes = [C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p]
         L.rs_convergence_test.argtypes = [C.c_int, c_double_p, c_double_p, c_double_p]
         L.rs_convergence_test_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rs_release_cached_memory.restype = C.c_longlong
         L.rs_comm_unique_id.argtypes = [C.c_char_p]
         L.rs_comm_init.argtypes = [C.c_int, C.c_int, C.c_char_p]
         L.rs_comm_finalize.restype = None

@@ -7,8 +7,13 @@
 //     test 2 ; new error weights }
 // and hand back y with the precis / steady attributes.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <map>
 #include <memory>
+#include <mutex>
 
 #include "solver.cuh"
 
@@ -24,6 +29,80 @@ void set_error(const char *fmt, ...)
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof g_err, fmt, ap);
     va_end(ap);
+}
+
+// ---- caching device allocator (see rs_internal.cuh) ------------------------------------------
+namespace {
+struct Pool {
+    std::mutex mu;
+    std::multimap<std::pair<int, size_t>, void *> free_blocks;   // (device, class bytes) -> block
+    size_t cached = 0;
+    size_t max_cached = 48ull << 30;
+    bool configured = false;
+    void configure()
+    {
+        if (configured) return;
+        configured = true;
+        if (const char *e = getenv("RS_POOL_MAX_BYTES")) max_cached = (size_t)strtoull(e, nullptr, 10);
+    }
+    // size classes: 512 B steps below 1 MiB, 1 MiB steps above -- solves of the same shape ask for the same sizes
+    static size_t klass(size_t bytes) { return bytes < (1u << 20) ? (bytes + 511) & ~(size_t)511 : (bytes + (1u << 20) - 1) & ~(size_t)((1u << 20) - 1); }
+    size_t drop_all_locked()
+    {
+        size_t freed = 0;
+        for (auto &kv : free_blocks) { cudaFree(kv.second); freed += kv.first.second; }
+        free_blocks.clear();
+        cached = 0;
+        return freed;
+    }
+};
+Pool &pool() { static Pool *p = new Pool(); return *p; }   // never destroyed: outlives the CUDA runtime's own teardown order
+}  // namespace
+
+cudaError_t pool_alloc(void **p, size_t bytes)
+{
+    Pool &P = pool();
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const size_t k = Pool::klass(bytes);
+    {
+        std::lock_guard<std::mutex> lk(P.mu);
+        P.configure();
+        auto it = P.free_blocks.find({dev, k});
+        if (it != P.free_blocks.end()) {
+            *p = it->second;
+            P.free_blocks.erase(it);
+            P.cached -= k;
+            return cudaSuccess;
+        }
+    }
+    e = cudaMalloc(p, k);
+    if (e == cudaErrorMemoryAllocation) {   // give the cache back and try once more
+        cudaGetLastError();
+        {
+            std::lock_guard<std::mutex> lk(P.mu);
+            P.drop_all_locked();
+        }
+        e = cudaMalloc(p, k);
+    }
+    return e;
+}
+
+void pool_free(void *p, size_t bytes)
+{
+    if (!p) return;
+    Pool &P = pool();
+    const size_t k = Pool::klass(bytes);
+    int dev = 0;
+    // cudaFree waits for the device; a block that goes back to the cache gets the same guarantee, so whoever is
+    // handed it next (possibly on another stream) cannot race with work still using it
+    const bool ok = cudaGetDevice(&dev) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess;
+    std::lock_guard<std::mutex> lk(P.mu);
+    P.configure();
+    if (!ok || P.cached + k > P.max_cached) { cudaFree(p); return; }
+    P.free_blocks.insert({{dev, k}, p});
+    P.cached += k;
 }
 
 const char *const kKernelNames[K_COUNT] = {"structure", "scan", "transpose", "jgroup", "perturb", "residual_batched",
@@ -328,8 +407,19 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
     RS_CUDA(cudaEventCreate(&e1));
     RS_CUDA(cudaEventRecord(e0, c.stream));
 
+    // RS_DEBUG_SETUP=1: wall-clock per set-up phase on stderr (each mark drains the stream)
+    static const bool debug_setup = getenv("RS_DEBUG_SETUP") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto mark = [&](const char *what) {
+        if (!debug_setup) return;
+        cudaStreamSynchronize(c.stream);
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[setup] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
     RS_TRY(s.y.alloc(n));
     RS_TRY(s.y.upload(a->y, n, c.stream));
+    mark("state upload");
     // structure (xsparsestruct, src/sparse.f:300-455)
     if (std::abs(a->Type) == RS_TYPE_DETECT) {
         RS_TRY(init_model(a->func, a->initpar, a->ninitpar, a->forcs, a->nforcs));
@@ -359,10 +449,13 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
             return RS_ESTRUCT;
         }
     }
+    mark("structure (ian, jan)");
     if (!s.structure_only) {
         RS_TRY(init_model(a->func, a->initpar, a->ninitpar, a->forcs, a->nforcs));
         RS_TRY(build_csr_pattern(c, n, s.nnz, s.ian.p, s.jan.p, s.rowptr, s.col));
+        mark("row-wise pattern");
         RS_TRY(jgroup_device(c, s.grid, n, s.nnz, s.ian.p, s.jan.p, s.rowptr.p, s.col.p, s.maxg, s.group_of, &s.ngp));
+        mark("column grouping");
         RS_TRY(s.val.alloc((size_t)s.nnz));
         RS_TRY(s.beta.alloc(n)); RS_TRY(s.ewt.alloc(n)); RS_TRY(s.x.alloc(n)); RS_TRY(s.ftmp.alloc(n));
         RS_TRY(s.atol.alloc(a->natol)); RS_TRY(s.rtol.alloc(a->nrtol));
@@ -401,10 +494,13 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
             s.halo.j0 = s.slab_j0; s.halo.j1 = s.slab_j1;
             s.halo.has_lo = rk > 0; s.halo.has_hi = rk < nr - 1;
         }
+        mark("newton vectors");
         RS_TRY(fd_setup(c, s.fd, n, s.ngp, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, s.slab_j0, s.slab_j1));
+        mark("fd work arrays");
         RS_TRY(krylov_setup(c, s.kry, n, s.nnz, s.rowptr.p, s.col.p, s.val.p, s.ctl.precond, s.grid.type ? s.grid.nspec : 1,
                             s.grid.type ? s.grid.ncell : n, &s.ctl, &s.own, comm_active() ? &s.halo : nullptr,
                             s.grid.type ? &s.grid : nullptr));
+        mark("krylov set-up");
     }
     RS_CUDA(cudaEventRecord(e1, c.stream));
     RS_CUDA(cudaEventSynchronize(e1));
@@ -910,4 +1006,10 @@ extern "C" int rs_device_count(void)
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
     return n;
+}
+extern "C" long long rs_release_cached_memory(void)
+{
+    Pool &P = pool();
+    std::lock_guard<std::mutex> lk(P.mu);
+    return (long long)P.drop_all_locked();
 }

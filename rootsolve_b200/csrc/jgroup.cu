@@ -8,7 +8,7 @@
 // independent set of the column-intersection graph.  Two exact device variants:
 //
 //  * wavefront (regular non-cyclic 1-D/2-D/3-D grids): with the level function
-//    phi = S*species + 4*j + 2*k + l (3-D), S*species + 2*j + k (2-D) or
+//    phi = S*species + 3*j + 2*k + l (3-D), S*species + 2*j + k (2-D) or
 //    S*species + j (1-D) every pair of conflicting columns lies on different
 //    levels and the lower index is always on the lower level, so sweeping the
 //    levels in order with a "row covered" bitmap is the sequential algorithm,
@@ -22,9 +22,14 @@
 #include <cooperative_groups.h>
 
 #include <cstdlib>
+#include <cstring>
 
 #include "solver.cuh"
 #include "grid_rows.cuh"
+
+#ifndef RS_WAVE_DEFAULT_VARIANT
+#define RS_WAVE_DEFAULT_VARIANT 0   // index into the variant table of jgroup_device
+#endif
 
 namespace cg = cooperative_groups;
 
@@ -79,56 +84,133 @@ __global__ void jg_commit_kernel(int n, unsigned char *__restrict__ state, int *
 // group_of[c] < 0 on entry marks the columns still to be grouped; a pass assigns base .. base+SLOTS-1.
 constexpr int WAVE_SLOTS = 16;
 
-__global__ void __launch_bounds__(256) jg_wave_kernel(GridDesc g, int S, int nlevels, unsigned *covered,
-                                                      int *__restrict__ group_of, int base, int *__restrict__ stats)
+//
+// Levels.  Column c = (species s, cell (j,k,l)) may only depend on columns of a lower level, i.e. on every EARLIER
+// column sharing a row with it: same species, cell offset a sum of two stencil offsets -- the worst cases
+// (-1,+1,0), (-1,0,+1), (0,-1,+1) ask for a > b > 1 in level = a j + b k + l, so 3 j + 2 k + l (2 j + k in 2-D) --
+// or an earlier species at a stencil neighbour (level difference at most a), hence the species weight S = a + 1.
+// U: (line, slot) pairs a thread takes through each memory round trip together; MINB: CTAs per SM the register
+// budget is cut for (more resident threads = fewer pairs per thread, against spills).
+// ONE: single species (branch-free rows, see the sweep).
+template <int U, int MINB, bool ONE>
+__global__ void __launch_bounds__(256, MINB) jg_wave_kernel(GridDesc g, int S, int nlevels, unsigned *covered,
+                                                            int *__restrict__ group_of, int base, int *__restrict__ stats,
+                                                            int *__restrict__ line_level)
 {
     cg::grid_group grid = cg::this_grid();
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x;          // 32-bit index arithmetic throughout: columns < 2^31,
-    const int nthreads = gridDim.x * blockDim.x;                    // and 64-bit divisions would dominate a step
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;          // 32-bit index arithmetic throughout: columns < 2^31
+    const int nthreads = gridDim.x * blockDim.x;
     const int d1 = g.d[0], d2 = g.d[1], d3 = g.d[2];
     const bool three = (g.type == RS_TYPE_3D), one = (g.type == RS_TYPE_1D);
     // candidate lines: (species, j, k) in 3-D, (species, j) in 2-D, (species) in 1-D; the last coordinate
-    // follows from the level
+    // follows from the level.  line_level[q] = level of the line's first cell, computed once: the sweep below
+    // visits (line, slot) pairs with shifts and one cached load, no division.
     const int nlines = three ? g.nspec * d1 * d2 : one ? g.nspec : g.nspec * d1;
     const int dl = three ? d3 : one ? d1 : d2;
+    // the grid as a 3-D box (leading extents 1): what the single-species path works with
+    const int box1 = three ? d1 : 1, box2 = three ? d2 : one ? 1 : d1, box3 = dl;
+    for (int q = tid; q < nlines; q += nthreads) {
+        int lv;
+        if (three) { const int k = q % d2, r = q / d2; lv = S * (r / d1) + 3 * (r % d1) + 2 * k; }
+        else if (one) lv = S * q;
+        else lv = S * (q / d1) + 2 * (q % d1);
+        if (ONE) {   // level and "neighbour line exists" flags (k-1, k+1, j-1, j+1) in one word
+            const int kf = q % box2, jf = q / box2;
+            lv = (lv << 4) | (kf > 0 ? 1 : 0) | (kf < box2 - 1 ? 2 : 0) | (jf > 0 ? 4 : 0) | (jf < box1 - 1 ? 8 : 0);
+        }
+        line_level[q] = lv;
+    }
+    grid.sync();
     int count = 0, top = -1;
     const int nsteps = nlevels + WAVE_SLOTS - 1;
+    static_assert(WAVE_SLOTS == 16, "the (line, slot) split below uses 4 bits for the slot");
+    const int work = nlines * WAVE_SLOTS;
+    // A step is latency bound (a few dependent L2 round trips, then the barrier), so a thread takes WAVE_UNROLL
+    // pairs through each round trip together: all their group_of loads, then all their covered loads, then the
+    // updates -- the loads of a phase are independent and in flight at once.
     for (int step = 0; step < nsteps; step++) {
-        const int slot_lo = max(0, step - nlevels + 1), slot_hi = min(WAVE_SLOTS - 1, step);
-        const int work = (slot_hi - slot_lo + 1) * nlines;
-        for (int wq = tid; wq < work; wq += nthreads) {
-            const int slot = slot_lo + (int)(wq / nlines);
-            const int q = wq % nlines;
-            const int t = step - slot;
-            int s, last;
-            int c;
-            if (three) {
-                const int k = (int)(q % d2);
-                const int r = q / d2;
-                const int j = (int)(r % d1);
-                s = (int)(r / d1);
-                last = t - S * s - 4 * j - 2 * k;
-                c = q * d3 + last;
-            } else if (one) {
-                s = (int)q;
-                last = t - S * s;
-                c = q * d1 + last;
-            } else {
-                const int j = (int)(q % d1);
-                s = (int)(q / d1);
-                last = t - S * s - 2 * j;
-                c = q * d2 + last;
+        if (ONE) {
+            // Single species: the (up to) 7 rows of a cell are computed branch-free -- a neighbour beyond the grid
+            // is replaced by the cell itself -- and every load is unconditional (a pair without a cell on this
+            // level reads cell 0 and is ignored), so the loads of all U pairs really are in flight together.
+            const int s1 = box2 * box3;
+            for (int w0 = tid; w0 < work; w0 += nthreads * U) {
+                int cc[U], fl[U], ll[U];
+                bool ok[U];
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    const int wq = min(w0 + u * nthreads, work - 1);
+                    const int packed = line_level[wq >> 4];
+                    const int last = step - (wq & (WAVE_SLOTS - 1)) - (packed >> 4);
+                    ok[u] = (w0 + u * nthreads < work) && last >= 0 && last < dl;
+                    cc[u] = ok[u] ? (wq >> 4) * dl + last : 0;
+                    ll[u] = ok[u] ? last : 0;
+                    fl[u] = ok[u] ? (packed & 15) : 0;
+                }
+                int taken[U];
+#pragma unroll
+                for (int u = 0; u < U; u++) taken[u] = group_of[cc[u]];
+                int rows[U][6];
+                unsigned seen[U];
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    const int cu = cc[u];
+                    rows[u][0] = ll[u] > 0 ? cu - 1 : cu;
+                    rows[u][1] = ll[u] < box3 - 1 ? cu + 1 : cu;
+                    rows[u][2] = (fl[u] & 1) ? cu - box3 : cu;
+                    rows[u][3] = (fl[u] & 2) ? cu + box3 : cu;
+                    rows[u][4] = (fl[u] & 4) ? cu - s1 : cu;
+                    rows[u][5] = (fl[u] & 8) ? cu + s1 : cu;
+                    seen[u] = covered[cu] | covered[rows[u][0]] | covered[rows[u][1]] | covered[rows[u][2]] | covered[rows[u][3]] |
+                              covered[rows[u][4]] | covered[rows[u][5]];
+                }
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    const int slot = (w0 + u * nthreads) & (WAVE_SLOTS - 1);
+                    const unsigned bit = 1u << slot;
+                    if (!ok[u] || taken[u] >= 0 || (seen[u] & bit)) continue;
+                    group_of[cc[u]] = base + slot;
+                    atomicOr(&covered[cc[u]], bit);
+#pragma unroll
+                    for (int i = 0; i < 6; i++)
+                        if (rows[u][i] != cc[u]) atomicOr(&covered[rows[u][i]], bit);
+                    count++;
+                    top = max(top, base + slot);
+                }
             }
-            if (last < 0 || last >= dl) continue;
-            if (group_of[c] >= 0) continue;          // taken by an earlier group (earlier step or pass)
-            const unsigned bit = 1u << slot;
-            bool clash = false;
-            emit_column(g, (int)c + 1, [&](int row) { clash = clash || (covered[row - 1] & bit); });
-            if (clash) continue;
-            group_of[c] = base + slot;
-            emit_column(g, (int)c + 1, [&](int row) { atomicOr(&covered[row - 1], bit); });
-            count++;
-            top = max(top, base + slot);
+            grid.sync();
+            continue;
+        }
+        for (int w0 = tid; w0 < work; w0 += nthreads * U) {
+            int cc[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int wq = w0 + u * nthreads;
+                cc[u] = -1;
+                if (wq < work) {
+                    const int last = step - (wq & (WAVE_SLOTS - 1)) - line_level[wq >> 4];   // slot g sweeps level step - g
+                    if (last >= 0 && last < dl) cc[u] = (wq >> 4) * dl + last;
+                }
+            }
+            int taken[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) taken[u] = cc[u] >= 0 ? group_of[cc[u]] : 0;   // >= 0: in an earlier group
+            unsigned seen[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                seen[u] = 0u;
+                if (cc[u] >= 0 && taken[u] < 0) emit_column(g, cc[u] + 1, [&](int row) { seen[u] |= covered[row - 1]; });
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int slot = (w0 + u * nthreads) & (WAVE_SLOTS - 1);
+                const unsigned bit = 1u << slot;
+                if (cc[u] < 0 || taken[u] >= 0 || (seen[u] & bit)) continue;
+                group_of[cc[u]] = base + slot;
+                emit_column(g, cc[u] + 1, [&](int row) { atomicOr(&covered[row - 1], bit); });
+                count++;
+                top = max(top, base + slot);
+            }
         }
         grid.sync();
     }
@@ -165,18 +247,33 @@ int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, c
         const bool three = g.type == RS_TYPE_3D;
         const bool one = g.type == RS_TYPE_1D;
         // species weight S: larger than the biggest level difference between neighbouring cells
-        const int S = three ? 5 : one ? 2 : 3;
-        const int nlevels = three ? S * (g.nspec - 1) + 4 * (g.d[0] - 1) + 2 * (g.d[1] - 1) + g.d[2]
+        const int S = three ? 4 : one ? 2 : 3;
+        const int nlevels = three ? S * (g.nspec - 1) + 3 * (g.d[0] - 1) + 2 * (g.d[1] - 1) + g.d[2]
                             : one ? S * (g.nspec - 1) + g.d[0]
                                   : S * (g.nspec - 1) + 2 * (g.d[0] - 1) + g.d[1];
+        // kernel variant (RS_WAVE_VARIANT picks another one for tuning sweeps)
+        struct Variant { const void *fn; const char *name; };
+        static const Variant variants[] = {
+            {(const void *)jg_wave_kernel<1, 6, true>, "u1b6"}, {(const void *)jg_wave_kernel<2, 6, true>, "u2b6"},
+            {(const void *)jg_wave_kernel<2, 4, true>, "u2b4"}, {(const void *)jg_wave_kernel<4, 4, true>, "u4b4"},
+            {(const void *)jg_wave_kernel<4, 3, true>, "u4b3"}, {(const void *)jg_wave_kernel<2, 8, true>, "u2b8"},
+            {(const void *)jg_wave_kernel<8, 2, true>, "u8b2"}, {(const void *)jg_wave_kernel<4, 6, true>, "u4b6"}};
+        int vi = RS_WAVE_DEFAULT_VARIANT;
+        if (const char *ve = getenv("RS_WAVE_VARIANT"))
+            for (int q = 0; q < (int)(sizeof(variants) / sizeof(variants[0])); q++)
+                if (strcmp(ve, variants[q].name) == 0) vi = q;
+        // several species: the general rows (emit_column), one pair at a time
+        const void *wave_fn = g.nspec == 1 ? variants[vi].fn : (const void *)jg_wave_kernel<1, 6, false>;
         int dev = 0, sms = 0, per_sm = 0;
         RS_CUDA(cudaGetDevice(&dev));
         RS_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, jg_wave_kernel, 256, 0));
+        RS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_fn, 256, 0));
         const long long nlines = three ? (long long)g.nspec * g.d[0] * g.d[1] : one ? (long long)g.nspec : (long long)g.nspec * g.d[0];
+        DevBuf<int> line_level;
+        RS_TRY(line_level.alloc((size_t)nlines));
         long long want = (nlines * WAVE_SLOTS + 255) / 256;
         const char *ctas_env = getenv("RS_WAVE_CTAS");
-        const int ctas = ctas_env ? atoi(ctas_env) : 4;
+        const int ctas = ctas_env ? atoi(ctas_env) : 8;   // CTAs per SM taking part (the kernel's occupancy caps it)
         long long cap = (long long)sms * (per_sm > ctas ? ctas : per_sm);
         int blocks = (int)(want < cap ? want : cap);
         if (blocks < 1) blocks = 1;
@@ -194,11 +291,11 @@ int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, c
             GridDesc gg = g;
             int Sx = S, nl = nlevels, bs = base;
             unsigned *cv = covered.p;
-            int *go = group_of.p, *st = counters.p;
-            void *args[] = {&gg, &Sx, &nl, &cv, &go, &bs, &st};
+            int *go = group_of.p, *st = counters.p, *ll = line_level.p;
+            void *args[] = {&gg, &Sx, &nl, &cv, &go, &bs, &st, &ll};
             {
                 Launch L(c, K_JGROUP, (double)WAVE_SLOTS * 4.0 * n);
-                RS_CUDA(cudaLaunchCooperativeKernel((void *)jg_wave_kernel, dim3(blocks), dim3(256), args, 0, c.stream));
+                RS_CUDA(cudaLaunchCooperativeKernel(wave_fn, dim3(blocks), dim3(256), args, 0, c.stream));
             }
             int st_h[2] = {0, -1};
             RS_CUDA(cudaMemcpyAsync(st_h, counters.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, c.stream));

@@ -73,6 +73,13 @@ struct Launch {
 // ---- device buffers ---------------------------------------------------------
 extern long long g_device_bytes;  // currently allocated through DevBuf
 
+// Caching device allocator (api.cu).  A steady-state solve allocates ~40 arrays (gigabytes at 256^3) and frees
+// them on return; cudaMalloc/cudaFree of that volume costs tens of milliseconds per call and now and then far
+// more.  Freed blocks are kept per (device, size class) and handed out again; rs_release_cached_memory() gives
+// them back to the driver, RS_POOL_MAX_BYTES caps what is kept (0 = no caching).
+cudaError_t pool_alloc(void **p, size_t bytes);
+void pool_free(void *p, size_t bytes);
+
 template <typename T>
 struct DevBuf {
     T *p = nullptr;
@@ -86,7 +93,7 @@ struct DevBuf {
         release();
         if (count == 0) count = 1;
         // 64 bytes of slack: bulk (TMA) copies round their byte ranges up to 16-byte multiples
-        cudaError_t e = cudaMalloc((void **)&p, count * sizeof(T) + 64);
+        cudaError_t e = pool_alloc((void **)&p, count * sizeof(T) + 64);
         if (e != cudaSuccess) {
             p = nullptr;
             set_error("cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e));
@@ -98,7 +105,7 @@ struct DevBuf {
     }
     void release()
     {
-        if (p) { cudaFree(p); g_device_bytes -= (long long)(n * sizeof(T)); }
+        if (p) { pool_free(p, n * sizeof(T) + 64); g_device_bytes -= (long long)(n * sizeof(T)); }
         p = nullptr; n = 0;
     }
     int zero(cudaStream_t s) { RS_CUDA(cudaMemsetAsync(p, 0, n * sizeof(T), s)); return RS_OK; }

@@ -427,6 +427,23 @@ def test_implicit_column_spmv_is_bit_identical(built, name, rdims):
     assert np.array_equal(a["y"], b["y"]) and np.array_equal(a.attributes["precis"], b.attributes["precis"])
 
 
+def test_work_arrays_are_cached_between_solves(built):
+    """device work arrays go back to a cache, not to cudaFree; rs_release_cached_memory hands them to the driver"""
+    import rootsolve_b200 as rs
+    d = (40, 40)
+    kw = dict(func="diff2d", parms=H.P_DIFF2D_LIN, sparsetype="2D", nnz=[1, d[0], d[1], 0, 0], ipar=[1, d[0], d[1], 1, 0],
+              positive=True, **H.TOL)
+    rs.release_cached_memory()
+    a = rs.stodes(np.full(d[0] * d[1], 10.0), **kw)
+    b = rs.stodes(np.full(d[0] * d[1], 10.0), **kw)          # served from the cache
+    assert np.array_equal(a["y"], b["y"])
+    freed = rs.release_cached_memory()
+    assert freed > 8 * d[0] * d[1] * 10
+    assert rs.release_cached_memory() == 0
+    c = rs.stodes(np.full(d[0] * d[1], 10.0), **kw)          # and from the driver again
+    assert np.array_equal(a["y"], c["y"])
+
+
 def test_forcings_through_initforc_on_gpu(built):
     """forcings / initforc / fcontrol (R/stodes.R:222-237, src/steady_utils.c:62-77): Flux and BO2 of the anoxic model
     arrive as forcing function values -- given directly, or as (time, value) data sets interpolated at `time` -- and
