@@ -52,9 +52,11 @@ enum { RS_TYPE_USER = 0, RS_TYPE_DETECT = 1, RS_TYPE_1D = 2, RS_TYPE_2D = 3, RS_
         * nspec*prod(dims) and the TotN map entries (src/call_stsparse.c:196-206) */
        RS_TYPE_2DMAP = 30, RS_TYPE_3DMAP = 40 };
 
-/* Linear-solver selection: the reference's imethod (1 = yale, 10 = yale +
- * return ian/jan; R/stodes.R:316-329).  On the GPU "yale" is served by the
- * preconditioned Krylov solver below. */
+/* Linear-solver selection: the reference's imethod (1 = yale, 2 = ilut, 3 = ilutp,
+ * 10 = yale + return ian/jan; R/stodes.R:314-329).  On the GPU every one of them is
+ * served by the preconditioned Krylov solver below (the reference's ilut/ilutp apply an
+ * incomplete LU once per Newton step, src/sparsekit.f:141-166: same tests, same steady
+ * state, more Newton steps); the ILUT options of `control' have nothing to act on. */
 enum { RS_PRECOND_NONE = 0, RS_PRECOND_JACOBI = 1, RS_PRECOND_BLOCK_JACOBI = 2, RS_PRECOND_AUTO = -1 };
 
 struct rs_model_desc;  /* device residual plug-in, see rootsolve_b200_model.cuh */
@@ -97,7 +99,7 @@ typedef struct {
     const int *ipar; int nipar;
     int Type;
     const int *ian; const int *jan;       /* Type 0 only: user structure, 1-based */
-    int imethod;            /* 1 or 10 */
+    int imethod;            /* 1, 2, 3 or 10 */
     const rs_krylov_control *control;     /* may be NULL */
 } rs_stsparse_args;
 

@@ -369,7 +369,11 @@ static int check_args(const rs_stsparse_args *a)
     if (!a->atol || !a->rtol || a->natol < 1 || a->nrtol < 1) { set_error("`atol' and `rtol' must be numeric"); return RS_EINVAL; }
     if (a->natol > 1 && a->natol != a->neq) { set_error("`atol' must either be a scalar, or as long as `y'"); return RS_EINVAL; }
     if (a->nrtol > 1 && a->nrtol != a->neq) { set_error("`rtol' must either be a scalar, or as long as `y'"); return RS_EINVAL; }
-    if (a->imethod != 1 && a->imethod != 10) { set_error("`spmethod' must be `yale' on this path (imethod 1 or 10)"); return RS_EINVAL; }
+    // 1 yale, 2 ilut, 3 ilutp, 10 yale + return the structure (R/stodes.R:314-329): all served by the Krylov solve
+    if (a->imethod != 1 && a->imethod != 2 && a->imethod != 3 && a->imethod != 10) {
+        set_error("`spmethod' must be one of `yale', `ilut' or `ilutp' (imethod 1, 2, 3 or 10)");
+        return RS_EINVAL;
+    }
     const int at = std::abs(a->Type);
     if (at != RS_TYPE_USER && at != RS_TYPE_DETECT && at != RS_TYPE_1D && at != RS_TYPE_2D && at != RS_TYPE_3D &&
         at != RS_TYPE_2DMAP && at != RS_TYPE_3DMAP) {

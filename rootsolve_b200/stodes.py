@@ -179,6 +179,10 @@ def _itol(n, atol, rtol):
 def _control(control):
     if control is None:
         return None
+    unknown = set(control) - {"precond", "max_krylov", "lin_rtol", "lin_ewt_factor", "check_every",
+                              "droptol", "permtol", "fillin", "lenplufac"}   # the last four: the reference's ILUT knobs
+    if unknown:
+        raise ValueError("unknown control option(s): %s" % sorted(unknown))
     kc = _capi.KrylovControl(precond=_capi.RS_PRECOND_AUTO)
     pc = control.get("precond", "auto")
     if pc not in _PRECOND:
@@ -221,11 +225,15 @@ def pack_args(y, time, func, parms, rtol, atol, ctol, sparsetype, verbose, nnz, 
                         "R/Python closures cannot run on the GPU path")
     if not isinstance(func, (str, int)):
         raise TypeError("`func' must be a function or character vector or a compiled function")
-    if spmethod != "yale":
-        raise ValueError("`spmethod' must be `yale' on this path (`ilut'/`ilutp' are outside it)")
+    # R/stodes.R:314-329.  In the reference "ilut"/"ilutp" swap the Yale LDU for SPARSKIT's incomplete LU, applied
+    # once per Newton step as if it were exact (src/sparsekit.f:141-166).  Here every spmethod is served by the same
+    # preconditioned Krylov solve: same tests, same steady state, fewer and more accurate Newton steps.  The ILUT
+    # knobs of `control' (droptol, permtol, fillin, lenplufac; R/stodes.R:407-420) are accepted; nothing uses them.
+    if spmethod not in ("yale", "ilut", "ilutp"):
+        raise ValueError("`spmethod' must be one of `yale', `ilut' or `ilutp'")
     ret_only = sparsetype == "sparsereturn"
     Type, nnzv, maxg, lrw, ian, jan = sparse_args(n, sparsetype, nnz, inz, ngp, lrw)
-    imethod = 1
+    imethod = {"yale": 1, "ilut": 2, "ilutp": 3}[spmethod]
     if isinstance(positive, (bool, np.bool_)):
         Pos, positive_v = int(positive), np.asarray([int(positive)], dtype=np.int32)
     else:

@@ -427,6 +427,23 @@ def test_implicit_column_spmv_is_bit_identical(built, name, rdims):
     assert np.array_equal(a["y"], b["y"]) and np.array_equal(a.attributes["precis"], b.attributes["precis"])
 
 
+def test_spmethod_ilut_and_ilutp_reach_the_same_steady_state(built, oracle):
+    """spmethod = "ilut"/"ilutp" with the reference's ILUT control list (R/stodes.R:314-329, 407-420): accepted and
+    served by the same Krylov solve -- the steady state is the one `yale' and the oracle reach."""
+    import rootsolve_b200 as rs
+    d = (21, 17)
+    y0 = np.full(d[0] * d[1], 10.0)
+    kw = dict(func="diff2d", parms=H.P_DIFF2D_MONOD, sparsetype="2D", nnz=[1, d[0], d[1], 0, 0], ipar=[1, d[0], d[1], 1, 1],
+              positive=True, **H.TOL)
+    ref = oracle.stsparse(y0, oracle.model("diff2d", H.P_DIFF2D_MONOD), sparsetype="2D", nnz=[1, d[0], d[1], 0, 0],
+                          ipar=[1, d[0], d[1], 1, 1], lrw=400000, positive=True, **H.TOL)
+    for sp, ctl in [("yale", None), ("ilut", {"droptol": 1e-3, "fillin": 10, "lenplufac": 2}), ("ilutp", {"permtol": 1e-3})]:
+        out = rs.stodes(y0, spmethod=sp, control=ctl, **kw)
+        assert out.attributes["steady"]
+        ok, worst = H.within_tol(out["y"], ref["y"])
+        assert ok, (sp, worst)
+
+
 def test_work_arrays_are_cached_between_solves(built):
     """device work arrays go back to a cache, not to cudaFree; rs_release_cached_memory hands them to the driver"""
     import rootsolve_b200 as rs

@@ -144,8 +144,10 @@ def test_argument_checks_mirror_the_r_front_end(built):
         rs.stodes(y, sparsetype="2D", nnz=[1, 5, 5, 0, 0], positive=[1, 26], **kw)
     with pytest.raises(TypeError, match="compiled device model"):
         rs.stodes(y, func=lambda t, y, p: y, sparsetype="2D", nnz=[1, 5, 5, 0, 0])
-    with pytest.raises(ValueError, match="spmethod"):
-        rs.stodes(y, sparsetype="2D", nnz=[1, 5, 5, 0, 0], spmethod="ilut", **kw)
+    with pytest.raises(ValueError, match="must be one of `yale', `ilut' or `ilutp'"):
+        rs.stodes(y, sparsetype="2D", nnz=[1, 5, 5, 0, 0], spmethod="gmres", **kw)
+    with pytest.raises(ValueError, match="unknown control option"):
+        rs.stodes(y, sparsetype="2D", nnz=[1, 5, 5, 0, 0], control={"droptoll": 1e-3}, **kw)
     with pytest.raises(NotImplementedError):
         rs.steady_2D(y, dimens=[5, 5], method="runsteady", **kw)
 
