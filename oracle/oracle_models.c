@@ -78,6 +78,17 @@ void anoxforc(int *neq, double *t, double *y, double *ydot, double *yout, int *i
     rsm_anox(y, ydot, yout, p);
 }
 
+/* man/steady.2D.Rd:167-206, the cyclic example */
+static double p_d2b[RSM_D2B_NPAR];
+void initdiff2db(void (*steadyparms)(int *, double *)) { int N = RSM_D2B_NPAR; steadyparms(&N, p_d2b); }
+void diff2db(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)yout;
+    const int d1 = ip[4], d2 = ip[5];
+    for (int j = 0; j < d1; j++)
+        for (int k = 0; k < d2; k++) ydot[j * d2 + k] = rsm_diff2db_point(y, j, k, d1, d2, p_d2b);
+}
+
 /* diffusion on a masked grid (sparsetype "2Dmap"/"3Dmap"); the map is in ipar, see model_math.h */
 static double p_dmap[RSM_DMAP_NPAR];
 void initdiffmap(void (*steadyparms)(int *, double *)) { int N = RSM_DMAP_NPAR; steadyparms(&N, p_dmap); }

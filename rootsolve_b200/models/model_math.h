@@ -75,6 +75,27 @@ RSM_HD double rsm_diff2d_point(const double *y, int j, int k, int d1, int d2,
     return dY;
 }
 
+/* The second example of man/steady.2D.Rd (:167-206, `diffusion2Db`): the same diffusion-consumption model with an
+ * extra flux on two sides and an exchange between the two sides of the second R dimension -- the one the example
+ * declares cyclic (cyclicBnd = 2).  The exchange is one-way (the last column of the R matrix is driven by the first),
+ * so the Jacobian is nonsymmetric and uses one of the two wrap entries of the cyclic pattern.
+ * p[0]=Dx p[1]=Dy p[2]=dx p[3]=dy p[4]=r p[5]=BND p[6]=extra flux (10) p[7]=exchange rate (10)
+ * j = index of the second R dimension (slow), k = index of the first (fast), as everywhere in this file. */
+#define RSM_D2B_NPAR 8
+RSM_HD double rsm_diff2db_point(const double *y, int j, int k, int d1, int d2, const double *p)
+{
+    const double Dx = p[0], Dy = p[1], dx = p[2], dy = p[3], r = p[4], bnd = p[5], extra = p[6], exch = p[7];
+    const int idx = j * d2 + k;
+    const double yc = y[idx];
+    double dY = -r * yc;
+    dY = dY - rsm_flux_div((k > 0) ? y[idx - 1] : bnd, yc, (k < d2 - 1) ? y[idx + 1] : bnd, Dx, dx);
+    dY = dY - rsm_flux_div((j > 0) ? y[idx - d2] : bnd, yc, (j < d1 - 1) ? y[idx + d2] : bnd, Dy, dy);
+    if (j == 0) dY = dY + extra;                              /* dY[,1]  <- dY[,1] + 10 */
+    if (k == 0) dY = dY + extra;                              /* dY[1,]  <- dY[1,] + 10 */
+    if (j == d1 - 1) dY = dY + (y[k] - yc) * exch;            /* dY[,ny] <- dY[,ny] + (y[,1] - y[,ny]) * 10 */
+    return dY;
+}
+
 /* variant: 0 = each direction once ; 1 = each direction applied twice, in the
  * order the vignette's three loops apply them (vignettes/rootSolve.Rnw:686-722):
  * (y,z) for fixed x-slices, (x,z), (x,y). */

@@ -12,6 +12,8 @@ P_DIFF3D = [1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 0.025, 1.0]
 # D1 D2 dx dy dz k m BNDu BNDv -- m > k*BNDu keeps dv/dv < 0 everywhere (a decaying, not a growing, species v)
 P_RD3D = [1.0, 0.5, 1.0, 1.0, 1.0, 0.01, 0.2, 10.0, 1.0, 0.0]
 P_RT1D = [1.0, 1.0, 1.0, 0.5, 0.5, 1.0, 0.1]
+# man/steady.2D.Rd:193-196 + the two constants 10 of diffusion2Db: Dx Dy dx dy r BND extra exchange
+P_DIFF2DB = [1.0, 1.0, 1.0, 1.0, 0.025, 1.0, 10.0, 10.0]
 
 
 def ip(a):

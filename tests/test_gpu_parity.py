@@ -427,6 +427,26 @@ def test_implicit_column_spmv_is_bit_identical(built, name, rdims):
     assert np.array_equal(a["y"], b["y"]) and np.array_equal(a.attributes["precis"], b.attributes["precis"])
 
 
+def test_man_page_cyclic_example_on_gpu(built, oracle):
+    """The second example of man/steady.2D.Rd (:167-206): 50 x 100, cyclic boundary in y, called the way the man page
+    calls it -- steady.2D(y, dimens = c(nx, ny), cyclicBnd = 2, pos = TRUE, atol = rtol = ctol = 1e-10).  A cyclic
+    pattern (general CSR kernels, `rounds' grouping) with a nonsymmetric Jacobian (BiCGStab); against the oracle."""
+    import rootsolve_b200 as rs
+    nx, ny = 50, 100
+    y = np.full((nx, ny), 10.0)
+    ref = oracle.stsparse(np.full(nx * ny, 10.0), oracle.model("diff2db", H.P_DIFF2DB), sparsetype="2D", nnz=[1, ny, nx, 1, 0],
+                          ipar=[1, ny, nx, 1, 0], lrw=283800, positive=True, **H.TOL)
+    out = rs.steady_2D(y, func="diff2db", parms=H.P_DIFF2DB, dimens=[nx, ny], cyclicBnd=2, positive=True, lrw=283800,
+                       ipar=[1, ny, nx, 1, 0], return_groups=True, **H.TOL)
+    A = out.attributes
+    assert A["steady"] and ref["steady"] and A["spmv_kernel"] == "csr-tma"
+    assert A["dims"]["nnz"] == ref["dims"]["nnz"] == 24800 and A["dims"]["ngp"] == ref["dims"]["ngp"]
+    assert np.array_equal(A["ian"], ref["ian"]) and np.array_equal(A["igp"], ref["igp"]) and np.array_equal(A["jgp"], ref["jgp"])
+    assert abs(A["precis"][0] - ref["precis"][0]) <= 1e-12 * ref["precis"][0]
+    ok, worst = H.within_tol(out["y"], ref["y"])
+    assert ok, worst
+
+
 def test_spmethod_ilut_and_ilutp_reach_the_same_steady_state(built, oracle):
     """spmethod = "ilut"/"ilutp" with the reference's ILUT control list (R/stodes.R:314-329, 407-420): accepted and
     served by the same Krylov solve -- the steady state is the one `yale' and the oracle reach."""

@@ -191,6 +191,32 @@ def test_oracle_newton_on_nonlinear_cases(oracle):
     assert ok, worst
 
 
+def test_man_page_examples_fit_their_work_arrays(oracle):
+    """The two steady.2D examples of the reference state the Yale work length they run with: lrw = 1e6 for the
+    100 x 100 model (man/steady.2D.Rd:139-143) and lrw = 283800 for the 50 x 100 model with a cyclic boundary in y
+    (:202-206).  The restated ordering + symbolic LDU must fit both (an upper-bound pin of md/nsfc fill), and the
+    cyclic pattern gets its wrap entries and one extra group per cyclic direction (R/stodes.R:123-131)."""
+    n = 100
+    a = oracle.stsparse(np.full(n * n, 10.0), oracle.model("diff2d", H.P_DIFF2D_LIN), sparsetype="2D", nnz=[1, n, n, 0, 0],
+                        ipar=[1, n, n, 1, 0], lrw=1000000, positive=True, **H.TOL)
+    assert a["steady"] and a["dims"]["nnz"] == 5 * n * n - 4 * n and a["dims"]["ngp"] == 7
+    assert 0 < a["dims"]["lrw"] <= 1000000
+    nx, ny = 50, 100                      # R: matrix(nrow = nx, ncol = ny); stodes sees rev(dimens) = (ny, nx), rev(Bnd) = (1, 0)
+    b = oracle.stsparse(np.full(nx * ny, 10.0), oracle.model("diff2db", H.P_DIFF2DB), sparsetype="2D", nnz=[1, ny, nx, 1, 0],
+                        ipar=[1, ny, nx, 1, 0], lrw=283800, positive=True, **H.TOL)
+    assert b["steady"]
+    assert b["dims"]["nnz"] == 5 * nx * ny - 2 * (nx + ny) + 2 * nx       # two wrap entries per line across the cyclic side
+    # 283800 is not just enough, it is EXACTLY what the restated minimum-degree ordering + symbolic LDU need -- the
+    # man page's author evidently copied attributes(ST2)$dims back into the call.  A second exact pin of md / nsfc /
+    # the cdrv storage carving (after the 82366 of pdf p.16), on a cyclic pattern with a nonsymmetric Jacobian.
+    assert b["dims"]["lrw"] == 283800
+    with pytest.raises(RuntimeError, match="insufficient storage"):
+        oracle.stsparse(np.full(nx * ny, 10.0), oracle.model("diff2db", H.P_DIFF2DB), sparsetype="2D", nnz=[1, ny, nx, 1, 0],
+                        ipar=[1, ny, nx, 1, 0], lrw=283799, positive=True, **H.TOL)
+    y = b["y"].reshape(ny, nx)
+    assert y.min() > 0 and y[0].mean() > y[ny // 2].mean()                # the extra flux enters along the first column of the R matrix
+
+
 def test_oracle_error_paths(oracle):
     with pytest.raises(RuntimeError, match="lrw"):
         oracle.stsparse(np.full(1000, 10.0), oracle.model("diff3d", H.P_DIFF3D), sparsetype="3D",
