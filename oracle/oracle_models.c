@@ -89,6 +89,18 @@ void diff2db(int *neq, double *t, double *y, double *ydot, double *yout, int *ip
         for (int k = 0; k < d2; k++) ydot[j * d2 + k] = rsm_diff2db_point(y, j, k, d1, d2, p_d2b);
 }
 
+/* man/steady.1D.Rd:113-153, BOD and oxygen in a river; yout[0..nout) = the BOD decay rate per box */
+static double p_o2bod[RSM_O2BOD_NPAR];
+void inito2bod(void (*steadyparms)(int *, double *)) { int N = RSM_O2BOD_NPAR; steadyparms(&N, p_o2bod); }
+void o2bod(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t;
+    const int nb = ip[4], nout = ip[0];
+    for (int s = 0; s < 2; s++)
+        for (int j = 0; j < nb; j++) ydot[s * nb + j] = rsm_o2bod_point(y, s, j, nb, p_o2bod);
+    for (int j = 0; j < nb && j < nout; j++) yout[j] = rsm_o2bod_rate(y, j, nb, p_o2bod);
+}
+
 /* diffusion on a masked grid (sparsetype "2Dmap"/"3Dmap"); the map is in ipar, see model_math.h */
 static double p_dmap[RSM_DMAP_NPAR];
 void initdiffmap(void (*steadyparms)(int *, double *)) { int N = RSM_DMAP_NPAR; steadyparms(&N, p_dmap); }

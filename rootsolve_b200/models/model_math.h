@@ -175,6 +175,28 @@ RSM_HD double rsm_rt1d_point(const double *y, int s, int j, int nspec, int nb, c
     return dY;
 }
 
+/* The first example of man/steady.1D.Rd (:113-153, `O2BOD`): biochemical oxygen demand and oxygen in a river,
+ * two species on nb boxes, upwind transport with velocity v, BOD decay limited by oxygen (Monod), re-aeration.
+ * One output VECTOR: the decay rate in every box (nout = nb).
+ * p[0]=v p[1]=dx p[2]=r p[3]=p p[4]=O2sat p[5]=O2_0 p[6]=BOD_0 p[7]=ksO2 (10 in the man page) */
+#define RSM_O2BOD_NPAR 8
+RSM_HD double rsm_o2bod_rate(const double *y, int j, int nb, const double *p)
+{
+    const double BOD = y[j], O2 = y[nb + j];
+    return p[2] * BOD * O2 / (O2 + p[7]);
+}
+RSM_HD double rsm_o2bod_point(const double *y, int s, int j, int nb, const double *p)
+{
+    const double v = p[0], dx = p[1], rea = p[3], O2sat = p[4];
+    const double *ys = y + (long)s * nb;
+    const double upstream = (j > 0) ? ys[j - 1] : ((s == 0) ? p[6] : p[5]);
+    const double flo = v * upstream, fhi = v * ys[j];      /* FluxX <- v * c(X_0, X) */
+    const double rate = rsm_o2bod_rate(y, j, nb, p);
+    double d = -(fhi - flo) / dx - rate;                   /* -diff(FluxX)/dx - BODrate */
+    if (s == 1) d = d + rea * (O2sat - ys[j]);             /* + p*(O2sat-O2) */
+    return d;
+}
+
 /* The 4-variable sediment model of the reference's vignette and of inst/dynload (organic matter OM, O2, SO4,
  * HS; vignettes/rootSolve.Rnw:352-372): oxic and anoxic mineralisation with Monod limitation, re-oxidation of
  * sulphide, exchange with the bottom water.  One output variable, SumS = SO4 + HS.

@@ -14,6 +14,8 @@ P_RD3D = [1.0, 0.5, 1.0, 1.0, 1.0, 0.01, 0.2, 10.0, 1.0, 0.0]
 P_RT1D = [1.0, 1.0, 1.0, 0.5, 0.5, 1.0, 0.1]
 # man/steady.2D.Rd:193-196 + the two constants 10 of diffusion2Db: Dx Dy dx dy r BND extra exchange
 P_DIFF2DB = [1.0, 1.0, 1.0, 1.0, 0.025, 1.0, 10.0, 10.0]
+# man/steady.1D.Rd:137-145: v dx r p O2sat O2_0 BOD_0 ksO2
+P_O2BOD = [1e2, 100.0, 0.1, 0.1, 300.0, 50.0, 1500.0, 10.0]
 
 
 def ip(a):

@@ -447,6 +447,24 @@ def test_man_page_cyclic_example_on_gpu(built, oracle):
     assert ok, worst
 
 
+def test_man_page_river_example_on_gpu(built, oracle):
+    """man/steady.1D.Rd:113-153 (O2BOD) called as the man page calls it, with method = "stodes": two named species, an
+    output VECTOR (nout = number of boxes), default tolerances of stodes.  State and outputs against the oracle."""
+    import rootsolve_b200 as rs
+    N = 100
+    y0 = np.concatenate([np.full(N, 200.0), np.full(N, 200.0)])
+    ref = oracle.stsparse(y0, oracle.model("o2bod", H.P_O2BOD), sparsetype="1D", nnz=[2, N, 0], ipar=[2, N], lrw=100000,
+                          positive=True, nout=N)
+    out = rs.steady_1D(y0, func="o2bod", parms=H.P_O2BOD, nspec=2, positive=True, names=["BOD", "O2"], method="stodes",
+                       ipar=[2, N], nout=N, outnames=["BODrate"] * N)
+    A = out.attributes
+    assert A["steady"] and ref["steady"] and A["dims"]["nnz"] == ref["dims"]["nnz"] and A["dims"]["ngp"] == ref["dims"]["ngp"] == 6
+    assert out["y"].shape == (N, 2) and A["ynames"] == ["BOD", "O2"]
+    ok, worst = H.within_tol(out["y"].ravel(order="F"), ref["y"], atol=1e-8, rtol=1e-6)
+    assert ok, worst
+    assert out["BODrate"].shape == (N,) and np.allclose(out["BODrate"], ref["out"], rtol=1e-6, atol=1e-8)
+
+
 def test_spmethod_ilut_and_ilutp_reach_the_same_steady_state(built, oracle):
     """spmethod = "ilut"/"ilutp" with the reference's ILUT control list (R/stodes.R:314-329, 407-420): accepted and
     served by the same Krylov solve -- the steady state is the one `yale' and the oracle reach."""

@@ -217,6 +217,21 @@ def test_man_page_examples_fit_their_work_arrays(oracle):
     assert y.min() > 0 and y[0].mean() > y[ny // 2].mean()                # the extra flux enters along the first column of the R matrix
 
 
+def test_man_page_river_example(oracle):
+    """man/steady.1D.Rd:113-153 (O2BOD), run through the stodes path: 2 species x 100 boxes, pos = TRUE, one output
+    vector.  No numbers are printed in the man page; what it shows is the physics: BOD decays downstream, the
+    oxygen sag recovers towards saturation, and the output vector is the decay rate at the returned state."""
+    N = 100
+    y0 = np.concatenate([np.full(N, 200.0), np.full(N, 200.0)])
+    r = oracle.stsparse(y0, oracle.model("o2bod", H.P_O2BOD), sparsetype="1D", nnz=[2, N, 0], ipar=[2, N], lrw=100000,
+                        positive=True, nout=N)
+    assert r["steady"] and r["dims"]["nnz"] == 2 * N * 4 - 4 and r["dims"]["ngp"] == 6
+    BOD, O2 = r["y"][:N], r["y"][N:]
+    assert np.all(np.diff(BOD) < 0) and BOD[0] < 1500 and BOD[-1] > 0
+    assert O2.min() < 50 and O2[-1] > O2.min() and np.all(O2 > 0)
+    assert np.allclose(r["out"], 0.1 * BOD * O2 / (O2 + 10.0), rtol=1e-12)
+
+
 def test_oracle_error_paths(oracle):
     with pytest.raises(RuntimeError, match="lrw"):
         oracle.stsparse(np.full(1000, 10.0), oracle.model("diff3d", H.P_DIFF3D), sparsetype="3D",
