@@ -45,6 +45,17 @@ PDF_P8_ANOX = {
     "steady": True,
 }
 
+# rootsolve_man_steady2d.json -- the arguments the two steady.2D man-page examples are CALLED with
+# (man/steady.2D.Rd:132-143 and :193-206).  The second lrw is exactly the work length the path needs for that
+# example (the oracle fails with one double less), i.e. a value the author read back from attributes()$dims.
+MAN_STEADY2D = {
+    "source": "rootSolve 1.8.2.4 man/steady.2D.Rd:106-207",
+    "example1": {"dimens": [100, 100], "cyclicBnd": None, "lrw_given": 1000000, "y0": 10.0, "tol": 1e-10,
+                 "parms": {"Dx": 1, "Dy": 1, "dx": 1, "dy": 1, "r": 0.025, "BND": 1}},
+    "example2": {"dimens": [50, 100], "cyclicBnd": 2, "lrw_given": 283800, "lrw_needed": 283800, "y0": 10.0, "tol": 1e-10,
+                 "parms": {"Dx": 1, "Dy": 1, "dx": 1, "dy": 1, "r": 0.025, "BND": 1, "extra_flux": 10, "exchange": 10}},
+}
+
 GRIDS = [
     ("1D", 1, [50], [0]), ("1D", 5, [1000], [0]), ("1D", 2, [30], [1]),
     ("2D", 1, [50, 50], [0, 0]), ("2D", 1, [100, 100], [0, 0]), ("2D", 2, [17, 9], [0, 0]), ("2D", 1, [50, 100], [0, 1]),
@@ -61,6 +72,7 @@ def main():
     from oracle import oracle as O
     json.dump(PDF_P16, open(os.path.join(HERE, "rootsolve_pdf_p16.json"), "w"), indent=1)
     json.dump(PDF_P8_ANOX, open(os.path.join(HERE, "rootsolve_pdf_p8_anox.json"), "w"), indent=1)
+    json.dump(MAN_STEADY2D, open(os.path.join(HERE, "rootsolve_man_steady2d.json"), "w"), indent=1)
     out = []
     for kind, nspec, dims, cyc in GRIDS:
         ian, jan = O.sparse_structure(kind, nspec, dims, cyc)

@@ -196,9 +196,11 @@ def test_man_page_examples_fit_their_work_arrays(oracle):
     100 x 100 model (man/steady.2D.Rd:139-143) and lrw = 283800 for the 50 x 100 model with a cyclic boundary in y
     (:202-206).  The restated ordering + symbolic LDU must fit both (an upper-bound pin of md/nsfc fill), and the
     cyclic pattern gets its wrap entries and one extra group per cyclic direction (R/stodes.R:123-131)."""
-    n = 100
+    g = json.load(open(os.path.join(GOLD, "rootsolve_man_steady2d.json")))
+    assert g["example1"]["lrw_given"] == 1000000 and g["example2"]["lrw_given"] == g["example2"]["lrw_needed"] == 283800
+    n = g["example1"]["dimens"][0]
     a = oracle.stsparse(np.full(n * n, 10.0), oracle.model("diff2d", H.P_DIFF2D_LIN), sparsetype="2D", nnz=[1, n, n, 0, 0],
-                        ipar=[1, n, n, 1, 0], lrw=1000000, positive=True, **H.TOL)
+                        ipar=[1, n, n, 1, 0], lrw=g["example1"]["lrw_given"], positive=True, **H.TOL)
     assert a["steady"] and a["dims"]["nnz"] == 5 * n * n - 4 * n and a["dims"]["ngp"] == 7
     assert 0 < a["dims"]["lrw"] <= 1000000
     nx, ny = 50, 100                      # R: matrix(nrow = nx, ncol = ny); stodes sees rev(dimens) = (ny, nx), rev(Bnd) = (1, 0)
