@@ -35,7 +35,7 @@ constexpr int SLOT = 8;        // doubles per parity slot: r0v, ts, tt, rr, rhon
 constexpr int S_R0V = 0, S_TS = 1, S_TT = 2, S_RR = 3, S_RHONEXT = 4, S_BAD = 5;
 constexpr int S_BNORM = 2 * SLOT, S_RTRUE = 2 * SLOT + 1, S_SYM = 2 * SLOT + 2;   // S_SYM: two doubles
 // slots of the CG recurrence (same parity scheme): <p,Ap>, <r,r>, <r,z> of the step, breakdown flag
-constexpr int C_PQ = 0, C_RR = 1, C_RZ = 2, C_BAD = 5;
+constexpr int C_PQ = 0, C_RR = 1, C_RZ = 2, C_ALPHA = 3, C_BAD = 5;
 struct Krylov;
 static inline double own_nnz_estimate(const Krylov &k);
 constexpr int NSCAL = 2 * SLOT + 8;
@@ -1101,22 +1101,28 @@ __global__ void __launch_bounds__(256) cg_unscale_x_kernel(int b, int e, const d
     for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x) x[i] *= s[i];
 }
 
-// p = z + beta p  [first: p = z],  z = dinv r  (SCALED: z = r, dinv is not read)
+// x += alpha_prev p  (the solution update of the PREVIOUS step, deferred to here because this kernel reads the old
+// p anyway: the step then touches p three times instead of four) ; p = z + beta p  [first: p = z, nothing pending],
+// z = dinv r  (SCALED: z = r, dinv is not read).  A cycle ends with cg_flush_x_kernel.
 template <bool SCALED>
 __global__ void __launch_bounds__(256) cg_update_p_kernel(int b, int e, int first, const double *scal, int cur,
                                                           const double *__restrict__ r, const double *__restrict__ dinv,
-                                                          double *__restrict__ p, HaloPush hp, unsigned *hticket)
+                                                          double *__restrict__ p, double *__restrict__ x, HaloPush hp,
+                                                          unsigned *hticket)
 {
-    double beta = 0.0;
+    double beta = 0.0, alpha = 0.0;
     if (!first) {
         beta = scal[SLOT * (cur ^ 1) + C_RZ] / scal[SLOT * cur + C_RZ];   // rho_k / rho_{k-1}
         if (!isfinite(beta)) beta = 0.0;
+        alpha = scal[SLOT * (cur ^ 1) + C_ALPHA];                         // step length of the previous step (0 if it broke down)
     }
     const double2 *r2 = reinterpret_cast<const double2 *>(r), *d2 = reinterpret_cast<const double2 *>(dinv);
-    double2 *p2 = reinterpret_cast<double2 *>(p);
-#define CP_ONE(i) { const double pn = (SCALED ? r[i] : dinv[i] * r[i]) + (first ? 0.0 : beta * p[i]); p[i] = pn; halo_store(hp, b, e, i, pn); }
+    double2 *p2 = reinterpret_cast<double2 *>(p), *x2 = reinterpret_cast<double2 *>(x);
+#define CP_ONE(i) { double pn = (SCALED ? r[i] : dinv[i] * r[i]); \
+                    if (!first) { const double po = p[i]; x[i] += alpha * po; pn += beta * po; } p[i] = pn; halo_store(hp, b, e, i, pn); }
 #define CP_TWO(i) { const double2 rv = r2[i]; double2 pn = rv; if (!SCALED) { const double2 dv = d2[i]; pn.x = dv.x * rv.x; pn.y = dv.y * rv.y; } \
-                    if (!first) { const double2 po = p2[i]; pn.x += beta * po.x; pn.y += beta * po.y; } p2[i] = pn; \
+                    if (!first) { const double2 po = p2[i]; double2 xv = x2[i]; xv.x += alpha * po.x; xv.y += alpha * po.y; x2[i] = xv; \
+                                  pn.x += beta * po.x; pn.y += beta * po.y; } p2[i] = pn; \
                     halo_store(hp, b, e, 2 * (i), pn.x); halo_store(hp, b, e, 2 * (i) + 1, pn.y); }
     RS_RANGE_LOOP(b, e, CP_ONE, CP_TWO);
 #undef CP_ONE
@@ -1124,29 +1130,37 @@ __global__ void __launch_bounds__(256) cg_update_p_kernel(int b, int e, int firs
     halo_signal_done(hp, hticket);
 }
 
-// alpha = rho / <p,q> ; x += alpha p ; r -= alpha q ; out = { <r,r>, <r, dinv r> }  (SCALED: both are <r,r>)
+// x += alpha p of the last step taken (end of a cycle: before the true residual is formed, before x is handed back)
+__global__ void __launch_bounds__(256) cg_flush_x_kernel(int b, int e, const double *scal, int cur, const double *__restrict__ p,
+                                                         double *__restrict__ x)
+{
+    const double alpha = scal[SLOT * cur + C_ALPHA];
+    for (long long i = b + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e; i += (long long)gridDim.x * blockDim.x)
+        x[i] += alpha * p[i];
+}
+
+// alpha = rho / <p,q> (kept in the slot for the deferred x update) ; r -= alpha q ; out = { <r,r>, <r, dinv r> }
+// (SCALED: both are <r,r>)
 template <bool SCALED>
-__global__ void __launch_bounds__(256) cg_update_xr_kernel(int b, int e, double *scal, int cur, const double *__restrict__ p,
-                                                           const double *__restrict__ q, const double *__restrict__ dinv,
-                                                           double *__restrict__ x, double *__restrict__ r,
+__global__ void __launch_bounds__(256) cg_update_xr_kernel(int b, int e, double *scal, int cur, const double *__restrict__ q,
+                                                           const double *__restrict__ dinv, double *__restrict__ r,
                                                            double *partials, unsigned *ticket, int accumulate, PeerRed pr)
 {
     double *slot = scal + SLOT * cur;
     const double rho = scal[SLOT * (cur ^ 1) + C_RZ];
     double alpha = rho / slot[C_PQ];
     // alpha must be positive for a definite matrix (rho and <p,Ap> share the sign of A): anything else means the
-    // matrix is indefinite or the recurrence broke down -- keep x, tell the host.
+    // matrix is indefinite or the recurrence broke down -- keep x (alpha = 0), tell the host.
     const bool bad = !isfinite(alpha) || !(alpha > 0.0);
     if (bad) alpha = 0.0;
-    if (blockIdx.x == 0 && threadIdx.x == 0) slot[C_BAD] = bad ? 1.0 : 0.0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { slot[C_BAD] = bad ? 1.0 : 0.0; slot[C_ALPHA] = alpha; }
     double acc[2] = {0.0, 0.0};
-    const double2 *p2 = reinterpret_cast<const double2 *>(p), *q2 = reinterpret_cast<const double2 *>(q);
-    const double2 *d2 = reinterpret_cast<const double2 *>(dinv);
-    double2 *x2 = reinterpret_cast<double2 *>(x), *r2 = reinterpret_cast<double2 *>(r);
-#define CX_ONE(i) { x[i] += alpha * p[i]; const double rn = r[i] - alpha * q[i]; r[i] = rn; acc[0] += rn * rn; \
+    const double2 *q2 = reinterpret_cast<const double2 *>(q), *d2 = reinterpret_cast<const double2 *>(dinv);
+    double2 *r2 = reinterpret_cast<double2 *>(r);
+#define CX_ONE(i) { const double rn = r[i] - alpha * q[i]; r[i] = rn; acc[0] += rn * rn; \
                     if (!SCALED) acc[1] += rn * dinv[i] * rn; }
-#define CX_TWO(i) { const double2 pv = p2[i], qv = q2[i]; double2 xv = x2[i], rn = r2[i]; \
-                    xv.x += alpha * pv.x; xv.y += alpha * pv.y; x2[i] = xv; rn.x -= alpha * qv.x; rn.y -= alpha * qv.y; r2[i] = rn; \
+#define CX_TWO(i) { const double2 qv = q2[i]; double2 rn = r2[i]; \
+                    rn.x -= alpha * qv.x; rn.y -= alpha * qv.y; r2[i] = rn; \
                     acc[0] += rn.x * rn.x + rn.y * rn.y; \
                     if (!SCALED) { const double2 dv = d2[i]; acc[1] += rn.x * dv.x * rn.x + rn.y * dv.y * rn.y; } }
     RS_RANGE_LOOP(b, e, CX_ONE, CX_TWO);
@@ -1229,14 +1243,15 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     const double rows = (double)k.own.total();
     const HaloSignal sig = k.push_ok ? comm_next_halo_signal() : HaloSignal();
     {
-        Launch L(c, K_VEC, ((first ? 24.0 : 32.0) - (k.scaled ? 8.0 : 0.0)) * rows);
+        // first: r -> p ; else r, p, x -> p, x  (+ dinv when the system is not scaled)
+        Launch L(c, K_VEC, ((first ? 16.0 : 40.0) + (k.scaled ? 0.0 : 8.0)) * rows);
         for (int q = 0; q < k.own.n; q++) {
             const int b = k.own.b[q], e = k.own.e[q];
             if (k.scaled)
-                cg_update_p_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, nullptr, k.ph_v,
+                cg_update_p_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, nullptr, k.ph_v, x,
                                                                                      make_push(k, 0, sig, q == k.own.n - 1), k.ticket.p + 1);
             else
-                cg_update_p_kernel<false><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, k.dinv.p, k.ph_v,
+                cg_update_p_kernel<false><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, k.dinv.p, k.ph_v, x,
                                                                                       make_push(k, 0, sig, q == k.own.n - 1), k.ticket.p + 1);
         }
     }
@@ -1248,16 +1263,16 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_PQ, 1));
     {
-        Launch L(c, K_VEC, (k.scaled ? 48.0 : 56.0) * rows);
+        Launch L(c, K_VEC, (k.scaled ? 24.0 : 32.0) * rows);   // q, r -> r (+ dinv)
         const PeerRed peer = comm_next_peer_red();
         for (int q = 0; q < k.own.n; q++) {
             const int b = k.own.b[q], e = k.own.e[q];
             if (k.scaled)
-                cg_update_xr_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph_v, k.v.p, nullptr, x, k.r.p,
+                cg_update_xr_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.v.p, nullptr, k.r.p,
                                                                                       k.partials.p, k.ticket.p, q > 0,
                                                                                       q == k.own.n - 1 ? peer : PeerRed());
             else
-                cg_update_xr_kernel<false><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.ph_v, k.v.p, k.dinv.p, x, k.r.p,
+                cg_update_xr_kernel<false><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.v.p, k.dinv.p, k.r.p,
                                                                                        k.partials.p, k.ticket.p, q > 0,
                                                                                        q == k.own.n - 1 ? peer : PeerRed());
         }
@@ -1359,6 +1374,11 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
         const bool looks_converged = rnorm <= target;
         const bool stagnated = since_best * k.check_every >= 40;
         if (!(looks_converged || stagnated || total >= k.max_iter)) continue;
+        {   // the solution update of the last step is still pending (it rides on the next step's direction update)
+            Launch L(c, K_VEC, 24.0 * (double)k.own.total());
+            for (int q = 0; q < k.own.n; q++)
+                cg_flush_x_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], k.scal.p, cur, k.ph_v, x);
+        }
         double rt = 0.0;
         RS_TRY(cg_start(c, k, b, x, true, S_RTRUE, &rt));
         if (debug) fprintf(stderr, "[pcg] cycle %d ends after %d its (%s): true residual %.6e (target %.3e)\n", restarts, cycle_it,
