@@ -26,6 +26,22 @@ def test_library_exports_every_declared_symbol(built):
     assert built.rs_abi_version() == 1
 
 
+def test_header_is_plain_c(tmp_path):
+    """the drop-in boundary is a C ABI: include/rootsolve_b200.h must compile as C99 on its own (no C++, no CUDA, no torch
+    types), and a C program must link against the library"""
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    src = tmp_path / "t.c"
+    src.write_text('#include "rootsolve_b200.h"\n'
+                   'int main(void) { rs_stsparse_args a; rs_stsparse_result r; (void)a; (void)r;\n'
+                   '                 return rs_abi_version() == 1 && rs_last_error() != 0 ? 0 : 1; }\n')
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(root, "include"),
+                    "-fsyntax-only", str(src)], check=True)
+
+
 def test_model_library_descriptors(built):
     from rootsolve_b200 import _capi
 
