@@ -7,9 +7,11 @@
  * __graft_entry__.smoke() and as the timed CPU baseline / reference arm in
  * bench.py.  Nothing under rootsolve_b200/ may include, link or call it.
  *
- * Parity status: PINNED against the only goldens the reference ships for this
- * path (inst/doc/rootSolve.pdf p.16: nnz=6400, ngp=12, work length 82366,
- * 3 iterations, precis[0]=11.05; closed-form nnz/ngp counts) -- see
+ * Parity status: PINNED against the goldens the reference ships for this path:
+ * inst/doc/rootSolve.pdf p.16 (nnz=6400, ngp=12, work length 82366, 3 iterations,
+ * all three printed precis values), pdf p.8-9 (the compiled anoxic model: y, SumS,
+ * eight precis values), man/steady.2D.Rd:202-206 (the cyclic example needs exactly
+ * the lrw = 283800 it is called with) and the closed-form nnz/ngp counts -- see
  * tests/test_oracle_golden.py.  The reference itself (R + Fortran 77) cannot be
  * compiled in this image (no R, no Fortran compiler), so there is no
  * oracle/_ref build; DESIGN.md says so.
