@@ -40,6 +40,10 @@ def test_header_is_plain_c(tmp_path):
                    '                 return rs_abi_version() == 1 && rs_last_error() != 0 ? 0 : 1; }\n')
     subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(root, "include"),
                     "-fsyntax-only", str(src)], check=True)
+    # the R-side binding shown in INTEGRATION.md (integration/call_stsparse_b200.c), against stand-in R declarations
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(root, "include"),
+                    "-I", os.path.join(root, "integration", "mock_r"), "-fsyntax-only",
+                    os.path.join(root, "integration", "call_stsparse_b200.c")], check=True)
 
 
 def test_model_library_descriptors(built):
