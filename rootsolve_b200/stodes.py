@@ -9,9 +9,9 @@ Differences that follow from BASELINE.json's north star:
   * ``func`` is a compiled *device* model: the name of a model exported by a
     model library (``dllname``; default: the bundled ``rs_models``).  R closures
     cannot run on the GPU and are rejected.
-  * ``spmethod="yale"`` is served by the preconditioned Krylov solver; ``lrw`` is
-    accepted and ignored; ``control`` carries the Krylov knobs
-    (``precond``, ``max_krylov``, ``lin_rtol``, ``lin_ewt_factor``, ``check_every``).
+  * every ``spmethod`` (``"yale"``, ``"ilut"``, ``"ilutp"``) is served by the preconditioned Krylov solver;
+    ``lrw`` is accepted and ignored; ``control`` carries the Krylov knobs (``precond``, ``max_krylov``,
+    ``lin_rtol``, ``lin_ewt_factor``, ``check_every``) and may carry the reference's ILUT options, which are ignored.
 """
 from __future__ import annotations
 
