@@ -465,6 +465,26 @@ def test_man_page_river_example_on_gpu(built, oracle):
     assert out["BODrate"].shape == (N,) and np.allclose(out["BODrate"], ref["out"], rtol=1e-6, atol=1e-8)
 
 
+def test_c_caller_example(built, oracle, tmp_path):
+    """integration/example_steady3d.c: the path called from plain C with arguments built as steady.3D builds them;
+    its printed nnz / ngp / precis[0] / centre value against the oracle"""
+    import re
+    import subprocess
+    from test_host_api import build_c_example
+    n = 12
+    exe = build_c_example(tmp_path)
+    p = subprocess.run([exe, str(n)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    m = re.search(r"nnz=(\d+) ngp=(\d+) steady=1 newton=(\d+) krylov=\d+ precis=([0-9.e+-]+)[, ].*y\[centre\]=([0-9.e+-]+)", p.stdout)
+    assert m, p.stdout
+    ref = oracle.stsparse(np.full(n ** 3, 10.0), oracle.model("diff3d", H.P_DIFF3D), sparsetype="3D", nnz=[1, n, n, n, 0, 0, 0],
+                          ipar=[1, n, n, n, 0], lrw=2000000, positive=True, **H.TOL)
+    assert int(m.group(1)) == ref["dims"]["nnz"] and int(m.group(2)) == ref["dims"]["ngp"] and int(m.group(3)) == len(ref["precis"])
+    assert abs(float(m.group(4)) - ref["precis"][0]) <= 1e-6 * ref["precis"][0]
+    c = (n // 2) * n * n + (n // 2) * n + n // 2
+    assert abs(float(m.group(5)) - ref["y"][c]) <= 1e-9 * abs(ref["y"][c]) + 1e-10
+
+
 def test_spmethod_ilut_and_ilutp_reach_the_same_steady_state(built, oracle):
     """spmethod = "ilut"/"ilutp" with the reference's ILUT control list (R/stodes.R:314-329, 407-420): accepted and
     served by the same Krylov solve -- the steady state is the one `yale' and the oracle reach."""

@@ -46,6 +46,32 @@ def test_header_is_plain_c(tmp_path):
                     os.path.join(root, "integration", "call_stsparse_b200.c")], check=True)
 
 
+def build_c_example(tmp_path):
+    """compiles and links integration/example_steady3d.c against the in-tree libraries; returns the executable"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.join(root, "rootsolve_b200")
+    exe = str(tmp_path / "example_steady3d")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(root, "include"),
+                    os.path.join(root, "integration", "example_steady3d.c"), "-L", libdir, "-lrootsolve_b200", "-lrs_models",
+                    "-Wl,-rpath," + libdir, "-o", exe], check=True)
+    return exe
+
+
+def test_c_caller_links_and_fails_loudly_without_a_gpu(built, tmp_path):
+    """a plain C program against the C ABI: links; and where there is no CUDA device it must stop with the library's
+    'no CPU path' error, not compute anything"""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    exe = build_c_example(tmp_path)
+    if built.rs_device_count() > 0:
+        pytest.skip("a CUDA device is present (the gpu suite runs the example)")
+    p = subprocess.run([exe, "8"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert p.returncode == 1 and "no CPU path" in p.stderr
+
+
 def test_model_library_descriptors(built):
     from rootsolve_b200 import _capi
 
