@@ -485,6 +485,28 @@ def test_c_caller_example(built, oracle, tmp_path):
     assert abs(float(m.group(5)) - ref["y"][c]) <= 1e-9 * abs(ref["y"][c]) + 1e-10
 
 
+def test_user_model_library_on_gpu(built, tmp_path):
+    """integration/example_model.cu built as its own library and solved through steady.1D(dllname = ...): the result
+    must satisfy the reference's own acceptance test with the residual recomputed in numpy, and sit between the imposed
+    left value and the carrying capacity"""
+    import rootsolve_b200 as rs
+    from test_host_api import build_user_model
+    so = build_user_model(tmp_path)
+    N, (D, dx, r, K, yl) = 500, (1.0, 0.2, 0.5, 10.0, 1.0)
+    # started near the carrying capacity, where the reaction term keeps the Jacobian well conditioned: from y = K/2 its
+    # derivative vanishes, the first Jacobian is a bare 500-box Laplacian (condition number ~ 1e5) and the
+    # Jacobi-preconditioned Krylov solve stalls (RS_ESINGULAR) where the reference's direct LDU would not -- DESIGN.md 8
+    out = rs.steady_1D(np.full(N, 9.0), func="fisher1d", dllname=so, parms=[D, dx, r, K, yl], nspec=1, positive=True,
+                       method="stodes", **H.TOL)
+    y = out["y"]
+    assert out.attributes["steady"] and out.attributes["dims"]["ngp"] == 3
+    lo = np.concatenate([[yl], y[:-1]])
+    hi = np.concatenate([y[1:], y[-1:]])
+    f = D * (hi - 2.0 * y + lo) / (dx * dx) + r * y * (1.0 - y / K)
+    assert _accept(y, f) <= 1.0 + 1e-6
+    assert np.all(np.diff(y[:40]) > 0) and np.all(np.diff(y) > -1e-9) and y[0] > yl and abs(y[-1] - K) < 1e-6
+
+
 def test_spmethod_ilut_and_ilutp_reach_the_same_steady_state(built, oracle):
     """spmethod = "ilut"/"ilutp" with the reference's ILUT control list (R/stodes.R:314-329, 407-420): accepted and
     served by the same Krylov solve -- the steady state is the one `yale' and the oracle reach."""

@@ -58,6 +58,29 @@ def build_c_example(tmp_path):
     return exe
 
 
+def build_user_model(tmp_path):
+    """compiles integration/example_model.cu into a model library of its own, the way its header says"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    so = str(tmp_path / "libfisher.so")
+    subprocess.run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-fmad=false", "-shared", "-Xcompiler", "-fPIC",
+                    "-I", os.path.join(root, "include"), os.path.join(root, "integration", "example_model.cu"), "-o", so], check=True)
+    return so
+
+
+def test_user_model_library_builds_and_exports_its_descriptor(built, tmp_path):
+    """a model outside the bundled library (the GPU analogue of a user's DLL): builds from the SDK header alone and is
+    found through dllname, as getNativeSymbolInfo(func, PACKAGE = dllname) finds a DLL's function (R/stodes.R:212-220)"""
+    import shutil
+    from rootsolve_b200 import _capi
+    if shutil.which("nvcc") is None:
+        pytest.skip("no nvcc")
+    so = build_user_model(tmp_path)
+    assert _capi.model_symbol("fisher1d", so)
+    with pytest.raises(ValueError, match="dyn function not loaded"):
+        _capi.model_symbol("diff3d", so)
+
+
 def test_c_caller_links_and_fails_loudly_without_a_gpu(built, tmp_path):
     """a plain C program against the C ABI: links; and where there is no CUDA device it must stop with the library's
     'no CPU path' error, not compute anything"""
