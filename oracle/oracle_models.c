@@ -111,3 +111,38 @@ void diffmap(int *neq, double *t, double *y, double *ydot, double *yout, int *ip
     for (int c = 0; c < *neq; c++)
         ydot[c] = rsm_diffmap_point(y, c, RSM_DMAP_INV(ip), RSM_DMAP_PRES(ip), d1, d2, d3, p_dmap);
 }
+
+/* manufactured-solution variant of diff3d: sine tables in rpar (= yout + nout) */
+static double p_d3ms[RSM_D3MS_NPAR];
+void initdiff3dms(void (*steadyparms)(int *, double *)) { int N = RSM_D3MS_NPAR; steadyparms(&N, p_d3ms); }
+void diff3dms(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t;
+    const int d1 = ip[4], d2 = ip[5], d3 = ip[6];
+    const double *tab = yout + ip[0];
+    for (int j = 0; j < d1; j++)
+        for (int k = 0; k < d2; k++)
+            for (int l = 0; l < d3; l++)
+                ydot[(j * d2 + k) * d3 + l] = rsm_diff3dms_point(y, j, k, l, d1, d2, d3, p_d3ms, tab);
+}
+
+/* vignettes/rootSolve.Rnw:615-663, zero-flux 2-D diffusion with quadratic consumption and point sources */
+static double p_d2q[RSM_D2Q_NPAR];
+void initdiff2dq(void (*steadyparms)(int *, double *)) { int N = RSM_D2Q_NPAR; steadyparms(&N, p_d2q); }
+void diff2dq(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)yout;
+    const int d1 = ip[4], d2 = ip[5], nsrc = ip[7];
+    for (int j = 0; j < d1; j++)
+        for (int k = 0; k < d2; k++) ydot[j * d2 + k] = rsm_diff2dq_point(y, j, k, d1, d2, p_d2q, ip + 8, nsrc);
+}
+
+/* man/stodes.Rd:225-252, the 1000-layer sediment model with non-local exchange */
+static double p_sed[RSM_SED_NPAR];
+void initsediment(void (*steadyparms)(int *, double *)) { int N = RSM_SED_NPAR; steadyparms(&N, p_sed); }
+void sediment(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
+{
+    (void)neq; (void)t; (void)yout;
+    const int N = ip[4];
+    for (int i = 0; i < N; i++) ydot[i] = rsm_sediment_point(y, i, N, p_sed);
+}

@@ -594,13 +594,16 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
         double relres = 0.0;
         // Absolute floor of the linear residual: once its RMS is a small fraction of the smallest error
         // weight, the next residual test (max |f/ewt| <= 1) passes and further Krylov work is wasted.
+        bool lin_converged = false;
         RS_TRY(krylov_solve(c, s.kry, s.beta.p, s.x.p, s.kry.lin_ewt_factor * s.min_atol * std::sqrt((double)n), &kit,
-                            &relres));
+                            &relres, &lin_converged));
         s.krylov_iters += kit;
         // An inexact Newton step is fine; no step at all is not: a solve that barely reduced the residual
         // would otherwise look like convergence to test 2 (max|x| <= ctol).  The reference's direct solve
         // cannot fail this way -- it stops with "zero pivot" instead (src/sparse.f:2376).
-        if (!(relres <= 0.1)) {
+        // A solve that stopped on its own target is a step, whatever its relative residual: close to the absolute
+        // floor ||beta|| itself is within a small factor of the target.
+        if (!lin_converged && !(relres <= 0.1)) {
             set_error("sparse solver: the Krylov solve of Newton iteration %d stalled at relative residual %.3e after %d "
                       "iterations (matrix too ill-conditioned or indefinite for the chosen preconditioner)", it, relres, kit);
             return RS_ESINGULAR;

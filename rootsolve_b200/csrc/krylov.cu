@@ -1325,17 +1325,19 @@ static int launch_step_graph(Ctx &c, Krylov &k, double *x, bool cg, int nsteps)
 
 // PCG with the same cycle logic as the BiCGStab driver below: convergence is declared on the true residual only.
 // *fallback is set when CG is not applicable after all (indefinite matrix / breakdown): the caller then runs BiCGStab.
-static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres, bool *fallback)
+static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres, bool *fallback,
+                     bool *converged)
 {
     cudaStream_t st = c.stream;
     static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
     *fallback = false;
+    *converged = false;
     *iters = 0;
     *relres = 0.0;
     double bnorm = 0.0;
     RS_TRY(cg_start(c, k, b, x, false, S_BNORM, &bnorm));
     if (!(bnorm == bnorm) || std::isinf(bnorm)) { set_error("sparse solver: right-hand side is not finite"); return RS_ESINGULAR; }
-    if (!(bnorm > 0.0)) return RS_OK;
+    if (!(bnorm > 0.0)) { *converged = true; return RS_OK; }
     double target = k.lin_rtol * bnorm;
     if (abs_floor > target) target = abs_floor;
     double rtrue = bnorm, best = bnorm;
@@ -1404,6 +1406,7 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
     }
     RS_CUDA(cudaGetLastError());
     *relres = rtrue / bnorm;
+    *converged = done;
     return RS_OK;
 }
 
@@ -1412,14 +1415,18 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
 // the true residual is recomputed, becomes the new shadow residual, and the recurrence restarts
 // from the x reached so far.  Convergence is only ever declared on the true residual.
 // All ranks take the same decisions: every number they are based on has been all-reduced.
-int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres)
+int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres, bool *converged)
 {
+    bool conv_local = false;
+    if (!converged) converged = &conv_local;
+    *converged = false;
     cudaStream_t st = c.stream;
     static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
     if (k.use_cg) {
         bool fallback = false;
-        RS_TRY(pcg_solve(c, k, b, x, abs_floor, iters, relres, &fallback));
+        RS_TRY(pcg_solve(c, k, b, x, abs_floor, iters, relres, &fallback, converged));
         if (!fallback) return RS_OK;
+        *converged = false;
         k.use_cg = false;   // not a CG matrix after all: BiCGStab below, from x = 0
         if (k.scaled) RS_TRY(cg_scale_matrix(c, k, true));   // ... on the matrix as assembled
     }
@@ -1439,7 +1446,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     *iters = 0;
     *relres = 0.0;
     if (!(bnorm == bnorm) || std::isinf(bnorm)) { set_error("sparse solver: right-hand side is not finite"); return RS_ESINGULAR; }
-    if (!(bnorm > 0.0)) return RS_OK;  // b == 0 -> x = 0
+    if (!(bnorm > 0.0)) { *converged = true; return RS_OK; }  // b == 0 -> x = 0
     double target = k.lin_rtol * bnorm;
     if (abs_floor > target) target = abs_floor;
     double rtrue = bnorm;     // true residual at the start of the current cycle
@@ -1492,6 +1499,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     }
     RS_CUDA(cudaGetLastError());
     *relres = rtrue / bnorm;
+    *converged = done;
     if (!done && debug) fprintf(stderr, "[krylov] not converged: relres %.3e after %d its\n", *relres, total);
     return RS_OK;
 }

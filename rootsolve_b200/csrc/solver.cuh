@@ -122,8 +122,11 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
                  int precond, int nspec, int ncell, const rs_krylov_control *ctl, const Ranges *own,
                  const HaloPlan *halo, const GridDesc *grid = nullptr);
 int krylov_precond_update(Ctx &c, Krylov &k);
-// solves A x = b (x overwritten, starts from 0); abs_floor: absolute 2-norm stop
-int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres);
+// solves A x = b (x overwritten, starts from 0); abs_floor: absolute 2-norm stop.  *converged: the true residual
+// reached the solve's own target max(lin_rtol ||b||, abs_floor) -- which can leave relres above any fixed fraction
+// when ||b|| is already close to the floor
+int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres,
+                 bool *converged = nullptr);
 int spmv_launch(Ctx &c, int n, int nnz, const int *rowptr, const int *col, const double *val, const double *x,
                 double *y, int lanes);
 int pick_lanes(int n, int nnz);

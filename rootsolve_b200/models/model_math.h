@@ -264,4 +264,61 @@ RSM_HD double rsm_diffmap_point(const double *y, int c, const int *inv, const in
     return dY;
 }
 
+
+/* Manufactured-solution variant of diff3d (SURVEY 8(c) protocol step 3): the diffusion-consumption model of
+ * man/steady.3D.Rd plus a source  S = c0 + c1 * sj[j]*sk[k]*sl[l]  built from three 1-D tables of discrete sine
+ * modes, sq[i] = sin(pi (i+1)/(dq+1)).  The product of the tables is an eigenvector of the 7-point operator with
+ * imposed boundary value BND, so with c0 = r*BND and c1 = a*(lambda + r) the discrete steady state is
+ * y* = BND + a*sj*sk*sl in closed form, at every grid size.  The tables arrive in rpar (after the nout outputs in
+ * yout, src/steady_utils.c:109-124); p[0..7] as diff3d, p[8] = c0, p[9] = c1. */
+#define RSM_D3MS_NPAR 10
+RSM_HD double rsm_diff3dms_point(const double *y, int j, int k, int l, int d1, int d2, int d3, const double *p,
+                                 const double *tab)
+{
+    const double S = p[8] + p[9] * ((tab[j] * tab[d1 + k]) * tab[d1 + d2 + l]);
+    return rsm_diff3d_point(y, j, k, l, d1, d2, d3, p, 0) + S;
+}
+
+/* The 2-D example of the vignette (vignettes/rootSolve.Rnw:615-663, `diffusion2D`): diffusion with ZERO-FLUX
+ * boundaries, second-order consumption -r*C^2 and a constant production p in a handful of cells.  The only example
+ * of the stodes path with a published run time (0.5 s / 0.16 s).  Without an imposed boundary value the Jacobian is
+ * a bare Laplacian plus -2 r C on the diagonal.
+ * p[0]=Dx p[1]=Dy p[2]=dx p[3]=dy p[4]=r p[5]=p ; ip[3]=1 ip[4]=d1 ip[5]=d2 ip[6]=1 ip[7]=nsrc, then nsrc 0-based
+ * state-vector positions of the producing cells (the R code draws them with runif; the tests seed them). */
+#define RSM_D2Q_NPAR 6
+RSM_HD double rsm_diff2dq_point(const double *y, int j, int k, int d1, int d2, const double *p, const int *src, int nsrc)
+{
+    const double Dx = p[0], Dy = p[1], dx = p[2], dy = p[3], r = p[4], prod = p[5];
+    const int idx = j * d2 + k;
+    const double yc = y[idx];
+    double dY = -r * yc * yc;
+    for (int q = 0; q < nsrc; q++)
+        if (src[q] == idx) { dY = dY + prod; break; }
+    double flo = (k > 0) ? -Dx * (yc - y[idx - 1]) / dx : 0.0;
+    double fhi = (k < d2 - 1) ? -Dx * (y[idx + 1] - yc) / dx : 0.0;
+    dY = dY - (fhi - flo) / dx;
+    flo = (j > 0) ? -Dy * (yc - y[idx - d2]) / dy : 0.0;
+    fhi = (j < d1 - 1) ? -Dy * (y[idx + d2] - yc) / dy : 0.0;
+    dY = dY - (fhi - flo) / dy;
+    return dY;
+}
+
+/* The first example of man/stodes.Rd (:225-252): organic carbon in N sediment layers -- advection v, bioturbation
+ * Kz (Kz/dx^2 = 1e4 against a decay of 5: diffusion dominated), imposed flux on top, zero gradient below, and a
+ * NON-LOCAL exchange: a fraction of the top five layers is moved to layer N/2, which puts five entries far from the
+ * diagonal into row N/2.  Solved by the reference with the default sparsetype = "sparseint".
+ * p[0]=v p[1]=flux p[2]=dx p[3]=Kz p[4]=decay p[5]=ing ; ip[3]=1 ip[4]=N. */
+#define RSM_SED_NPAR 6
+RSM_HD double rsm_sediment_point(const double *y, int i, int N, const double *p)
+{
+    const double v = p[0], flux = p[1], dx = p[2], Kz = p[3], decay = p[4], ing = p[5];
+    /* Flux through the upper (i) and lower (i+1) interface of layer i */
+    const double up = (i > 0) ? v * y[i - 1] + -Kz * (y[i] - y[i - 1]) / dx : flux;
+    const double dn = (i < N - 1) ? v * y[i] + -Kz * (y[i + 1] - y[i]) / dx : v * y[i] + -Kz * (y[i] - y[i]) / dx;
+    double d = -(dn - up) / dx - decay * y[i];
+    if (i < 5) d = d - ing * y[i];
+    if (i == N / 2 - 1) d = d + ing * ((((y[0] + y[1]) + y[2]) + y[3]) + y[4]);
+    return d;
+}
+
 #endif /* RSM_MODEL_MATH_H */

@@ -54,3 +54,46 @@ def within_tol(y, yref, atol=1e-10, rtol=1e-10, factor=1.0):
     err = np.abs(np.asarray(y) - np.asarray(yref))
     bound = factor * (atol + rtol * np.abs(yref))
     return bool(np.all(err <= bound)), float(np.max(err / bound))
+
+
+def ms_setup(d, a=3.0, r=0.025, D=1.0, h=1.0, bnd=1.0):
+    """Manufactured solution of the bundled `diff3dms` model (model_math.h): parameters, the rpar sine tables and
+    the closed-form discrete steady state y* = bnd + a * sj x sk x sl on the grid d = (d1, d2, d3)."""
+    tabs = [np.sin(np.pi * (np.arange(q) + 1) / (q + 1)) for q in d]
+    lam = sum(D / h ** 2 * 2.0 * (1.0 - np.cos(np.pi / (q + 1))) for q in d)
+    parms = [D, D, D, h, h, h, r, bnd, r * bnd, a * (lam + r)]
+    ystar = bnd + a * np.einsum("j,k,l->jkl", *tabs).ravel()
+    return parms, np.concatenate(tabs), ystar
+
+
+# vignettes/rootSolve.Rnw:635-643: Dx Dy dx dy r p ; the ten producing cells are drawn by runif in the vignette,
+# here from default_rng(20260101) (SURVEY 8(d): seeds)
+P_DIFF2DQ = [1.5, 1.5, 1.0, 1.0, 0.01, 20.0]
+
+
+def diff2dq_ipar(n, nsrc=10, seed=20260101):
+    rng = np.random.default_rng(seed)
+    cells = np.unique(np.stack([rng.integers(0, n, nsrc), rng.integers(0, n, nsrc)], 1), axis=0)
+    src = (cells[:, 1] * n + cells[:, 0]).astype(np.int32)
+    return [1, n, n, 1, len(src)] + [int(v) for v in src]
+
+
+# man/stodes.Rd:243-251: v flux dx Kz decay ing
+P_SEDIMENT = [0.1, 10.0, 0.01, 1.0, 5.0, 20.0]
+
+
+def host_residual(oracle, model, parms, ipar, y, rpar=None):
+    """f(y) evaluated by the oracle's host model (independent of every CUDA kernel)"""
+    func = C.cast(oracle.model(model, parms), oracle.DERIV)
+    n = len(y)
+    f = np.zeros(n)
+    ipfull = np.concatenate([[0, 0 if rpar is None else len(rpar), 3 + len(ipar)], ipar]).astype(np.int32)
+    out = np.zeros(1) if rpar is None else np.ascontiguousarray(rpar, dtype=np.float64)
+    neq, t = C.c_int(n), C.c_double(0.0)
+    func(C.byref(neq), C.byref(t), dp(np.ascontiguousarray(y)), dp(f), dp(out), ip(ipfull))
+    return f
+
+
+def accept(y, f, atol=1e-10, rtol=1e-10):
+    """the reference's own acceptance test (src/sparse.f:126-129): max |f / ewt| with ewt = rtol|y| + atol"""
+    return float(np.max(np.abs(f) / (rtol * np.abs(y) + atol)))

@@ -493,11 +493,10 @@ def test_user_model_library_on_gpu(built, tmp_path):
     from test_host_api import build_user_model
     so = build_user_model(tmp_path)
     N, (D, dx, r, K, yl) = 500, (1.0, 0.2, 0.5, 10.0, 1.0)
-    # started near the carrying capacity, where the reaction term keeps the Jacobian well conditioned: from y = K/2 its
-    # derivative vanishes, the first Jacobian is a bare 500-box Laplacian (condition number ~ 1e5) and the
-    # Jacobi-preconditioned Krylov solve stalled (RS_ESINGULAR) where the reference's direct LDU would not; the CG
-    # plateau rule has been changed since, that start has not been re-run on a GPU yet -- DESIGN.md 8
-    out = rs.steady_1D(np.full(N, 9.0), func="fisher1d", dllname=so, parms=[D, dx, r, K, yl], nspec=1, positive=True,
+    # started at y = K/2, where the derivative of the reaction term vanishes: the first Jacobian is a bare 500-box
+    # Laplacian (condition number ~ 1e5), the case that ended in RS_ESINGULAR under the Jacobi-preconditioned Krylov
+    # solve of round 1 and that the reference's direct LDU solves without thought
+    out = rs.steady_1D(np.full(N, K / 2), func="fisher1d", dllname=so, parms=[D, dx, r, K, yl], nspec=1, positive=True,
                        method="stodes", **H.TOL)
     y = out["y"]
     assert out.attributes["steady"] and out.attributes["dims"]["ngp"] == 3
@@ -695,7 +694,7 @@ def test_config_c2_full_size(built, oracle):
     n = ns * nb
     assert A["steady"] and A["dims"]["nnz"] == n * (2 + ns) - 2 * ns and A["dims"]["ngp"] == 3 * ns
     f = _host_residual(oracle, "rt1d", H.P_RT1D, ipar, out["y"])
-    assert _accept(out["y"], f) <= 1.0 or np.abs(f).max() <= 1e-8
+    assert _accept(out["y"], f) <= 1.0
     assert out["y"].min() >= 0 and out["y"].max() <= 1.0 + 1e-9
     # far downstream the column no longer changes: the last boxes of every species agree with their neighbours
     Y = out["y"].reshape(ns, nb)
@@ -717,7 +716,7 @@ def test_config_c4_full_size(built, oracle):
     assert A["steady"] and A["dims"]["nnz"] == n * (6 + 2) - 2 * 2 * 3 * d * d
     assert 16 <= A["dims"]["ngp"] <= 24
     f = _host_residual(oracle, "rd3d", H.P_RD3D, ipar, out["y"])
-    assert _accept(out["y"], f) <= 1.0 or np.abs(f).max() <= 1e-8
+    assert _accept(out["y"], f) <= 1.0
     assert out["y"].min() >= 0
     U = out["y"][:nc].reshape(d, d, d)
     assert np.allclose(U, U[::-1], rtol=0, atol=1e-7) and np.allclose(U, U.transpose(1, 0, 2), rtol=0, atol=1e-7)
@@ -733,7 +732,7 @@ def test_config_c3_full_size(built, oracle):
     A = out.attributes
     assert A["steady"] and A["dims"]["nnz"] == d * d * 5 - 4 * d and A["dims"]["ngp"] == 7
     f = _host_residual(oracle, "diff2d", H.P_DIFF2D_MONOD, ipar, out["y"])
-    assert _accept(out["y"], f) <= 1.0 or np.abs(f).max() <= 1e-8
+    assert _accept(out["y"], f) <= 1.0
     Y = out["y"].reshape(d, d)
     assert np.allclose(Y, Y[::-1, :], rtol=0, atol=1e-8) and np.allclose(Y, Y.T, rtol=0, atol=1e-8)
 
@@ -761,7 +760,7 @@ def test_full_size_properties(built):
     _capi.check(built.rs_residual(_capi.model_symbol("diff2d"), H.dp(p), len(p), N, 0.0, H.dp(y), None, 0, H.ip(ip),
                                   len(ip), H.dp(f)))
     ewt = 1e-10 * np.abs(y) + 1e-10
-    assert np.max(np.abs(f) / ewt) <= 1.0 or A["precis"][-1] / N <= 1e-9
+    assert np.max(np.abs(f) / ewt) <= 1.0
     Y = y.reshape(n, n)
     assert np.allclose(Y, Y[::-1, :], rtol=0, atol=1e-8) and np.allclose(Y, Y.T, rtol=0, atol=1e-8)
     assert y.min() >= 0 and y.max() < 1.0 + 1e-9   # positive=TRUE clamps at exactly 0 deep inside the grid

@@ -50,6 +50,9 @@ def test_noalloc_matches_existing_entry_point_twice_in_a_row(built):
         want = _reference(built, beta, ewt)
         assert abs(got[0] - want[0]) <= 1e-13 * abs(want[0])
         assert got[1] == want[1]
+        # and, independently of the library's other entry point, against numpy
+        assert abs(got[0] - np.abs(beta).sum()) <= 1e-13 * np.abs(beta).sum()
+        assert got[1] == np.max(np.abs(beta / ewt))
 
 
 def test_noalloc_rejects_sizes_beyond_the_static_scratch(built):
