@@ -57,7 +57,14 @@ enum { RS_TYPE_USER = 0, RS_TYPE_DETECT = 1, RS_TYPE_1D = 2, RS_TYPE_2D = 3, RS_
  * served by the preconditioned Krylov solver below (the reference's ilut/ilutp apply an
  * incomplete LU once per Newton step, src/sparsekit.f:141-166: same tests, same steady
  * state, more Newton steps); the ILUT options of `control' have nothing to act on. */
-enum { RS_PRECOND_NONE = 0, RS_PRECOND_JACOBI = 1, RS_PRECOND_BLOCK_JACOBI = 2, RS_PRECOND_AUTO = -1 };
+enum { RS_PRECOND_NONE = 0, RS_PRECOND_JACOBI = 1, RS_PRECOND_BLOCK_JACOBI = 2,
+       /* aggregation multigrid V-cycle on the 2-D / 3-D grid (slab-local when sharded): what makes the step count of
+        * the solve independent of the grid size, the role of the exact factors of nsfc/nnfc (src/sparse.f:1937-2447) */
+       RS_PRECOND_MG = 3,
+       /* exact solve of the (block-)tridiagonal part by cyclic reduction: 1-D grids (blocks of nspec x nspec) and
+        * general structures whose weight sits next to the diagonal */
+       RS_PRECOND_BTD = 4,
+       RS_PRECOND_AUTO = -1 };
 
 struct rs_model_desc;  /* device residual plug-in, see rootsolve_b200_model.cuh */
 
@@ -65,7 +72,8 @@ struct rs_model_desc;  /* device residual plug-in, see rootsolve_b200_model.cuh 
  * (R/stodes.R:407-420 holds the ILUT knobs of the reference).  Zero / negative
  * fields take the defaults in parentheses. */
 typedef struct {
-    int precond;            /* RS_PRECOND_* (AUTO: block-Jacobi on multi-species grids, else Jacobi) */
+    int precond;            /* RS_PRECOND_* (AUTO: multigrid on 2-D/3-D grids, block-tridiagonal on 1-D grids and banded
+                             * general structures, else block-Jacobi on multi-species grids, else Jacobi) */
     int max_krylov;         /* per Newton step (10000) */
     double lin_rtol;        /* ||J x - beta||_2 <= lin_rtol * ||beta||_2 (1e-8: the accuracy of the FD Jacobian) */
     double lin_ewt_factor;  /* ... or rms(J x - beta) <= lin_ewt_factor * min(atol) (5e-4): far below the error
@@ -122,6 +130,9 @@ typedef struct {
     double t_newton_s;      /* Newton loop */
     int spmv_kernel;        /* SpMV the Krylov solver ran: 0 sub-warp CSR, 1 TMA-staged CSR, 2 TMA-staged with
                              * implicit columns (non-cyclic grid, <= 2 species) */
+    int precond;            /* preconditioner the last linear solve ran under (RS_PRECOND_*); a handle that had to
+                             * drop the multigrid cycle reports the (block-)Jacobi it fell back to */
+    int krylov_method;      /* 0 BiCGStab, 1 CG (Jacobian symmetric to finite-difference noise) */
 } rs_stsparse_result;
 
 /* The path: replaces call_stsparse -> dsparse (src/call_stsparse.c:60-320, src/sparse.f:30-195). */
@@ -181,6 +192,13 @@ int rs_residual(const struct rs_model_desc *func, const double *initpar, int nin
  * columns as (ian, jan, a).  Returns Krylov iterations in *iters, final relative residual in *relres. */
 int rs_linsolve(int neq, const int *ian, const int *jan, const double *a, const double *b, int transposed,
                 int nspec_block, const rs_krylov_control *control, double *x, int *iters, double *relres);
+
+/* The same solve for a matrix that lives on a 1-D / 2-D / 3-D grid (the structures of sparse1d/2d/3d,
+ * src/sparsecoeff.f:5-312), so that the grid preconditioners -- multigrid, block-tridiagonal -- can be exercised
+ * on their own.  grid = { RS_TYPE_1D/2D/3D, nspec, d1, d2, d3, cyc1, cyc2, cyc3 } with unused extents 1 (d1 slowest,
+ * as in the nnz vector of stodes).  *used = { preconditioner (RS_PRECOND_*), method (0 BiCGStab, 1 CG) } the solve ran. */
+int rs_linsolve_grid(int neq, const int *ian, const int *jan, const double *a, const double *b, const int *grid,
+                     const rs_krylov_control *control, double *x, int *iters, double *relres, int *used);
 
 /* y = J x with J given by columns as (ian, jan, a) -- the SpMV kernel on its own. */
 int rs_spmv(int neq, const int *ian, const int *jan, const double *a, const double *x, double *y);

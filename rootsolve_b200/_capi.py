@@ -15,7 +15,7 @@ LIB_MODELS = os.path.join(HERE, "librs_models.so")
 RS_OK = 0
 RS_TYPE_USER, RS_TYPE_1D, RS_TYPE_2D, RS_TYPE_3D = 0, 2, 3, 4
 RS_TYPE_2DMAP, RS_TYPE_3DMAP = 30, 40
-RS_PRECOND_NONE, RS_PRECOND_JACOBI, RS_PRECOND_BLOCK_JACOBI, RS_PRECOND_AUTO = 0, 1, 2, -1
+RS_PRECOND_NONE, RS_PRECOND_JACOBI, RS_PRECOND_BLOCK_JACOBI, RS_PRECOND_MG, RS_PRECOND_BTD, RS_PRECOND_AUTO = 0, 1, 2, 3, 4, -1
 ERROR_NAMES = {-1: "RS_EINVAL", -2: "RS_ENODEVICE", -3: "RS_ENOMEM", -4: "RS_ESTRUCT", -5: "RS_EGROUP",
                -6: "RS_EDUPLICATE", -7: "RS_ESINGULAR", -8: "RS_EMODEL", -9: "RS_ECOMM", -10: "RS_ETOOBIG"}
 
@@ -55,6 +55,7 @@ class StsparseResult(C.Structure):
         ("ian", c_int_p), ("jan", c_int_p), ("igp", c_int_p), ("jgp", c_int_p),
         ("krylov_iters", C.c_int), ("kernel_launches", C.c_int),
         ("t_setup_s", C.c_double), ("t_newton_s", C.c_double), ("spmv_kernel", C.c_int),
+        ("precond", C.c_int), ("krylov_method", C.c_int),
     ]
 
 
@@ -101,6 +102,8 @@ def lib():
                                   c_int_p, C.c_int, c_double_p]
         L.rs_linsolve.argtypes = [C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, C.c_int, C.c_int,
                                   C.POINTER(KrylovControl), c_double_p, c_int_p, c_double_p]
+        L.rs_linsolve_grid.argtypes = [C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, c_int_p,
+                                       C.POINTER(KrylovControl), c_double_p, c_int_p, c_double_p, c_int_p]
         L.rs_spmv.argtypes = [C.c_int, c_int_p, c_int_p, c_double_p, c_double_p, c_double_p]
         L.rs_errset.argtypes = [C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p]
         L.rs_convergence_test.argtypes = [C.c_int, c_double_p, c_double_p, c_double_p]

@@ -662,6 +662,8 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
         meta->t_setup_s = s.t_setup;
         meta->t_newton_s = s.t_newton;
         meta->spmv_kernel = s.kry.gridcols ? 2 : s.kry.tma_ok ? 1 : 0;
+        meta->precond = s.kry.mg_on ? RS_PRECOND_MG : s.kry.precond;
+        meta->krylov_method = s.kry.use_cg ? 1 : 0;
         if (meta->precis) for (int q = 0; q < s.niter && q < s.maxiter; q++) meta->precis[q] = s.precis[q];
     }
     return RS_OK;
@@ -971,6 +973,41 @@ extern "C" int rs_linsolve(int neq, const int *ian, const int *jan, const double
     RS_CUDA(cudaStreamSynchronize(c.stream));
     if (iters) *iters = it;
     if (relres) *relres = rr;
+    return RS_OK;
+}
+
+extern "C" int rs_linsolve_grid(int neq, const int *ian, const int *jan, const double *a, const double *b, const int *grid,
+                                const rs_krylov_control *control, double *x, int *iters, double *relres, int *used)
+{
+    if (!ian || !jan || !a || !b || !x || !grid) { set_error("null argument"); return RS_EINVAL; }
+    RS_TRY(ensure_device());
+    Ctx c;
+    const int nnz = ian[neq] - 1;
+    GridDesc g;
+    g.type = grid[0]; g.nspec = grid[1];
+    const int nd = g.type == RS_TYPE_1D ? 1 : g.type == RS_TYPE_2D ? 2 : g.type == RS_TYPE_3D ? 3 : 0;
+    if (!nd) { set_error("grid[0] must be RS_TYPE_1D, 2D or 3D"); return RS_EINVAL; }
+    long long cells = 1;
+    for (int q = 0; q < nd; q++) { g.d[q] = grid[2 + q]; g.cyc[q] = grid[5 + q]; cells *= g.d[q]; }
+    g.ncell = (int)cells;
+    if ((long long)g.nspec * cells != neq) { set_error("grid does not match neq"); return RS_EINVAL; }
+    DevBuf<int> rowptr, col;
+    DevBuf<double> val, d_b, d_x;
+    RS_TRY(csr_from_columns(c, neq, nnz, ian, jan, a, 0, rowptr, col, val));
+    RS_TRY(d_b.alloc(neq)); RS_TRY(d_x.alloc(neq));
+    RS_TRY(d_b.upload(b, neq, c.stream));
+    Krylov k;
+    RS_TRY(krylov_setup(c, k, neq, nnz, rowptr.p, col.p, val.p, control ? control->precond : RS_PRECOND_AUTO, g.nspec, g.ncell,
+                        control, nullptr, nullptr, &g));
+    RS_TRY(krylov_precond_update(c, k));
+    int it = 0;
+    double rr = 0.0;
+    RS_TRY(krylov_solve(c, k, d_b.p, d_x.p, 0.0, &it, &rr));
+    RS_TRY(d_x.download(x, neq, c.stream));
+    RS_CUDA(cudaStreamSynchronize(c.stream));
+    if (iters) *iters = it;
+    if (relres) *relres = rr;
+    if (used) { used[0] = k.mg_on ? RS_PRECOND_MG : k.precond; used[1] = k.use_cg ? 1 : 0; }
     return RS_OK;
 }
 

@@ -44,6 +44,7 @@ Krylov::~Krylov()
 {
     if (h_scal) cudaFreeHost(h_scal);
     for (int w = 0; w < 2; w++) if (g_exec[w]) cudaGraphExecDestroy(g_exec[w]);
+    if (mg) mg_destroy(mg);
 }
 
 int pick_lanes(int n, int nnz)
@@ -732,6 +733,11 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
     if (halo) k.halo = *halo; else k.halo = HaloPlan();
     k.cell0 = 0; k.cell1 = ncell;
     if (halo && halo->nspec > 0) { k.cell0 = halo->j0 * halo->plane; k.cell1 = halo->j1 * halo->plane; }
+    // multigrid on 2-D / 3-D grids (asked for, or AUTO); the (block-)Jacobi preconditioner below stays the base: the
+    // fallback should a solve with the cycle fail, and what every other structure uses
+    const bool want_mg = (precond == RS_PRECOND_MG || precond == RS_PRECOND_AUTO) && grid && !getenv("RS_NO_MG") &&
+                         mg_applicable(*grid, k.halo.nspec > 0 ? k.halo.j0 : 0, k.halo.nspec > 0 ? k.halo.j1 : 0);
+    if (precond == RS_PRECOND_MG || precond == RS_PRECOND_BTD) precond = RS_PRECOND_AUTO;
     if (precond == RS_PRECOND_AUTO) precond = (nspec > 1 && nspec <= MAXS && ncell > 0) ? RS_PRECOND_BLOCK_JACOBI : RS_PRECOND_JACOBI;
     if (precond == RS_PRECOND_BLOCK_JACOBI && !(nspec > 1 && nspec <= MAXS && ncell > 0 && (long long)nspec * ncell == n))
         precond = RS_PRECOND_JACOBI;
@@ -829,6 +835,12 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
     }
     if (precond == RS_PRECOND_JACOBI) RS_TRY(k.dinv.alloc(n));
     if (precond == RS_PRECOND_BLOCK_JACOBI) RS_TRY(k.binv.alloc((size_t)nspec * nspec * ncell));
+    if (want_mg) {
+        if (k.mg) { mg_destroy(k.mg); k.mg = nullptr; }
+        RS_TRY(mg_setup(c, &k.mg, *grid, k.halo.nspec > 0 ? k.halo.j0 : 0, k.halo.nspec > 0 ? k.halo.j1 : 0));
+        RS_TRY(k.z.alloc(n));
+        if (comm_active()) RS_TRY(k.z.zero(c.stream));
+    }
     RS_TRY(k.partials.alloc(4 * 148 * 16));
     RS_TRY(k.scal.alloc(NSCAL));
     RS_TRY(k.ticket.alloc(4));
@@ -938,6 +950,10 @@ int krylov_precond_update(Ctx &c, Krylov &k)
             block_setup_kernel<<<(cells + 127) / 128, 128, 0, c.stream>>>(k.nspec, k.ncell, k.cell0, k.cell1, k.rowptr, k.col, k.val, k.binv.p);
         }
     }
+    // the hierarchy is rebuilt from the values the solve will use (the scaled ones when CG runs on sigma S A S)
+    k.mg_on = k.mg != nullptr && !k.mg_failed;
+    if (k.mg_on && k.use_cg && !k.scaled) k.use_cg = false;   // the CG kernels take z = M^-1 r only on the scaled system
+    if (k.mg_on) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));
     RS_CUDA(cudaGetLastError());
     return RS_OK;
 }
@@ -945,10 +961,10 @@ int krylov_precond_update(Ctx &c, Krylov &k)
 static inline double own_nnz_estimate(const Krylov &k) { return (double)k.nnz * (double)k.own.total() / (double)k.n; }
 
 // descriptor for pushing the first / last owned plane of vector `vi` (0: ph, 1: sh) to the slab neighbours
-static HaloPush make_push(const Krylov &k, int vi, const HaloSignal &sig, bool last_launch)
+static HaloPush make_push(const Krylov &k, int vi, const HaloSignal &sig, bool last_launch, bool enabled = true)
 {
     HaloPush hp;
-    if (!k.push_ok) return hp;
+    if (!k.push_ok || !enabled) return hp;
     hp.lo = (double *)k.nb_lo[vi];
     hp.hi = (double *)k.nb_hi[vi];
     hp.plane = k.halo.plane;
@@ -963,28 +979,33 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     cudaStream_t st = c.stream;
     double *slot = k.scal.p + SLOT * cur;
     const double rows = (double)k.own.total();
-    const double pre_bytes = (k.precond == RS_PRECOND_BLOCK_JACOBI) ? 8.0 * k.nspec * rows : (k.precond == RS_PRECOND_JACOBI ? 8.0 * rows : 0.0);
+    // with the multigrid cycle the vector kernels apply no preconditioner themselves (ph = M^-1 p follows them), and
+    // the halo planes of ph / sh can only travel once the cycle has produced them: no push from the update kernels
+    const int pre = k.mg_on ? RS_PRECOND_NONE : k.precond;
+    const bool push = k.push_ok && !k.mg_on;
+    const double pre_bytes = (pre == RS_PRECOND_BLOCK_JACOBI) ? 8.0 * k.nspec * rows : (pre == RS_PRECOND_JACOBI ? 8.0 * rows : 0.0);
     // halo handshakes of this step (sequence numbers advance identically on every rank)
-    const HaloSignal sig_p = k.push_ok ? comm_next_halo_signal() : HaloSignal();
-    const HaloSignal sig_s = k.push_ok ? comm_next_halo_signal() : HaloSignal();
+    const HaloSignal sig_p = push ? comm_next_halo_signal() : HaloSignal();
+    const HaloSignal sig_s = push ? comm_next_halo_signal() : HaloSignal();
     {
         Launch L(c, K_VEC, (first ? 24.0 : 40.0) * rows + pre_bytes);
-        if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
+        if (pre == RS_PRECOND_BLOCK_JACOBI) {
             update_p_kernel<2><<<grid_for(k.cell1 - k.cell0, 256), 256, 0, st>>>(k.cell0, k.cell1, k.nspec, k.ncell, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph_v, nullptr, k.binv.p,
-                                                                                 make_push(k, 0, sig_p, true), k.ticket.p + 1);
+                                                                                 make_push(k, 0, sig_p, true, push), k.ticket.p + 1);
         } else {
             for (int q = 0; q < k.own.n; q++) {
                 const int b = k.own.b[q], e = k.own.e[q];
-                if (k.precond == RS_PRECOND_JACOBI)
+                if (pre == RS_PRECOND_JACOBI)
                     update_p_kernel<1><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph_v, k.dinv.p, nullptr,
-                                                                                   make_push(k, 0, sig_p, q == k.own.n - 1), k.ticket.p + 1);
+                                                                                   make_push(k, 0, sig_p, q == k.own.n - 1, push), k.ticket.p + 1);
                 else
                     update_p_kernel<0><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, first, k.scal.p, cur, k.r.p, k.v.p, k.p.p, k.ph_v, nullptr, nullptr,
-                                                                                   make_push(k, 0, sig_p, q == k.own.n - 1), k.ticket.p + 1);
+                                                                                   make_push(k, 0, sig_p, q == k.own.n - 1, push), k.ticket.p + 1);
             }
         }
     }
-    if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.ph_v, k.halo));
+    if (k.mg_on) RS_TRY(mg_apply(c, *k.mg, k.p.p, k.ph_v, nullptr, nullptr, nullptr, PeerRed()));
+    if (!push) RS_TRY(comm_halo_exchange(c, k.ph_v, k.halo));
     {
         Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)) + 8.0 * rows);
         spmv_run<1>(k, st, k.ph_v, k.v.p, k.r0.p, slot + S_R0V, comm_next_peer_red(), sig_p);
@@ -992,22 +1013,23 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + S_R0V, 1));
     {
         Launch L(c, K_VEC, 32.0 * rows + pre_bytes);
-        if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
+        if (pre == RS_PRECOND_BLOCK_JACOBI) {
             update_s_kernel<2><<<grid_for(k.cell1 - k.cell0, 256), 256, 0, st>>>(k.cell0, k.cell1, k.nspec, k.ncell, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh_v, nullptr, k.binv.p,
-                                                                                 make_push(k, 1, sig_s, true), k.ticket.p + 1);
+                                                                                 make_push(k, 1, sig_s, true, push), k.ticket.p + 1);
         } else {
             for (int q = 0; q < k.own.n; q++) {
                 const int b = k.own.b[q], e = k.own.e[q];
-                if (k.precond == RS_PRECOND_JACOBI)
+                if (pre == RS_PRECOND_JACOBI)
                     update_s_kernel<1><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh_v, k.dinv.p, nullptr,
-                                                                                   make_push(k, 1, sig_s, q == k.own.n - 1), k.ticket.p + 1);
+                                                                                   make_push(k, 1, sig_s, q == k.own.n - 1, push), k.ticket.p + 1);
                 else
                     update_s_kernel<0><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, 1, 0, k.scal.p, cur, k.r.p, k.v.p, k.s.p, k.sh_v, nullptr, nullptr,
-                                                                                   make_push(k, 1, sig_s, q == k.own.n - 1), k.ticket.p + 1);
+                                                                                   make_push(k, 1, sig_s, q == k.own.n - 1, push), k.ticket.p + 1);
             }
         }
     }
-    if (!k.push_ok) RS_TRY(comm_halo_exchange(c, k.sh_v, k.halo));
+    if (k.mg_on) RS_TRY(mg_apply(c, *k.mg, k.s.p, k.sh_v, nullptr, nullptr, nullptr, PeerRed()));
+    if (!push) RS_TRY(comm_halo_exchange(c, k.sh_v, k.halo));
     {
         Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)) + 8.0 * rows);
         spmv_run<2>(k, st, k.sh_v, k.t.p, k.s.p, slot + S_TS, comm_next_peer_red(), sig_s);
@@ -1228,6 +1250,10 @@ static int cg_start(Ctx &c, Krylov &k, const double *b, double *x, bool restart,
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, k.scal.p + 6, 2));
     cg_seed_kernel<<<1, 1, 0, st>>>(k.scal.p, dst_rr);
     c.launches++;
+    if (k.mg_on) {   // preconditioned recurrence: z = M^-1 r, rho_0 = <r, z>
+        RS_TRY(mg_apply(c, *k.mg, k.r.p, k.z.p, k.partials.p, k.ticket.p, k.scal.p + SLOT * 1 + C_RZ, comm_next_peer_red()));
+        if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, k.scal.p + SLOT * 1 + C_RZ, 1));
+    }
     RS_CUDA(cudaMemcpyAsync(k.h_scal + 6, k.scal.p + 6, 2 * sizeof(double), cudaMemcpyDeviceToHost, st));
     RS_CUDA(cudaStreamSynchronize(st));
     *rnorm = std::sqrt(k.h_scal[6]);
@@ -1248,7 +1274,7 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
         for (int q = 0; q < k.own.n; q++) {
             const int b = k.own.b[q], e = k.own.e[q];
             if (k.scaled)
-                cg_update_p_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, nullptr, k.ph_v, x,
+                cg_update_p_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.mg_on ? k.z.p : k.r.p, nullptr, k.ph_v, x,
                                                                                      make_push(k, 0, sig, q == k.own.n - 1), k.ticket.p + 1);
             else
                 cg_update_p_kernel<false><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.r.p, k.dinv.p, k.ph_v, x,
@@ -1278,6 +1304,10 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
         }
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_RR, 2));
+    if (k.mg_on) {   // z = M^-1 r and the rho of the next step, <r, z>, over the <r, r> the kernel above left there
+        RS_TRY(mg_apply(c, *k.mg, k.r.p, k.z.p, k.partials.p, k.ticket.p, slot + C_RZ, comm_next_peer_red()));
+        if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_RZ, 1));
+    }
     return RS_OK;
 }
 
@@ -1293,6 +1323,9 @@ static int graph_steps_per_launch(const Ctx &c, const Krylov &k)
 {
     static const bool no_graph = getenv("RS_NO_GRAPH") != nullptr;
     if (no_graph || c.profile) return 0;
+    // with the multigrid cycle a step is ~40 launches and the solve ~10 steps: on large grids launch latency is
+    // nothing and a graph would only add a possibly wasted step; small grids replay two steps per host call
+    if (k.mg_on) return k.own.total() > 500000 ? 0 : 2;
     int g = k.check_every & ~1;
     return g >= 2 ? g : 2;
 }
@@ -1301,8 +1334,9 @@ static int launch_step_graph(Ctx &c, Krylov &k, double *x, bool cg, int nsteps)
 {
     const int w = cg ? 1 : 0;
     cudaStream_t st = c.stream;
-    if (!k.g_exec[w] || k.g_x[w] != x || k.g_n[w] != nsteps || k.g_scaled[w] != k.scaled) {
+    if (!k.g_exec[w] || k.g_x[w] != x || k.g_n[w] != nsteps || k.g_scaled[w] != k.scaled || k.g_mg[w] != k.mg_on) {
         k.g_scaled[w] = k.scaled;
+        k.g_mg[w] = k.mg_on;
         if (k.g_exec[w]) { cudaGraphExecDestroy(k.g_exec[w]); k.g_exec[w] = nullptr; }
         cudaGraph_t g = nullptr;
         const long long l0 = c.launches;
@@ -1344,6 +1378,7 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
     int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
     bool done = false;
     const int gsteps = graph_steps_per_launch(c, k);
+    const int check_every = k.mg_on ? 1 : k.check_every;   // a multigrid step is worth a look: the solve has ~10 of them
     while (!done && total < k.max_iter) {
         int cur = cycle_it & 1;
         bool looked = false;
@@ -1357,7 +1392,7 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
             total++; cycle_it++;
         }
         *iters = total;
-        if (!looked && total % k.check_every != 0 && total != k.max_iter) continue;
+        if (!looked && total % check_every != 0 && total != k.max_iter) continue;
         double *slot = k.scal.p + SLOT * cur;
         RS_CUDA(cudaMemcpyAsync(k.h_scal + SLOT * cur, slot, sizeof(double) * 6, cudaMemcpyDeviceToHost, st));
         RS_CUDA(cudaStreamSynchronize(st));
@@ -1380,7 +1415,7 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
         // (scratch check in DESIGN.md 8).  So a plateau only counts as stagnation once it is as long as the problem
         // itself (finite termination); the iteration budget bounds everything else.
         const long long plateau = std::max<long long>(40, std::min<long long>(k.n, k.max_iter));
-        const bool stagnated = (long long)since_best * k.check_every >= plateau;
+        const bool stagnated = (long long)since_best * check_every >= plateau;
         if (!(looks_converged || stagnated || total >= k.max_iter)) continue;
         {   // the solution update of the last step is still pending (it rides on the next step's direction update)
             Launch L(c, K_VEC, 24.0 * (double)k.own.total());
@@ -1415,10 +1450,8 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
 // the true residual is recomputed, becomes the new shadow residual, and the recurrence restarts
 // from the x reached so far.  Convergence is only ever declared on the true residual.
 // All ranks take the same decisions: every number they are based on has been all-reduced.
-int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres, bool *converged)
+static int krylov_solve_inner(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres, bool *converged)
 {
-    bool conv_local = false;
-    if (!converged) converged = &conv_local;
     *converged = false;
     cudaStream_t st = c.stream;
     static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
@@ -1428,7 +1461,10 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
         if (!fallback) return RS_OK;
         *converged = false;
         k.use_cg = false;   // not a CG matrix after all: BiCGStab below, from x = 0
-        if (k.scaled) RS_TRY(cg_scale_matrix(c, k, true));   // ... on the matrix as assembled
+        if (k.scaled) {
+            RS_TRY(cg_scale_matrix(c, k, true));   // ... on the matrix as assembled
+            if (k.mg_on) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));   // and so is the hierarchy
+        }
     }
     {
         Launch L(c, K_VEC, 32.0 * (double)k.own.total());
@@ -1454,6 +1490,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
     bool done = false;
     const int gsteps = graph_steps_per_launch(c, k);
+    const int check_every = k.mg_on ? 1 : k.check_every;   // a multigrid step is worth a look: the solve has ~10 of them
     while (!done && total < k.max_iter) {
         int cur = cycle_it & 1;
         bool looked = false;
@@ -1467,7 +1504,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
             total++; cycle_it++;
         }
         *iters = total;
-        if (!looked && total % k.check_every != 0 && total != k.max_iter) continue;
+        if (!looked && total % check_every != 0 && total != k.max_iter) continue;
         double *slot = k.scal.p + SLOT * cur;
         RS_CUDA(cudaMemcpyAsync(k.h_scal + SLOT * cur, slot, sizeof(double) * SLOT, cudaMemcpyDeviceToHost, st));
         RS_CUDA(cudaStreamSynchronize(st));
@@ -1481,7 +1518,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
         const double rnorm = finite ? std::sqrt(rr) : best;
         if (finite && rnorm < 0.9 * best) { best = rnorm; since_best = 0; } else since_best++;
         const bool looks_converged = finite && !broke && rnorm <= target;
-        const bool stagnated = since_best * k.check_every >= 40;   // ~40 steps without a 10 % gain
+        const bool stagnated = since_best * check_every >= 40;   // ~40 steps without a 10 % gain
         if (!(looks_converged || broke || stagnated || total >= k.max_iter)) continue;
         // end of cycle: what did it really achieve?
         double rt = 0.0;
@@ -1502,6 +1539,26 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     *converged = done;
     if (!done && debug) fprintf(stderr, "[krylov] not converged: relres %.3e after %d its\n", *relres, total);
     return RS_OK;
+}
+
+// The solve with the preconditioner of the handle.  Should a solve under the multigrid cycle fail -- no convergence
+// within the budget, breakdown -- the handle drops the cycle for good and the system is solved again with the
+// (block-)Jacobi preconditioner: never worse than without it.
+int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor, int *iters, double *relres, bool *converged)
+{
+    static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
+    bool conv_local = false;
+    if (!converged) converged = &conv_local;
+    int rc = krylov_solve_inner(c, k, b, x, abs_floor, iters, relres, converged);
+    if (k.mg_on && (rc == RS_ESINGULAR || (rc == RS_OK && !*converged && !(*relres <= 0.1)))) {
+        if (debug) fprintf(stderr, "[krylov] solve under the multigrid cycle failed (rc %d, relres %.3e after %d its): back to Jacobi\n", rc, *relres, *iters);
+        k.mg_failed = true;
+        k.mg_on = false;
+        const int it0 = *iters;
+        rc = krylov_solve_inner(c, k, b, x, abs_floor, iters, relres, converged);
+        *iters += it0;
+    }
+    return rc;
 }
 
 }  // namespace rs

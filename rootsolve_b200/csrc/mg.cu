@@ -1,0 +1,706 @@
+// mg.cu -- aggregation multigrid on the grid the Jacobian comes from: the preconditioner of the Newton linear
+// solve for steady.2D / steady.3D.  It takes the role the exact LDU factors play in the reference (nsfc/nnfc/nntc,
+// src/sparse.f:1937-2563): make the step count of the solve independent of the conditioning of J.  Jacobi-
+// preconditioned Krylov needs O(sqrt(cond)) steps -- 170 per solve on the 256^3 diffusion-reaction grid, and it
+// stalls on a bare Laplacian; one V-cycle per step brings that to ~10, at any grid size.
+//
+//   levels     2x2x2 (2x2 in 2-D) piecewise-constant aggregation of CELLS, every species on its own: a coarse
+//              unknown is (species, aggregate).  A dimension of extent <= 2 is not coarsened.  Coarsening stops
+//              at <= 32 cells; that level is solved with an explicit dense inverse.
+//   operators  Galerkin P'AP, which for this stencil is again a (2 nd + nspec)-point stencil on the coarse grid,
+//              built by summing values (mg_build_coarse_kernel).  Entries that cross an aggregate face in a
+//              coarsened direction are halved and the removed half is added to the diagonal: piecewise-constant
+//              transfer makes the second-order part of P'AP twice too stiff (4 faces of size h^-2 against the
+//              8 (2h)^-2 a coarse discretisation has), while the zeroth-order part (reaction, boundary terms =
+//              the row sums) is summed exactly; the correction keeps the row sums and restores h-independent
+//              convergence (scratch/mg_proto.py: 27 -> 9 CG steps at 64^3, zero-flux boundaries).
+//   storage    every level, the finest included, holds its matrix by stencil slot ("ELL by diagonal"):
+//              val[slot][row], slot 0 = diagonal, 1..6 = -j +j -k +k -l +l neighbour of the same species,
+//              7.. = the other species of the same cell.  Columns are implicit, loads are coalesced, there is
+//              no row pointer.  The finest level is a copy of the solver's row-wise arrays (one pass per Newton
+//              iteration) restricted to the rank's slab: the preconditioner is slab-local, so a
+//              cycle needs no communication.
+//   smoother   Chebyshev polynomial of degree 2 in (block-)Jacobi-preconditioned form on [lmax/4, lmax], lmax
+//              from a Gershgorin bound computed on the device; the cell block (nspec x nspec) is inverted
+//              exactly, which takes the stiff reaction coupling out of the iteration.  Same smoother before and
+//              after the coarse correction: for a symmetric matrix the cycle is a symmetric positive definite
+//              operator and preconditions CG; BiCGStab uses the same cycle on nonsymmetric Jacobians.
+//
+// Bytes (level 0, N rows, 7-point): a cycle makes 4 passes over the matrix (56 N each) plus ~170 N of vector
+// traffic; levels below add 1/7 in 3-D.  All kernels are thread-per-cell with grid-stride loops and run on the
+// solver's stream without host synchronisation, so whole Krylov steps including the cycle replay from CUDA graphs.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <memory>
+
+#include "solver.cuh"
+
+namespace rs {
+
+constexpr int MG_MAXLEV = 28;
+constexpr int MG_MAXS = 8;             // species handled (same bound as the block-Jacobi preconditioner)
+constexpr int MG_COARSEST_CELLS = 32;  // stop coarsening here: <= 256 unknowns, inverted densely
+constexpr int MG_MIN_CELLS = 64;       // smaller grids keep the (block-)Jacobi preconditioner
+constexpr double MG_CHEB_RATIO = 4.0;  // smoothing interval [lmax / ratio, lmax]
+
+// a vector addressed by (species, cell): internal vectors are packed (stride = cells of the level); the Krylov
+// vectors at level 0 keep the solver's global indexing (stride = cells of the whole grid, off = first cell of the slab)
+struct VecView {
+    double *p;
+    int stride, off;
+    __device__ __forceinline__ double &at(int s, int c) const { return p[(long long)s * stride + off + c]; }
+};
+
+struct MgLevelDev {
+    int nspec, d1, d2, d3, cyc1, cyc2, cyc3, ncell, n;
+    const double *ell;    // [7 + nspec - 1][n]
+    const double *dinv;   // nspec == 1: 1/diag per row; else the inverse cell blocks [s][s'][cell]
+    const double *lmax;   // Gershgorin bound of the (block-)Jacobi-preconditioned operator of this level
+};
+
+struct MgLevel {
+    MgLevelDev dev;
+    int f[3] = {1, 1, 1};   // coarsening factors towards the next level
+    DevBuf<double> ell, dinv, b, x, r, d;
+};
+
+struct Mg {
+    int nlev = 0;
+    MgLevel lev[MG_MAXLEV];
+    DevBuf<double> lmax;      // one per level
+    DevBuf<double> cinv;      // dense inverse of the coarsest operator, column-major
+    DevBuf<double> cwork;     // 2 nc^2 work array of the inversion
+    DevBuf<int> flag;         // != 0: the coarsest operator was singular to working precision
+    int gstride = 0, goff = 0;   // level-0 view of the solver's vectors
+    int nc = 0;               // unknowns of the coarsest level
+};
+
+// ---- stencil geometry ------------------------------------------------------------------------------------
+struct Cell3 { int j, k, l; };
+
+__device__ __forceinline__ Cell3 cell_coords(int c, int d2, int d3)
+{
+    Cell3 q;
+    const int s1 = d2 * d3;
+    q.j = c / s1;
+    const int rem = c - q.j * s1;
+    q.k = rem / d3;
+    q.l = rem - q.k * d3;
+    return q;
+}
+
+// cell index of the six neighbours (-j +j -k +k -l +l); a missing neighbour returns the cell itself (its matrix
+// entry is zero) and has = false
+__device__ __forceinline__ void neighbours(const MgLevelDev &L, int c, const Cell3 &q, int (&nb)[6], bool (&has)[6])
+{
+    const int s1 = L.d2 * L.d3;
+    has[0] = q.j > 0 || (L.cyc1 && L.d1 > 1);          nb[0] = q.j > 0 ? c - s1 : c + (L.d1 - 1) * s1;
+    has[1] = q.j < L.d1 - 1 || (L.cyc1 && L.d1 > 1);   nb[1] = q.j < L.d1 - 1 ? c + s1 : c - (L.d1 - 1) * s1;
+    has[2] = q.k > 0 || (L.cyc2 && L.d2 > 1);          nb[2] = q.k > 0 ? c - L.d3 : c + (L.d2 - 1) * L.d3;
+    has[3] = q.k < L.d2 - 1 || (L.cyc2 && L.d2 > 1);   nb[3] = q.k < L.d2 - 1 ? c + L.d3 : c - (L.d2 - 1) * L.d3;
+    has[4] = q.l > 0 || (L.cyc3 && L.d3 > 1);          nb[4] = q.l > 0 ? c - 1 : c + (L.d3 - 1);
+    has[5] = q.l < L.d3 - 1 || (L.cyc3 && L.d3 > 1);   nb[5] = q.l < L.d3 - 1 ? c + 1 : c - (L.d3 - 1);
+#pragma unroll
+    for (int t = 0; t < 6; t++)
+        if (!has[t]) nb[t] = c;
+}
+
+#define MG_NSA (NS > 0 ? NS : MG_MAXS)
+
+// (A v)(s, c) for every species s of cell c.  NS > 0: species count known at compile time.
+template <int NS>
+__device__ __forceinline__ void cell_apply(const MgLevelDev &L, int c, const int (&nb)[6], const VecView &v, double (&t)[MG_NSA])
+{
+    const int ns = NS > 0 ? NS : L.nspec;
+    double vc[MG_NSA];
+#pragma unroll
+    for (int s = 0; s < MG_NSA; s++)
+        if (s < ns) vc[s] = v.at(s, c);
+#pragma unroll
+    for (int s = 0; s < MG_NSA; s++) {
+        if (s >= ns) break;
+        const long long r = (long long)s * L.ncell + c;
+        double a = L.ell[r] * vc[s];
+#pragma unroll
+        for (int q = 0; q < 6; q++) a += L.ell[(long long)(1 + q) * L.n + r] * v.at(s, nb[q]);
+        int o = 0;
+#pragma unroll
+        for (int s2 = 0; s2 < MG_NSA; s2++) {
+            if (s2 >= ns) break;
+            if (s2 == s) continue;
+            a += L.ell[(long long)(7 + o) * L.n + r] * vc[s2];
+            o++;
+        }
+        t[s] = a;
+    }
+}
+
+// w = Dinv v over the species of cell c (point inverse for one species, inverse cell block otherwise)
+template <int NS>
+__device__ __forceinline__ void cell_dinv(const MgLevelDev &L, int c, const double (&v)[MG_NSA], double (&w)[MG_NSA])
+{
+    const int ns = NS > 0 ? NS : L.nspec;
+    if (NS == 1) { w[0] = L.dinv[c] * v[0]; return; }
+#pragma unroll
+    for (int s = 0; s < MG_NSA; s++) {
+        if (s >= ns) break;
+        double a = 0.0;
+#pragma unroll
+        for (int s2 = 0; s2 < MG_NSA; s2++) {
+            if (s2 >= ns) break;
+            a += L.dinv[((long long)s * ns + s2) * L.ncell + c] * v[s2];
+        }
+        w[s] = a;
+    }
+}
+
+struct Cheb { double inv_theta, c1, c2; };
+__device__ __forceinline__ Cheb cheb_coeffs(const MgLevelDev &L)
+{
+    const double lmax = *L.lmax, lmin = lmax / MG_CHEB_RATIO;
+    const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin);
+    const double sigma = theta / delta, rho0 = 1.0 / sigma, rho1 = 1.0 / (2.0 * sigma - rho0);
+    Cheb ch;
+    ch.inv_theta = 1.0 / theta;
+    ch.c1 = rho1 * rho0;
+    ch.c2 = 2.0 * rho1 / delta;
+    return ch;
+}
+
+#define MG_CELL_LOOP(c, ncell) for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < (ncell); c += gridDim.x * blockDim.x)
+
+// ---- cycle kernels (thread per cell, all species of the cell) ------------------------------------------------
+// first Chebyshev step from a zero guess:  d = Dinv b / theta   (x = d is implied)
+template <int NS>
+__global__ void __launch_bounds__(256) mg_first_kernel(MgLevelDev L, VecView b, VecView d)
+{
+    const int ns = NS > 0 ? NS : L.nspec;
+    const Cheb ch = cheb_coeffs(L);
+    MG_CELL_LOOP(c, L.ncell) {
+        double bv[MG_NSA], w[MG_NSA];
+#pragma unroll
+        for (int s = 0; s < MG_NSA; s++)
+            if (s < ns) bv[s] = b.at(s, c);
+        cell_dinv<NS>(L, c, bv, w);
+#pragma unroll
+        for (int s = 0; s < MG_NSA; s++)
+            if (s < ns) d.at(s, c) = ch.inv_theta * w[s];
+    }
+}
+
+// second Chebyshev step:  r1 = r - A d ;  d1 = c1 d + c2 Dinv r1 ;  xout = [xin +] d + d1
+// DOT: also out[0] = <w, xout> (w = the right-hand side of the cycle: the <r, z> of preconditioned CG when this is
+// the last kernel of the cycle)
+template <int NS, bool DOT>
+__global__ void __launch_bounds__(256) mg_second_kernel(MgLevelDev L, VecView r, VecView d, VecView xin, VecView xout, VecView w_,
+                                                        double *partials, unsigned *ticket, double *out, PeerRed pr)
+{
+    const int ns = NS > 0 ? NS : L.nspec;
+    const Cheb ch = cheb_coeffs(L);
+    double acc[1] = {0.0};
+    MG_CELL_LOOP(c, L.ncell) {
+        const Cell3 q = cell_coords(c, L.d2, L.d3);
+        int nb[6];
+        bool has[6];
+        neighbours(L, c, q, nb, has);
+        double t[MG_NSA], r1[MG_NSA], w[MG_NSA];
+        cell_apply<NS>(L, c, nb, d, t);
+#pragma unroll
+        for (int s = 0; s < MG_NSA; s++)
+            if (s < ns) r1[s] = r.at(s, c) - t[s];
+        cell_dinv<NS>(L, c, r1, w);
+#pragma unroll
+        for (int s = 0; s < MG_NSA; s++) {
+            if (s >= ns) break;
+            const double dv = d.at(s, c);
+            double xn = dv + (ch.c1 * dv + ch.c2 * w[s]);
+            if (xin.p != nullptr) xn += xin.at(s, c);
+            xout.at(s, c) = xn;
+            if (DOT) acc[0] += w_.at(s, c) * xn;
+        }
+    }
+    if (DOT) grid_reduce<1>(acc, 0u, partials, ticket, out, false, &pr);
+}
+
+// start of the post-smoothing:  r = b - A x ;  d = Dinv r / theta
+template <int NS>
+__global__ void __launch_bounds__(256) mg_resid_first_kernel(MgLevelDev L, VecView b, VecView x, VecView r, VecView d)
+{
+    const int ns = NS > 0 ? NS : L.nspec;
+    const Cheb ch = cheb_coeffs(L);
+    MG_CELL_LOOP(c, L.ncell) {
+        const Cell3 q = cell_coords(c, L.d2, L.d3);
+        int nb[6];
+        bool has[6];
+        neighbours(L, c, q, nb, has);
+        double t[MG_NSA], rr[MG_NSA], w[MG_NSA];
+        cell_apply<NS>(L, c, nb, x, t);
+#pragma unroll
+        for (int s = 0; s < MG_NSA; s++)
+            if (s < ns) { rr[s] = b.at(s, c) - t[s]; r.at(s, c) = rr[s]; }
+        cell_dinv<NS>(L, c, rr, w);
+#pragma unroll
+        for (int s = 0; s < MG_NSA; s++)
+            if (s < ns) d.at(s, c) = ch.inv_theta * w[s];
+    }
+}
+
+// residual of the fine level summed over each aggregate:  bc(s, I) = sum_{c in I} (b - A x)(s, c)
+// thread per COARSE cell (cd1 x cd2 x cd3 of them); f: the coarsening factors
+template <int NS>
+__global__ void __launch_bounds__(256) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, int cd1, int cd2, int cd3,
+                                                                VecView b, VecView x, VecView bc)
+{
+    const int ns = NS > 0 ? NS : L.nspec;
+    const int ncc = cd1 * cd2 * cd3;
+    MG_CELL_LOOP(I, ncc) {
+        const Cell3 Q = cell_coords(I, cd2, cd3);
+        double sum[MG_NSA];
+#pragma unroll
+        for (int s = 0; s < MG_NSA; s++) sum[s] = 0.0;
+        for (int dj = 0; dj < f1; dj++) {
+            const int j = Q.j * f1 + dj;
+            if (j >= L.d1) break;
+            for (int dk = 0; dk < f2; dk++) {
+                const int k = Q.k * f2 + dk;
+                if (k >= L.d2) break;
+                for (int dl = 0; dl < f3; dl++) {
+                    const int l = Q.l * f3 + dl;
+                    if (l >= L.d3) break;
+                    const int c = (j * L.d2 + k) * L.d3 + l;
+                    Cell3 q;
+                    q.j = j; q.k = k; q.l = l;
+                    int nb[6];
+                    bool has[6];
+                    neighbours(L, c, q, nb, has);
+                    double t[MG_NSA];
+                    cell_apply<NS>(L, c, nb, x, t);
+#pragma unroll
+                    for (int s = 0; s < MG_NSA; s++)
+                        if (s < ns) sum[s] += b.at(s, c) - t[s];
+                }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < MG_NSA; s++)
+            if (s < ns) bc.at(s, I) = sum[s];
+    }
+}
+
+// x(s, c) += xc(s, aggregate of c)
+__global__ void __launch_bounds__(256) mg_prolong_kernel(int nspec, int d1, int d2, int d3, int f1, int f2, int f3, int cd2, int cd3,
+                                                         VecView xc, VecView x)
+{
+    const int ncell = d1 * d2 * d3;
+    MG_CELL_LOOP(c, ncell) {
+        const Cell3 q = cell_coords(c, d2, d3);
+        const int I = ((q.j / f1) * cd2 + (q.k / f2)) * cd3 + (q.l / f3);
+        for (int s = 0; s < nspec; s++) x.at(s, c) += xc.at(s, I);
+    }
+}
+
+// coarsest level:  x = Cinv b  (dense, column-major so that thread i reads a coalesced column slice)
+__global__ void __launch_bounds__(256) mg_coarse_solve_kernel(int nc, const double *__restrict__ cinv, const double *__restrict__ b,
+                                                              double *__restrict__ x)
+{
+    extern __shared__ double sb[];
+    for (int i = threadIdx.x; i < nc; i += blockDim.x) sb[i] = b[i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < nc; i += blockDim.x) {
+        double a = 0.0;
+        for (int j = 0; j < nc; j++) a += cinv[(size_t)j * nc + i] * sb[j];
+        x[i] = a;
+    }
+}
+
+// ---- set-up kernels ------------------------------------------------------------------------------------------
+// Level 0 from the solver's row-wise arrays (global indices, columns ascending).  Thread per (species, local cell).
+// An entry of the same species goes to the slot of the neighbour it addresses, an entry of another species of the
+// same cell to that species' slot; anything else -- a column outside the rank's slab, a pattern entry that is not
+// part of the stencil -- is left out of the preconditioner.  ell must be zero on entry.
+__global__ void __launch_bounds__(256) mg_build_l0_kernel(MgLevelDev L, int gstride, int goff, const int *__restrict__ rowptr,
+                                                          const int *__restrict__ col, const double *__restrict__ val,
+                                                          double *__restrict__ ell)
+{
+    const long long total = (long long)L.nspec * L.ncell;
+    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < total; r += (long long)gridDim.x * blockDim.x) {
+        const int s = (int)(r / L.ncell), c = (int)(r - (long long)s * L.ncell);
+        const Cell3 q = cell_coords(c, L.d2, L.d3);
+        int nb[6];
+        bool has[6];
+        neighbours(L, c, q, nb, has);
+        const long long g = (long long)s * gstride + goff + c;
+        double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        for (int p = rowptr[g]; p < rowptr[g + 1]; p++) {
+            const int cj = col[p];
+            const int s2 = cj / gstride;
+            const int c2 = cj - s2 * gstride - goff;
+            if (c2 < 0 || c2 >= L.ncell) continue;
+            const double v = val[p];
+            if (s2 != s) {
+                if (c2 == c) ell[(long long)(7 + (s2 < s ? s2 : s2 - 1)) * L.n + r] += v;
+                continue;
+            }
+            if (c2 == c) { acc[0] += v; continue; }
+#pragma unroll
+            for (int t = 0; t < 6; t++)
+                if (has[t] && nb[t] == c2) { acc[1 + t] += v; break; }
+        }
+#pragma unroll
+        for (int t = 0; t < 7; t++) ell[(long long)t * L.n + r] = acc[t];
+    }
+}
+
+// Galerkin coarse operator by summation.  Thread per (species, coarse cell).  w = weight kept by an entry that
+// crosses an aggregate face in a coarsened direction (the rest goes to the diagonal, see the file header).
+__global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLevelDev Cc, int f1, int f2, int f3, double w,
+                                                              double *__restrict__ ellc)
+{
+    const long long total = (long long)Cc.nspec * Cc.ncell;
+    const int nother = F.nspec - 1;
+    for (long long R = (long long)blockIdx.x * blockDim.x + threadIdx.x; R < total; R += (long long)gridDim.x * blockDim.x) {
+        const int s = (int)(R / Cc.ncell), I = (int)(R - (long long)s * Cc.ncell);
+        const Cell3 Q = cell_coords(I, Cc.d2, Cc.d3);
+        double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        double oth[MG_MAXS];
+        for (int o = 0; o < MG_MAXS; o++) oth[o] = 0.0;
+        const int fq[3] = {f1, f2, f3};
+        const int IQ[3] = {Q.j, Q.k, Q.l};
+        for (int dj = 0; dj < f1; dj++) {
+            const int j = Q.j * f1 + dj;
+            if (j >= F.d1) break;
+            for (int dk = 0; dk < f2; dk++) {
+                const int k = Q.k * f2 + dk;
+                if (k >= F.d2) break;
+                for (int dl = 0; dl < f3; dl++) {
+                    const int l = Q.l * f3 + dl;
+                    if (l >= F.d3) break;
+                    const int c = (j * F.d2 + k) * F.d3 + l;
+                    const long long r = (long long)s * F.ncell + c;
+                    Cell3 q;
+                    q.j = j; q.k = k; q.l = l;
+                    int nb[6];
+                    bool has[6];
+                    neighbours(F, c, q, nb, has);
+                    acc[0] += F.ell[r];
+#pragma unroll
+                    for (int t = 0; t < 6; t++) {
+                        if (!has[t]) continue;
+                        const double v = F.ell[(long long)(1 + t) * F.n + r];
+                        const Cell3 qn = cell_coords(nb[t], F.d2, F.d3);
+                        const int dim = t >> 1;
+                        const int cn = dim == 0 ? qn.j : dim == 1 ? qn.k : qn.l;
+                        if (cn / fq[dim] == IQ[dim]) acc[0] += v;                 // inside the aggregate
+                        else if (fq[dim] == 2) { acc[1 + t] += w * v; acc[0] += (1.0 - w) * v; }
+                        else acc[1 + t] += v;
+                    }
+                    for (int o = 0; o < nother; o++) oth[o] += F.ell[(long long)(7 + o) * F.n + r];
+                }
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < 7; t++) ellc[(long long)t * Cc.n + R] = acc[t];
+        for (int o = 0; o < nother; o++) ellc[(long long)(7 + o) * Cc.n + R] = oth[o];
+    }
+}
+
+__device__ __forceinline__ void atomic_max_pos(double *addr, double v)   // v >= 0: the bit patterns order like the values
+{
+    atomicMax(reinterpret_cast<unsigned long long *>(addr), (unsigned long long)__double_as_longlong(v));
+}
+
+// Smoother data of a level: the inverse of every cell block (nspec = 1: of the diagonal) and the Gershgorin bound
+//   lmax = 1 + max over rows of  sum_s' |Binv(s,s')| * (sum over the six neighbour entries of row (s', cell))
+// of the block-Jacobi-preconditioned operator Binv A = I + Binv T.  lmax[0] must be zero on entry.
+__global__ void __launch_bounds__(128) mg_smoother_setup_kernel(MgLevelDev L, double *__restrict__ dinv, double *__restrict__ lmax)
+{
+    const int ns = L.nspec;
+    double worst = 0.0;
+    MG_CELL_LOOP(c, L.ncell) {
+        double A[MG_MAXS][MG_MAXS], B[MG_MAXS][MG_MAXS], tsum[MG_MAXS];
+        for (int s = 0; s < ns; s++) {
+            const long long r = (long long)s * L.ncell + c;
+            int o = 0;
+            for (int s2 = 0; s2 < ns; s2++) {
+                A[s][s2] = (s2 == s) ? L.ell[r] : L.ell[(long long)(7 + o++) * L.n + r];
+                B[s][s2] = (s == s2) ? 1.0 : 0.0;
+            }
+            double ts = 0.0;
+            for (int t = 0; t < 6; t++) ts += fabs(L.ell[(long long)(1 + t) * L.n + r]);
+            tsum[s] = ts;
+        }
+        bool singular = false;
+        for (int k = 0; k < ns && !singular; k++) {   // Gauss-Jordan with partial pivoting
+            int piv = k;
+            double best = fabs(A[k][k]);
+            for (int s = k + 1; s < ns; s++)
+                if (fabs(A[s][k]) > best) { best = fabs(A[s][k]); piv = s; }
+            if (!(best > 0.0)) { singular = true; break; }
+            if (piv != k)
+                for (int q = 0; q < ns; q++) {
+                    const double ta = A[k][q]; A[k][q] = A[piv][q]; A[piv][q] = ta;
+                    const double tb = B[k][q]; B[k][q] = B[piv][q]; B[piv][q] = tb;
+                }
+            const double inv = 1.0 / A[k][k];
+            for (int q = 0; q < ns; q++) { A[k][q] *= inv; B[k][q] *= inv; }
+            for (int s = 0; s < ns; s++) {
+                if (s == k) continue;
+                const double f = A[s][k];
+                if (f == 0.0) continue;
+                for (int q = 0; q < ns; q++) { A[s][q] -= f * A[k][q]; B[s][q] -= f * B[k][q]; }
+            }
+        }
+        if (singular)
+            for (int s = 0; s < ns; s++)
+                for (int q = 0; q < ns; q++) B[s][q] = (s == q) ? 1.0 : 0.0;
+        for (int s = 0; s < ns; s++) {
+            double g = 0.0;
+            for (int q = 0; q < ns; q++) {
+                g += fabs(B[s][q]) * tsum[q];
+                if (ns == 1) dinv[c] = B[0][0];
+                else dinv[((long long)s * ns + q) * L.ncell + c] = B[s][q];
+            }
+            worst = fmax(worst, 1.0 + g);
+        }
+    }
+    worst = warp_max(worst);
+    if ((threadIdx.x & 31) == 0 && worst > 0.0) atomic_max_pos(lmax, worst);
+}
+
+// Dense inverse of the coarsest operator (n <= 256) by Gauss-Jordan with partial pivoting, one block.
+// work: 2 n^2 doubles (A | Inv), row-major; cinv: the inverse, column-major.  flag: set when a pivot vanishes.
+__global__ void __launch_bounds__(1024) mg_coarse_invert_kernel(MgLevelDev L, double *__restrict__ work, double *__restrict__ cinv,
+                                                                int *__restrict__ flag)
+{
+    const int n = L.n, tid = threadIdx.x, nt = blockDim.x;
+    double *A = work, *B = work + (size_t)n * n;
+    __shared__ double fcol[256];
+    __shared__ int s_piv;
+    __shared__ double s_inv;
+    for (int e = tid; e < n * n; e += nt) { A[e] = 0.0; B[e] = (e / n == e % n) ? 1.0 : 0.0; }
+    __syncthreads();
+    for (int r = tid; r < n; r += nt) {   // expand the stencil rows
+        const int s = r / L.ncell, c = r - s * L.ncell;
+        const Cell3 q = cell_coords(c, L.d2, L.d3);
+        int nb[6];
+        bool has[6];
+        neighbours(L, c, q, nb, has);
+        A[(size_t)r * n + r] += L.ell[r];
+        for (int t = 0; t < 6; t++)
+            if (has[t]) A[(size_t)r * n + s * L.ncell + nb[t]] += L.ell[(size_t)(1 + t) * n + r];
+        int o = 0;
+        for (int s2 = 0; s2 < L.nspec; s2++) {
+            if (s2 == s) continue;
+            A[(size_t)r * n + s2 * L.ncell + c] += L.ell[(size_t)(7 + o) * n + r];
+            o++;
+        }
+    }
+    __syncthreads();
+    for (int k = 0; k < n; k++) {
+        if (tid == 0) {
+            int piv = k;
+            double best = fabs(A[(size_t)k * n + k]);
+            for (int i = k + 1; i < n; i++) {
+                const double v = fabs(A[(size_t)i * n + k]);
+                if (v > best) { best = v; piv = i; }
+            }
+            s_piv = piv;
+            if (!(best > 1.0e-300)) { *flag = 1; s_inv = 1.0; }
+            else s_inv = 1.0 / A[(size_t)piv * n + k];
+        }
+        __syncthreads();
+        const int piv = s_piv;
+        const double inv = s_inv;
+        for (int j = tid; j < n; j += nt) {   // swap rows k <-> piv and scale the pivot row
+            const double a = A[(size_t)piv * n + j], b = B[(size_t)piv * n + j];
+            if (piv != k) {
+                A[(size_t)piv * n + j] = A[(size_t)k * n + j];
+                B[(size_t)piv * n + j] = B[(size_t)k * n + j];
+            }
+            A[(size_t)k * n + j] = a * inv;
+            B[(size_t)k * n + j] = b * inv;
+        }
+        __syncthreads();
+        for (int i = tid; i < n; i += nt) fcol[i] = (i == k) ? 0.0 : A[(size_t)i * n + k];
+        __syncthreads();
+        for (int e = tid; e < n * n; e += nt) {
+            const int i = e / n, j = e - i * n;
+            const double f = fcol[i];
+            if (f != 0.0) {
+                A[e] -= f * A[(size_t)k * n + j];
+                B[e] -= f * B[(size_t)k * n + j];
+            }
+        }
+        __syncthreads();
+    }
+    for (int e = tid; e < n * n; e += nt) {
+        const int i = e / n, j = e - i * n;
+        cinv[(size_t)j * n + i] = B[e];
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------
+static inline int mg_grid(long long work) { return grid_for(work, 256, 148 * 8); }
+static inline VecView view(double *p, int stride, int off = 0) { VecView v; v.p = p; v.stride = stride; v.off = off; return v; }
+
+bool mg_applicable(const GridDesc &g, int j0, int j1)
+{
+    if (g.type != RS_TYPE_2D && g.type != RS_TYPE_3D) return false;
+    if (g.nspec < 1 || g.nspec > MG_MAXS) return false;
+    const int d1 = j1 > j0 ? j1 - j0 : g.d[0];
+    const long long cells = (long long)d1 * (g.ncell / g.d[0]);
+    return cells >= MG_MIN_CELLS;
+}
+
+void mg_destroy(Mg *m) { delete m; }
+
+// Lays out the hierarchy for the rank's box of the grid: planes [j0, j1) of the slowest dimension (j1 <= j0: the
+// whole grid).  The grid is handled as a 3-D box with leading extents 1 (a 2-D grid (a, b) is (1, a, b)).
+int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
+{
+    std::unique_ptr<Mg> M(new Mg());
+    const int nd = g.type == RS_TYPE_2D ? 2 : 3;
+    int d[3] = {1, 1, 1}, cyc[3] = {0, 0, 0};
+    for (int q = 0; q < nd; q++) { d[3 - nd + q] = g.d[q]; cyc[3 - nd + q] = g.cyc[q]; }
+    const int slow = 3 - nd;   // position of the sharded (slowest) dimension in the box
+    M->gstride = g.ncell;
+    M->goff = 0;
+    if (j1 > j0) {
+        M->goff = j0 * (g.ncell / g.d[0]);
+        if (j1 - j0 != g.d[0]) cyc[slow] = 0;   // a slab of a cyclic dimension is an open box: the wrap crosses ranks
+        d[slow] = j1 - j0;
+    }
+    int nlev = 0;
+    for (;;) {
+        MgLevel &L = M->lev[nlev];
+        MgLevelDev &D = L.dev;
+        D.nspec = g.nspec;
+        D.d1 = d[0]; D.d2 = d[1]; D.d3 = d[2];
+        D.cyc1 = cyc[0]; D.cyc2 = cyc[1]; D.cyc3 = cyc[2];
+        D.ncell = d[0] * d[1] * d[2];
+        D.n = D.nspec * D.ncell;
+        const size_t nslot = 7 + (size_t)D.nspec - 1;
+        RS_TRY(L.ell.alloc(nslot * D.n));
+        RS_TRY(L.dinv.alloc(D.nspec == 1 ? (size_t)D.n : (size_t)D.nspec * D.n));
+        RS_TRY(L.x.alloc(D.n)); RS_TRY(L.r.alloc(D.n)); RS_TRY(L.d.alloc(D.n));
+        if (nlev > 0) RS_TRY(L.b.alloc(D.n));
+        D.ell = L.ell.p; D.dinv = L.dinv.p;
+        nlev++;
+        bool any = false;
+        for (int q = 0; q < 3; q++) { L.f[q] = d[q] > 2 ? 2 : 1; any = any || L.f[q] == 2; }
+        if (D.ncell <= MG_COARSEST_CELLS || !any || nlev == MG_MAXLEV) { L.f[0] = L.f[1] = L.f[2] = 1; break; }
+        for (int q = 0; q < 3; q++) d[q] = (d[q] + L.f[q] - 1) / L.f[q];
+    }
+    M->nlev = nlev;
+    RS_TRY(M->lmax.alloc(nlev));
+    for (int l = 0; l < nlev; l++) M->lev[l].dev.lmax = M->lmax.p + l;
+    M->nc = M->lev[nlev - 1].dev.n;
+    if (M->nc > 256 || nlev < 2) { set_error("multigrid: unusable hierarchy (%d levels, %d coarsest unknowns)", nlev, M->nc); return RS_ETOOBIG; }
+    RS_TRY(M->cinv.alloc((size_t)M->nc * M->nc));
+    RS_TRY(M->cwork.alloc(2 * (size_t)M->nc * M->nc));
+    RS_TRY(M->flag.alloc(1));
+    (void)c;
+    *out = M.release();
+    return RS_OK;
+}
+
+// Rebuilds every level from the matrix values the Krylov solver is about to use (once per Newton iteration).
+int mg_update(Ctx &c, Mg &M, const int *rowptr, const int *col, const double *val)
+{
+    cudaStream_t st = c.stream;
+    RS_TRY(M.lmax.zero(st));
+    RS_TRY(M.flag.zero(st));
+    {
+        MgLevel &L = M.lev[0];
+        RS_TRY(L.ell.zero(st));
+        const double nz = (double)L.dev.n * (6.0 + L.dev.nspec);
+        Launch La(c, K_PRECOND_SETUP, 12.0 * nz + 8.0 * nz);
+        mg_build_l0_kernel<<<mg_grid(L.dev.n), 256, 0, st>>>(L.dev, M.gstride, M.goff, rowptr, col, val, L.ell.p);
+    }
+    for (int l = 0; l < M.nlev; l++) {
+        MgLevel &L = M.lev[l];
+        const double nz = (double)L.dev.n * (6.0 + L.dev.nspec);
+        if (l + 1 < M.nlev) {
+            MgLevel &Cn = M.lev[l + 1];
+            Launch La(c, K_PRECOND_SETUP, 8.0 * nz + 8.0 * nz / 8.0);
+            mg_build_coarse_kernel<<<mg_grid(Cn.dev.n), 256, 0, st>>>(L.dev, Cn.dev, L.f[0], L.f[1], L.f[2], 0.5, Cn.ell.p);
+        }
+        {
+            Launch La(c, K_PRECOND_SETUP, 8.0 * nz + 8.0 * L.dev.nspec * L.dev.n);
+            mg_smoother_setup_kernel<<<grid_for(L.dev.ncell, 128, 148 * 16), 128, 0, st>>>(L.dev, L.dinv.p, M.lmax.p + l);
+        }
+    }
+    {
+        Launch La(c, K_PRECOND_SETUP, 24.0 * M.nc * M.nc);
+        mg_coarse_invert_kernel<<<1, 1024, 0, st>>>(M.lev[M.nlev - 1].dev, M.cwork.p, M.cinv.p, M.flag.p);
+    }
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+template <int NS>
+static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double *partials, unsigned *ticket, double *dot_out,
+                           const PeerRed &pr)
+{
+    cudaStream_t st = c.stream;
+    MgLevel &L = M.lev[l];
+    const MgLevelDev &D = L.dev;
+    const double n = (double)D.n, mat = 8.0 * n * (6.0 + D.nspec);
+    const int grid = mg_grid(D.ncell);
+    if (l == M.nlev - 1) {
+        Launch La(c, K_PRECOND_APPLY, 8.0 * M.nc * M.nc + 16.0 * M.nc);
+        mg_coarse_solve_kernel<<<1, 256, sizeof(double) * M.nc, st>>>(M.nc, M.cinv.p, b.p, xout.p);
+        return;
+    }
+    MgLevel &Cn = M.lev[l + 1];
+    const VecView x = view(L.x.p, D.ncell), r = view(L.r.p, D.ncell), d = view(L.d.p, D.ncell);
+    const VecView none = view(nullptr, 0);
+    {   // pre-smoothing from a zero guess: two Chebyshev steps, one pass over the matrix
+        Launch La(c, K_PRECOND_APPLY, 16.0 * n + 8.0 * D.nspec * n);
+        mg_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, d);
+    }
+    {
+        Launch La(c, K_PRECOND_APPLY, mat + 24.0 * n + 8.0 * D.nspec * n);
+        mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, b, d, none, x, none, nullptr, nullptr, nullptr, PeerRed());
+    }
+    {   // residual, summed over the aggregates
+        Launch La(c, K_PRECOND_APPLY, mat + 16.0 * n + 8.0 * Cn.dev.n);
+        mg_resid_restrict_kernel<NS><<<mg_grid(Cn.dev.ncell), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d1, Cn.dev.d2, Cn.dev.d3,
+                                                                          b, x, view(Cn.b.p, Cn.dev.ncell));
+    }
+    mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.x.p, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
+    {
+        Launch La(c, K_PRECOND_APPLY, 16.0 * n + 8.0 * Cn.dev.n);
+        mg_prolong_kernel<<<grid, 256, 0, st>>>(D.nspec, D.d1, D.d2, D.d3, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3,
+                                                view(Cn.x.p, Cn.dev.ncell), x);
+    }
+    {   // post-smoothing: the same two Chebyshev steps, two passes
+        Launch La(c, K_PRECOND_APPLY, mat + 32.0 * n + 8.0 * D.nspec * n);
+        mg_resid_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, x, r, d);
+    }
+    {
+        Launch La(c, K_PRECOND_APPLY, mat + 32.0 * n + 8.0 * D.nspec * n);
+        if (dot_out)
+            mg_second_kernel<NS, true><<<grid, 256, 0, st>>>(D, r, d, x, xout, b, partials, ticket, dot_out, pr);
+        else
+            mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, r, d, x, xout, none, nullptr, nullptr, nullptr, PeerRed());
+    }
+}
+
+// z = M^-1 r: one V-cycle.  r and z are Krylov vectors in the solver's global indexing (only the rank's slab is
+// read and written); dot_out != nullptr: *dot_out = <r, z> over the slab, all-reduced over the ranks (pr).
+int mg_apply(Ctx &c, Mg &M, const double *r, double *z, double *partials, unsigned *ticket, double *dot_out, const PeerRed &pr)
+{
+    const VecView b = view(const_cast<double *>(r), M.gstride, M.goff), xo = view(z, M.gstride, M.goff);
+    const int ns = M.lev[0].dev.nspec;
+    if (ns == 1) mg_cycle_level<1>(c, M, 0, b, xo, partials, ticket, dot_out, pr);
+    else if (ns == 2) mg_cycle_level<2>(c, M, 0, b, xo, partials, ticket, dot_out, pr);
+    else mg_cycle_level<0>(c, M, 0, b, xo, partials, ticket, dot_out, pr);
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
+
+int mg_levels(const Mg &M) { return M.nlev; }
+
+}  // namespace rs

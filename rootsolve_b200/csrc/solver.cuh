@@ -74,6 +74,16 @@ int gather_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan
 int scatter_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, const int *d_rowptr,
                        const int *d_col, const double *d_a, double *d_val);
 
+// mg.cu -- aggregation multigrid preconditioner for 2-D / 3-D grids (slab-local when sharded)
+struct Mg;
+bool mg_applicable(const GridDesc &g, int j0, int j1);
+int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1);   // planes [j0, j1) of the slowest dimension; j1 <= j0: all
+int mg_update(Ctx &c, Mg &m, const int *rowptr, const int *col, const double *val);
+// z = M^-1 r (one V-cycle) on the rank's slab of global-index vectors; dot_out: <r, z>, all-reduced through pr
+int mg_apply(Ctx &c, Mg &m, const double *r, double *z, double *partials, unsigned *ticket, double *dot_out, const PeerRed &pr);
+int mg_levels(const Mg &m);
+void mg_destroy(Mg *m);
+
 // krylov.cu
 struct Krylov {
     int n = 0, nnz = 0;
@@ -83,7 +93,10 @@ struct Krylov {
     Ranges own;                 // rows of this rank
     int cell0 = 0, cell1 = 0;   // cells of this rank (block preconditioner)
     HaloPlan halo;
-    DevBuf<double> r, r0, p, v, s, t, ph, sh, dinv, binv;
+    DevBuf<double> r, r0, p, v, s, t, ph, sh, dinv, binv, z;
+    Mg *mg = nullptr;          // multigrid preconditioner; z = M^-1 r of preconditioned CG
+    bool mg_on = false;        // the current solve is preconditioned by the cycle
+    bool mg_failed = false;    // a solve with it did not converge: this handle goes back to (block-)Jacobi
     DevBuf<double> partials, scal;
     DevBuf<unsigned> ticket;
     double *h_scal = nullptr;  // pinned mirror
@@ -101,7 +114,7 @@ struct Krylov {
     DevBuf<double> sc;
     bool scaled = false;
     double sigma = 1.0, norm_conv = 1.0;
-    bool g_scaled[2] = {false, false};
+    bool g_scaled[2] = {false, false}, g_mg[2] = {false, false};
     bool push_ok = false;                  // halos of ph / sh are pushed into the neighbours' vectors over NVLink
     void *nb_lo[2] = {nullptr, nullptr}, *nb_hi[2] = {nullptr, nullptr};   // neighbours' ph (0) and sh (1)
     // captured Krylov steps ([0] BiCGStab, [1] CG): graph, the solution vector it updates, steps and launches per replay

@@ -23,7 +23,8 @@ import numpy as np
 from . import _capi
 
 _PRECOND = {"none": _capi.RS_PRECOND_NONE, "jacobi": _capi.RS_PRECOND_JACOBI,
-            "block-jacobi": _capi.RS_PRECOND_BLOCK_JACOBI, "auto": _capi.RS_PRECOND_AUTO}
+            "block-jacobi": _capi.RS_PRECOND_BLOCK_JACOBI, "mg": _capi.RS_PRECOND_MG, "btd": _capi.RS_PRECOND_BTD,
+            "auto": _capi.RS_PRECOND_AUTO}
 
 
 class SteadyResult(dict):
@@ -345,6 +346,8 @@ def stodes(y, time=0, func=None, parms=None, rtol=1e-6, atol=1e-8, ctol=1e-8, sp
     out.attributes["krylov_iters"] = R.krylov_iters
     out.attributes["kernel_launches"] = R.kernel_launches
     out.attributes["spmv_kernel"] = {0: "csr-subwarp", 1: "csr-tma", 2: "grid-implicit-columns"}.get(R.spmv_kernel)
+    out.attributes["precond"] = {0: "none", 1: "jacobi", 2: "block-jacobi", 3: "mg", 4: "btd"}.get(R.precond)
+    out.attributes["krylov_method"] = {0: "bicgstab", 1: "cg"}.get(R.krylov_method)
     out.attributes["timing"] = {"setup_s": R.t_setup_s, "newton_s": R.t_newton_s}
     if verbose:
         print("precision at each steady state step")
