@@ -33,6 +33,19 @@
  *     yout[0..nout) outputs, then rpar.  The two ints after the user's ipar are
  *     the slab bounds (J1 < 0: not partitioned).
  *
+ * Accessor form (optional, faster).  The finite-difference Jacobian evaluates the model on ngp perturbed copies of
+ * the state (src/sparse.f:497-508).  A model written as above needs those copies in memory.  A model that takes its
+ * state as an `rs_state' instead of a `double *' --
+ *
+ *     __device__ void mymod(int *neq, double *t, rs_state y, double *ydot, double *yout, int *ip)
+ *     {   RS_FOR_EACH(i, *neq) ydot[i] = -parms[0] * y[i];   }        // y[i], y + offset work as on a pointer
+ *     RS_MODEL_ACC(mymod, 3)
+ *
+ * -- reads the ONE state vector of the solve, and y[i] adds the solver's increment (Perturb, src/steady.f:208-226)
+ * on the fly when unknown i belongs to the column group the evaluation perturbs: the ngp copies are never written
+ * or read.  The body of the function does not change.  RS_FOR_EACH_CELL walks a box of grid cells line by line
+ * without an integer division per cell.
+ *
  * The kernel that calls func is instantiated in the model's own translation
  * unit (template argument = the function), so the residual is inlined into
  * the batched launch; the solver library reaches it through the host function
@@ -44,7 +57,7 @@
 
 #include <cuda_runtime.h>
 
-#define RS_MODEL_ABI 1
+#define RS_MODEL_ABI 2
 
 typedef void rs_deriv_func_t(int *, double *, double *, double *, double *, int *);
 typedef void rs_init_func_t(void (*)(int *, double *));
@@ -59,7 +72,67 @@ struct rs_model_desc {
                   double *yout, long long ldout, int *ip, long long work);
     rs_init_func_t *initfunc; /* reference signature; copies parms to the device */
     rs_init_func_t *initforc;
+    /* Accessor-form models only (else NULL): evaluates the model on y with the columns of group g0 + b perturbed,
+     * b = 0 .. ngroups-1, in ONE launch; evaluation b writes ydot + b*ld and uses yout + b*ldout.
+     * group_of[i] = 0-based column group of unknown i. */
+    int (*launch_groups)(void *stream, int neq, double t, const double *y, const int *group_of, int g0, int ngroups,
+                         double *ydot, long long ld, double *yout, long long ldout, int *ip, long long work);
 };
+
+/* The state vector as an accessor-form model sees it. */
+struct rs_state {
+    const double *y;
+    const int *grp; /* column group of every unknown; may be NULL when g < 0 */
+    int g;          /* group whose columns carry the finite-difference increment; < 0: the state itself */
+    __device__ __forceinline__ double operator[](long long i) const
+    {
+        const double v = y[i];
+        if (g >= 0 && grp[i] == g) {
+            double d = fabs(v) * 1.0e-8; /* Perturb, src/steady.f:219-224 */
+            if (d < 1.0e-8) d = 1.0e-8;
+            return v + d;
+        }
+        return v;
+    }
+    __device__ __forceinline__ rs_state operator+(long long off) const
+    {
+        rs_state s = {y + off, grp ? grp + off : grp, g};
+        return s;
+    }
+};
+typedef void rs_deriv_acc_func_t(int *, double *, rs_state, double *, double *, int *);
+
+/* Line-by-line walk over the cells (j, k, l) of planes [j0, j1) of a box with extents (*, d2, d3), l fastest: the
+ * threads of a block share lines of l, a thread finds its (j, k) by one division when it starts and by additions
+ * afterwards.  A 2-D grid (a, b) is walked as planes [j0, j1) of (*, 1, b).
+ *     RS_FOR_EACH_CELL(it, l, j0, j1, d2, d3) { ... it.j, it.k, l ... }                                          */
+struct rs_lines {
+    int j, k, ln, nl, stride, d2, tl, lstep;
+    __device__ __forceinline__ rs_lines(int j0, int j1, int d2_, int d3)
+    {
+        int sh = 0;
+        while ((1 << sh) < d3 && (1 << sh) < (int)blockDim.x) sh++;
+        lstep = 1 << sh;
+        tl = threadIdx.x & (lstep - 1);
+        const int per_block = (int)blockDim.x >> sh;
+        d2 = d2_;
+        nl = (j1 - j0) * d2_;
+        ln = blockIdx.x * per_block + ((int)threadIdx.x >> sh);
+        stride = gridDim.x * per_block;
+        j = j0 + ln / d2_;
+        k = ln - (j - j0) * d2_;
+    }
+    __device__ __forceinline__ bool ok() const { return ln < nl; }
+    __device__ __forceinline__ void next()
+    {
+        ln += stride;
+        k += stride;
+        while (k >= d2) { k -= d2; j++; }
+    }
+};
+#define RS_FOR_EACH_CELL(it, l, j0, j1, d2, d3) \
+    for (rs_lines it((j0), (j1), (d2), (d3)); it.ok(); it.next()) \
+        for (int l = it.tl; l < (d3); l += it.lstep)
 
 #define RS_THREAD_ID ((long long)blockIdx.x * blockDim.x + threadIdx.x)
 #define RS_THREAD_COUNT ((long long)gridDim.x * blockDim.x)
@@ -107,6 +180,79 @@ static int rs_launch_batched(void *stream, int neq, double t, const double *y, d
     return (int)cudaGetLastError();
 }
 
+/* ---- accessor form ---- */
+template <rs_deriv_acc_func_t F>
+__global__ void __launch_bounds__(256) rs_residual_batched_acc_kernel(int neq, double t, const double *y, double *ydot,
+                                                                       long long ld, double *yout, long long ldout, int *ip)
+{
+    const long long b = blockIdx.y;
+    int n = neq;
+    double tt = t;
+    rs_state s = {y + b * ld, nullptr, -1};
+    F(&n, &tt, s, ydot + b * ld, yout + b * ldout, ip);
+}
+
+template <rs_deriv_acc_func_t F>
+__global__ void __launch_bounds__(256) rs_residual_groups_kernel(int neq, double t, const double *y, const int *group_of, int g0,
+                                                                  double *ydot, long long ld, double *yout, long long ldout,
+                                                                  int *ip)
+{
+    const long long b = blockIdx.y;
+    int n = neq;
+    double tt = t;
+    rs_state s = {y, group_of, g0 + (int)b};
+    F(&n, &tt, s, ydot + b * ld, yout + b * ldout, ip);
+}
+
+template <typename K>
+static long long rs_wave_blocks_(K kernel, int threads, int nbatch, int *cache)
+{
+    if (*cache == 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) == cudaSuccess && sms > 0 && per_sm > 0)
+            *cache = sms * per_sm;
+        else
+            *cache = 148 * 4;
+    }
+    long long cap = *cache / nbatch;
+    return cap < 1 ? 1 : cap;
+}
+
+template <rs_deriv_acc_func_t F>
+static int rs_launch_batched_acc(void *stream, int neq, double t, const double *y, double *ydot, long long ld,
+                                 int nbatch, double *yout, long long ldout, int *ip, long long work)
+{
+    if (work <= 0 || nbatch <= 0) return 0;
+    const int threads = 256;
+    static int resident = 0;
+    long long blocks = (work + threads - 1) / threads;
+    const long long cap = rs_wave_blocks_(rs_residual_batched_acc_kernel<F>, threads, nbatch, &resident);
+    if (blocks > cap) blocks = cap;
+    dim3 grid((unsigned)blocks, (unsigned)nbatch);
+    rs_residual_batched_acc_kernel<F><<<grid, threads, 0, (cudaStream_t)stream>>>(neq, t, y, ydot, ld, yout, ldout, ip);
+    return (int)cudaGetLastError();
+}
+
+template <rs_deriv_acc_func_t F>
+static int rs_launch_groups(void *stream, int neq, double t, const double *y, const int *group_of, int g0, int ngroups,
+                            double *ydot, long long ld, double *yout, long long ldout, int *ip, long long work)
+{
+    if (work <= 0 || ngroups <= 0) return 0;
+    const int threads = 256;
+    static int resident = 0;
+    long long blocks = (work + threads - 1) / threads;
+    /* One resident wave over all evaluations (grid.y = evaluation), every thread striding over cells: the evaluations
+     * sweep the state together and share its lines in L2.  (Looping over the evaluations inside one kernel whose grid
+     * covers the cells once was measured 4.5 times slower on B200 at 256^3: 13 widely spaced output streams per block.) */
+    const long long cap = rs_wave_blocks_(rs_residual_groups_kernel<F>, threads, ngroups, &resident);
+    if (blocks > cap) blocks = cap;
+    dim3 grid((unsigned)blocks, (unsigned)ngroups);
+    rs_residual_groups_kernel<F><<<grid, threads, 0, (cudaStream_t)stream>>>(neq, t, y, group_of, g0, ydot, ld, yout, ldout, ip);
+    return (int)cudaGetLastError();
+}
+
 /* N parameters in __constant__ memory + the reference-style initialiser that fills them */
 #define RS_MODEL_PARMS(N)                                                        \
     static __constant__ double parms[N];                                         \
@@ -134,10 +280,20 @@ static int rs_launch_batched(void *stream, int neq, double t, const double *y, d
 #define RS_MODEL_NAMED_F(NAME, FUNC, NPARMS, INITFN, FORCFN)                     \
     extern "C" const rs_model_desc *rs_model_##NAME(void)                        \
     {                                                                            \
-        static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched<FUNC>, INITFN, FORCFN}; \
+        static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched<FUNC>, INITFN, FORCFN, nullptr}; \
         return &d;                                                               \
     }
 #define RS_MODEL_NAMED(NAME, FUNC, NPARMS, INITFN) RS_MODEL_NAMED_F(NAME, FUNC, NPARMS, INITFN, nullptr)
+
+#define RS_MODEL_ACC_NAMED_F(NAME, FUNC, NPARMS, INITFN, FORCFN)                 \
+    extern "C" const rs_model_desc *rs_model_##NAME(void)                        \
+    {                                                                            \
+        static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched_acc<FUNC>, INITFN, FORCFN, \
+                                        rs_launch_groups<FUNC>};                 \
+        return &d;                                                               \
+    }
+/* accessor-form model with RS_MODEL_PARMS(NPARMS) declared earlier in the same file */
+#define RS_MODEL_ACC(FUNC, NPARMS) RS_MODEL_ACC_NAMED_F(FUNC, FUNC, NPARMS, rs_model_init_, nullptr)
 
 /* model with RS_MODEL_PARMS(NPARMS) declared earlier in the same file */
 #define RS_MODEL(FUNC, NPARMS) RS_MODEL_NAMED(FUNC, FUNC, NPARMS, rs_model_init_)

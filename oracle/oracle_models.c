@@ -23,18 +23,20 @@ void diff2d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
 {
     (void)neq; (void)t; (void)yout;
     const int d1 = ip[4], d2 = ip[5], variant = ip[7];
+    const rsm_d2_coef c = rsm_diff2d_coef(p_d2);
     for (int j = 0; j < d1; j++)
-        for (int k = 0; k < d2; k++) ydot[j * d2 + k] = rsm_diff2d_point(y, j, k, d1, d2, p_d2, variant);
+        for (int k = 0; k < d2; k++) ydot[j * d2 + k] = rsm_diff2d_point(y, j, k, d1, d2, c, variant);
 }
 
 void diff3d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
 {
     (void)neq; (void)t; (void)yout;
     const int d1 = ip[4], d2 = ip[5], d3 = ip[6], variant = ip[7];
+    const rsm_d3_coef c = rsm_diff3d_coef(p_d3);
     for (int j = 0; j < d1; j++)
         for (int k = 0; k < d2; k++)
             for (int l = 0; l < d3; l++)
-                ydot[(j * d2 + k) * d3 + l] = rsm_diff3d_point(y, j, k, l, d1, d2, d3, p_d3, variant);
+                ydot[(j * d2 + k) * d3 + l] = rsm_diff3d_point(y, j, k, l, d1, d2, d3, c, variant);
 }
 
 void rd3d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
@@ -42,11 +44,12 @@ void rd3d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
     (void)neq; (void)t; (void)yout;
     const int d1 = ip[4], d2 = ip[5], d3 = ip[6];
     const long nc = (long)d1 * d2 * d3;
+    const rsm_rd3_coef c = rsm_rd3d_coef(p_rd3);
     for (int s = 0; s < 2; s++)
         for (int j = 0; j < d1; j++)
             for (int k = 0; k < d2; k++)
                 for (int l = 0; l < d3; l++)
-                    ydot[s * nc + (j * d2 + k) * d3 + l] = rsm_rd3d_point(y, s, j, k, l, d1, d2, d3, p_rd3);
+                    ydot[s * nc + (j * d2 + k) * d3 + l] = rsm_rd3d_point(y, s, j, k, l, d1, d2, d3, c);
 }
 
 void rt1d(int *neq, double *t, double *y, double *ydot, double *yout, int *ip)
@@ -120,10 +123,11 @@ void diff3dms(int *neq, double *t, double *y, double *ydot, double *yout, int *i
     (void)neq; (void)t;
     const int d1 = ip[4], d2 = ip[5], d3 = ip[6];
     const double *tab = yout + ip[0];
+    const rsm_d3_coef c = rsm_diff3d_coef(p_d3ms);
     for (int j = 0; j < d1; j++)
         for (int k = 0; k < d2; k++)
             for (int l = 0; l < d3; l++)
-                ydot[(j * d2 + k) * d3 + l] = rsm_diff3dms_point(y, j, k, l, d1, d2, d3, p_d3ms, tab);
+                ydot[(j * d2 + k) * d3 + l] = rsm_diff3dms_point(y, j, k, l, d1, d2, d3, c, p_d3ms[8], p_d3ms[9], tab);
 }
 
 /* vignettes/rootSolve.Rnw:615-663, zero-flux 2-D diffusion with quadratic consumption and point sources */

@@ -505,6 +505,8 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
                             s.grid.type ? s.grid.ncell : n, &s.ctl, &s.own, comm_active() ? &s.halo : nullptr,
                             s.grid.type ? &s.grid : nullptr));
         mark("krylov set-up");
+        // the FD assembly shares the SpMV's knowledge of the grid (pattern verified row by row in krylov_setup)
+        s.fd.gridcols = s.kry.gridcols; s.fd.gd1 = s.kry.gd1; s.fd.gd2 = s.kry.gd2; s.fd.gd3 = s.kry.gd3; s.fd.gncell = s.kry.ncell;
     }
     RS_CUDA(cudaEventRecord(e1, c.stream));
     RS_CUDA(cudaEventSynchronize(e1));

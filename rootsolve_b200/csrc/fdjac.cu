@@ -16,6 +16,7 @@
 // arithmetic is.
 #include <algorithm>
 
+#include "grid_stencil.cuh"
 #include "solver.cuh"
 
 namespace rs {
@@ -67,12 +68,61 @@ __global__ void __launch_bounds__(256) assemble_kernel(int row0, int row1, const
     }
 }
 
+// The same on a verified regular grid (FdWork::gridcols): one thread per row, the row's columns computed from its
+// grid position (GridRow, ascending = the order of the row-wise arrays), so col[] is not read; all gathers of a row
+// (y, group, then the residual planes) are issued back to back, and the values of a 256-row tile leave through shared
+// memory as one contiguous, coalesced slice of val[].  Same arithmetic per entry as assemble_kernel.
+template <int NSPEC>
+__global__ void __launch_bounds__(256) assemble_grid_kernel(GridCols g, int row0, int row1, const int *__restrict__ rowptr,
+                                                            const int *__restrict__ group_of, const double *__restrict__ y,
+                                                            const double *__restrict__ F, long long ld,
+                                                            double *__restrict__ val, double *__restrict__ beta)
+{
+    constexpr int NSLOT = GridRow<NSPEC>::NSLOT;
+    __shared__ double sv[256 * NSLOT];
+    __shared__ int s_base, s_end;
+    const int ntiles = (row1 - row0 + 255) / 256;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int i0 = row0 + tile * 256, i1 = min(row1, i0 + 256);
+        const int i = i0 + (int)threadIdx.x;
+        const bool valid = i < i1;
+        if (threadIdx.x == 0) { s_base = rowptr[i0]; s_end = rowptr[i1]; }
+        GridRow<NSPEC> gr;
+        gr.set(g, valid ? i : i0, valid);
+        const double f0 = valid ? F[i] : 0.0;
+        if (valid) beta[i] = -f0;
+        const int pb = valid ? rowptr[i] : 0;
+        double yv[NSLOT], fg[NSLOT];
+        int gg[NSLOT];
+#pragma unroll
+        for (int q = 0; q < NSLOT; q++) {
+            yv[q] = gr.has[q] ? y[gr.c[q]] : 0.0;
+            gg[q] = gr.has[q] ? group_of[gr.c[q]] : 0;
+        }
+#pragma unroll
+        for (int q = 0; q < NSLOT; q++) fg[q] = gr.has[q] ? F[(long long)(gg[q] + 1) * ld + i] : 0.0;
+        __syncthreads();
+        int p = pb - s_base;
+#pragma unroll
+        for (int q = 0; q < NSLOT; q++)
+            if (gr.has[q]) {
+                const double divdelt = perturbed(yv[q]) - yv[q];
+                sv[p++] = (fg[q] + (-f0)) / divdelt;
+            }
+        __syncthreads();
+        const int cnt = s_end - s_base;
+        for (int e = threadIdx.x; e < cnt; e += 256) val[s_base + e] = sv[e];
+        __syncthreads();
+    }
+}
+
 int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, int nrpar, const int *ipar,
              int nipar, int slab_j0, int slab_j1)
 {
     // 256-byte aligned leading dimension so every evaluation starts on a fresh line
     w.ld = ((long long)n + 31) / 32 * 32;
-    RS_TRY(w.Y.alloc((size_t)w.ld * (ngp + 1)));
+    w.ngp_alloc = ngp;
+    // Y (the ngp perturbed states side by side) is only needed by models in pointer form: allocated on first use
     RS_TRY(w.F.alloc((size_t)w.ld * (ngp + 1)));
     // ipar / out exactly as initOut builds them (src/steady_utils.c:109-124), then the slab bounds
     const int lrpar = nout + nrpar, lipar = 3 + nipar;
@@ -124,14 +174,22 @@ int fd_groups(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp
 {
     const long long work = own.total();
     const double frac = (double)work / (double)n;
-    {
-        const double nt = (double)touch.total();
-        Launch L(c, K_PERTURB, 12.0 * nt + 8.0 * nt * ngp);
-        for (int q = 0; q < touch.n; q++)
-            perturb_kernel<<<grid_for(touch.e[q] - touch.b[q], 256), 256, 0, c.stream>>>(touch.b[q], touch.e[q], ngp, d_y, d_group_of,
-                                                                                       w.Y.p, w.ld);
-    }
-    if (ngp > 0) {
+    if (m->launch_groups && ngp > 0) {
+        // accessor-form model: the ngp perturbed states are never written -- every evaluation reads y and the group
+        // map and adds its increment on the fly (B_res = 8N + 4N + 8N per evaluation written)
+        Launch L(c, K_RESIDUAL, 12.0 * work + 8.0 * work * ngp);
+        const int e = m->launch_groups((void *)c.stream, n, t, d_y, d_group_of, 0, ngp, w.F.p + w.ld, w.ld, w.yout.p + w.ldout, w.ldout,
+                                       w.ip.p, work);
+        if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
+    } else if (ngp > 0) {
+        if (!w.Y.p) RS_TRY(w.Y.alloc((size_t)w.ld * (w.ngp_alloc + 1)));
+        {
+            const double nt = (double)touch.total();
+            Launch L(c, K_PERTURB, 12.0 * nt + 8.0 * nt * ngp);
+            for (int q = 0; q < touch.n; q++)
+                perturb_kernel<<<grid_for(touch.e[q] - touch.b[q], 256), 256, 0, c.stream>>>(touch.b[q], touch.e[q], ngp, d_y, d_group_of,
+                                                                                           w.Y.p, w.ld);
+        }
         Launch L(c, K_RESIDUAL, 16.0 * work * ngp);
         const int e = m->launch((void *)c.stream, n, t, w.Y.p + w.ld, w.F.p + w.ld, w.ld, ngp, w.yout.p + w.ldout, w.ldout, w.ip.p, work);
         if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
@@ -140,8 +198,18 @@ int fd_groups(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp
         Launch L(c, K_ASSEMBLE, (20.0 * nnz + 20.0 * n) * frac);
         for (int q = 0; q < own.n; q++) {
             const long long rows = own.e[q] - own.b[q];
-            assemble_kernel<8><<<grid_for(rows * 8, 256, 148 * 16), 256, 0, c.stream>>>(own.b[q], own.e[q], d_rowptr, d_col,
-                                                                                      d_group_of, d_y, w.F.p, w.ld, d_val, d_beta);
+            if (rows <= 0) continue;
+            if (w.gridcols) {
+                const GridCols g{w.gd1, w.gd2, w.gd3, w.gd2 * w.gd3, w.gncell};
+                const int blocks = (int)std::min<long long>((rows + 255) / 256, 148 * 8);
+                if (w.gridcols == 1)
+                    assemble_grid_kernel<1><<<blocks, 256, 0, c.stream>>>(g, own.b[q], own.e[q], d_rowptr, d_group_of, d_y, w.F.p, w.ld, d_val, d_beta);
+                else
+                    assemble_grid_kernel<2><<<blocks, 256, 0, c.stream>>>(g, own.b[q], own.e[q], d_rowptr, d_group_of, d_y, w.F.p, w.ld, d_val, d_beta);
+            } else {
+                assemble_kernel<8><<<grid_for(rows * 8, 256, 148 * 16), 256, 0, c.stream>>>(own.b[q], own.e[q], d_rowptr, d_col,
+                                                                                          d_group_of, d_y, w.F.p, w.ld, d_val, d_beta);
+            }
         }
     }
     RS_CUDA(cudaGetLastError());
@@ -231,6 +299,7 @@ int detect_structure(Ctx &c, const rs_model_desc *m, int n, double t, const doub
     if (B > n) B = n;
     FdWork w;
     RS_TRY(fd_setup(c, w, n, (int)B - 1, nout, rpar, nrpar, ipar, nipar, 0, -1));
+    RS_TRY(w.Y.alloc((size_t)w.ld * B));
     const int words = (n + 31) / 32;
     DevBuf<double> F0;
     DevBuf<unsigned> mask;

@@ -26,6 +26,7 @@
 #include <cstdlib>
 #include <cstring>
 
+#include "grid_stencil.cuh"
 #include "solver.cuh"
 
 namespace rs {
@@ -296,34 +297,6 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int row0, int row
 // Algorithmic bytes: 8 Z + 4 (N+1) + 16 N.  The arithmetic (entry order, one FMA chain per row) is that
 // of the CSR kernels, so the result is bit-identical.  krylov_setup verifies the pattern row by row
 // (grid_cols_check_kernel) before this path is taken.
-struct GridCols { int d1, d2, d3, s1, ncell; };
-
-template <int NSPEC>
-struct GridRow {
-    static constexpr int NSLOT = NSPEC == 1 ? 7 : 9;
-    int c[NSLOT];
-    bool has[NSLOT];
-    // candidate columns of row r in ascending order; has[q]: the entry exists
-    __device__ __forceinline__ void set(const GridCols &g, int r, bool valid)
-    {
-        int sp = 0, cell = r;
-        if (NSPEC == 2 && r >= g.ncell) { sp = 1; cell = r - g.ncell; }
-        const int j = cell / g.s1, rem = cell - j * g.s1, k = rem / g.d3, l = rem - k * g.d3;
-        constexpr int o = NSPEC == 1 ? 0 : 1;
-        if (NSPEC == 2) {
-            has[0] = valid && sp == 1; c[0] = cell;                    // species 0 of the same cell
-            has[NSLOT - 1] = valid && sp == 0; c[NSLOT - 1] = cell + g.ncell;   // species 1 of the same cell
-        }
-        has[o + 0] = valid && j > 0;        c[o + 0] = r - g.s1;
-        has[o + 1] = valid && k > 0;        c[o + 1] = r - g.d3;
-        has[o + 2] = valid && l > 0;        c[o + 2] = r - 1;
-        has[o + 3] = valid;                 c[o + 3] = r;
-        has[o + 4] = valid && l < g.d3 - 1; c[o + 4] = r + 1;
-        has[o + 5] = valid && k < g.d2 - 1; c[o + 5] = r + g.d3;
-        has[o + 6] = valid && j < g.d1 - 1; c[o + 6] = r + g.s1;
-    }
-};
-
 template <int NSPEC>
 __global__ void grid_cols_check_kernel(GridCols g, int row0, int row1, const int *__restrict__ rowptr,
                                        const int *__restrict__ col, int *__restrict__ bad)

@@ -49,6 +49,10 @@ struct FdWork {
     DevBuf<double> yout;     // (ngp+1) x ldout
     DevBuf<int> ip;          // reference ipar block + slab bounds
     long long ld = 0, ldout = 0;
+    int ngp_alloc = 0;
+    // non-cyclic grid with 1-2 species whose row-wise pattern krylov_setup verified (0 = general structure): the
+    // assembly then computes the column of every entry from the row's grid position instead of reading col[]
+    int gridcols = 0, gd1 = 1, gd2 = 1, gd3 = 1, gncell = 0;
 };
 int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, int nrpar, const int *ipar,
              int nipar, int slab_j0, int slab_j1);

@@ -25,10 +25,19 @@
 #ifndef RSM_MODEL_MATH_H
 #define RSM_MODEL_MATH_H
 
+#ifndef RSM_HD
 #ifdef __CUDACC__
 #define RSM_HD __host__ __device__ __forceinline__
 #else
 #define RSM_HD static inline
+#endif
+#endif
+
+/* The state argument of the point functions: a plain vector for the host wrappers; the device models define it as
+ * the SDK's rs_state before including this file, so that y[i] carries the finite-difference increment of the
+ * evaluation on the fly (rootsolve_b200_model.cuh, accessor form).  Both support y[i] and y + offset. */
+#ifndef RSM_STATE
+#define RSM_STATE const double *
 #endif
 
 /* ---- parameter slots ------------------------------------------------- */
@@ -56,22 +65,35 @@ RSM_HD double rsm_flux_div(double ylo, double yc, double yhi, double D, double h
     return (fhi - flo) / h;
 }
 
-/* variant: 0 = first-order consumption -r*y ; 1 = Monod -rmax*y/(y+ks) */
-RSM_HD double rsm_diff2d_point(const double *y, int j, int k, int d1, int d2,
-                               const double *p, int variant)
+/* The same flux divergence with the coefficient w = D / h^2 formed once per model call instead of three divisions
+ * per direction and cell: (Flux_hi - Flux_lo)/h = w * ((yc - ylo) - (yhi - yc)).  For D = h = 1 (the reference's
+ * examples, the goldens) both forms round identically. */
+RSM_HD double rsm_flux_div_w(double ylo, double yc, double yhi, double w)
 {
-    const double Dx = p[0], Dy = p[1], dx = p[2], dy = p[3], r = p[4], ks = p[5], bnd = p[6];
+    return w * ((yc - ylo) - (yhi - yc));
+}
+
+/* variant: 0 = first-order consumption -r*y ; 1 = Monod -rmax*y/(y+ks) */
+typedef struct { double wx, wy, r, ks, bnd; } rsm_d2_coef;
+RSM_HD rsm_d2_coef rsm_diff2d_coef(const double *p)
+{
+    rsm_d2_coef c;
+    c.wx = p[0] / (p[2] * p[2]); c.wy = p[1] / (p[3] * p[3]); c.r = p[4]; c.ks = p[5]; c.bnd = p[6];
+    return c;
+}
+RSM_HD double rsm_diff2d_point(RSM_STATE y, int j, int k, int d1, int d2, const rsm_d2_coef c, int variant)
+{
     const int idx = j * d2 + k;
     const double yc = y[idx];
-    double dY = (variant == 1) ? -r * yc / (yc + ks) : -r * yc;
+    double dY = (variant == 1) ? -c.r * yc / (yc + c.ks) : -c.r * yc;
     /* "X" = first R dimension = fastest index k */
-    double ylo = (k > 0) ? y[idx - 1] : bnd;
-    double yhi = (k < d2 - 1) ? y[idx + 1] : bnd;
-    dY = dY - rsm_flux_div(ylo, yc, yhi, Dx, dx);
+    double ylo = (k > 0) ? y[idx - 1] : c.bnd;
+    double yhi = (k < d2 - 1) ? y[idx + 1] : c.bnd;
+    dY = dY - rsm_flux_div_w(ylo, yc, yhi, c.wx);
     /* "Y" = second R dimension = j */
-    ylo = (j > 0) ? y[idx - d2] : bnd;
-    yhi = (j < d1 - 1) ? y[idx + d2] : bnd;
-    dY = dY - rsm_flux_div(ylo, yc, yhi, Dy, dy);
+    ylo = (j > 0) ? y[idx - d2] : c.bnd;
+    yhi = (j < d1 - 1) ? y[idx + d2] : c.bnd;
+    dY = dY - rsm_flux_div_w(ylo, yc, yhi, c.wy);
     return dY;
 }
 
@@ -82,7 +104,7 @@ RSM_HD double rsm_diff2d_point(const double *y, int j, int k, int d1, int d2,
  * p[0]=Dx p[1]=Dy p[2]=dx p[3]=dy p[4]=r p[5]=BND p[6]=extra flux (10) p[7]=exchange rate (10)
  * j = index of the second R dimension (slow), k = index of the first (fast), as everywhere in this file. */
 #define RSM_D2B_NPAR 8
-RSM_HD double rsm_diff2db_point(const double *y, int j, int k, int d1, int d2, const double *p)
+RSM_HD double rsm_diff2db_point(RSM_STATE y, int j, int k, int d1, int d2, const double *p)
 {
     const double Dx = p[0], Dy = p[1], dx = p[2], dy = p[3], r = p[4], bnd = p[5], extra = p[6], exch = p[7];
     const int idx = j * d2 + k;
@@ -99,19 +121,24 @@ RSM_HD double rsm_diff2db_point(const double *y, int j, int k, int d1, int d2, c
 /* variant: 0 = each direction once ; 1 = each direction applied twice, in the
  * order the vignette's three loops apply them (vignettes/rootSolve.Rnw:686-722):
  * (y,z) for fixed x-slices, (x,z), (x,y). */
-RSM_HD double rsm_diff3d_point(const double *y, int j, int k, int l, int d1, int d2, int d3,
-                               const double *p, int variant)
+typedef struct { double wx, wy, wz, r, bnd; } rsm_d3_coef;
+RSM_HD rsm_d3_coef rsm_diff3d_coef(const double *p)
 {
-    const double Dx = p[0], Dy = p[1], Dz = p[2], dx = p[3], dy = p[4], dz = p[5], r = p[6],
-                 bnd = p[7];
+    rsm_d3_coef c;
+    c.wx = p[0] / (p[3] * p[3]); c.wy = p[1] / (p[4] * p[4]); c.wz = p[2] / (p[5] * p[5]); c.r = p[6]; c.bnd = p[7];
+    return c;
+}
+RSM_HD double rsm_diff3d_point(RSM_STATE y, int j, int k, int l, int d1, int d2, int d3, const rsm_d3_coef c, int variant)
+{
+    const double r = c.r, bnd = c.bnd;
     const int s2 = d3, s1 = d2 * d3;
     const int idx = j * s1 + k * s2 + l;
     const double yc = y[idx];
     double dY = -r * yc;
     /* x = first R dim = l ; y = second R dim = k ; z = third R dim = j */
-    const double gx = rsm_flux_div((l > 0) ? y[idx - 1] : bnd, yc, (l < d3 - 1) ? y[idx + 1] : bnd, Dx, dx);
-    const double gy = rsm_flux_div((k > 0) ? y[idx - s2] : bnd, yc, (k < d2 - 1) ? y[idx + s2] : bnd, Dy, dy);
-    const double gz = rsm_flux_div((j > 0) ? y[idx - s1] : bnd, yc, (j < d1 - 1) ? y[idx + s1] : bnd, Dz, dz);
+    const double gx = rsm_flux_div_w((l > 0) ? y[idx - 1] : bnd, yc, (l < d3 - 1) ? y[idx + 1] : bnd, c.wx);
+    const double gy = rsm_flux_div_w((k > 0) ? y[idx - s2] : bnd, yc, (k < d2 - 1) ? y[idx + s2] : bnd, c.wy);
+    const double gz = rsm_flux_div_w((j > 0) ? y[idx - s1] : bnd, yc, (j < d1 - 1) ? y[idx + s1] : bnd, c.wz);
     if (variant == 1) {
         dY = dY - gy; dY = dY - gz;
         dY = dY - gx; dY = dY - gz;
@@ -124,22 +151,30 @@ RSM_HD double rsm_diff3d_point(const double *y, int j, int k, int l, int d1, int
 
 /* Two species u (s=0), v (s=1) on a 3-D grid:
  *   du = D1 lap(u) - k u v ;  dv = D2 lap(v) + k u v - m v ; Dirichlet faces. */
-RSM_HD double rsm_rd3d_point(const double *y, int s, int j, int k, int l, int d1, int d2, int d3,
-                             const double *p)
+typedef struct { double wx[2], wy[2], wz[2], kk, m, bnd[2]; } rsm_rd3_coef;
+RSM_HD rsm_rd3_coef rsm_rd3d_coef(const double *p)
 {
-    const double D = (s == 0) ? p[0] : p[1];
-    const double dx = p[2], dy = p[3], dz = p[4], kk = p[5], m = p[6];
-    const double bnd = (s == 0) ? p[7] : p[8];
+    rsm_rd3_coef c;
+    for (int s = 0; s < 2; s++) {
+        c.wx[s] = p[s] / (p[2] * p[2]); c.wy[s] = p[s] / (p[3] * p[3]); c.wz[s] = p[s] / (p[4] * p[4]);
+        c.bnd[s] = p[7 + s];
+    }
+    c.kk = p[5]; c.m = p[6];
+    return c;
+}
+RSM_HD double rsm_rd3d_point(RSM_STATE y, int s, int j, int k, int l, int d1, int d2, int d3, const rsm_rd3_coef c)
+{
+    const double bnd = c.bnd[s];
     const int s2 = d3, s1 = d2 * d3, nc = d1 * d2 * d3;
     const int cell = j * s1 + k * s2 + l;
-    const double *ys = y + (long)s * nc;
+    RSM_STATE ys = y + (long)s * nc;
     const double yc = ys[cell];
     const double u = y[cell], v = y[nc + cell];
-    const double react = kk * u * v;
-    double dY = (s == 0) ? -react : (react - m * v);
-    dY = dY - rsm_flux_div((l > 0) ? ys[cell - 1] : bnd, yc, (l < d3 - 1) ? ys[cell + 1] : bnd, D, dx);
-    dY = dY - rsm_flux_div((k > 0) ? ys[cell - s2] : bnd, yc, (k < d2 - 1) ? ys[cell + s2] : bnd, D, dy);
-    dY = dY - rsm_flux_div((j > 0) ? ys[cell - s1] : bnd, yc, (j < d1 - 1) ? ys[cell + s1] : bnd, D, dz);
+    const double react = c.kk * u * v;
+    double dY = (s == 0) ? -react : (react - c.m * v);
+    dY = dY - rsm_flux_div_w((l > 0) ? ys[cell - 1] : bnd, yc, (l < d3 - 1) ? ys[cell + 1] : bnd, c.wx[s]);
+    dY = dY - rsm_flux_div_w((k > 0) ? ys[cell - s2] : bnd, yc, (k < d2 - 1) ? ys[cell + s2] : bnd, c.wy[s]);
+    dY = dY - rsm_flux_div_w((j > 0) ? ys[cell - s1] : bnd, yc, (j < d1 - 1) ? ys[cell + s1] : bnd, c.wz[s]);
     return dY;
 }
 
@@ -152,10 +187,10 @@ RSM_HD double rsm_rd3d_point(const double *y, int s, int j, int k, int l, int d1
  * gradient.  The coupling is one-sided (species s depends on s+1), so the
  * Jacobian is nonsymmetric, while sparse1d still allocates the full
  * nspec x nspec cell block (src/sparsecoeff.f:70-75). */
-RSM_HD double rsm_rt1d_point(const double *y, int s, int j, int nspec, int nb, const double *p)
+RSM_HD double rsm_rt1d_point(RSM_STATE y, int s, int j, int nspec, int nb, const double *p)
 {
     const double v = p[0], D = p[1], dx = p[2], r = p[3], ks = p[4], bnd = p[5], r0 = p[6];
-    const double *ys = y + (long)s * nb;
+    RSM_STATE ys = y + (long)s * nb;
     const double yc = ys[j];
     const double ylo = (j > 0) ? ys[j - 1] : bnd;
     const double yhi = (j < nb - 1) ? ys[j + 1] : yc; /* zero gradient */
@@ -180,15 +215,15 @@ RSM_HD double rsm_rt1d_point(const double *y, int s, int j, int nspec, int nb, c
  * One output VECTOR: the decay rate in every box (nout = nb).
  * p[0]=v p[1]=dx p[2]=r p[3]=p p[4]=O2sat p[5]=O2_0 p[6]=BOD_0 p[7]=ksO2 (10 in the man page) */
 #define RSM_O2BOD_NPAR 8
-RSM_HD double rsm_o2bod_rate(const double *y, int j, int nb, const double *p)
+RSM_HD double rsm_o2bod_rate(RSM_STATE y, int j, int nb, const double *p)
 {
     const double BOD = y[j], O2 = y[nb + j];
     return p[2] * BOD * O2 / (O2 + p[7]);
 }
-RSM_HD double rsm_o2bod_point(const double *y, int s, int j, int nb, const double *p)
+RSM_HD double rsm_o2bod_point(RSM_STATE y, int s, int j, int nb, const double *p)
 {
     const double v = p[0], dx = p[1], rea = p[3], O2sat = p[4];
-    const double *ys = y + (long)s * nb;
+    RSM_STATE ys = y + (long)s * nb;
     const double upstream = (j > 0) ? ys[j - 1] : ((s == 0) ? p[6] : p[5]);
     const double flo = v * upstream, fhi = v * ys[j];      /* FluxX <- v * c(X_0, X) */
     const double rate = rsm_o2bod_rate(y, j, nb, p);
@@ -272,11 +307,11 @@ RSM_HD double rsm_diffmap_point(const double *y, int c, const int *inv, const in
  * y* = BND + a*sj*sk*sl in closed form, at every grid size.  The tables arrive in rpar (after the nout outputs in
  * yout, src/steady_utils.c:109-124); p[0..7] as diff3d, p[8] = c0, p[9] = c1. */
 #define RSM_D3MS_NPAR 10
-RSM_HD double rsm_diff3dms_point(const double *y, int j, int k, int l, int d1, int d2, int d3, const double *p,
-                                 const double *tab)
+RSM_HD double rsm_diff3dms_point(RSM_STATE y, int j, int k, int l, int d1, int d2, int d3, const rsm_d3_coef c,
+                                 double c0, double c1, const double *tab)
 {
-    const double S = p[8] + p[9] * ((tab[j] * tab[d1 + k]) * tab[d1 + d2 + l]);
-    return rsm_diff3d_point(y, j, k, l, d1, d2, d3, p, 0) + S;
+    const double S = c0 + c1 * ((tab[j] * tab[d1 + k]) * tab[d1 + d2 + l]);
+    return rsm_diff3d_point(y, j, k, l, d1, d2, d3, c, 0) + S;
 }
 
 /* The 2-D example of the vignette (vignettes/rootSolve.Rnw:615-663, `diffusion2D`): diffusion with ZERO-FLUX
@@ -286,7 +321,7 @@ RSM_HD double rsm_diff3dms_point(const double *y, int j, int k, int l, int d1, i
  * p[0]=Dx p[1]=Dy p[2]=dx p[3]=dy p[4]=r p[5]=p ; ip[3]=1 ip[4]=d1 ip[5]=d2 ip[6]=1 ip[7]=nsrc, then nsrc 0-based
  * state-vector positions of the producing cells (the R code draws them with runif; the tests seed them). */
 #define RSM_D2Q_NPAR 6
-RSM_HD double rsm_diff2dq_point(const double *y, int j, int k, int d1, int d2, const double *p, const int *src, int nsrc)
+RSM_HD double rsm_diff2dq_point(RSM_STATE y, int j, int k, int d1, int d2, const double *p, const int *src, int nsrc)
 {
     const double Dx = p[0], Dy = p[1], dx = p[2], dy = p[3], r = p[4], prod = p[5];
     const int idx = j * d2 + k;
@@ -309,7 +344,7 @@ RSM_HD double rsm_diff2dq_point(const double *y, int j, int k, int d1, int d2, c
  * diagonal into row N/2.  Solved by the reference with the default sparsetype = "sparseint".
  * p[0]=v p[1]=flux p[2]=dx p[3]=Kz p[4]=decay p[5]=ing ; ip[3]=1 ip[4]=N. */
 #define RSM_SED_NPAR 6
-RSM_HD double rsm_sediment_point(const double *y, int i, int N, const double *p)
+RSM_HD double rsm_sediment_point(RSM_STATE y, int i, int N, const double *p)
 {
     const double v = p[0], flux = p[1], dx = p[2], Kz = p[3], decay = p[4], ing = p[5];
     /* Flux through the upper (i) and lower (i+1) interface of layer i */

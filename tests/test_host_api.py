@@ -100,11 +100,13 @@ def test_model_library_descriptors(built):
 
     class Desc(C.Structure):
         _fields_ = [("abi", C.c_int), ("name", C.c_char_p), ("nparms", C.c_int), ("launch", C.c_void_p),
-                    ("initfunc", C.c_void_p), ("initforc", C.c_void_p)]
+                    ("initfunc", C.c_void_p), ("initforc", C.c_void_p), ("launch_groups", C.c_void_p)]
     for name, npar in [("diff2d", 7), ("diff3d", 8), ("rd3d", 10), ("rt1d", 7), ("anoxmod", 9), ("diffmap", 8), ("anoxforc", 9)]:
         d = C.cast(_capi.model_symbol(name), C.POINTER(Desc)).contents
-        assert d.abi == 1 and d.name.decode() == name and d.nparms == npar and d.launch and d.initfunc
+        assert d.abi == 2 and d.name.decode() == name and d.nparms == npar and d.launch and d.initfunc
         assert bool(d.initforc) == (name == "anoxforc")
+        # the grid models are in accessor form (perturbation on the fly), the small general ones in pointer form
+        assert bool(d.launch_groups) == (name in ("diff2d", "diff3d", "rd3d", "rt1d"))
     with pytest.raises(ValueError, match="dyn function not loaded"):
         _capi.model_symbol("no_such_model")
 
