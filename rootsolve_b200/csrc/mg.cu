@@ -648,8 +648,10 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     const MgLevelDev &D = L.dev;
     const double n = (double)D.n, mat = 8.0 * n * (6.0 + D.nspec);
     const int grid = mg_grid(D.ncell);
+    // statistics: the smoothing passes and the transfers of the finest level on their own, every level below as one class
+    const int k_smooth = l == 0 ? K_MG_SMOOTH_L0 : K_MG_COARSE, k_transfer = l == 0 ? K_MG_TRANSFER_L0 : K_MG_COARSE;
     if (l == M.nlev - 1) {
-        Launch La(c, K_PRECOND_APPLY, 8.0 * M.nc * M.nc + 16.0 * M.nc);
+        Launch La(c, K_MG_COARSE, 8.0 * M.nc * M.nc + 16.0 * M.nc);
         mg_coarse_solve_kernel<<<1, 256, sizeof(double) * M.nc, st>>>(M.nc, M.cinv.p, b.p, xout.p);
         return;
     }
@@ -657,30 +659,30 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     const VecView x = view(L.x.p, D.ncell), r = view(L.r.p, D.ncell), d = view(L.d.p, D.ncell);
     const VecView none = view(nullptr, 0);
     {   // pre-smoothing from a zero guess: two Chebyshev steps, one pass over the matrix
-        Launch La(c, K_PRECOND_APPLY, 16.0 * n + 8.0 * D.nspec * n);
+        Launch La(c, k_smooth, 16.0 * n + 8.0 * D.nspec * n);
         mg_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, d);
     }
     {
-        Launch La(c, K_PRECOND_APPLY, mat + 24.0 * n + 8.0 * D.nspec * n);
+        Launch La(c, k_smooth, mat + 24.0 * n + 8.0 * D.nspec * n);
         mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, b, d, none, x, none, nullptr, nullptr, nullptr, PeerRed());
     }
     {   // residual, summed over the aggregates
-        Launch La(c, K_PRECOND_APPLY, mat + 16.0 * n + 8.0 * Cn.dev.n);
+        Launch La(c, k_transfer, mat + 16.0 * n + 8.0 * Cn.dev.n);
         mg_resid_restrict_kernel<NS><<<mg_grid(Cn.dev.ncell), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d1, Cn.dev.d2, Cn.dev.d3,
                                                                           b, x, view(Cn.b.p, Cn.dev.ncell));
     }
     mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.x.p, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
     {
-        Launch La(c, K_PRECOND_APPLY, 16.0 * n + 8.0 * Cn.dev.n);
+        Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
         mg_prolong_kernel<<<grid, 256, 0, st>>>(D.nspec, D.d1, D.d2, D.d3, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3,
                                                 view(Cn.x.p, Cn.dev.ncell), x);
     }
     {   // post-smoothing: the same two Chebyshev steps, two passes
-        Launch La(c, K_PRECOND_APPLY, mat + 32.0 * n + 8.0 * D.nspec * n);
+        Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         mg_resid_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, x, r, d);
     }
     {
-        Launch La(c, K_PRECOND_APPLY, mat + 32.0 * n + 8.0 * D.nspec * n);
+        Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         if (dot_out)
             mg_second_kernel<NS, true><<<grid, 256, 0, st>>>(D, r, d, x, xout, b, partials, ticket, dot_out, pr);
         else
