@@ -46,6 +46,19 @@
  * or read.  The body of the function does not change.  RS_FOR_EACH_CELL walks a box of grid cells line by line
  * without an integer division per cell.
  *
+ * Row form (optional, on top of either form above).  xSparseJacob (src/sparse.f:461-525) perturbs all columns of a
+ * group at once because a model call is expensive and computes every row; what it extracts for entry (i, j) is
+ * f_i with column j alone perturbed -- the other columns of the group do not reach row i, that is what a group is.
+ * A model that can evaluate ONE row,
+ *
+ *     __device__ double mymod_row(long long i, double t, rs_state y, const double *yout, const int *ip)
+ *     {   return -parms[0] * y[i];   }           // must be, bit for bit, what mymod writes to ydot[i]
+ *     RS_MODEL_ACC_ROW(mymod, mymod_row, 3)
+ *
+ * lets the solver compute every entry of the Jacobian from registers: per row one evaluation of the row function for
+ * f_i(y) and one per entry of the row, the state read once, the values written once, no residual vectors in between.
+ * The entries are bit-identical to the grouped evaluation's.
+ *
  * The kernel that calls func is instantiated in the model's own translation
  * unit (template argument = the function), so the residual is inlined into
  * the batched launch; the solver library reaches it through the host function
@@ -77,17 +90,23 @@ struct rs_model_desc {
      * group_of[i] = 0-based column group of unknown i. */
     int (*launch_groups)(void *stream, int neq, double t, const double *y, const int *group_of, int g0, int ngroups,
                          double *ydot, long long ld, double *yout, long long ldout, int *ip, long long work);
+    /* Models that also export a ROW function (else NULL): the whole finite-difference Jacobian of rows [row0, row1) in
+     * one launch, val[p] = (f_i(y + delta_j e_j) - f_i(y)) / ((y_j + delta_j) - y_j) for entry p = (i, j = col[p]) of the
+     * row-wise arrays; nothing but y, the pattern and val touches memory. */
+    int (*launch_fd_rows)(void *stream, int row0, int row1, double t, const double *y, const int *rowptr, const int *col,
+                          double *val, const double *yout, const int *ip);
 };
 
 /* The state vector as an accessor-form model sees it. */
 struct rs_state {
     const double *y;
     const int *grp; /* column group of every unknown; may be NULL when g < 0 */
-    int g;          /* group whose columns carry the finite-difference increment; < 0: the state itself */
+    int g;          /* group whose columns carry the finite-difference increment; < 0: none */
+    long long pj;   /* single unknown that carries the increment (row form); < 0: none */
     __device__ __forceinline__ double operator[](long long i) const
     {
         const double v = y[i];
-        if (g >= 0 && grp[i] == g) {
+        if ((g >= 0 && grp[i] == g) || i == pj) {
             double d = fabs(v) * 1.0e-8; /* Perturb, src/steady.f:219-224 */
             if (d < 1.0e-8) d = 1.0e-8;
             return v + d;
@@ -96,7 +115,7 @@ struct rs_state {
     }
     __device__ __forceinline__ rs_state operator+(long long off) const
     {
-        rs_state s = {y + off, grp ? grp + off : grp, g};
+        rs_state s = {y + off, grp ? grp + off : grp, g, pj >= 0 ? pj - off : pj};
         return s;
     }
 };
@@ -188,7 +207,7 @@ __global__ void __launch_bounds__(256) rs_residual_batched_acc_kernel(int neq, d
     const long long b = blockIdx.y;
     int n = neq;
     double tt = t;
-    rs_state s = {y + b * ld, nullptr, -1};
+    rs_state s = {y + b * ld, nullptr, -1, -1};
     F(&n, &tt, s, ydot + b * ld, yout + b * ldout, ip);
 }
 
@@ -200,7 +219,7 @@ __global__ void __launch_bounds__(256) rs_residual_groups_kernel(int neq, double
     const long long b = blockIdx.y;
     int n = neq;
     double tt = t;
-    rs_state s = {y, group_of, g0 + (int)b};
+    rs_state s = {y, group_of, g0 + (int)b, -1};
     F(&n, &tt, s, ydot + b * ld, yout + b * ldout, ip);
 }
 
@@ -253,6 +272,61 @@ static int rs_launch_groups(void *stream, int neq, double t, const double *y, co
     return (int)cudaGetLastError();
 }
 
+/* ---- row form: the fused finite-difference Jacobian ---- */
+typedef double rs_row_func_t(long long, double, rs_state, const double *, const int *);
+#define RS_FD_TILE 256
+#define RS_FD_STAGE (RS_FD_TILE * 9)
+
+template <rs_row_func_t F>
+__global__ void __launch_bounds__(RS_FD_TILE) rs_fd_rows_kernel(int row0, int row1, double t, const double *__restrict__ y,
+                                                                 const int *__restrict__ rowptr, const int *__restrict__ col,
+                                                                 double *__restrict__ val, const double *yout, const int *ip)
+{
+    /* a tile of 256 consecutive rows owns one contiguous slice of val[]: staged in shared memory, written coalesced */
+    __shared__ double sv[RS_FD_STAGE];
+    __shared__ int s_base, s_end;
+    const int ntiles = (row1 - row0 + RS_FD_TILE - 1) / RS_FD_TILE;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int i0 = row0 + tile * RS_FD_TILE, i1 = min(row1, i0 + RS_FD_TILE);
+        const int i = i0 + (int)threadIdx.x;
+        const bool valid = i < i1;
+        if (threadIdx.x == 0) { s_base = rowptr[i0]; s_end = rowptr[i1]; }
+        __syncthreads();
+        const int base_p = s_base, cnt = s_end - s_base;
+        const bool staged = cnt <= RS_FD_STAGE;
+        if (valid) {
+            const rs_state s0 = {y, nullptr, -1, -1};
+            const double f0 = F(i, t, s0, yout, ip);
+            const int pe = rowptr[i + 1];
+            for (int p = rowptr[i]; p < pe; p++) {
+                const int j = col[p];
+                const double yj = y[j];
+                double d = fabs(yj) * 1.0e-8; /* Perturb, src/steady.f:219-224 */
+                if (d < 1.0e-8) d = 1.0e-8;
+                const double divdelt = (yj + d) - yj; /* the rounded difference, src/sparse.f:511 */
+                const rs_state sj = {y, nullptr, -1, j};
+                const double a = (F(i, t, sj, yout, ip) + (-f0)) / divdelt;
+                if (staged) sv[p - base_p] = a; else val[p] = a;
+            }
+        }
+        __syncthreads();
+        if (staged)
+            for (int e = threadIdx.x; e < cnt; e += RS_FD_TILE) val[base_p + e] = sv[e];
+        __syncthreads();
+    }
+}
+
+template <rs_row_func_t F>
+static int rs_launch_fd_rows(void *stream, int row0, int row1, double t, const double *y, const int *rowptr, const int *col,
+                             double *val, const double *yout, const int *ip)
+{
+    if (row1 <= row0) return 0;
+    long long blocks = ((long long)(row1 - row0) + RS_FD_TILE - 1) / RS_FD_TILE;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    rs_fd_rows_kernel<F><<<(unsigned)blocks, RS_FD_TILE, 0, (cudaStream_t)stream>>>(row0, row1, t, y, rowptr, col, val, yout, ip);
+    return (int)cudaGetLastError();
+}
+
 /* N parameters in __constant__ memory + the reference-style initialiser that fills them */
 #define RS_MODEL_PARMS(N)                                                        \
     static __constant__ double parms[N];                                         \
@@ -280,7 +354,7 @@ static int rs_launch_groups(void *stream, int neq, double t, const double *y, co
 #define RS_MODEL_NAMED_F(NAME, FUNC, NPARMS, INITFN, FORCFN)                     \
     extern "C" const rs_model_desc *rs_model_##NAME(void)                        \
     {                                                                            \
-        static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched<FUNC>, INITFN, FORCFN, nullptr}; \
+        static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched<FUNC>, INITFN, FORCFN, nullptr, nullptr}; \
         return &d;                                                               \
     }
 #define RS_MODEL_NAMED(NAME, FUNC, NPARMS, INITFN) RS_MODEL_NAMED_F(NAME, FUNC, NPARMS, INITFN, nullptr)
@@ -289,9 +363,18 @@ static int rs_launch_groups(void *stream, int neq, double t, const double *y, co
     extern "C" const rs_model_desc *rs_model_##NAME(void)                        \
     {                                                                            \
         static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched_acc<FUNC>, INITFN, FORCFN, \
-                                        rs_launch_groups<FUNC>};                 \
+                                        rs_launch_groups<FUNC>, nullptr};        \
         return &d;                                                               \
     }
+#define RS_MODEL_ACC_ROW_NAMED_F(NAME, FUNC, ROWFUNC, NPARMS, INITFN, FORCFN)    \
+    extern "C" const rs_model_desc *rs_model_##NAME(void)                        \
+    {                                                                            \
+        static const rs_model_desc d = {RS_MODEL_ABI, #NAME, NPARMS, rs_launch_batched_acc<FUNC>, INITFN, FORCFN, \
+                                        rs_launch_groups<FUNC>, rs_launch_fd_rows<ROWFUNC>}; \
+        return &d;                                                               \
+    }
+/* accessor-form model that also exports its row function */
+#define RS_MODEL_ACC_ROW(FUNC, ROWFUNC, NPARMS) RS_MODEL_ACC_ROW_NAMED_F(FUNC, FUNC, ROWFUNC, NPARMS, rs_model_init_, nullptr)
 /* accessor-form model with RS_MODEL_PARMS(NPARMS) declared earlier in the same file */
 #define RS_MODEL_ACC(FUNC, NPARMS) RS_MODEL_ACC_NAMED_F(FUNC, FUNC, NPARMS, rs_model_init_, nullptr)
 

@@ -108,7 +108,7 @@ void pool_free(void *p, size_t bytes)
 const char *const kKernelNames[K_COUNT] = {"structure", "scan", "transpose", "jgroup", "perturb", "residual_batched",
                                            "fd_assemble", "spmv_csr", "krylov_vec", "precond_setup", "precond_apply",
                                            "newton", "halo", "misc", "spmv_grid", "mg_smooth_l0", "mg_transfer_l0",
-                                           "mg_coarse_levels"};
+                                           "mg_coarse_levels", "fd_rows_fused"};
 
 void Ctx::begin(int id, double algo_bytes)
 {

@@ -15,6 +15,7 @@
 // -fmad=false, so a[] is bit-identical to the reference's when the model's own
 // arithmetic is.
 #include <algorithm>
+#include <cstdlib>
 
 #include "grid_stencil.cuh"
 #include "solver.cuh"
@@ -122,8 +123,9 @@ int fd_setup(Ctx &c, FdWork &w, int n, int ngp, int nout, const double *rpar, in
     // 256-byte aligned leading dimension so every evaluation starts on a fresh line
     w.ld = ((long long)n + 31) / 32 * 32;
     w.ngp_alloc = ngp;
-    // Y (the ngp perturbed states side by side) is only needed by models in pointer form: allocated on first use
-    RS_TRY(w.F.alloc((size_t)w.ld * (ngp + 1)));
+    // Y (the ngp perturbed states side by side) is only needed by models in pointer form, the ngp residual planes of
+    // F only by models without a row function: both are allocated on first use; plane 0 of F holds f(y)
+    RS_TRY(w.F.alloc((size_t)w.ld));
     // ipar / out exactly as initOut builds them (src/steady_utils.c:109-124), then the slab bounds
     const int lrpar = nout + nrpar, lipar = 3 + nipar;
     w.ldout = lrpar > 0 ? lrpar : 1;
@@ -174,6 +176,25 @@ int fd_groups(Ctx &c, const rs_model_desc *m, FdWork &w, int n, int nnz, int ngp
 {
     const long long work = own.total();
     const double frac = (double)work / (double)n;
+    const bool no_rows = getenv("RS_NO_FD_ROWS") != nullptr;   // tests compare the two routes
+    if (m->launch_fd_rows && !no_rows) {
+        // row form: every entry of J from one evaluation of the model's row function with the entry's column perturbed;
+        // bit-identical to the grouped evaluation (a column of a group is the only one of its group that reaches the row)
+        Launch L(c, K_FD_ROWS, (8.0 * n + 4.0 * (n + 1) + 12.0 * nnz) * frac);
+        for (int q = 0; q < own.n; q++) {
+            const int e = m->launch_fd_rows((void *)c.stream, own.b[q], own.e[q], t, d_y, d_rowptr, d_col, d_val, w.yout.p, w.ip.p);
+            if (e) { set_error("model launch failed: %s", cudaGetErrorString((cudaError_t)e)); return RS_ENODEVICE; }
+        }
+        return RS_OK;
+    }
+    if (w.F.n < (size_t)w.ld * (w.ngp_alloc + 1)) {   // grow F to its ngp + 1 planes, keeping f(y) in plane 0
+        DevBuf<double> big;
+        RS_TRY(big.alloc((size_t)w.ld * (w.ngp_alloc + 1)));
+        RS_CUDA(cudaMemcpyAsync(big.p, w.F.p, sizeof(double) * (size_t)w.ld, cudaMemcpyDeviceToDevice, c.stream));
+        RS_CUDA(cudaStreamSynchronize(c.stream));
+        std::swap(w.F.p, big.p);
+        std::swap(w.F.n, big.n);
+    }
     if (m->launch_groups && ngp > 0) {
         // accessor-form model: the ngp perturbed states are never written -- every evaluation reads y and the group
         // map and adds its increment on the fly (B_res = 8N + 4N + 8N per evaluation written)
@@ -300,6 +321,7 @@ int detect_structure(Ctx &c, const rs_model_desc *m, int n, double t, const doub
     FdWork w;
     RS_TRY(fd_setup(c, w, n, (int)B - 1, nout, rpar, nrpar, ipar, nipar, 0, -1));
     RS_TRY(w.Y.alloc((size_t)w.ld * B));
+    RS_TRY(w.F.alloc((size_t)w.ld * B));
     const int words = (n + 31) / 32;
     DevBuf<double> F0;
     DevBuf<unsigned> mask;

@@ -39,7 +39,7 @@ void set_error(const char *fmt, ...);
 enum KernelId {
     K_STRUCT = 0, K_SCAN, K_TRANSPOSE, K_JGROUP, K_PERTURB, K_RESIDUAL, K_ASSEMBLE, K_SPMV, K_VEC,
     K_PRECOND_SETUP, K_PRECOND_APPLY, K_NEWTON, K_HALO, K_MISC, K_SPMV_GRID, K_MG_SMOOTH_L0, K_MG_TRANSFER_L0, K_MG_COARSE,
-    K_COUNT
+    K_FD_ROWS, K_COUNT
 };
 extern const char *const kKernelNames[K_COUNT];
 

@@ -14,4 +14,11 @@ __device__ void diff2d(int *neq, double *t, rs_state y, double *ydot, double *yo
         ydot[it.j * d2 + k] = rsm_diff2d_point(y, it.j, k, d1, d2, c, variant);
 }
 
-RS_MODEL_ACC(diff2d, RSM_D2_NPAR)
+__device__ double diff2d_row(long long i, double t, rs_state y, const double *yout, const int *ip)
+{
+    const int d1 = ip[4], d2 = ip[5], variant = ip[7], idx = (int)i;
+    const int j = idx / d2, k = idx - j * d2;
+    return rsm_diff2d_point(y, j, k, d1, d2, rsm_diff2d_coef(parms), variant);
+}
+
+RS_MODEL_ACC_ROW(diff2d, diff2d_row, RSM_D2_NPAR)

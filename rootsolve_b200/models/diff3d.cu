@@ -16,4 +16,13 @@ __device__ void diff3d(int *neq, double *t, rs_state y, double *ydot, double *yo
         ydot[(it.j * d2 + it.k) * d3 + l] = rsm_diff3d_point(y, it.j, it.k, l, d1, d2, d3, c, variant);
 }
 
-RS_MODEL_ACC(diff3d, RSM_D3_NPAR)
+// one row of the same function: what the fused finite-difference Jacobian evaluates (row form of the SDK)
+__device__ double diff3d_row(long long i, double t, rs_state y, const double *yout, const int *ip)
+{
+    const int d1 = ip[4], d2 = ip[5], d3 = ip[6], variant = ip[7];
+    const int plane = d2 * d3, idx = (int)i;
+    const int j = idx / plane, rem = idx - j * plane, k = rem / d3, l = rem - k * d3;
+    return rsm_diff3d_point(y, j, k, l, d1, d2, d3, rsm_diff3d_coef(parms), variant);
+}
+
+RS_MODEL_ACC_ROW(diff3d, diff3d_row, RSM_D3_NPAR)

@@ -16,4 +16,12 @@ __device__ void diff3dms(int *neq, double *t, rs_state y, double *ydot, double *
         ydot[(it.j * d2 + it.k) * d3 + l] = rsm_diff3dms_point(y, it.j, it.k, l, d1, d2, d3, c, c0, c1, tab);
 }
 
-RS_MODEL_ACC(diff3dms, RSM_D3MS_NPAR)
+__device__ double diff3dms_row(long long i, double t, rs_state y, const double *yout, const int *ip)
+{
+    const int d1 = ip[4], d2 = ip[5], d3 = ip[6];
+    const int plane = d2 * d3, idx = (int)i;
+    const int j = idx / plane, rem = idx - j * plane, k = rem / d3, l = rem - k * d3;
+    return rsm_diff3dms_point(y, j, k, l, d1, d2, d3, rsm_diff3d_coef(parms), parms[8], parms[9], yout + ip[0]);
+}
+
+RS_MODEL_ACC_ROW(diff3dms, diff3dms_row, RSM_D3MS_NPAR)

@@ -17,4 +17,13 @@ __device__ void rd3d(int *neq, double *t, rs_state y, double *ydot, double *yout
     }
 }
 
-RS_MODEL_ACC(rd3d, RSM_RD3_NPAR)
+__device__ double rd3d_row(long long i, double t, rs_state y, const double *yout, const int *ip)
+{
+    const int d1 = ip[4], d2 = ip[5], d3 = ip[6];
+    const int plane = d2 * d3, nc = plane * d1, idx = (int)i;
+    const int s = idx >= nc ? 1 : 0, cell = idx - s * nc;
+    const int j = cell / plane, rem = cell - j * plane, k = rem / d3, l = rem - k * d3;
+    return rsm_rd3d_point(y, s, j, k, l, d1, d2, d3, rsm_rd3d_coef(parms));
+}
+
+RS_MODEL_ACC_ROW(rd3d, rd3d_row, RSM_RD3_NPAR)
