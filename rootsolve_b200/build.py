@@ -31,7 +31,7 @@ COMMON = ARCH + ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-Wno-
 # oracle (residuals, FD quotients, error weights) must not contract a*b+c into FMA.
 NO_FMA = {"fdjac.cu", "api.cu"}
 
-SOLVER_SRCS = ["structure.cu", "jgroup.cu", "fdjac.cu", "krylov.cu", "mg.cu", "api.cu", "comm.cu", "noalloc.cu"]
+SOLVER_SRCS = ["structure.cu", "jgroup.cu", "fdjac.cu", "krylov.cu", "mg.cu", "btd.cu", "api.cu", "comm.cu", "noalloc.cu"]
 MODEL_SRCS = ["diff2d.cu", "diff3d.cu", "rd3d.cu", "rt1d.cu", "anox.cu", "diffmap.cu", "anoxforc.cu", "diff2db.cu", "o2bod.cu", "diff3dms.cu", "diff2dq.cu", "sediment.cu"]
 
 

@@ -665,7 +665,7 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
         meta->t_setup_s = s.t_setup;
         meta->t_newton_s = s.t_newton;
         meta->spmv_kernel = s.kry.gridcols ? 2 : s.kry.tma_ok ? 1 : 0;
-        meta->precond = s.kry.mg_on ? RS_PRECOND_MG : s.kry.precond;
+        meta->precond = s.kry.mg_on ? RS_PRECOND_MG : s.kry.btd_on ? RS_PRECOND_BTD : s.kry.precond;
         meta->krylov_method = s.kry.use_cg ? 1 : 0;
         if (meta->precis) for (int q = 0; q < s.niter && q < s.maxiter; q++) meta->precis[q] = s.precis[q];
     }
@@ -1010,7 +1010,7 @@ extern "C" int rs_linsolve_grid(int neq, const int *ian, const int *jan, const d
     RS_CUDA(cudaStreamSynchronize(c.stream));
     if (iters) *iters = it;
     if (relres) *relres = rr;
-    if (used) { used[0] = k.mg_on ? RS_PRECOND_MG : k.precond; used[1] = k.use_cg ? 1 : 0; }
+    if (used) { used[0] = k.mg_on ? RS_PRECOND_MG : k.btd_on ? RS_PRECOND_BTD : k.precond; used[1] = k.use_cg ? 1 : 0; }
     return RS_OK;
 }
 

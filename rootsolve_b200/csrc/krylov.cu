@@ -46,6 +46,7 @@ Krylov::~Krylov()
     if (h_scal) cudaFreeHost(h_scal);
     for (int w = 0; w < 2; w++) if (g_exec[w]) cudaGraphExecDestroy(g_exec[w]);
     if (mg) mg_destroy(mg);
+    if (btd) btd_destroy(btd);
 }
 
 int pick_lanes(int n, int nnz)
@@ -710,6 +711,12 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
     // fallback should a solve with the cycle fail, and what every other structure uses
     const bool want_mg = (precond == RS_PRECOND_MG || precond == RS_PRECOND_AUTO) && grid && !getenv("RS_NO_MG") &&
                          mg_applicable(*grid, k.halo.nspec > 0 ? k.halo.j0 : 0, k.halo.nspec > 0 ? k.halo.j1 : 0);
+    // block-tridiagonal solve: 1-D grids (blocks of nspec), general structures (scalar band; AUTO decides at the first
+    // update whether the band carries enough of the weight)
+    const bool is_1d = grid && grid->type == RS_TYPE_1D && nspec <= MAXS;
+    const bool want_btd = !want_mg && !getenv("RS_NO_BTD") && n >= 2 &&
+                          ((precond == RS_PRECOND_BTD && (is_1d || !grid || !grid->type)) || (precond == RS_PRECOND_AUTO && (is_1d || !grid || !grid->type)));
+    k.btd_decide = (want_btd && !is_1d && precond == RS_PRECOND_AUTO) ? 1 : 0;
     if (precond == RS_PRECOND_MG || precond == RS_PRECOND_BTD) precond = RS_PRECOND_AUTO;
     if (precond == RS_PRECOND_AUTO) precond = (nspec > 1 && nspec <= MAXS && ncell > 0) ? RS_PRECOND_BLOCK_JACOBI : RS_PRECOND_JACOBI;
     if (precond == RS_PRECOND_BLOCK_JACOBI && !(nspec > 1 && nspec <= MAXS && ncell > 0 && (long long)nspec * ncell == n))
@@ -808,6 +815,15 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
     }
     if (precond == RS_PRECOND_JACOBI) RS_TRY(k.dinv.alloc(n));
     if (precond == RS_PRECOND_BLOCK_JACOBI) RS_TRY(k.binv.alloc((size_t)nspec * nspec * ncell));
+    if (want_btd) {
+        if (k.btd) { btd_destroy(k.btd); k.btd = nullptr; }
+        if (is_1d) {
+            const int j0 = k.halo.nspec > 0 ? k.halo.j0 : 0, j1 = k.halo.nspec > 0 ? k.halo.j1 : grid->d[0];
+            RS_TRY(btd_setup(c, &k.btd, nspec, j1 - j0, grid->ncell, j0));
+        } else {
+            RS_TRY(btd_setup(c, &k.btd, 1, n, n, 0));
+        }
+    }
     if (want_mg) {
         if (k.mg) { mg_destroy(k.mg); k.mg = nullptr; }
         RS_TRY(mg_setup(c, &k.mg, *grid, k.halo.nspec > 0 ? k.halo.j0 : 0, k.halo.nspec > 0 ? k.halo.j1 : 0));
@@ -881,7 +897,7 @@ int krylov_precond_update(Ctx &c, Krylov &k)
         // A Jacobian that is symmetric up to finite-difference noise (single-species diffusion-reaction: the
         // reference's own examples) is solved by preconditioned CG: one SpMV per step instead of two.
         static const bool no_cg = getenv("RS_NO_CG") != nullptr;
-        if (!no_cg && k.own.n == 1) {
+        if (!no_cg && k.own.n == 1 && !(k.btd && !k.btd_failed)) {
             {
                 Launch L(c, K_PRECOND_SETUP, 24.0 * own_nnz_estimate(k));
                 symmetry_kernel<<<grid_for(k.own.e[0] - k.own.b[0], 256), 256, 0, c.stream>>>(k.own.b[0], k.own.e[0], k.rowptr, k.col, k.val,
@@ -927,6 +943,14 @@ int krylov_precond_update(Ctx &c, Krylov &k)
     k.mg_on = k.mg != nullptr && !k.mg_failed;
     if (k.mg_on && k.use_cg && !k.scaled) k.use_cg = false;   // the CG kernels take z = M^-1 r only on the scaled system
     if (k.mg_on) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));
+    if (k.btd && !k.btd_failed && k.btd_decide == 1) {   // general structure: is the matrix banded enough?
+        double share = 0.0;
+        RS_TRY(btd_band_share(c, k.n, k.rowptr, k.col, k.val, k.partials.p, k.ticket.p, k.scal.p + S_SYM, &share));
+        k.btd_decide = 2;
+        if (!(share >= 0.5)) k.btd_failed = true;
+    }
+    k.btd_on = k.btd != nullptr && !k.btd_failed;
+    if (k.btd_on) RS_TRY(btd_update(c, *k.btd, k.rowptr, k.col, k.val));
     RS_CUDA(cudaGetLastError());
     return RS_OK;
 }
@@ -954,8 +978,9 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     const double rows = (double)k.own.total();
     // with the multigrid cycle the vector kernels apply no preconditioner themselves (ph = M^-1 p follows them), and
     // the halo planes of ph / sh can only travel once the cycle has produced them: no push from the update kernels
-    const int pre = k.mg_on ? RS_PRECOND_NONE : k.precond;
-    const bool push = k.push_ok && !k.mg_on;
+    const bool ext = k.mg_on || k.btd_on;
+    const int pre = ext ? RS_PRECOND_NONE : k.precond;
+    const bool push = k.push_ok && !ext;
     const double pre_bytes = (pre == RS_PRECOND_BLOCK_JACOBI) ? 8.0 * k.nspec * rows : (pre == RS_PRECOND_JACOBI ? 8.0 * rows : 0.0);
     // halo handshakes of this step (sequence numbers advance identically on every rank)
     const HaloSignal sig_p = push ? comm_next_halo_signal() : HaloSignal();
@@ -978,6 +1003,7 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
         }
     }
     if (k.mg_on) RS_TRY(mg_apply(c, *k.mg, k.p.p, k.ph_v, nullptr, nullptr, nullptr, PeerRed()));
+    if (k.btd_on) RS_TRY(btd_apply(c, *k.btd, k.p.p, k.ph_v));
     if (!push) RS_TRY(comm_halo_exchange(c, k.ph_v, k.halo));
     {
         Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)) + 8.0 * rows);
@@ -1002,6 +1028,7 @@ static int bicgstab_step(Ctx &c, Krylov &k, double *x, int cur, int first)
         }
     }
     if (k.mg_on) RS_TRY(mg_apply(c, *k.mg, k.s.p, k.sh_v, nullptr, nullptr, nullptr, PeerRed()));
+    if (k.btd_on) RS_TRY(btd_apply(c, *k.btd, k.s.p, k.sh_v));
     if (!push) RS_TRY(comm_halo_exchange(c, k.sh_v, k.halo));
     {
         Launch L(c, k.gridcols ? K_SPMV_GRID : K_SPMV, spmv_bytes(k, rows, own_nnz_estimate(k)) + 8.0 * rows);
@@ -1298,7 +1325,7 @@ static int graph_steps_per_launch(const Ctx &c, const Krylov &k)
     if (no_graph || c.profile) return 0;
     // with the multigrid cycle a step is ~40 launches and the solve ~10 steps: on large grids launch latency is
     // nothing and a graph would only add a possibly wasted step; small grids replay two steps per host call
-    if (k.mg_on) return k.own.total() > 500000 ? 0 : 2;
+    if (k.mg_on || k.btd_on) return k.own.total() > 500000 ? 0 : 2;
     int g = k.check_every & ~1;
     return g >= 2 ? g : 2;
 }
@@ -1307,9 +1334,9 @@ static int launch_step_graph(Ctx &c, Krylov &k, double *x, bool cg, int nsteps)
 {
     const int w = cg ? 1 : 0;
     cudaStream_t st = c.stream;
-    if (!k.g_exec[w] || k.g_x[w] != x || k.g_n[w] != nsteps || k.g_scaled[w] != k.scaled || k.g_mg[w] != k.mg_on) {
+    if (!k.g_exec[w] || k.g_x[w] != x || k.g_n[w] != nsteps || k.g_scaled[w] != k.scaled || k.g_mg[w] != (k.mg_on || k.btd_on)) {
         k.g_scaled[w] = k.scaled;
-        k.g_mg[w] = k.mg_on;
+        k.g_mg[w] = k.mg_on || k.btd_on;
         if (k.g_exec[w]) { cudaGraphExecDestroy(k.g_exec[w]); k.g_exec[w] = nullptr; }
         cudaGraph_t g = nullptr;
         const long long l0 = c.launches;
@@ -1351,7 +1378,7 @@ static int pcg_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_f
     int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
     bool done = false;
     const int gsteps = graph_steps_per_launch(c, k);
-    const int check_every = k.mg_on ? 1 : k.check_every;   // a multigrid step is worth a look: the solve has ~10 of them
+    const int check_every = (k.mg_on || k.btd_on) ? 1 : k.check_every;   // a step under the cycle / the exact band solve is worth a look
     while (!done && total < k.max_iter) {
         int cur = cycle_it & 1;
         bool looked = false;
@@ -1463,7 +1490,7 @@ static int krylov_solve_inner(Ctx &c, Krylov &k, const double *b, double *x, dou
     int since_best = 0, cycle_it = 0, total = 0, restarts = 0, fruitless = 0;
     bool done = false;
     const int gsteps = graph_steps_per_launch(c, k);
-    const int check_every = k.mg_on ? 1 : k.check_every;   // a multigrid step is worth a look: the solve has ~10 of them
+    const int check_every = (k.mg_on || k.btd_on) ? 1 : k.check_every;   // a step under the cycle / the exact band solve is worth a look
     while (!done && total < k.max_iter) {
         int cur = cycle_it & 1;
         bool looked = false;
@@ -1523,10 +1550,13 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     bool conv_local = false;
     if (!converged) converged = &conv_local;
     int rc = krylov_solve_inner(c, k, b, x, abs_floor, iters, relres, converged);
-    if (k.mg_on && (rc == RS_ESINGULAR || (rc == RS_OK && !*converged && !(*relres <= 0.1)))) {
-        if (debug) fprintf(stderr, "[krylov] solve under the multigrid cycle failed (rc %d, relres %.3e after %d its): back to Jacobi\n", rc, *relres, *iters);
-        k.mg_failed = true;
+    if ((k.mg_on || k.btd_on) && (rc == RS_ESINGULAR || (rc == RS_OK && !*converged && !(*relres <= 0.1)))) {
+        if (debug) fprintf(stderr, "[krylov] solve under the %s failed (rc %d, relres %.3e after %d its): back to Jacobi\n",
+                           k.mg_on ? "multigrid cycle" : "block-tridiagonal solve", rc, *relres, *iters);
+        if (k.mg_on) k.mg_failed = true;
+        if (k.btd_on) k.btd_failed = true;
         k.mg_on = false;
+        k.btd_on = false;
         const int it0 = *iters;
         rc = krylov_solve_inner(c, k, b, x, abs_floor, iters, relres, converged);
         *iters += it0;

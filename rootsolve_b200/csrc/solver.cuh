@@ -88,6 +88,15 @@ int mg_apply(Ctx &c, Mg &m, const double *r, double *z, double *partials, unsign
 int mg_levels(const Mg &m);
 void mg_destroy(Mg *m);
 
+// btd.cu -- block-tridiagonal part solved exactly by cyclic reduction (1-D grids, banded general structures)
+struct Btd;
+int btd_setup(Ctx &c, Btd **out, int ns, int nb, int stride, int off);
+int btd_update(Ctx &c, Btd &t, const int *rowptr, const int *col, const double *val);
+int btd_apply(Ctx &c, Btd &t, const double *r, double *z);
+int btd_band_share(Ctx &c, int n, const int *rowptr, const int *col, const double *val, double *partials, unsigned *ticket,
+                   double *d_out2, double *share);
+void btd_destroy(Btd *t);
+
 // krylov.cu
 struct Krylov {
     int n = 0, nnz = 0;
@@ -101,6 +110,9 @@ struct Krylov {
     Mg *mg = nullptr;          // multigrid preconditioner; z = M^-1 r of preconditioned CG
     bool mg_on = false;        // the current solve is preconditioned by the cycle
     bool mg_failed = false;    // a solve with it did not converge: this handle goes back to (block-)Jacobi
+    Btd *btd = nullptr;        // block-tridiagonal preconditioner (same life cycle as mg)
+    bool btd_on = false, btd_failed = false;
+    int btd_decide = 0;        // general structure: 1 = decide at the first update from the band's share of the weight
     DevBuf<double> partials, scal;
     DevBuf<unsigned> ticket;
     double *h_scal = nullptr;  // pinned mirror
