@@ -642,7 +642,11 @@ __global__ void __launch_bounds__(256) update_xr_kernel(int b, int e, double *sc
     double omega = slot[S_TS] / slot[S_TT];
     // A zero or non-finite recurrence scalar is a BiCGStab breakdown.  Leave x untouched (alpha =
     // omega = 0 keeps x and turns r into s = r) and raise the flag the host restarts on.
-    const bool bad = !(isfinite(alpha) && isfinite(omega)) || rho == 0.0 || omega == 0.0;
+    // s = 0 to the last bit (t = A M^-1 s = 0, <t,t> = 0): the half step x + alpha ph solved the system -- what an exact
+    // preconditioner (the block-tridiagonal solve on a small 1-D grid) produces.  Not a breakdown: take the half step.
+    const bool lucky = isfinite(alpha) && rho != 0.0 && slot[S_TT] == 0.0;
+    if (lucky) omega = 0.0;
+    const bool bad = !lucky && (!(isfinite(alpha) && isfinite(omega)) || rho == 0.0 || omega == 0.0);
     if (bad) { alpha = 0.0; omega = 0.0; }
     if (blockIdx.x == 0 && threadIdx.x == 0) slot[S_BAD] = bad ? 1.0 : 0.0;
     double acc[2] = {0.0, 0.0};
