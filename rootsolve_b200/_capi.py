@@ -140,7 +140,9 @@ def model_symbol(func: str, dllname: str | None = None) -> int:
                               "`python -m rootsolve_b200.build`)")
     L = _model_libs.get(path)
     if L is None:
-        L = _model_libs[path] = C.CDLL(path, mode=C.RTLD_GLOBAL)
+        # RTLD_LOCAL: two model libraries may instantiate kernels of the same name (copies of one model); each must
+        # keep its own
+        L = _model_libs[path] = C.CDLL(path, mode=C.RTLD_LOCAL)
     try:
         getter = getattr(L, f"rs_model_{func}")
     except AttributeError as e:

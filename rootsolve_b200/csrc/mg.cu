@@ -74,6 +74,8 @@ struct Mg {
     DevBuf<int> flag;         // != 0: the coarsest operator was singular to working precision
     int gstride = 0, goff = 0;   // level-0 view of the solver's vectors
     int nc = 0;               // unknowns of the coarsest level
+    int tail = 0;             // first level of the one-launch tail (levels of <= MG_TAIL_CELLS cells); nlev: no tail
+    DevBuf<unsigned char> tail_levels;   // MgTailLevel[nlev] on the device
 };
 
 // ---- stencil geometry ------------------------------------------------------------------------------------
@@ -168,12 +170,15 @@ __device__ __forceinline__ Cheb cheb_coeffs(const MgLevelDev &L)
     return ch;
 }
 
-#define MG_CELL_LOOP(c, ncell) for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < (ncell); c += gridDim.x * blockDim.x)
+// every cycle kernel is a body (a __device__ function working on cells c0, c0 + cs, ...) with two callers: a __global__
+// wrapper over the whole grid for the large levels, and the one-block tail kernel that runs all small levels in one launch
+#define MG_CELL_LOOP(c, ncell) for (int c = c0; c < (ncell); c += cs)
+#define MG_GRID_ARGS (int)(blockIdx.x * blockDim.x + threadIdx.x), (int)(gridDim.x * blockDim.x)
 
 // ---- cycle kernels (thread per cell, all species of the cell) ------------------------------------------------
 // first Chebyshev step from a zero guess:  d = Dinv b / theta   (x = d is implied)
 template <int NS>
-__global__ void __launch_bounds__(256) mg_first_kernel(MgLevelDev L, VecView b, VecView d)
+__device__ __forceinline__ void mg_first_body(const MgLevelDev &L, VecView b, VecView d, int c0, int cs)
 {
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
@@ -189,12 +194,18 @@ __global__ void __launch_bounds__(256) mg_first_kernel(MgLevelDev L, VecView b, 
     }
 }
 
+template <int NS>
+__global__ void __launch_bounds__(256) mg_first_kernel(MgLevelDev L, VecView b, VecView d)
+{
+    mg_first_body<NS>(L, b, d, MG_GRID_ARGS);
+}
+
 // second Chebyshev step:  r1 = r - A d ;  d1 = c1 d + c2 Dinv r1 ;  xout = [xin +] d + d1
 // DOT: also out[0] = <w, xout> (w = the right-hand side of the cycle: the <r, z> of preconditioned CG when this is
 // the last kernel of the cycle)
 template <int NS, bool DOT>
-__global__ void __launch_bounds__(256) mg_second_kernel(MgLevelDev L, VecView r, VecView d, VecView xin, VecView xout, VecView w_,
-                                                        double *partials, unsigned *ticket, double *out, PeerRed pr)
+__device__ __forceinline__ double mg_second_body(const MgLevelDev &L, VecView r, VecView d, VecView xin, VecView xout, VecView w_,
+                                                 int c0, int cs)
 {
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
@@ -220,12 +231,21 @@ __global__ void __launch_bounds__(256) mg_second_kernel(MgLevelDev L, VecView r,
             if (DOT) acc[0] += w_.at(s, c) * xn;
         }
     }
+    return acc[0];
+}
+
+template <int NS, bool DOT>
+__global__ void __launch_bounds__(256) mg_second_kernel(MgLevelDev L, VecView r, VecView d, VecView xin, VecView xout, VecView w_,
+                                                        double *partials, unsigned *ticket, double *out, PeerRed pr)
+{
+    double acc[1];
+    acc[0] = mg_second_body<NS, DOT>(L, r, d, xin, xout, w_, MG_GRID_ARGS);
     if (DOT) grid_reduce<1>(acc, 0u, partials, ticket, out, false, &pr);
 }
 
 // start of the post-smoothing:  r = b - A x ;  d = Dinv r / theta
 template <int NS>
-__global__ void __launch_bounds__(256) mg_resid_first_kernel(MgLevelDev L, VecView b, VecView x, VecView r, VecView d)
+__device__ __forceinline__ void mg_resid_first_body(const MgLevelDev &L, VecView b, VecView x, VecView r, VecView d, int c0, int cs)
 {
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
@@ -246,11 +266,17 @@ __global__ void __launch_bounds__(256) mg_resid_first_kernel(MgLevelDev L, VecVi
     }
 }
 
+template <int NS>
+__global__ void __launch_bounds__(256) mg_resid_first_kernel(MgLevelDev L, VecView b, VecView x, VecView r, VecView d)
+{
+    mg_resid_first_body<NS>(L, b, x, r, d, MG_GRID_ARGS);
+}
+
 // residual of the fine level summed over each aggregate:  bc(s, I) = sum_{c in I} (b - A x)(s, c)
 // thread per COARSE cell (cd1 x cd2 x cd3 of them); f: the coarsening factors
 template <int NS>
-__global__ void __launch_bounds__(256) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, int cd1, int cd2, int cd3,
-                                                                VecView b, VecView x, VecView bc)
+__device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int f1, int f2, int f3, int cd1, int cd2, int cd3,
+                                                       VecView b, VecView x, VecView bc, int c0, int cs)
 {
     const int ns = NS > 0 ? NS : L.nspec;
     const int ncc = cd1 * cd2 * cd3;
@@ -288,9 +314,16 @@ __global__ void __launch_bounds__(256) mg_resid_restrict_kernel(MgLevelDev L, in
     }
 }
 
+template <int NS>
+__global__ void __launch_bounds__(256) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, int cd1, int cd2, int cd3,
+                                                                VecView b, VecView x, VecView bc)
+{
+    mg_resid_restrict_body<NS>(L, f1, f2, f3, cd1, cd2, cd3, b, x, bc, MG_GRID_ARGS);
+}
+
 // x(s, c) += xc(s, aggregate of c)
-__global__ void __launch_bounds__(256) mg_prolong_kernel(int nspec, int d1, int d2, int d3, int f1, int f2, int f3, int cd2, int cd3,
-                                                         VecView xc, VecView x)
+__device__ __forceinline__ void mg_prolong_body(int nspec, int d1, int d2, int d3, int f1, int f2, int f3, int cd2, int cd3,
+                                                VecView xc, VecView x, int c0, int cs)
 {
     const int ncell = d1 * d2 * d3;
     MG_CELL_LOOP(c, ncell) {
@@ -298,6 +331,12 @@ __global__ void __launch_bounds__(256) mg_prolong_kernel(int nspec, int d1, int 
         const int I = ((q.j / f1) * cd2 + (q.k / f2)) * cd3 + (q.l / f3);
         for (int s = 0; s < nspec; s++) x.at(s, c) += xc.at(s, I);
     }
+}
+
+__global__ void __launch_bounds__(256) mg_prolong_kernel(int nspec, int d1, int d2, int d3, int f1, int f2, int f3, int cd2, int cd3,
+                                                         VecView xc, VecView x)
+{
+    mg_prolong_body(nspec, d1, d2, d3, f1, f2, f3, cd2, cd3, xc, x, MG_GRID_ARGS);
 }
 
 // coarsest level:  x = Cinv b  (dense, column-major so that thread i reads a coalesced column slice)
@@ -311,6 +350,76 @@ __global__ void __launch_bounds__(256) mg_coarse_solve_kernel(int nc, const doub
         double a = 0.0;
         for (int j = 0; j < nc; j++) a += cinv[(size_t)j * nc + i] * sb[j];
         x[i] = a;
+    }
+}
+
+// ---- the small levels in one launch ---------------------------------------------------------------------------
+// Below a few thousand cells a level is a handful of microseconds of work per kernel and six kernels per visit: launch
+// latency, not bandwidth.  One block walks all those levels -- down, the dense coarsest solve, up -- with a block
+// barrier where the separate kernels had a launch boundary.  When the whole grid is that small (config C1) the
+// entire cycle is this one launch, its <r, z> included.
+struct MgTailLevel {
+    MgLevelDev D;
+    int f1, f2, f3;
+    double *b, *x, *r, *d;
+};
+constexpr int MG_TAIL_THREADS = 1024;
+constexpr int MG_TAIL_CELLS = 4096;
+
+template <int NS>
+__global__ void __launch_bounds__(MG_TAIL_THREADS) mg_tail_kernel(const MgTailLevel *__restrict__ lv, int l0, int nlev, int nc,
+                                                                  const double *__restrict__ cinv, VecView b0, VecView xout0,
+                                                                  int want_dot, double *dot_out)
+{
+    const int c0 = threadIdx.x, cs = blockDim.x;
+    const VecView none = {nullptr, 0, 0};
+    for (int l = l0; l < nlev - 1; l++) {   // down
+        const MgTailLevel T = lv[l];
+        const MgLevelDev Dn = lv[l + 1].D;
+        const VecView b = (l == l0 && b0.p != nullptr) ? b0 : VecView{T.b, T.D.ncell, 0};
+        const VecView x = {T.x, T.D.ncell, 0}, d = {T.d, T.D.ncell, 0};
+        mg_first_body<NS>(T.D, b, d, c0, cs);
+        __syncthreads();
+        mg_second_body<NS, false>(T.D, b, d, none, x, none, c0, cs);
+        __syncthreads();
+        mg_resid_restrict_body<NS>(T.D, T.f1, T.f2, T.f3, Dn.d1, Dn.d2, Dn.d3, b, x, VecView{lv[l + 1].b, Dn.ncell, 0}, c0, cs);
+        __syncthreads();
+    }
+    {   // coarsest level: x = Cinv b
+        const MgTailLevel T = lv[nlev - 1];
+        const double *bb = T.b;
+        for (int i = c0; i < nc; i += cs) {
+            double a = 0.0;
+            for (int j = 0; j < nc; j++) a += cinv[(size_t)j * nc + i] * bb[j];
+            T.x[i] = a;
+        }
+        __syncthreads();
+    }
+    double acc = 0.0;
+    for (int l = nlev - 2; l >= l0; l--) {   // up
+        const MgTailLevel T = lv[l];
+        const MgLevelDev Dn = lv[l + 1].D;
+        const bool top = l == l0 && b0.p != nullptr;
+        const VecView b = top ? b0 : VecView{T.b, T.D.ncell, 0};
+        const VecView x = {T.x, T.D.ncell, 0}, r = {T.r, T.D.ncell, 0}, d = {T.d, T.D.ncell, 0};
+        mg_prolong_body(T.D.nspec, T.D.d1, T.D.d2, T.D.d3, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, VecView{lv[l + 1].x, Dn.ncell, 0}, x, c0, cs);
+        __syncthreads();
+        mg_resid_first_body<NS>(T.D, b, x, r, d, c0, cs);
+        __syncthreads();
+        if (top && want_dot) acc = mg_second_body<NS, true>(T.D, r, d, x, xout0, b, c0, cs);
+        else mg_second_body<NS, false>(T.D, r, d, x, top ? xout0 : x, none, c0, cs);
+        __syncthreads();
+    }
+    if (want_dot) {   // <r, z> over the block
+        __shared__ double red[32];
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            double v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
+            v = warp_sum(v);
+            if (threadIdx.x == 0) dot_out[0] = v;
+        }
     }
 }
 
@@ -417,6 +526,7 @@ __global__ void __launch_bounds__(128) mg_smoother_setup_kernel(MgLevelDev L, do
 {
     const int ns = L.nspec;
     double worst = 0.0;
+    const int c0 = blockIdx.x * blockDim.x + threadIdx.x, cs = gridDim.x * blockDim.x;
     MG_CELL_LOOP(c, L.ncell) {
         double A[MG_MAXS][MG_MAXS], B[MG_MAXS][MG_MAXS], tsum[MG_MAXS];
         for (int s = 0; s < ns; s++) {
@@ -600,7 +710,23 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
     RS_TRY(M->cinv.alloc((size_t)M->nc * M->nc));
     RS_TRY(M->cwork.alloc(2 * (size_t)M->nc * M->nc));
     RS_TRY(M->flag.alloc(1));
-    (void)c;
+    // the levels small enough for the one-launch tail
+    M->tail = nlev;
+    for (int l = 0; l < nlev; l++)
+        if (M->lev[l].dev.ncell <= MG_TAIL_CELLS) { M->tail = l; break; }
+    if (getenv("RS_NO_MG_TAIL")) M->tail = nlev;
+    if (M->tail < nlev) {
+        std::vector<MgTailLevel> tl(nlev);
+        for (int l = 0; l < nlev; l++) {
+            MgLevel &L = M->lev[l];
+            tl[l].D = L.dev;
+            tl[l].f1 = L.f[0]; tl[l].f2 = L.f[1]; tl[l].f3 = L.f[2];
+            tl[l].b = L.b.p; tl[l].x = L.x.p; tl[l].r = L.r.p; tl[l].d = L.d.p;
+        }
+        RS_TRY(M->tail_levels.alloc(sizeof(MgTailLevel) * nlev));
+        RS_CUDA(cudaMemcpyAsync(M->tail_levels.p, tl.data(), sizeof(MgTailLevel) * nlev, cudaMemcpyHostToDevice, c.stream));
+        RS_CUDA(cudaStreamSynchronize(c.stream));
+    }
     *out = M.release();
     return RS_OK;
 }
@@ -650,6 +776,16 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     const int grid = mg_grid(D.ncell);
     // statistics: the smoothing passes and the transfers of the finest level on their own, every level below as one class
     const int k_smooth = l == 0 ? K_MG_SMOOTH_L0 : K_MG_COARSE, k_transfer = l == 0 ? K_MG_TRANSFER_L0 : K_MG_COARSE;
+    if (l == M.tail && !(l == 0 && dot_out && pr.nranks > 1)) {
+        // this level and everything below it in one block
+        double bytes = 0.0;
+        for (int q = l; q < M.nlev; q++) bytes += 4.0 * 8.0 * M.lev[q].dev.n * (6.0 + D.nspec) + 150.0 * M.lev[q].dev.n;
+        Launch La(c, K_MG_COARSE, bytes);
+        const VecView none0 = view(nullptr, 0);
+        mg_tail_kernel<NS><<<1, MG_TAIL_THREADS, 0, st>>>(reinterpret_cast<const MgTailLevel *>(M.tail_levels.p), l, M.nlev, M.nc, M.cinv.p,
+                                                         l == 0 ? b : none0, l == 0 ? xout : none0, dot_out ? 1 : 0, dot_out);
+        return;
+    }
     if (l == M.nlev - 1) {
         Launch La(c, K_MG_COARSE, 8.0 * M.nc * M.nc + 16.0 * M.nc);
         mg_coarse_solve_kernel<<<1, 256, sizeof(double) * M.nc, st>>>(M.nc, M.cinv.p, b.p, xout.p);

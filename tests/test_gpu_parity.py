@@ -84,6 +84,13 @@ def test_jgroup_1d_bit_exact(built, oracle, nspec, nb, cyc, wave):
     _jg_case(built, oracle, "1D", nspec, [nb], [cyc], hint)
 
 
+@pytest.mark.parametrize("nspec,nb", [(1, 400), (2, 1000), (3, 1001), (8, 5002), (16, 999), (5, 200000)])
+def test_jgroup_1d_periodic_expansion(built, oracle, nspec, nb):
+    """long non-cyclic 1-D columns: the grouping is computed on a short column and laid out periodically
+    (jgroup.cu); must be the sequential JGROUP's, bit for bit -- config C2's 5 x 200 000 included"""
+    _jg_case(built, oracle, "1D", nspec, [nb], [0], [2, nspec, nb, 1, 1, 0, 0, 0])
+
+
 def test_jgroup_1d_long_column(built, oracle):
     """config C2's shape at a tenth of its length: 5 species x 20 000 boxes through the pipelined wavefront"""
     _jg_case(built, oracle, "1D", 5, [20000], [0], [2, 5, 20000, 1, 1, 0, 0, 0])
