@@ -316,11 +316,21 @@ extern "C" void rs_comm_finalize(void)
 #endif
 }
 
-// Planes [j0, j1) of the slowest grid dimension owned by `rank`: as even as possible, the first
-// d1 % nranks ranks get one more.
+// Planes [j0, j1) of the slowest grid dimension owned by `rank`: as even as possible (the first d1 % nranks ranks get
+// one more), with the interior bounds then moved down to a multiple of A = 2, 4, 8 or 16 planes while every rank keeps
+// at least 3A: whole 2^k aggregates per rank are what lets the finest multigrid levels span the ranks (mg.cu).
+static int slab_bound(int d1, int nranks, int r)
+{
+    if (r <= 0) return 0;
+    if (r >= nranks) return d1;
+    const int base = d1 / nranks, rem = d1 % nranks;
+    int A = 1;
+    while (A < 16 && d1 >= nranks * 4 * (2 * A)) A *= 2;
+    const int even = r * base + (r < rem ? r : rem);
+    return even / A * A;
+}
 extern "C" void rs_slab_bounds(int d1, int nranks, int rank, int *j0, int *j1)
 {
-    const int base = d1 / nranks, rem = d1 % nranks;
-    *j0 = rank * base + (rank < rem ? rank : rem);
-    *j1 = *j0 + base + (rank < rem ? 1 : 0);
+    *j0 = slab_bound(d1, nranks, rank);
+    *j1 = slab_bound(d1, nranks, rank + 1);
 }

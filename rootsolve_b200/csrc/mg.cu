@@ -54,6 +54,7 @@ struct VecView {
 
 struct MgLevelDev {
     int nspec, d1, d2, d3, cyc1, cyc2, cyc3, ncell, n;
+    int cb, ce;           // cells this rank works on: all of a local level's box, the rank's planes of a global level
     const double *ell;    // [7 + nspec - 1][n]
     const double *dinv;   // nspec == 1: 1/diag per row; else the inverse cell blocks [s][s'][cell]
     const double *lmax;   // Gershgorin bound of the (block-)Jacobi-preconditioned operator of this level
@@ -62,6 +63,9 @@ struct MgLevelDev {
 struct MgLevel {
     MgLevelDev dev;
     int f[3] = {1, 1, 1};   // coarsening factors towards the next level
+    bool global = false;    // sharded solve: the level spans all ranks (global cell indices, halo planes exchanged)
+    int cjoff = 0;          // transfer to the next level: plane 0 of that level's box in this level's aggregate numbering
+    HaloPlan hp;            // global levels: the planes that travel before every application of the level's operator
     DevBuf<double> ell, dinv, b, x, r, d;
 };
 
@@ -74,6 +78,7 @@ struct Mg {
     DevBuf<int> flag;         // != 0: the coarsest operator was singular to working precision
     int gstride = 0, goff = 0;   // level-0 view of the solver's vectors
     int nc = 0;               // unknowns of the coarsest level
+    int nglobal = 0;          // number of global levels (0: single GPU, or a purely slab-local hierarchy)
     int tail = 0;             // first level of the one-launch tail (levels of <= MG_TAIL_CELLS cells); nlev: no tail
     DevBuf<unsigned char> tail_levels;   // MgTailLevel[nlev] on the device
 };
@@ -172,7 +177,7 @@ __device__ __forceinline__ Cheb cheb_coeffs(const MgLevelDev &L)
 
 // every cycle kernel is a body (a __device__ function working on cells c0, c0 + cs, ...) with two callers: a __global__
 // wrapper over the whole grid for the large levels, and the one-block tail kernel that runs all small levels in one launch
-#define MG_CELL_LOOP(c, ncell) for (int c = c0; c < (ncell); c += cs)
+#define MG_CELL_LOOP(c, L) for (int c = (L).cb + c0; c < (L).ce; c += cs)
 #define MG_GRID_ARGS (int)(blockIdx.x * blockDim.x + threadIdx.x), (int)(gridDim.x * blockDim.x)
 
 // ---- cycle kernels (thread per cell, all species of the cell) ------------------------------------------------
@@ -182,7 +187,7 @@ __device__ __forceinline__ void mg_first_body(const MgLevelDev &L, VecView b, Ve
 {
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
-    MG_CELL_LOOP(c, L.ncell) {
+    MG_CELL_LOOP(c, L) {
         double bv[MG_NSA], w[MG_NSA];
 #pragma unroll
         for (int s = 0; s < MG_NSA; s++)
@@ -210,7 +215,7 @@ __device__ __forceinline__ double mg_second_body(const MgLevelDev &L, VecView r,
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
     double acc[1] = {0.0};
-    MG_CELL_LOOP(c, L.ncell) {
+    MG_CELL_LOOP(c, L) {
         const Cell3 q = cell_coords(c, L.d2, L.d3);
         int nb[6];
         bool has[6];
@@ -249,7 +254,7 @@ __device__ __forceinline__ void mg_resid_first_body(const MgLevelDev &L, VecView
 {
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
-    MG_CELL_LOOP(c, L.ncell) {
+    MG_CELL_LOOP(c, L) {
         const Cell3 q = cell_coords(c, L.d2, L.d3);
         int nb[6];
         bool has[6];
@@ -275,13 +280,13 @@ __global__ void __launch_bounds__(256) mg_resid_first_kernel(MgLevelDev L, VecVi
 // residual of the fine level summed over each aggregate:  bc(s, I) = sum_{c in I} (b - A x)(s, c)
 // thread per COARSE cell (cd1 x cd2 x cd3 of them); f: the coarsening factors
 template <int NS>
-__device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int f1, int f2, int f3, int cd1, int cd2, int cd3,
+__device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int f1, int f2, int f3, const MgLevelDev &Cc, int cjoff,
                                                        VecView b, VecView x, VecView bc, int c0, int cs)
 {
     const int ns = NS > 0 ? NS : L.nspec;
-    const int ncc = cd1 * cd2 * cd3;
-    MG_CELL_LOOP(I, ncc) {
-        const Cell3 Q = cell_coords(I, cd2, cd3);
+    MG_CELL_LOOP(I, Cc) {
+        Cell3 Q = cell_coords(I, Cc.d2, Cc.d3);
+        Q.j += cjoff;   // plane of the aggregate in the fine level's coordinates / f1
         double sum[MG_NSA];
 #pragma unroll
         for (int s = 0; s < MG_NSA; s++) sum[s] = 0.0;
@@ -315,28 +320,27 @@ __device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int 
 }
 
 template <int NS>
-__global__ void __launch_bounds__(256) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, int cd1, int cd2, int cd3,
+__global__ void __launch_bounds__(256) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, MgLevelDev Cc, int cjoff,
                                                                 VecView b, VecView x, VecView bc)
 {
-    mg_resid_restrict_body<NS>(L, f1, f2, f3, cd1, cd2, cd3, b, x, bc, MG_GRID_ARGS);
+    mg_resid_restrict_body<NS>(L, f1, f2, f3, Cc, cjoff, b, x, bc, MG_GRID_ARGS);
 }
 
 // x(s, c) += xc(s, aggregate of c)
-__device__ __forceinline__ void mg_prolong_body(int nspec, int d1, int d2, int d3, int f1, int f2, int f3, int cd2, int cd3,
+__device__ __forceinline__ void mg_prolong_body(const MgLevelDev &L, int f1, int f2, int f3, int cd2, int cd3, int cjoff,
                                                 VecView xc, VecView x, int c0, int cs)
 {
-    const int ncell = d1 * d2 * d3;
-    MG_CELL_LOOP(c, ncell) {
-        const Cell3 q = cell_coords(c, d2, d3);
-        const int I = ((q.j / f1) * cd2 + (q.k / f2)) * cd3 + (q.l / f3);
-        for (int s = 0; s < nspec; s++) x.at(s, c) += xc.at(s, I);
+    MG_CELL_LOOP(c, L) {
+        const Cell3 q = cell_coords(c, L.d2, L.d3);
+        const int I = ((q.j / f1 - cjoff) * cd2 + (q.k / f2)) * cd3 + (q.l / f3);
+        for (int s = 0; s < L.nspec; s++) x.at(s, c) += xc.at(s, I);
     }
 }
 
-__global__ void __launch_bounds__(256) mg_prolong_kernel(int nspec, int d1, int d2, int d3, int f1, int f2, int f3, int cd2, int cd3,
+__global__ void __launch_bounds__(256) mg_prolong_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, int cjoff,
                                                          VecView xc, VecView x)
 {
-    mg_prolong_body(nspec, d1, d2, d3, f1, f2, f3, cd2, cd3, xc, x, MG_GRID_ARGS);
+    mg_prolong_body(L, f1, f2, f3, cd2, cd3, cjoff, xc, x, MG_GRID_ARGS);
 }
 
 // coarsest level:  x = Cinv b  (dense, column-major so that thread i reads a coalesced column slice)
@@ -382,7 +386,7 @@ __global__ void __launch_bounds__(MG_TAIL_THREADS) mg_tail_kernel(const MgTailLe
         __syncthreads();
         mg_second_body<NS, false>(T.D, b, d, none, x, none, c0, cs);
         __syncthreads();
-        mg_resid_restrict_body<NS>(T.D, T.f1, T.f2, T.f3, Dn.d1, Dn.d2, Dn.d3, b, x, VecView{lv[l + 1].b, Dn.ncell, 0}, c0, cs);
+        mg_resid_restrict_body<NS>(T.D, T.f1, T.f2, T.f3, Dn, 0, b, x, VecView{lv[l + 1].b, Dn.ncell, 0}, c0, cs);
         __syncthreads();
     }
     {   // coarsest level: x = Cinv b
@@ -402,7 +406,7 @@ __global__ void __launch_bounds__(MG_TAIL_THREADS) mg_tail_kernel(const MgTailLe
         const bool top = l == l0 && b0.p != nullptr;
         const VecView b = top ? b0 : VecView{T.b, T.D.ncell, 0};
         const VecView x = {T.x, T.D.ncell, 0}, r = {T.r, T.D.ncell, 0}, d = {T.d, T.D.ncell, 0};
-        mg_prolong_body(T.D.nspec, T.D.d1, T.D.d2, T.D.d3, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, VecView{lv[l + 1].x, Dn.ncell, 0}, x, c0, cs);
+        mg_prolong_body(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, 0, VecView{lv[l + 1].x, Dn.ncell, 0}, x, c0, cs);
         __syncthreads();
         mg_resid_first_body<NS>(T.D, b, x, r, d, c0, cs);
         __syncthreads();
@@ -432,9 +436,11 @@ __global__ void __launch_bounds__(256) mg_build_l0_kernel(MgLevelDev L, int gstr
                                                           const int *__restrict__ col, const double *__restrict__ val,
                                                           double *__restrict__ ell)
 {
-    const long long total = (long long)L.nspec * L.ncell;
-    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < total; r += (long long)gridDim.x * blockDim.x) {
-        const int s = (int)(r / L.ncell), c = (int)(r - (long long)s * L.ncell);
+    const int own = L.ce - L.cb;
+    const long long total = (long long)L.nspec * own;
+    for (long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
+        const int s = (int)(w / own), c = L.cb + (int)(w - (long long)s * own);
+        const long long r = (long long)s * L.ncell + c;
         const Cell3 q = cell_coords(c, L.d2, L.d3);
         int nb[6];
         bool has[6];
@@ -463,13 +469,17 @@ __global__ void __launch_bounds__(256) mg_build_l0_kernel(MgLevelDev L, int gstr
 
 // Galerkin coarse operator by summation.  Thread per (species, coarse cell).  w = weight kept by an entry that
 // crosses an aggregate face in a coarsened direction (the rest goes to the diagonal, see the file header).
-__global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLevelDev Cc, int f1, int f2, int f3, double w,
+__global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLevelDev Cc, int f1, int f2, int f3, int cjoff, double w,
                                                               double *__restrict__ ellc)
 {
-    const long long total = (long long)Cc.nspec * Cc.ncell;
+    // cjoff: plane of the coarse box's plane 0 in the fine level's aggregate numbering (the fine level is global,
+    // the coarse one the rank's own box); an aggregate outside the coarse box belongs to another rank: dropped
+    const int own = Cc.ce - Cc.cb;
+    const long long total = (long long)Cc.nspec * own;
     const int nother = F.nspec - 1;
-    for (long long R = (long long)blockIdx.x * blockDim.x + threadIdx.x; R < total; R += (long long)gridDim.x * blockDim.x) {
-        const int s = (int)(R / Cc.ncell), I = (int)(R - (long long)s * Cc.ncell);
+    for (long long W = (long long)blockIdx.x * blockDim.x + threadIdx.x; W < total; W += (long long)gridDim.x * blockDim.x) {
+        const int s = (int)(W / own), I = Cc.cb + (int)(W - (long long)s * own);
+        const long long R = (long long)s * Cc.ncell + I;
         const Cell3 Q = cell_coords(I, Cc.d2, Cc.d3);
         double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
         double oth[MG_MAXS];
@@ -477,7 +487,7 @@ __global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLe
         const int fq[3] = {f1, f2, f3};
         const int IQ[3] = {Q.j, Q.k, Q.l};
         for (int dj = 0; dj < f1; dj++) {
-            const int j = Q.j * f1 + dj;
+            const int j = (Q.j + cjoff) * f1 + dj;
             if (j >= F.d1) break;
             for (int dk = 0; dk < f2; dk++) {
                 const int k = Q.k * f2 + dk;
@@ -500,7 +510,9 @@ __global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLe
                         const Cell3 qn = cell_coords(nb[t], F.d2, F.d3);
                         const int dim = t >> 1;
                         const int cn = dim == 0 ? qn.j : dim == 1 ? qn.k : qn.l;
-                        if (cn / fq[dim] == IQ[dim]) acc[0] += v;                 // inside the aggregate
+                        const int an = cn / fq[dim] - (dim == 0 ? cjoff : 0);     // the neighbour's aggregate, coarse coordinates
+                        if (dim == 0 && (an < 0 || an >= Cc.d1)) continue;        // another rank's
+                        if (an == IQ[dim]) acc[0] += v;                           // inside the aggregate
                         else if (fq[dim] == 2) { acc[1 + t] += w * v; acc[0] += (1.0 - w) * v; }
                         else acc[1 + t] += v;
                     }
@@ -527,7 +539,7 @@ __global__ void __launch_bounds__(128) mg_smoother_setup_kernel(MgLevelDev L, do
     const int ns = L.nspec;
     double worst = 0.0;
     const int c0 = blockIdx.x * blockDim.x + threadIdx.x, cs = gridDim.x * blockDim.x;
-    MG_CELL_LOOP(c, L.ncell) {
+    MG_CELL_LOOP(c, L) {
         double A[MG_MAXS][MG_MAXS], B[MG_MAXS][MG_MAXS], tsum[MG_MAXS];
         for (int s = 0; s < ns; s++) {
             const long long r = (long long)s * L.ncell + c;
@@ -665,8 +677,16 @@ bool mg_applicable(const GridDesc &g, int j0, int j1)
 
 void mg_destroy(Mg *m) { delete m; }
 
-// Lays out the hierarchy for the rank's box of the grid: planes [j0, j1) of the slowest dimension (j1 <= j0: the
+// Lays out the hierarchy for the rank's part of the grid: planes [j0, j1) of the slowest dimension (j1 <= j0: the
 // whole grid).  The grid is handled as a 3-D box with leading extents 1 (a 2-D grid (a, b) is (1, a, b)).
+//
+// Sharded solves.  A hierarchy built on the rank's slab alone (couplings across slab faces cut) is a block-Jacobi
+// preconditioner over the ranks: measured at 2 GPUs, 256^3, 47 Krylov steps instead of 17 -- the cut is felt over the
+// screening length of the operator.  So the finest levels are GLOBAL: same aggregates as on one GPU, every rank working
+// on its planes of global-index level vectors, one halo exchange before each application of the level's operator (four
+// per level and cycle).  A level can be global while every rank's planes are whole aggregates (even bounds); below
+// that -- and below RS_MG_GLOBAL_LEVELS (default 4) levels, where the planes per rank get few and an exchange costs
+// more than the level's arithmetic -- the rank's coarse box is cut off and continues as a local hierarchy.
 int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
 {
     std::unique_ptr<Mg> M(new Mg());
@@ -676,30 +696,66 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
     const int slow = 3 - nd;   // position of the sharded (slowest) dimension in the box
     M->gstride = g.ncell;
     M->goff = 0;
-    if (j1 > j0) {
+    const bool sharded = j1 > j0 && j1 - j0 != g.d[0];
+    const int nr = sharded && comm_active() ? comm_nranks() : 1, rank = nr > 1 ? comm_rank() : 0;
+    // my planes at every global level; G = number of global levels
+    int G = 0, myj0[MG_MAXLEV], myj1[MG_MAXLEV];
+    if (nr > 1 && !getenv("RS_MG_LOCAL")) {
+        const char *e = getenv("RS_MG_GLOBAL_LEVELS");
+        const int gmax = e ? atoi(e) : 4;
+        std::vector<int> lo(nr), hi(nr);
+        for (int r = 0; r < nr; r++) rs_slab_bounds(g.d[0], nr, r, &lo[r], &hi[r]);
+        int dl = g.d[0];
+        while (G < gmax && G < MG_MAXLEV - 2) {
+            bool ok = dl > 2;
+            for (int r = 0; r < nr && ok; r++)
+                ok = lo[r] % 2 == 0 && (hi[r] % 2 == 0 || hi[r] == dl) && hi[r] - lo[r] >= 2;
+            if (!ok) break;
+            myj0[G] = lo[rank]; myj1[G] = hi[rank];
+            G++;
+            for (int r = 0; r < nr; r++) { lo[r] /= 2; hi[r] = (hi[r] + 1) / 2; }
+            dl = (dl + 1) / 2;
+        }
+        myj0[G] = lo[rank]; myj1[G] = hi[rank];   // my planes of the first local level
+    }
+    M->nglobal = G;
+    if (sharded && G == 0) {   // purely slab-local
         M->goff = j0 * (g.ncell / g.d[0]);
-        if (j1 - j0 != g.d[0]) cyc[slow] = 0;   // a slab of a cyclic dimension is an open box: the wrap crosses ranks
         d[slow] = j1 - j0;
     }
+    if (sharded) cyc[slow] = 0;   // a slab of a cyclic dimension is an open box: the wrap crosses ranks (not sharded today)
     int nlev = 0;
     for (;;) {
         MgLevel &L = M->lev[nlev];
         MgLevelDev &D = L.dev;
+        if (G > 0 && nlev == G) d[slow] = myj1[G] - myj0[G];   // from here on: the rank's own box
+        L.global = nlev < G;
         D.nspec = g.nspec;
         D.d1 = d[0]; D.d2 = d[1]; D.d3 = d[2];
         D.cyc1 = cyc[0]; D.cyc2 = cyc[1]; D.cyc3 = cyc[2];
         D.ncell = d[0] * d[1] * d[2];
         D.n = D.nspec * D.ncell;
+        D.cb = 0; D.ce = D.ncell;
+        if (L.global) {
+            const int plane = D.ncell / d[slow];
+            D.cb = myj0[nlev] * plane; D.ce = myj1[nlev] * plane;
+            L.hp.nspec = D.nspec; L.hp.ncell = D.ncell; L.hp.plane = plane;
+            L.hp.j0 = myj0[nlev]; L.hp.j1 = myj1[nlev];
+            L.hp.has_lo = rank > 0; L.hp.has_hi = rank < nr - 1;
+            if (nlev == G - 1) L.cjoff = myj0[G];
+        }
         const size_t nslot = 7 + (size_t)D.nspec - 1;
         RS_TRY(L.ell.alloc(nslot * D.n));
         RS_TRY(L.dinv.alloc(D.nspec == 1 ? (size_t)D.n : (size_t)D.nspec * D.n));
         RS_TRY(L.x.alloc(D.n)); RS_TRY(L.r.alloc(D.n)); RS_TRY(L.d.alloc(D.n));
         if (nlev > 0) RS_TRY(L.b.alloc(D.n));
+        if (L.global) { RS_TRY(L.x.zero(c.stream)); RS_TRY(L.d.zero(c.stream)); }
         D.ell = L.ell.p; D.dinv = L.dinv.p;
         nlev++;
         bool any = false;
         for (int q = 0; q < 3; q++) { L.f[q] = d[q] > 2 ? 2 : 1; any = any || L.f[q] == 2; }
-        if (D.ncell <= MG_COARSEST_CELLS || !any || nlev == MG_MAXLEV) { L.f[0] = L.f[1] = L.f[2] = 1; break; }
+        const bool more_global = nlev < G;   // a global level always hands on to the next one
+        if (!more_global && nlev > G && (D.ncell <= MG_COARSEST_CELLS || !any || nlev == MG_MAXLEV)) { L.f[0] = L.f[1] = L.f[2] = 1; break; }
         for (int q = 0; q < 3; q++) d[q] = (d[q] + L.f[q] - 1) / L.f[q];
     }
     M->nlev = nlev;
@@ -710,9 +766,9 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
     RS_TRY(M->cinv.alloc((size_t)M->nc * M->nc));
     RS_TRY(M->cwork.alloc(2 * (size_t)M->nc * M->nc));
     RS_TRY(M->flag.alloc(1));
-    // the levels small enough for the one-launch tail
+    // the levels small enough for the one-launch tail (local levels only: a block cannot exchange halos)
     M->tail = nlev;
-    for (int l = 0; l < nlev; l++)
+    for (int l = G; l < nlev; l++)
         if (M->lev[l].dev.ncell <= MG_TAIL_CELLS) { M->tail = l; break; }
     if (getenv("RS_NO_MG_TAIL")) M->tail = nlev;
     if (M->tail < nlev) {
@@ -742,7 +798,7 @@ int mg_update(Ctx &c, Mg &M, const int *rowptr, const int *col, const double *va
         RS_TRY(L.ell.zero(st));
         const double nz = (double)L.dev.n * (6.0 + L.dev.nspec);
         Launch La(c, K_PRECOND_SETUP, 12.0 * nz + 8.0 * nz);
-        mg_build_l0_kernel<<<mg_grid(L.dev.n), 256, 0, st>>>(L.dev, M.gstride, M.goff, rowptr, col, val, L.ell.p);
+        mg_build_l0_kernel<<<mg_grid((long long)L.dev.nspec * (L.dev.ce - L.dev.cb)), 256, 0, st>>>(L.dev, M.gstride, M.goff, rowptr, col, val, L.ell.p);
     }
     for (int l = 0; l < M.nlev; l++) {
         MgLevel &L = M.lev[l];
@@ -750,13 +806,16 @@ int mg_update(Ctx &c, Mg &M, const int *rowptr, const int *col, const double *va
         if (l + 1 < M.nlev) {
             MgLevel &Cn = M.lev[l + 1];
             Launch La(c, K_PRECOND_SETUP, 8.0 * nz + 8.0 * nz / 8.0);
-            mg_build_coarse_kernel<<<mg_grid(Cn.dev.n), 256, 0, st>>>(L.dev, Cn.dev, L.f[0], L.f[1], L.f[2], 0.5, Cn.ell.p);
+            mg_build_coarse_kernel<<<mg_grid((long long)Cn.dev.nspec * (Cn.dev.ce - Cn.dev.cb)), 256, 0, st>>>(L.dev, Cn.dev, L.f[0], L.f[1], L.f[2], L.cjoff, 0.5,
+                                                                                                         Cn.ell.p);
         }
         {
             Launch La(c, K_PRECOND_SETUP, 8.0 * nz + 8.0 * L.dev.nspec * L.dev.n);
-            mg_smoother_setup_kernel<<<grid_for(L.dev.ncell, 128, 148 * 16), 128, 0, st>>>(L.dev, L.dinv.p, M.lmax.p + l);
+            mg_smoother_setup_kernel<<<grid_for(L.dev.ce - L.dev.cb, 128, 148 * 16), 128, 0, st>>>(L.dev, L.dinv.p, M.lmax.p + l);
         }
     }
+    // a global level is one operator: every rank smooths with the same polynomial
+    if (M.nglobal > 0) RS_TRY(comm_allreduce_max(c, M.lmax.p, M.nglobal));
     {
         Launch La(c, K_PRECOND_SETUP, 24.0 * M.nc * M.nc);
         mg_coarse_invert_kernel<<<1, 1024, 0, st>>>(M.lev[M.nlev - 1].dev, M.cwork.p, M.cinv.p, M.flag.p);
@@ -772,8 +831,8 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     cudaStream_t st = c.stream;
     MgLevel &L = M.lev[l];
     const MgLevelDev &D = L.dev;
-    const double n = (double)D.n, mat = 8.0 * n * (6.0 + D.nspec);
-    const int grid = mg_grid(D.ncell);
+    const double n = (double)D.nspec * (D.ce - D.cb), mat = 8.0 * n * (6.0 + D.nspec);
+    const int grid = mg_grid(D.ce - D.cb);
     // statistics: the smoothing passes and the transfers of the finest level on their own, every level below as one class
     const int k_smooth = l == 0 ? K_MG_SMOOTH_L0 : K_MG_COARSE, k_transfer = l == 0 ? K_MG_TRANSFER_L0 : K_MG_COARSE;
     if (l == M.tail && !(l == 0 && dot_out && pr.nranks > 1)) {
@@ -798,25 +857,28 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
         Launch La(c, k_smooth, 16.0 * n + 8.0 * D.nspec * n);
         mg_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, d);
     }
+    if (L.global) comm_halo_exchange(c, L.d.p, L.hp);
     {
         Launch La(c, k_smooth, mat + 24.0 * n + 8.0 * D.nspec * n);
         mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, b, d, none, x, none, nullptr, nullptr, nullptr, PeerRed());
     }
+    if (L.global) comm_halo_exchange(c, L.x.p, L.hp);
     {   // residual, summed over the aggregates
         Launch La(c, k_transfer, mat + 16.0 * n + 8.0 * Cn.dev.n);
-        mg_resid_restrict_kernel<NS><<<mg_grid(Cn.dev.ncell), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d1, Cn.dev.d2, Cn.dev.d3,
-                                                                          b, x, view(Cn.b.p, Cn.dev.ncell));
+        mg_resid_restrict_kernel<NS><<<mg_grid(Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev, L.cjoff,
+                                                                                   b, x, view(Cn.b.p, Cn.dev.ncell));
     }
     mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.x.p, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
     {
         Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
-        mg_prolong_kernel<<<grid, 256, 0, st>>>(D.nspec, D.d1, D.d2, D.d3, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3,
-                                                view(Cn.x.p, Cn.dev.ncell), x);
+        mg_prolong_kernel<<<grid, 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.x.p, Cn.dev.ncell), x);
     }
+    if (L.global) comm_halo_exchange(c, L.x.p, L.hp);
     {   // post-smoothing: the same two Chebyshev steps, two passes
         Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         mg_resid_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, x, r, d);
     }
+    if (L.global) comm_halo_exchange(c, L.d.p, L.hp);
     {
         Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         if (dot_out)
@@ -830,6 +892,8 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
 // read and written); dot_out != nullptr: *dot_out = <r, z> over the slab, all-reduced over the ranks (pr).
 int mg_apply(Ctx &c, Mg &M, const double *r, double *z, double *partials, unsigned *ticket, double *dot_out, const PeerRed &pr)
 {
+    // level 0 addresses the Krylov vectors directly: cells of the rank's box (slab-local hierarchy: offset to its first
+    // plane) or of the whole grid (global top level: the level's own cell range picks the rank's planes)
     const VecView b = view(const_cast<double *>(r), M.gstride, M.goff), xo = view(z, M.gstride, M.goff);
     const int ns = M.lev[0].dev.nspec;
     if (ns == 1) mg_cycle_level<1>(c, M, 0, b, xo, partials, ticket, dot_out, pr);

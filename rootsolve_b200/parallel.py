@@ -16,11 +16,23 @@ import ctypes as C
 import numpy as np
 
 
-def slab_bounds(d1: int, nranks: int, rank: int):
-    """Planes [j0, j1) of the slowest grid dimension owned by ``rank`` (same rule as rs_slab_bounds)."""
+def _slab_bound(d1: int, nranks: int, r: int) -> int:
+    if r <= 0:
+        return 0
+    if r >= nranks:
+        return d1
     base, rem = divmod(d1, nranks)
-    j0 = rank * base + min(rank, rem)
-    return j0, j0 + base + (1 if rank < rem else 0)
+    A = 1
+    while A < 16 and d1 >= nranks * 4 * (2 * A):
+        A *= 2
+    return (r * base + min(r, rem)) // A * A
+
+
+def slab_bounds(d1: int, nranks: int, rank: int):
+    """Planes [j0, j1) of the slowest grid dimension owned by ``rank`` (same rule as rs_slab_bounds): an even split
+    whose interior bounds are moved down to a multiple of 2..16 planes while every rank keeps enough of them -- whole
+    2^k aggregates per rank are what lets the finest multigrid levels span the ranks."""
+    return _slab_bound(d1, nranks, rank), _slab_bound(d1, nranks, rank + 1)
 
 
 def owned_ranges(nspec: int, dims, nranks: int, rank: int):
