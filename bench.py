@@ -304,6 +304,10 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- rootsolve_b200 has no CPU path to measure")
     torch.cuda.set_device(local_rank)
+    # libraries (NCCL's version banner) write to stdout: everything but the JSON line goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     L = _capi.lib()
@@ -372,13 +376,13 @@ def run_ours(args):
     method = "cg" if R.krylov_method else "bicgstab"
 
     # ---- second pass: per-kernel CUDA events (single GPU: graphs are off while profiling) -------------------------
+    # (sharded: rank 0's table; a kernel's time then includes its waits for the neighbours' halos and partial sums)
     raw, ktab, psteps = {}, {}, max(1, min(args.steps, 3))
-    if world == 1:
-        _capi.check(L.rs_solver_set_profiling(h, 1))
-        for _ in range(psteps):
-            step()
-        raw, ktab = kernel_table(L, h, psteps)
-        _capi.check(L.rs_solver_set_profiling(h, 0))
+    _capi.check(L.rs_solver_set_profiling(h, 1))
+    for _ in range(psteps):
+        step()
+    raw, ktab = kernel_table(L, h, psteps)
+    _capi.check(L.rs_solver_set_profiling(h, 0))
     L.rs_solver_destroy(h)
 
     # ---- end-to-end arm: the reference-facing call with host buffers ------------------------------
@@ -500,6 +504,8 @@ def run_ours(args):
                                               f"(FD Jacobian {big['oracle_phases_s']['jac']:.3f} s, LDU factor "
                                               f"{big['oracle_phases_s']['factor']:.2f} s, solves {big['oracle_phases_s']['solve']:.2f} s); "
                                               f"the reference cannot run {S}^3"}
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -172,6 +172,40 @@ bool comm_pooled_vectors(size_t n, double **mine, void **lo, void **hi)
     return true;
 }
 
+// One more peer-mapped buffer, for the level vectors of the multigrid hierarchy whose halo planes travel (mg.cu):
+// same life cycle as the pool above.
+static size_t g_arena_n = 0;
+static double *g_arena_mine = nullptr;
+static void *g_arena_lo = nullptr, *g_arena_hi = nullptr;
+static bool g_arena_ok = false;
+
+static void arena_release()
+{
+    if (g_arena_ok) comm_unshare_vectors(1, &g_arena_lo, &g_arena_hi);
+    if (g_arena_mine) cudaFree(g_arena_mine);
+    g_arena_mine = nullptr; g_arena_lo = g_arena_hi = nullptr;
+    g_arena_n = 0;
+    g_arena_ok = false;
+}
+
+bool comm_pooled_arena(size_t n, double **mine, void **lo, void **hi)
+{
+    if (!comm_peer_enabled()) return false;
+    if (!g_arena_ok || g_arena_n < n) {   // collective: every rank asks for the same n in the same order
+        cudaDeviceSynchronize();
+        arena_release();
+        if (cudaMalloc((void **)&g_arena_mine, (n + 8) * sizeof(double)) != cudaSuccess) { cudaGetLastError(); g_arena_mine = nullptr; }
+        if (g_arena_mine) cudaMemset(g_arena_mine, 0, (n + 8) * sizeof(double));
+        void *m[1] = {g_arena_mine};
+        // every rank takes part in the share even if its own allocation failed: a NULL handle fails it for all
+        g_arena_ok = comm_share_vectors(m, 1, &g_arena_lo, &g_arena_hi);
+        if (!g_arena_ok) { arena_release(); return false; }
+        g_arena_n = n;
+    }
+    *mine = g_arena_mine; *lo = g_arena_lo; *hi = g_arena_hi;
+    return true;
+}
+
 // flag words of the halo handshake live behind the reduction slots of every mailbox:
 //   [HALO_FROM_LO] is written by rank-1, [HALO_FROM_HI] by rank+1
 HaloSignal comm_next_halo_signal()
@@ -244,6 +278,7 @@ bool comm_peer_enabled() { return false; }
 PeerRed comm_next_peer_red() { return PeerRed(); }
 bool comm_share_vectors(void *const *, int count, void **lo, void **hi) { for (int i = 0; i < count; i++) lo[i] = hi[i] = nullptr; return false; }
 bool comm_pooled_vectors(size_t, double **, void **, void **) { return false; }
+bool comm_pooled_arena(size_t, double **, void **, void **) { return false; }
 void comm_unshare_vectors(int, void **, void **) {}
 HaloSignal comm_next_halo_signal() { return HaloSignal(); }
 int comm_nranks() { return 1; }
@@ -307,6 +342,7 @@ extern "C" void rs_comm_finalize(void)
             rs::g_mail[p] = nullptr;
         }
         rs::pool_release();
+        rs::arena_release();
         if (rs::g_seq_dev) { cudaFree(rs::g_seq_dev); rs::g_seq_dev = nullptr; }
         if (rs::g_mail_local) { cudaFree(rs::g_mail_local); rs::g_mail_local = nullptr; }
         rs::g_peer_ok = false;

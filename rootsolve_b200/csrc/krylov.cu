@@ -1329,7 +1329,8 @@ static int graph_steps_per_launch(const Ctx &c, const Krylov &k)
     if (no_graph || c.profile) return 0;
     // with the multigrid cycle a step is ~40 launches and the solve ~10 steps: on large grids launch latency is
     // nothing and a graph would only add a possibly wasted step; small grids replay two steps per host call
-    if (k.mg_on || k.btd_on) return k.own.total() > 500000 ? 0 : 2;
+    // (a sharded solve is launch bound at any size: ~80 launches per step against a slab's worth of work)
+    if (k.mg_on || k.btd_on) return (k.own.total() > 500000 && !comm_active() && !getenv("RS_MG_GRAPH")) ? 0 : 2;
     int g = k.check_every & ~1;
     return g >= 2 ? g : 2;
 }

@@ -66,6 +66,8 @@ struct MgLevel {
     bool global = false;    // sharded solve: the level spans all ranks (global cell indices, halo planes exchanged)
     int cjoff = 0;          // transfer to the next level: plane 0 of that level's box in this level's aggregate numbering
     HaloPlan hp;            // global levels: the planes that travel before every application of the level's operator
+    double *xp = nullptr, *dp = nullptr;   // x and d of the level (own buffers, or slices of the peer-mapped arena)
+    double *x_lo = nullptr, *x_hi = nullptr, *d_lo = nullptr, *d_hi = nullptr;   // the slab neighbours' copies (halo push)
     DevBuf<double> ell, dinv, b, x, r, d;
 };
 
@@ -78,6 +80,8 @@ struct Mg {
     DevBuf<int> flag;         // != 0: the coarsest operator was singular to working precision
     int gstride = 0, goff = 0;   // level-0 view of the solver's vectors
     int nc = 0;               // unknowns of the coarsest level
+    bool push = false;        // halo planes of the global levels are stored into the neighbours over NVLink
+    DevBuf<unsigned> hticket;
     int nglobal = 0;          // number of global levels (0: single GPU, or a purely slab-local hierarchy)
     int tail = 0;             // first level of the one-launch tail (levels of <= MG_TAIL_CELLS cells); nlev: no tail
     DevBuf<unsigned char> tail_levels;   // MgTailLevel[nlev] on the device
@@ -356,6 +360,27 @@ __global__ void __launch_bounds__(256) mg_coarse_solve_kernel(int nc, const doub
         x[i] = a;
     }
 }
+
+// ---- halo planes of a global level over NVLink ----------------------------------------------------------------
+// The rank's first / last plane of every species goes straight into the slab neighbours' copy of the vector (peer
+// stores), the last block raises the neighbours' flags; the one-thread kernel behind it waits for both neighbours'
+// flags, so everything later in the stream sees complete halos.  Two small launches instead of an NCCL send/recv
+// group (~40 us at 8 GPUs): a cycle has sixteen of these.
+__global__ void __launch_bounds__(256) mg_halo_push_kernel(int nspec, int ncell, int plane, int j0, int j1, const double *__restrict__ v,
+                                                           HaloPush hp, unsigned *ticket)
+{
+    const long long per = (long long)nspec * plane;
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < 2 * per; q += (long long)gridDim.x * blockDim.x) {
+        const int side = q >= per ? 1 : 0;
+        const long long w = q - side * per;
+        const int s = (int)(w / plane), o = (int)(w - (long long)s * plane);
+        const long long i = (long long)s * ncell + (long long)(side ? j1 - 1 : j0) * plane + o;
+        double *dst = side ? hp.hi : hp.lo;
+        if (dst != nullptr) dst[i] = v[i];
+    }
+    halo_signal_done(hp, ticket);
+}
+__global__ void mg_halo_wait_kernel(HaloSignal hs) { halo_wait(hs); }
 
 // ---- the small levels in one launch ---------------------------------------------------------------------------
 // Below a few thousand cells a level is a handful of microseconds of work per kernel and six kernels per visit: launch
@@ -747,9 +772,9 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
         const size_t nslot = 7 + (size_t)D.nspec - 1;
         RS_TRY(L.ell.alloc(nslot * D.n));
         RS_TRY(L.dinv.alloc(D.nspec == 1 ? (size_t)D.n : (size_t)D.nspec * D.n));
-        RS_TRY(L.x.alloc(D.n)); RS_TRY(L.r.alloc(D.n)); RS_TRY(L.d.alloc(D.n));
+        RS_TRY(L.r.alloc(D.n));
+        if (!L.global) { RS_TRY(L.x.alloc(D.n)); RS_TRY(L.d.alloc(D.n)); L.xp = L.x.p; L.dp = L.d.p; }   // global: below
         if (nlev > 0) RS_TRY(L.b.alloc(D.n));
-        if (L.global) { RS_TRY(L.x.zero(c.stream)); RS_TRY(L.d.zero(c.stream)); }
         D.ell = L.ell.p; D.dinv = L.dinv.p;
         nlev++;
         bool any = false;
@@ -759,6 +784,31 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
         for (int q = 0; q < 3; q++) d[q] = (d[q] + L.f[q] - 1) / L.f[q];
     }
     M->nlev = nlev;
+    if (G > 0) {
+        // x and d of the global levels: one peer-mapped arena when the halo planes can be pushed over NVLink
+        size_t total = 0;
+        for (int l = 0; l < G; l++) total += 2 * (((size_t)M->lev[l].dev.n + 31) & ~(size_t)31);
+        double *mine = nullptr;
+        void *alo = nullptr, *ahi = nullptr;
+        M->push = !getenv("RS_NO_PUSH") && comm_pooled_arena(total, &mine, &alo, &ahi);
+        size_t off = 0;
+        for (int l = 0; l < G; l++) {
+            MgLevel &L = M->lev[l];
+            const size_t nl = ((size_t)L.dev.n + 31) & ~(size_t)31;
+            if (M->push) {
+                L.xp = mine + off; L.dp = mine + off + nl;
+                L.x_lo = alo ? (double *)alo + off : nullptr; L.d_lo = alo ? (double *)alo + off + nl : nullptr;
+                L.x_hi = ahi ? (double *)ahi + off : nullptr; L.d_hi = ahi ? (double *)ahi + off + nl : nullptr;
+            } else {
+                RS_TRY(L.x.alloc(L.dev.n)); RS_TRY(L.d.alloc(L.dev.n));
+                RS_TRY(L.x.zero(c.stream)); RS_TRY(L.d.zero(c.stream));
+                L.xp = L.x.p; L.dp = L.d.p;
+            }
+            off += 2 * nl;
+        }
+        RS_TRY(M->hticket.alloc(1));
+        RS_TRY(M->hticket.zero(c.stream));
+    }
     RS_TRY(M->lmax.alloc(nlev));
     for (int l = 0; l < nlev; l++) M->lev[l].dev.lmax = M->lmax.p + l;
     M->nc = M->lev[nlev - 1].dev.n;
@@ -777,7 +827,7 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
             MgLevel &L = M->lev[l];
             tl[l].D = L.dev;
             tl[l].f1 = L.f[0]; tl[l].f2 = L.f[1]; tl[l].f3 = L.f[2];
-            tl[l].b = L.b.p; tl[l].x = L.x.p; tl[l].r = L.r.p; tl[l].d = L.d.p;
+            tl[l].b = L.b.p; tl[l].x = L.xp; tl[l].r = L.r.p; tl[l].d = L.dp;
         }
         RS_TRY(M->tail_levels.alloc(sizeof(MgTailLevel) * nlev));
         RS_CUDA(cudaMemcpyAsync(M->tail_levels.p, tl.data(), sizeof(MgTailLevel) * nlev, cudaMemcpyHostToDevice, c.stream));
@@ -824,6 +874,25 @@ int mg_update(Ctx &c, Mg &M, const int *rowptr, const int *col, const double *va
     return RS_OK;
 }
 
+// halo planes of x (or d) of a global level to the slab neighbours
+static void mg_halo(Ctx &c, Mg &M, MgLevel &L, bool is_x)
+{
+    double *v = is_x ? L.xp : L.dp;
+    if (!M.push) { comm_halo_exchange(c, v, L.hp); return; }
+    const HaloSignal sig = comm_next_halo_signal();
+    HaloPush hp;
+    hp.lo = L.hp.has_lo ? (is_x ? L.x_lo : L.d_lo) : nullptr;
+    hp.hi = L.hp.has_hi ? (is_x ? L.x_hi : L.d_hi) : nullptr;
+    hp.plane = L.hp.plane;
+    hp.signal = 1;
+    hp.sig = sig;
+    Launch La(c, K_HALO, 32.0 * L.hp.nspec * L.hp.plane);
+    mg_halo_push_kernel<<<grid_for(2LL * L.hp.nspec * L.hp.plane, 256, 148), 256, 0, c.stream>>>(L.hp.nspec, L.hp.ncell, L.hp.plane, L.hp.j0, L.hp.j1,
+                                                                                            v, hp, M.hticket.p);
+    mg_halo_wait_kernel<<<1, 32, 0, c.stream>>>(sig);
+    c.launches++;
+}
+
 template <int NS>
 static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double *partials, unsigned *ticket, double *dot_out,
                            const PeerRed &pr)
@@ -851,34 +920,34 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
         return;
     }
     MgLevel &Cn = M.lev[l + 1];
-    const VecView x = view(L.x.p, D.ncell), r = view(L.r.p, D.ncell), d = view(L.d.p, D.ncell);
+    const VecView x = view(L.xp, D.ncell), r = view(L.r.p, D.ncell), d = view(L.dp, D.ncell);
     const VecView none = view(nullptr, 0);
     {   // pre-smoothing from a zero guess: two Chebyshev steps, one pass over the matrix
         Launch La(c, k_smooth, 16.0 * n + 8.0 * D.nspec * n);
         mg_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, d);
     }
-    if (L.global) comm_halo_exchange(c, L.d.p, L.hp);
+    if (L.global) mg_halo(c, M, L, false);
     {
         Launch La(c, k_smooth, mat + 24.0 * n + 8.0 * D.nspec * n);
         mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, b, d, none, x, none, nullptr, nullptr, nullptr, PeerRed());
     }
-    if (L.global) comm_halo_exchange(c, L.x.p, L.hp);
+    if (L.global) mg_halo(c, M, L, true);
     {   // residual, summed over the aggregates
         Launch La(c, k_transfer, mat + 16.0 * n + 8.0 * Cn.dev.n);
         mg_resid_restrict_kernel<NS><<<mg_grid(Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev, L.cjoff,
                                                                                    b, x, view(Cn.b.p, Cn.dev.ncell));
     }
-    mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.x.p, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
+    mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.xp, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
     {
         Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
-        mg_prolong_kernel<<<grid, 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.x.p, Cn.dev.ncell), x);
+        mg_prolong_kernel<<<grid, 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.xp, Cn.dev.ncell), x);
     }
-    if (L.global) comm_halo_exchange(c, L.x.p, L.hp);
+    if (L.global) mg_halo(c, M, L, true);
     {   // post-smoothing: the same two Chebyshev steps, two passes
         Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         mg_resid_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, x, r, d);
     }
-    if (L.global) comm_halo_exchange(c, L.d.p, L.hp);
+    if (L.global) mg_halo(c, M, L, false);
     {
         Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         if (dot_out)

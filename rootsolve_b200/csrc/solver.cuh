@@ -172,6 +172,8 @@ bool comm_share_vectors(void *const *mine, int count, void **lo, void **hi);
 void comm_unshare_vectors(int count, void **lo, void **hi);
 // two n-vectors from a pool that stays mapped into the slab neighbours for the life of the communicator
 bool comm_pooled_vectors(size_t n, double **mine, void **lo, void **hi);
+// one more peer-mapped buffer of n doubles (multigrid level vectors whose halo planes travel); same life cycle
+bool comm_pooled_arena(size_t n, double **mine, void **lo, void **hi);
 HaloSignal comm_next_halo_signal();
 int comm_allreduce_sum(Ctx &c, double *d_buf, int count);
 int comm_allreduce_max(Ctx &c, double *d_buf, int count);
