@@ -44,6 +44,15 @@ constexpr int MG_COARSEST_CELLS = 32;  // stop coarsening here: <= 256 unknowns,
 constexpr int MG_MIN_CELLS = 64;       // smaller grids keep the (block-)Jacobi preconditioner
 constexpr double MG_CHEB_RATIO = 4.0;  // smoothing interval [lmax / ratio, lmax]
 
+// The level matrices are a preconditioner's data: stored in single precision (half the bytes of the four matrix passes
+// of a cycle), promoted to double in every product.  The cycle stays a fixed linear operator; the Krylov method around
+// it works on the double-precision Jacobian.  -DRS_MG_FP64 keeps them in double (A/B measurements).
+#ifdef RS_MG_FP64
+typedef double mg_real;
+#else
+typedef float mg_real;
+#endif
+
 // a vector addressed by (species, cell): internal vectors are packed (stride = cells of the level); the Krylov
 // vectors at level 0 keep the solver's global indexing (stride = cells of the whole grid, off = first cell of the slab)
 struct VecView {
@@ -55,7 +64,7 @@ struct VecView {
 struct MgLevelDev {
     int nspec, d1, d2, d3, cyc1, cyc2, cyc3, ncell, n;
     int cb, ce;           // cells this rank works on: all of a local level's box, the rank's planes of a global level
-    const double *ell;    // [7 + nspec - 1][n]
+    const mg_real *ell;   // [7 + nspec - 1][n]
     const double *dinv;   // nspec == 1: 1/diag per row; else the inverse cell blocks [s][s'][cell]
     const double *lmax;   // Gershgorin bound of the (block-)Jacobi-preconditioned operator of this level
 };
@@ -68,7 +77,8 @@ struct MgLevel {
     HaloPlan hp;            // global levels: the planes that travel before every application of the level's operator
     double *xp = nullptr, *dp = nullptr;   // x and d of the level (own buffers, or slices of the peer-mapped arena)
     double *x_lo = nullptr, *x_hi = nullptr, *d_lo = nullptr, *d_hi = nullptr;   // the slab neighbours' copies (halo push)
-    DevBuf<double> ell, dinv, b, x, r, d;
+    DevBuf<mg_real> ell;
+    DevBuf<double> dinv, b, x, r, d;
 };
 
 struct Mg {
@@ -459,7 +469,7 @@ __global__ void __launch_bounds__(MG_TAIL_THREADS) mg_tail_kernel(const MgTailLe
 // part of the stencil -- is left out of the preconditioner.  ell must be zero on entry.
 __global__ void __launch_bounds__(256) mg_build_l0_kernel(MgLevelDev L, int gstride, int goff, const int *__restrict__ rowptr,
                                                           const int *__restrict__ col, const double *__restrict__ val,
-                                                          double *__restrict__ ell)
+                                                          mg_real *__restrict__ ell)
 {
     const int own = L.ce - L.cb;
     const long long total = (long long)L.nspec * own;
@@ -479,7 +489,7 @@ __global__ void __launch_bounds__(256) mg_build_l0_kernel(MgLevelDev L, int gstr
             if (c2 < 0 || c2 >= L.ncell) continue;
             const double v = val[p];
             if (s2 != s) {
-                if (c2 == c) ell[(long long)(7 + (s2 < s ? s2 : s2 - 1)) * L.n + r] += v;
+                if (c2 == c) ell[(long long)(7 + (s2 < s ? s2 : s2 - 1)) * L.n + r] += (mg_real)v;
                 continue;
             }
             if (c2 == c) { acc[0] += v; continue; }
@@ -488,14 +498,14 @@ __global__ void __launch_bounds__(256) mg_build_l0_kernel(MgLevelDev L, int gstr
                 if (has[t] && nb[t] == c2) { acc[1 + t] += v; break; }
         }
 #pragma unroll
-        for (int t = 0; t < 7; t++) ell[(long long)t * L.n + r] = acc[t];
+        for (int t = 0; t < 7; t++) ell[(long long)t * L.n + r] = (mg_real)acc[t];
     }
 }
 
 // Galerkin coarse operator by summation.  Thread per (species, coarse cell).  w = weight kept by an entry that
 // crosses an aggregate face in a coarsened direction (the rest goes to the diagonal, see the file header).
 __global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLevelDev Cc, int f1, int f2, int f3, int cjoff, double w,
-                                                              double *__restrict__ ellc)
+                                                              mg_real *__restrict__ ellc)
 {
     // cjoff: plane of the coarse box's plane 0 in the fine level's aggregate numbering (the fine level is global,
     // the coarse one the rank's own box); an aggregate outside the coarse box belongs to another rank: dropped
@@ -546,8 +556,8 @@ __global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLe
             }
         }
 #pragma unroll
-        for (int t = 0; t < 7; t++) ellc[(long long)t * Cc.n + R] = acc[t];
-        for (int o = 0; o < nother; o++) ellc[(long long)(7 + o) * Cc.n + R] = oth[o];
+        for (int t = 0; t < 7; t++) ellc[(long long)t * Cc.n + R] = (mg_real)acc[t];
+        for (int o = 0; o < nother; o++) ellc[(long long)(7 + o) * Cc.n + R] = (mg_real)oth[o];
     }
 }
 
@@ -689,6 +699,21 @@ __global__ void __launch_bounds__(1024) mg_coarse_invert_kernel(MgLevelDev L, do
 
 // ---- host side ---------------------------------------------------------------------------------------------
 static inline int mg_grid(long long work) { return grid_for(work, 256, 148 * 8); }
+// one resident wave of THIS kernel: a grid sized for 8 blocks per SM leaves a kernel that fits 5 or 6 (the reducing
+// variant of the smoothing pass, the restriction) with a second, mostly empty wave -- measured +40 % on its run time
+template <typename K>
+static int mg_wave_grid(K kernel, long long work)
+{
+    static int resident = 0;   // per instantiation = per kernel
+    if (resident == 0) {
+        int dev = 0, sms = 148, occ = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 256, 0) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 4; }
+        resident = sms * occ;
+    }
+    return grid_for(work, 256, resident);
+}
 static inline VecView view(double *p, int stride, int off = 0) { VecView v; v.p = p; v.stride = stride; v.off = off; return v; }
 
 bool mg_applicable(const GridDesc &g, int j0, int j1)
@@ -900,14 +925,14 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     cudaStream_t st = c.stream;
     MgLevel &L = M.lev[l];
     const MgLevelDev &D = L.dev;
-    const double n = (double)D.nspec * (D.ce - D.cb), mat = 8.0 * n * (6.0 + D.nspec);
+    const double n = (double)D.nspec * (D.ce - D.cb), mat = (double)sizeof(mg_real) * n * (6.0 + D.nspec);
     const int grid = mg_grid(D.ce - D.cb);
     // statistics: the smoothing passes and the transfers of the finest level on their own, every level below as one class
     const int k_smooth = l == 0 ? K_MG_SMOOTH_L0 : K_MG_COARSE, k_transfer = l == 0 ? K_MG_TRANSFER_L0 : K_MG_COARSE;
     if (l == M.tail && !(l == 0 && dot_out && pr.nranks > 1)) {
         // this level and everything below it in one block
         double bytes = 0.0;
-        for (int q = l; q < M.nlev; q++) bytes += 4.0 * 8.0 * M.lev[q].dev.n * (6.0 + D.nspec) + 150.0 * M.lev[q].dev.n;
+        for (int q = l; q < M.nlev; q++) bytes += 4.0 * sizeof(mg_real) * M.lev[q].dev.n * (6.0 + D.nspec) + 150.0 * M.lev[q].dev.n;
         Launch La(c, K_MG_COARSE, bytes);
         const VecView none0 = view(nullptr, 0);
         mg_tail_kernel<NS><<<1, MG_TAIL_THREADS, 0, st>>>(reinterpret_cast<const MgTailLevel *>(M.tail_levels.p), l, M.nlev, M.nc, M.cinv.p,
@@ -934,7 +959,7 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     if (L.global) mg_halo(c, M, L, true);
     {   // residual, summed over the aggregates
         Launch La(c, k_transfer, mat + 16.0 * n + 8.0 * Cn.dev.n);
-        mg_resid_restrict_kernel<NS><<<mg_grid(Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev, L.cjoff,
+        mg_resid_restrict_kernel<NS><<<mg_wave_grid(mg_resid_restrict_kernel<NS>, Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev, L.cjoff,
                                                                                    b, x, view(Cn.b.p, Cn.dev.ncell));
     }
     mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.xp, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
@@ -951,7 +976,8 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     {
         Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         if (dot_out)
-            mg_second_kernel<NS, true><<<grid, 256, 0, st>>>(D, r, d, x, xout, b, partials, ticket, dot_out, pr);
+            mg_second_kernel<NS, true><<<mg_wave_grid(mg_second_kernel<NS, true>, D.ce - D.cb), 256, 0, st>>>(D, r, d, x, xout, b, partials, ticket,
+                                                                                                            dot_out, pr);
         else
             mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, r, d, x, xout, none, nullptr, nullptr, nullptr, PeerRed());
     }
