@@ -21,7 +21,7 @@ namespace rs {
 
 // ---- error text, context ---------------------------------------------------------
 static thread_local char g_err[512] = "";
-long long g_device_bytes = 0;
+std::atomic<long long> g_device_bytes{0};
 
 void set_error(const char *fmt, ...)
 {
@@ -94,10 +94,14 @@ void pool_free(void *p, size_t bytes)
     if (!p) return;
     Pool &P = pool();
     const size_t k = Pool::klass(bytes);
-    int dev = 0;
     // cudaFree waits for the device; a block that goes back to the cache gets the same guarantee, so whoever is
-    // handed it next (possibly on another stream) cannot race with work still using it
-    const bool ok = cudaGetDevice(&dev) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess;
+    // handed it next (possibly on another stream) cannot race with work still using it.  The cache is keyed by the
+    // device that OWNS the block, not by whichever is current when it is freed.
+    int dev = 0;
+    cudaPointerAttributes attr;
+    bool ok = cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeDevice;
+    if (ok) dev = attr.device; else cudaGetLastError();
+    ok = ok && cudaDeviceSynchronize() == cudaSuccess;
     std::lock_guard<std::mutex> lk(P.mu);
     P.configure();
     if (!ok || P.cached + k > P.max_cached) { cudaFree(p); return; }
@@ -255,6 +259,13 @@ __global__ void __launch_bounds__(256) sumabs_kernel(int b, int e, const double 
 
 using namespace rs;
 
+// a pair of CUDA events that does not leak on an early return
+struct EventPair {
+    cudaEvent_t a = nullptr, b = nullptr;
+    int create() { RS_CUDA(cudaEventCreate(&a)); RS_CUDA(cudaEventCreate(&b)); return RS_OK; }
+    ~EventPair() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+};
+
 // ---- the handle ----------------------------------------------------------------------------
 struct rs_solver {
     Ctx ctx;
@@ -407,9 +418,9 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
     s.structure_only = a->Type < 0;
     if (a->control) s.ctl = *a->control;
     const int n = s.n;
-    cudaEvent_t e0, e1;
-    RS_CUDA(cudaEventCreate(&e0));
-    RS_CUDA(cudaEventCreate(&e1));
+    EventPair ev;
+    RS_TRY(ev.create());
+    cudaEvent_t e0 = ev.a, e1 = ev.b;
     RS_CUDA(cudaEventRecord(e0, c.stream));
 
     // RS_DEBUG_SETUP=1: wall-clock per set-up phase on stderr (each mark drains the stream)
@@ -514,8 +525,6 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e0, e1);
     s.t_setup = ms * 1e-3;
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     s.setup_launches = c.launches;
     *out = S.release();
     return RS_OK;
@@ -559,9 +568,9 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
     const Ranges &own = s.own;
     const double rows = (double)own.total();
     cudaStream_t st = c.stream;
-    cudaEvent_t e0, e1;
-    RS_CUDA(cudaEventCreate(&e0));
-    RS_CUDA(cudaEventCreate(&e1));
+    EventPair ev;
+    RS_TRY(ev.create());
+    cudaEvent_t e0 = ev.a, e1 = ev.b;
     RS_CUDA(cudaEventRecord(e0, st));
     s.precis.assign(s.maxiter, 0.0);
     s.niter = 0; s.steady = 0; s.krylov_iters = 0;
@@ -654,12 +663,10 @@ extern "C" int rs_solver_run(rs_solver *sp, rs_stsparse_result *meta)
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e0, e1);
     s.t_newton = ms * 1e-3;
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     if (meta) {
         meta->niter = s.niter;
         meta->steady[0] = s.steady; meta->steady[1] = s.nnz; meta->steady[2] = s.ngp;
-        meta->steady[3] = (int)std::min<long long>(g_device_bytes / 8, 2147483647LL);
+        meta->steady[3] = (int)std::min<long long>(g_device_bytes.load() / 8, 2147483647LL);
         meta->krylov_iters = s.krylov_iters;
         meta->kernel_launches = (int)(c.launches - launches0);
         meta->t_setup_s = s.t_setup;
@@ -741,7 +748,7 @@ extern "C" int rs_stsparse(const rs_stsparse_args *a, rs_stsparse_result *r)
         r->t_setup_s = s->t_setup;
         r->t_newton_s = s->t_newton;
         r->krylov_iters = s->krylov_iters;
-        r->steady[3] = (int)std::min<long long>(g_device_bytes / 8, 2147483647LL);
+        r->steady[3] = (int)std::min<long long>(g_device_bytes.load() / 8, 2147483647LL);
     }
     rs_solver_destroy(s);
     return rc;

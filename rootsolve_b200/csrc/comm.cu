@@ -144,8 +144,14 @@ static double *g_pool_mine[2] = {nullptr, nullptr};
 static void *g_pool_lo[2] = {nullptr, nullptr}, *g_pool_hi[2] = {nullptr, nullptr};
 static bool g_pool_ok = false;
 
+// bumped whenever the pool or the arena below is re-created: a solver handle that still holds pointers into the old
+// buffers must not run on them (krylov_solve checks)
+static int g_pool_generation = 0;
+int comm_pool_generation() { return g_pool_generation; }
+
 static void pool_release()
 {
+    g_pool_generation++;
     if (g_pool_ok) comm_unshare_vectors(2, g_pool_lo, g_pool_hi);
     for (int i = 0; i < 2; i++) { if (g_pool_mine[i]) cudaFree(g_pool_mine[i]); g_pool_mine[i] = nullptr; }
     g_pool_n = 0;
@@ -181,6 +187,7 @@ static bool g_arena_ok = false;
 
 static void arena_release()
 {
+    g_pool_generation++;
     if (g_arena_ok) comm_unshare_vectors(1, &g_arena_lo, &g_arena_hi);
     if (g_arena_mine) cudaFree(g_arena_mine);
     g_arena_mine = nullptr; g_arena_lo = g_arena_hi = nullptr;
@@ -279,6 +286,7 @@ PeerRed comm_next_peer_red() { return PeerRed(); }
 bool comm_share_vectors(void *const *, int count, void **lo, void **hi) { for (int i = 0; i < count; i++) lo[i] = hi[i] = nullptr; return false; }
 bool comm_pooled_vectors(size_t, double **, void **, void **) { return false; }
 bool comm_pooled_arena(size_t, double **, void **, void **) { return false; }
+int comm_pool_generation() { return 0; }
 void comm_unshare_vectors(int, void **, void **) {}
 HaloSignal comm_next_halo_signal() { return HaloSignal(); }
 int comm_nranks() { return 1; }

@@ -58,6 +58,14 @@ int pick_lanes(int n, int nnz)
     return 32;
 }
 
+// The x gathers of the SpMV kernels go through the read-only (non-coherent) path -- except when the slab neighbours
+// store the halo planes of that very vector while the kernel is already resident and waiting for them (halo push):
+// read-only data must not change during the kernel's lifetime, so those launches load through L2 (ld.global.cg).
+__device__ __forceinline__ double ld_x(const double *__restrict__ x, int i, bool pushed)
+{
+    return pushed ? __ldcg(x + i) : __ldg(x + i);
+}
+
 // ---- SpMV, sub-warp variant --------------------------------------------------------
 // NDOT = 0: plain product.  NDOT = 1: out[0] = <w, y>.  NDOT = 2: out[0] = <y, w>, out[1] = <y, y>.
 template <int LANES, int NDOT>
@@ -81,7 +89,7 @@ __global__ void __launch_bounds__(256) spmv_kernel(int row0, int row1, const int
         const long long r = row0 + q;
         if (q < n) {
             const int e = rowptr[r + 1];
-            for (int p = rowptr[r] + lane; p < e; p += LANES) sum += val[p] * __ldg(&x[col[p]]);
+            for (int p = rowptr[r] + lane; p < e; p += LANES) sum += val[p] * ld_x(x, col[p], hw.seq != nullptr);
         }
 #pragma unroll
         for (int o = LANES / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
@@ -277,7 +285,7 @@ __global__ void __launch_bounds__(TMA_THREADS) spmv_tma_kernel(int row0, int row
                 }
 #pragma unroll
                 for (int q = 0; q < 8; q++)
-                    if (c[q] >= 0) sum += v[q] * __ldg(&x[c[q]]);
+                    if (c[q] >= 0) sum += v[q] * ld_x(x, c[q], hw.seq != nullptr);
             }
             if (r < row1) {
                 y[r] = sum;
@@ -379,7 +387,7 @@ spmv_grid_kernel(GridCols g, int row0, int row1, int ntiles, const int *__restri
             gr.set(g, r, r < row1);
             double xv[NSLOT];
 #pragma unroll
-            for (int q = 0; q < NSLOT; q++) xv[q] = gr.has[q] ? __ldg(&x[gr.c[q]]) : 0.0;
+            for (int q = 0; q < NSLOT; q++) xv[q] = gr.has[q] ? ld_x(x, gr.c[q], hw.seq != nullptr) : 0.0;
             mbar_wait(&full[s], parity);
             const double *sval = reinterpret_cast<const double *>(smem + s * GRID_STAGE_BYTES) - a0s[s];
             double v[NSLOT];
@@ -834,6 +842,7 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
         RS_TRY(k.z.alloc(n));
         if (comm_active()) RS_TRY(k.z.zero(c.stream));
     }
+    k.pool_generation = comm_pool_generation();   // after every pooled buffer of this handle has been obtained
     RS_TRY(k.partials.alloc(4 * 148 * 16));
     RS_TRY(k.scal.alloc(NSCAL));
     RS_TRY(k.ticket.alloc(4));
@@ -1554,6 +1563,11 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
     static const bool debug = getenv("RS_DEBUG_KRYLOV") != nullptr;
     bool conv_local = false;
     if (!converged) converged = &conv_local;
+    if (comm_active() && k.pool_generation != comm_pool_generation()) {
+        set_error("the peer-mapped vector pool was re-created for a larger solve after this solver handle was set up; "
+                  "create the handle again (one sharded solver at a time per process, or the largest one first)");
+        return RS_ECOMM;
+    }
     int rc = krylov_solve_inner(c, k, b, x, abs_floor, iters, relres, converged);
     if ((k.mg_on || k.btd_on) && (rc == RS_ESINGULAR || (rc == RS_OK && !*converged && !(*relres <= 0.1)))) {
         if (debug) fprintf(stderr, "[krylov] solve under the %s failed (rc %d, relres %.3e after %d its): back to Jacobi\n",

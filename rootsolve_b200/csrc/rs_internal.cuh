@@ -5,6 +5,7 @@
 
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -72,7 +73,7 @@ struct Launch {
 };
 
 // ---- device buffers ---------------------------------------------------------
-extern long long g_device_bytes;  // currently allocated through DevBuf
+extern std::atomic<long long> g_device_bytes;  // currently allocated through DevBuf (any thread)
 
 // Caching device allocator (api.cu).  A steady-state solve allocates ~40 arrays (gigabytes at 256^3) and frees
 // them on return; cudaMalloc/cudaFree of that volume costs tens of milliseconds per call and now and then far
@@ -202,8 +203,10 @@ __device__ __forceinline__ void halo_wait(const HaloSignal &hs)
     if (threadIdx.x == 0) {
         const double want = (double)*(volatile const unsigned *)hs.seq;
         const long long t0 = clock64();
-        if (hs.wait_lo) while (*(volatile const double *)hs.wait_lo < want) { if (clock64() - t0 > 4000000000LL) break; }
-        if (hs.wait_hi) while (*(volatile const double *)hs.wait_hi < want) { if (clock64() - t0 > 4000000000LL) break; }
+        // a neighbour that does not deliver within ~2 s is gone: stop the kernel with a launch error (the host reports it)
+        // rather than compute on a stale halo
+        if (hs.wait_lo) while (*(volatile const double *)hs.wait_lo < want) { if (clock64() - t0 > 4000000000LL) __trap(); }
+        if (hs.wait_hi) while (*(volatile const double *)hs.wait_hi < want) { if (clock64() - t0 > 4000000000LL) __trap(); }
         __threadfence_system();
     }
     __syncthreads();

@@ -112,6 +112,7 @@ struct Krylov {
     bool mg_failed = false;    // a solve with it did not converge: this handle goes back to (block-)Jacobi
     Btd *btd = nullptr;        // block-tridiagonal preconditioner (same life cycle as mg)
     bool btd_on = false, btd_failed = false;
+    int pool_generation = 0;   // of the peer-mapped buffers this handle points into (sharded solves)
     int btd_decide = 0;        // general structure: 1 = decide at the first update from the band's share of the weight
     DevBuf<double> partials, scal;
     DevBuf<unsigned> ticket;
@@ -174,6 +175,7 @@ void comm_unshare_vectors(int count, void **lo, void **hi);
 bool comm_pooled_vectors(size_t n, double **mine, void **lo, void **hi);
 // one more peer-mapped buffer of n doubles (multigrid level vectors whose halo planes travel); same life cycle
 bool comm_pooled_arena(size_t n, double **mine, void **lo, void **hi);
+int comm_pool_generation();   // changes whenever those buffers are re-created (a larger solve asked for more)
 HaloSignal comm_next_halo_signal();
 int comm_allreduce_sum(Ctx &c, double *d_buf, int count);
 int comm_allreduce_max(Ctx &c, double *d_buf, int count);
