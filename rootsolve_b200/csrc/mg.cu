@@ -375,7 +375,9 @@ __global__ void __launch_bounds__(256) mg_coarse_solve_kernel(int nc, const doub
 // The rank's first / last plane of every species goes straight into the slab neighbours' copy of the vector (peer
 // stores), the last block raises the neighbours' flags; the one-thread kernel behind it waits for both neighbours'
 // flags, so everything later in the stream sees complete halos.  Two small launches instead of an NCCL send/recv
-// group (~40 us at 8 GPUs): a cycle has sixteen of these.
+// group: a cycle has twelve of these.  (Pushing from the producing kernel and waiting in the consuming one, as the
+// Krylov kernels do for their one vector, was measured SLOWER here -- 35.7 against 30.7 ms at 2 GPUs: every block of
+// the large level kernels then pays the system-scope fence and the flag wait that these two small kernels pay once.)
 __global__ void __launch_bounds__(256) mg_halo_push_kernel(int nspec, int ncell, int plane, int j0, int j1, const double *__restrict__ v,
                                                            HaloPush hp, unsigned *ticket)
 {
@@ -735,7 +737,7 @@ void mg_destroy(Mg *m) { delete m; }
 // screening length of the operator.  So the finest levels are GLOBAL: same aggregates as on one GPU, every rank working
 // on its planes of global-index level vectors, one halo exchange before each application of the level's operator (four
 // per level and cycle).  A level can be global while every rank's planes are whole aggregates (even bounds); below
-// that -- and below RS_MG_GLOBAL_LEVELS (default 4) levels, where the planes per rank get few and an exchange costs
+// that -- and below RS_MG_GLOBAL_LEVELS (default 3; at 2 GPUs, 256^3: 36 / 31 / 32 ms with 2 / 3 / 4) levels, where the planes per rank get few and an exchange costs
 // more than the level's arithmetic -- the rank's coarse box is cut off and continues as a local hierarchy.
 int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
 {
@@ -752,7 +754,7 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
     int G = 0, myj0[MG_MAXLEV], myj1[MG_MAXLEV];
     if (nr > 1 && !getenv("RS_MG_LOCAL")) {
         const char *e = getenv("RS_MG_GLOBAL_LEVELS");
-        const int gmax = e ? atoi(e) : 4;
+        const int gmax = e ? atoi(e) : 3;
         std::vector<int> lo(nr), hi(nr);
         for (int r = 0; r < nr; r++) rs_slab_bounds(g.d[0], nr, r, &lo[r], &hi[r]);
         int dl = g.d[0];
