@@ -914,7 +914,8 @@ static void mg_halo(Ctx &c, Mg &M, MgLevel &L, bool is_x)
     hp.signal = 1;
     hp.sig = sig;
     Launch La(c, K_HALO, 32.0 * L.hp.nspec * L.hp.plane);
-    mg_halo_push_kernel<<<grid_for(2LL * L.hp.nspec * L.hp.plane, 256, 148), 256, 0, c.stream>>>(L.hp.nspec, L.hp.ncell, L.hp.plane, L.hp.j0, L.hp.j1,
+    static const int push_blocks = getenv("RS_MG_PUSH_BLOCKS") ? atoi(getenv("RS_MG_PUSH_BLOCKS")) : 148;
+    mg_halo_push_kernel<<<grid_for(2LL * L.hp.nspec * L.hp.plane, 256, push_blocks), 256, 0, c.stream>>>(L.hp.nspec, L.hp.ncell, L.hp.plane, L.hp.j0, L.hp.j1,
                                                                                             v, hp, M.hticket.p);
     mg_halo_wait_kernel<<<1, 32, 0, c.stream>>>(sig);
     c.launches++;
