@@ -109,6 +109,32 @@ void pool_free(void *p, size_t bytes)
     P.cached += k;
 }
 
+namespace {
+struct PinnedPool {
+    std::mutex mu;
+    std::vector<void *> free_blocks;
+};
+PinnedPool &pinned_pool() { static PinnedPool *p = new PinnedPool(); return *p; }
+}  // namespace
+
+cudaError_t pinned_alloc(void **p)
+{
+    PinnedPool &P = pinned_pool();
+    {
+        std::lock_guard<std::mutex> lk(P.mu);
+        if (!P.free_blocks.empty()) { *p = P.free_blocks.back(); P.free_blocks.pop_back(); return cudaSuccess; }
+    }
+    return cudaMallocHost(p, PINNED_BLOCK);
+}
+
+void pinned_free(void *p)
+{
+    if (!p) return;
+    PinnedPool &P = pinned_pool();
+    std::lock_guard<std::mutex> lk(P.mu);
+    if (P.free_blocks.size() < 64) P.free_blocks.push_back(p); else cudaFreeHost(p);
+}
+
 const char *const kKernelNames[K_COUNT] = {"structure", "scan", "transpose", "jgroup", "perturb", "residual_batched",
                                            "fd_assemble", "spmv_csr", "krylov_vec", "precond_setup", "precond_apply",
                                            "newton", "halo", "misc", "spmv_grid", "mg_smooth_l0", "mg_transfer_l0",
@@ -291,7 +317,7 @@ struct rs_solver {
     int niter = 0, steady = 0, krylov_iters = 0;
     double t_setup = 0.0, t_newton = 0.0;
     long long setup_launches = 0;
-    ~rs_solver() { if (h_red) cudaFreeHost(h_red); }
+    ~rs_solver() { pinned_free(h_red); }
 };
 
 // parameters reach the model through its initialiser, as in src/call_stsparse.c:231-240
@@ -487,7 +513,7 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         RS_TRY(s.red.alloc(8));
         RS_TRY(s.ticket.alloc(4));
         RS_TRY(s.ticket.zero(c.stream));
-        RS_CUDA(cudaMallocHost((void **)&s.h_red, 8 * sizeof(double)));
+        RS_CUDA(pinned_alloc((void **)&s.h_red));
         // who owns what: one range [0, n) on a single GPU; planes [j0, j1) of every species when sharded
         s.own.n = 1; s.own.b[0] = 0; s.own.e[0] = n;
         s.touch = s.own;
@@ -1063,6 +1089,12 @@ extern "C" int rs_device_count(void)
 }
 extern "C" long long rs_release_cached_memory(void)
 {
+    {   // the pinned host blocks too (not counted: the return value is device memory)
+        PinnedPool &H = pinned_pool();
+        std::lock_guard<std::mutex> lk(H.mu);
+        for (void *q : H.free_blocks) cudaFreeHost(q);
+        H.free_blocks.clear();
+    }
     Pool &P = pool();
     std::lock_guard<std::mutex> lk(P.mu);
     return (long long)P.drop_all_locked();

@@ -43,7 +43,7 @@ constexpr int NSCAL = 2 * SLOT + 8;
 
 Krylov::~Krylov()
 {
-    if (h_scal) cudaFreeHost(h_scal);
+    pinned_free(h_scal);
     for (int w = 0; w < 2; w++) if (g_exec[w]) cudaGraphExecDestroy(g_exec[w]);
     if (mg) mg_destroy(mg);
     if (btd) btd_destroy(btd);
@@ -848,7 +848,8 @@ int krylov_setup(Ctx &c, Krylov &k, int n, int nnz, const int *rowptr, const int
     RS_TRY(k.ticket.alloc(4));
     RS_TRY(k.ticket.zero(c.stream));
     RS_TRY(k.scal.zero(c.stream));
-    if (!k.h_scal) RS_CUDA(cudaMallocHost((void **)&k.h_scal, sizeof(double) * NSCAL));
+    static_assert(sizeof(double) * NSCAL <= PINNED_BLOCK, "pinned block too small for the Krylov scalars");
+    if (!k.h_scal) RS_CUDA(pinned_alloc((void **)&k.h_scal));
     return RS_OK;
 }
 

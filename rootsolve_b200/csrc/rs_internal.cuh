@@ -81,6 +81,11 @@ extern std::atomic<long long> g_device_bytes;  // currently allocated through De
 // them back to the driver, RS_POOL_MAX_BYTES caps what is kept (0 = no caching).
 cudaError_t pool_alloc(void **p, size_t bytes);
 void pool_free(void *p, size_t bytes);
+// Small pinned host buffers (the scalars the host reads back): cudaMallocHost costs a millisecond or more per call --
+// two of them were most of the set-up of a 50 x 50 solve -- so blocks of one fixed size are kept for reuse.
+constexpr size_t PINNED_BLOCK = 512;   // bytes
+cudaError_t pinned_alloc(void **p);
+void pinned_free(void *p);
 
 template <typename T>
 struct DevBuf {
