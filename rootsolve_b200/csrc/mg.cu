@@ -373,9 +373,8 @@ __global__ void __launch_bounds__(256) mg_coarse_solve_kernel(int nc, const doub
 
 // ---- halo planes of a global level over NVLink ----------------------------------------------------------------
 // The rank's first / last plane of every species goes straight into the slab neighbours' copy of the vector (peer
-// stores), the last block raises the neighbours' flags; the one-thread kernel behind it waits for both neighbours'
-// flags, so everything later in the stream sees complete halos.  Two small launches instead of an NCCL send/recv
-// group: a cycle has twelve of these.  (Pushing from the producing kernel and waiting in the consuming one, as the
+// stores), the last block raises the neighbours' flags and waits for theirs, so everything later in the stream sees
+// complete halos.  One small launch instead of an NCCL send/recv group: a cycle has twelve of these.  (Pushing from the producing kernel and waiting in the consuming one, as the
 // Krylov kernels do for their one vector, was measured SLOWER here -- 35.7 against 30.7 ms at 2 GPUs: every block of
 // the large level kernels then pays the system-scope fence and the flag wait that these two small kernels pay once.)
 __global__ void __launch_bounds__(256) mg_halo_push_kernel(int nspec, int ncell, int plane, int j0, int j1, const double *__restrict__ v,
@@ -390,9 +389,28 @@ __global__ void __launch_bounds__(256) mg_halo_push_kernel(int nspec, int ncell,
         double *dst = side ? hp.hi : hp.lo;
         if (dst != nullptr) dst[i] = v[i];
     }
-    halo_signal_done(hp, ticket);
+    // the last block to finish raises the neighbours' flags -- and then stays until the neighbours' own flags for this
+    // exchange have arrived: the kernel ends when the halos are complete, so one launch does what the push kernel and
+    // a separate waiting kernel did (raising never depends on waiting: no rank can block another)
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(ticket, 1u);
+        if (t == gridDim.x - 1) {
+            *ticket = 0;
+            const unsigned seq = *hp.sig.seq + 1u;
+            __threadfence_system();
+            if (hp.sig.tell_lo) *(volatile double *)hp.sig.tell_lo = (double)seq;
+            if (hp.sig.tell_hi) *(volatile double *)hp.sig.tell_hi = (double)seq;
+            *hp.sig.seq = seq;
+            const double want = (double)seq;
+            const long long t0 = clock64();
+            if (hp.sig.wait_lo) while (*(volatile const double *)hp.sig.wait_lo < want) { if (clock64() - t0 > 4000000000LL) __trap(); }
+            if (hp.sig.wait_hi) while (*(volatile const double *)hp.sig.wait_hi < want) { if (clock64() - t0 > 4000000000LL) __trap(); }
+            __threadfence_system();
+        }
+    }
 }
-__global__ void mg_halo_wait_kernel(HaloSignal hs) { halo_wait(hs); }
 
 // ---- the small levels in one launch ---------------------------------------------------------------------------
 // Below a few thousand cells a level is a handful of microseconds of work per kernel and six kernels per visit: launch
@@ -917,8 +935,6 @@ static void mg_halo(Ctx &c, Mg &M, MgLevel &L, bool is_x)
     static const int push_blocks = getenv("RS_MG_PUSH_BLOCKS") ? atoi(getenv("RS_MG_PUSH_BLOCKS")) : 148;
     mg_halo_push_kernel<<<grid_for(2LL * L.hp.nspec * L.hp.plane, 256, push_blocks), 256, 0, c.stream>>>(L.hp.nspec, L.hp.ncell, L.hp.plane, L.hp.j0, L.hp.j1,
                                                                                             v, hp, M.hticket.p);
-    mg_halo_wait_kernel<<<1, 32, 0, c.stream>>>(sig);
-    c.launches++;
 }
 
 template <int NS>
