@@ -924,8 +924,13 @@ int krylov_precond_update(Ctx &c, Krylov &k)
             k.asym = amax > 0.0 ? da / amax : 1.0;
             k.use_cg = (k.asym == k.asym) && k.asym <= 1.0e-6;
             // fold the Jacobi preconditioner into the system (see the CG kernels): needs one sign on the whole diagonal
+            // Under the multigrid cycle there is nothing to fold: z = M^-1 r comes from the cycle, whose smoother carries
+            // the diagonal itself, and CG runs on the matrix as assembled (a negative definite J with the equally
+            // negative definite cycle is CG on -J: alpha stays positive) -- no scaling pass over the matrix, no
+            // unscaling of x.
             static const bool no_scale = getenv("RS_NO_CG_SCALING") != nullptr;
-            if (k.use_cg && !no_scale) {
+            const bool mg_wanted = k.mg != nullptr && !k.mg_failed;
+            if (k.use_cg && !no_scale && !mg_wanted) {
                 if (!k.sc.p) RS_TRY(k.sc.alloc(k.n));
                 {
                     Launch L(c, K_PRECOND_SETUP, 16.0 * (double)(k.own.e[0] - k.own.b[0]));
@@ -953,9 +958,8 @@ int krylov_precond_update(Ctx &c, Krylov &k)
             block_setup_kernel<<<(cells + 127) / 128, 128, 0, c.stream>>>(k.nspec, k.ncell, k.cell0, k.cell1, k.rowptr, k.col, k.val, k.binv.p);
         }
     }
-    // the hierarchy is rebuilt from the values the solve will use (the scaled ones when CG runs on sigma S A S)
+    // the hierarchy is rebuilt from the values the solve will use
     k.mg_on = k.mg != nullptr && !k.mg_failed;
-    if (k.mg_on && k.use_cg && !k.scaled) k.use_cg = false;   // the CG kernels take z = M^-1 r only on the scaled system
     if (k.mg_on) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));
     if (k.btd && !k.btd_failed && k.btd_decide == 1) {   // general structure: is the matrix banded enough?
         double share = 0.0;
@@ -1282,12 +1286,14 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     double *slot = k.scal.p + SLOT * cur;
     const double rows = (double)k.own.total();
     const HaloSignal sig = k.push_ok ? comm_next_halo_signal() : HaloSignal();
+    // the kernel variants without dinv: the Jacobi-scaled system (z = r), or z handed in by the multigrid cycle
+    const bool nodinv = k.scaled || k.mg_on;
     {
-        // first: r -> p ; else r, p, x -> p, x  (+ dinv when the system is not scaled)
-        Launch L(c, K_VEC, ((first ? 16.0 : 40.0) + (k.scaled ? 0.0 : 8.0)) * rows);
+        // first: r -> p ; else r, p, x -> p, x  (+ dinv when the kernel applies the Jacobi preconditioner itself)
+        Launch L(c, K_VEC, ((first ? 16.0 : 40.0) + (nodinv ? 0.0 : 8.0)) * rows);
         for (int q = 0; q < k.own.n; q++) {
             const int b = k.own.b[q], e = k.own.e[q];
-            if (k.scaled)
+            if (nodinv)
                 cg_update_p_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, first, k.scal.p, cur, k.mg_on ? k.z.p : k.r.p, nullptr, k.ph_v, x,
                                                                                      make_push(k, 0, sig, q == k.own.n - 1), k.ticket.p + 1);
             else
@@ -1303,11 +1309,11 @@ static int cg_step(Ctx &c, Krylov &k, double *x, int cur, int first)
     }
     if (!comm_peer_enabled()) RS_TRY(comm_allreduce_sum(c, slot + C_PQ, 1));
     {
-        Launch L(c, K_VEC, (k.scaled ? 24.0 : 32.0) * rows);   // q, r -> r (+ dinv)
+        Launch L(c, K_VEC, (nodinv ? 24.0 : 32.0) * rows);   // q, r -> r (+ dinv)
         const PeerRed peer = comm_next_peer_red();
         for (int q = 0; q < k.own.n; q++) {
             const int b = k.own.b[q], e = k.own.e[q];
-            if (k.scaled)
+            if (nodinv)
                 cg_update_xr_kernel<true><<<grid_for((e - b) / 2, 256), 256, 0, st>>>(b, e, k.scal.p, cur, k.v.p, nullptr, k.r.p,
                                                                                       k.partials.p, k.ticket.p, q > 0,
                                                                                       q == k.own.n - 1 ? peer : PeerRed());
