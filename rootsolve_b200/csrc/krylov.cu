@@ -901,6 +901,7 @@ int krylov_precond_update(Ctx &c, Krylov &k)
     k.use_cg = false;
     k.scaled = false;
     k.norm_conv = 1.0;
+    bool mg_built = false;
     if (k.precond == RS_PRECOND_JACOBI) {
         for (int q = 0; q < k.own.n; q++) {
             const int rows = k.own.e[q] - k.own.b[q];
@@ -912,7 +913,13 @@ int krylov_precond_update(Ctx &c, Krylov &k)
         // reference's own examples) is solved by preconditioned CG: one SpMV per step instead of two.
         static const bool no_cg = getenv("RS_NO_CG") != nullptr;
         if (!no_cg && k.own.n == 1 && !(k.btd && !k.btd_failed)) {
-            {
+            if (k.mg != nullptr && !k.mg_failed) {
+                // the hierarchy's slot-major copy of the matrix knows where every transposed entry is: build it now and
+                // read the asymmetry off it (0.15 ms at 256^3 against 0.7 ms for the search through the row-wise arrays)
+                RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));
+                mg_built = true;
+                RS_TRY(mg_asymmetry(c, *k.mg, k.partials.p, k.ticket.p, k.scal.p + S_SYM));
+            } else {
                 Launch L(c, K_PRECOND_SETUP, 24.0 * own_nnz_estimate(k));
                 symmetry_kernel<<<grid_for(k.own.e[0] - k.own.b[0], 256), 256, 0, c.stream>>>(k.own.b[0], k.own.e[0], k.rowptr, k.col, k.val,
                                                                                             k.partials.p, k.ticket.p, k.scal.p + S_SYM, 0);
@@ -960,7 +967,7 @@ int krylov_precond_update(Ctx &c, Krylov &k)
     }
     // the hierarchy is rebuilt from the values the solve will use
     k.mg_on = k.mg != nullptr && !k.mg_failed;
-    if (k.mg_on) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));
+    if (k.mg_on && !mg_built) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));
     if (k.btd && !k.btd_failed && k.btd_decide == 1) {   // general structure: is the matrix banded enough?
         double share = 0.0;
         RS_TRY(btd_band_share(c, k.n, k.rowptr, k.col, k.val, k.partials.p, k.ticket.p, k.scal.p + S_SYM, &share));

@@ -645,6 +645,43 @@ __global__ void __launch_bounds__(128) mg_smoother_setup_kernel(MgLevelDev L, do
     if ((threadIdx.x & 31) == 0 && worst > 0.0) atomic_max_pos(lmax, worst);
 }
 
+// out = { max |a_ij - a_ji| , max |a_ij| } over the rank's rows of level 0, read off the slot-major copy: the transposed
+// entry of slot t of cell c is slot t^1 of the neighbour (the other species' slot of the same cell) -- no search.
+// Pairs whose partner row belongs to another rank are skipped.  Single precision is enough for the 1e-6 threshold of
+// the symmetric / nonsymmetric decision (krylov.cu).
+__global__ void __launch_bounds__(256) mg_asymmetry_kernel(MgLevelDev L, double *partials, unsigned *ticket, double *out)
+{
+    const int c0 = blockIdx.x * blockDim.x + threadIdx.x, cs = gridDim.x * blockDim.x;
+    double acc[2] = {0.0, 0.0};
+    MG_CELL_LOOP(c, L) {
+        const Cell3 q = cell_coords(c, L.d2, L.d3);
+        int nb[6];
+        bool has[6];
+        neighbours(L, c, q, nb, has);
+        for (int s = 0; s < L.nspec; s++) {
+            const long long r = (long long)s * L.ncell + c;
+            acc[1] = fmax(acc[1], fabs((double)L.ell[r]));
+#pragma unroll
+            for (int t = 0; t < 6; t++) {
+                const double v = L.ell[(long long)(1 + t) * L.n + r];
+                acc[1] = fmax(acc[1], fabs(v));
+                if (has[t] && nb[t] >= L.cb && nb[t] < L.ce)
+                    acc[0] = fmax(acc[0], fabs(v - (double)L.ell[(long long)(1 + (t ^ 1)) * L.n + (long long)s * L.ncell + nb[t]]));
+            }
+            int o = 0;
+            for (int s2 = 0; s2 < L.nspec; s2++) {
+                if (s2 == s) continue;
+                const double v = L.ell[(long long)(7 + o) * L.n + r];
+                const int o2 = s < s2 ? s : s - 1;   // slot of species s in the row of species s2
+                acc[1] = fmax(acc[1], fabs(v));
+                acc[0] = fmax(acc[0], fabs(v - (double)L.ell[(long long)(7 + o2) * L.n + (long long)s2 * L.ncell + c]));
+                o++;
+            }
+        }
+    }
+    grid_reduce<2>(acc, 3u, partials, ticket, out, false);
+}
+
 // Dense inverse of the coarsest operator (n <= 256) by Gauss-Jordan with partial pivoting, one block.
 // work: 2 n^2 doubles (A | Inv), row-major; cinv: the inverse, column-major.  flag: set when a pivot vanishes.
 __global__ void __launch_bounds__(1024) mg_coarse_invert_kernel(MgLevelDev L, double *__restrict__ work, double *__restrict__ cinv,
@@ -1018,5 +1055,15 @@ int mg_apply(Ctx &c, Mg &M, const double *r, double *z, double *partials, unsign
 }
 
 int mg_levels(const Mg &M) { return M.nlev; }
+
+// out2 (device) = { max |a_ij - a_ji| , max |a_ij| } of the matrix the hierarchy was last built from (mg_update first)
+int mg_asymmetry(Ctx &c, Mg &M, double *partials, unsigned *ticket, double *out2)
+{
+    const MgLevelDev &D = M.lev[0].dev;
+    Launch La(c, K_PRECOND_SETUP, 2.0 * sizeof(mg_real) * (double)D.nspec * (D.ce - D.cb) * (6.0 + D.nspec));
+    mg_asymmetry_kernel<<<mg_grid(D.ce - D.cb), 256, 0, c.stream>>>(D, partials, ticket, out2);
+    RS_CUDA(cudaGetLastError());
+    return RS_OK;
+}
 
 }  // namespace rs

@@ -86,6 +86,8 @@ int mg_update(Ctx &c, Mg &m, const int *rowptr, const int *col, const double *va
 // z = M^-1 r (one V-cycle) on the rank's slab of global-index vectors; dot_out: <r, z>, all-reduced through pr
 int mg_apply(Ctx &c, Mg &m, const double *r, double *z, double *partials, unsigned *ticket, double *dot_out, const PeerRed &pr);
 int mg_levels(const Mg &m);
+// { max |a_ij - a_ji|, max |a_ij| } (device) read off the level-0 copy of the matrix mg_update was last given
+int mg_asymmetry(Ctx &c, Mg &m, double *partials, unsigned *ticket, double *out2);
 void mg_destroy(Mg *m);
 
 // btd.cu -- block-tridiagonal part solved exactly by cyclic reduction (1-D grids, banded general structures)
