@@ -78,7 +78,7 @@ struct MgLevel {
     double *xp = nullptr, *dp = nullptr;   // x and d of the level (own buffers, or slices of the peer-mapped arena)
     double *x_lo = nullptr, *x_hi = nullptr, *d_lo = nullptr, *d_hi = nullptr;   // the slab neighbours' copies (halo push)
     DevBuf<mg_real> ell;
-    DevBuf<double> dinv, b, x, r, d;
+    DevBuf<double> dinv, b, x, r, d, x2;   // x2: the corrected x of the fused prolongation (one species, local levels)
 };
 
 struct Mg {
@@ -262,6 +262,30 @@ __global__ void __launch_bounds__(256) mg_second_kernel(MgLevelDev L, VecView r,
     if (DOT) grid_reduce<1>(acc, 0u, partials, ticket, out, false, &pr);
 }
 
+// Both Chebyshev steps of the pre-smoothing in one pass (one species, local levels): the first step is pointwise,
+// d = Dinv b / theta, so the neighbours' d are formed from their b and Dinv on the fly and d is never stored:
+//     x = d + c1 d + c2 Dinv (b - A d)
+__device__ __forceinline__ void mg_pre_body(const MgLevelDev &L, VecView b, VecView x, int c0, int cs)
+{
+    const Cheb ch = cheb_coeffs(L);
+    MG_CELL_LOOP(c, L) {
+        const Cell3 q = cell_coords(c, L.d2, L.d3);
+        int nb[6];
+        bool has[6];
+        neighbours(L, c, q, nb, has);
+        const double bc = b.at(0, c), dic = L.dinv[c];
+        const double dc = ch.inv_theta * dic * bc;
+        double t = L.ell[c] * dc;
+#pragma unroll
+        for (int k = 0; k < 6; k++) t += L.ell[(long long)(1 + k) * L.n + c] * (ch.inv_theta * L.dinv[nb[k]] * b.at(0, nb[k]));
+        x.at(0, c) = dc + (ch.c1 * dc + ch.c2 * (dic * (bc - t)));
+    }
+}
+__global__ void __launch_bounds__(256) mg_pre_kernel(MgLevelDev L, VecView b, VecView x)
+{
+    mg_pre_body(L, b, x, MG_GRID_ARGS);
+}
+
 // start of the post-smoothing:  r = b - A x ;  d = Dinv r / theta
 template <int NS>
 __device__ __forceinline__ void mg_resid_first_body(const MgLevelDev &L, VecView b, VecView x, VecView r, VecView d, int c0, int cs)
@@ -289,6 +313,45 @@ template <int NS>
 __global__ void __launch_bounds__(256) mg_resid_first_kernel(MgLevelDev L, VecView b, VecView x, VecView r, VecView d)
 {
     mg_resid_first_body<NS>(L, b, x, r, d, MG_GRID_ARGS);
+}
+
+// Prolongation and the start of the post-smoothing in one pass (one species, local levels):
+//     xt = x + P xc ;  r = b - A xt ;  d = Dinv r / theta
+// The corrected value of a neighbour is formed on the fly from its x and its aggregate's xc; xt of the cell itself goes
+// to a second buffer (x2), because the neighbours still read the uncorrected x.
+__device__ __forceinline__ void mg_post_first_body(const MgLevelDev &L, int f1, int f2, int f3, int cd2, int cd3, VecView b, VecView x,
+                                                   VecView xc, VecView x2, VecView r, VecView d, int c0, int cs)
+{
+    const Cheb ch = cheb_coeffs(L);
+    const int s1 = f1 == 2 ? 1 : 0, s2 = f2 == 2 ? 1 : 0, s3 = f3 == 2 ? 1 : 0;   // coarsening factors are 1 or 2: shifts
+    MG_CELL_LOOP(c, L) {
+        const Cell3 q = cell_coords(c, L.d2, L.d3);
+        int nb[6];
+        bool has[6];
+        neighbours(L, c, q, nb, has);
+        const int J = q.j >> s1, K = q.k >> s2, Lc = q.l >> s3;
+        const int I = (J * cd2 + K) * cd3 + Lc;
+        // aggregate of each neighbour: one coarse coordinate may differ (the neighbour's own coordinate with wrap-around)
+        const int jm = q.j > 0 ? q.j - 1 : L.d1 - 1, jp = q.j < L.d1 - 1 ? q.j + 1 : 0;
+        const int km = q.k > 0 ? q.k - 1 : L.d2 - 1, kp = q.k < L.d2 - 1 ? q.k + 1 : 0;
+        const int lm = q.l > 0 ? q.l - 1 : L.d3 - 1, lp = q.l < L.d3 - 1 ? q.l + 1 : 0;
+        const int In[6] = {I + ((jm >> s1) - J) * cd2 * cd3, I + ((jp >> s1) - J) * cd2 * cd3, I + ((km >> s2) - K) * cd3,
+                           I + ((kp >> s2) - K) * cd3,       I + ((lm >> s3) - Lc),            I + ((lp >> s3) - Lc)};
+        const double xt = x.at(0, c) + xc.at(0, I);
+        double t = L.ell[c] * xt;
+#pragma unroll
+        for (int k = 0; k < 6; k++)
+            if (has[k]) t += L.ell[(long long)(1 + k) * L.n + c] * (x.at(0, nb[k]) + xc.at(0, In[k]));
+        const double rr = b.at(0, c) - t;
+        x2.at(0, c) = xt;
+        r.at(0, c) = rr;
+        d.at(0, c) = ch.inv_theta * (L.dinv[c] * rr);
+    }
+}
+__global__ void __launch_bounds__(256) mg_post_first_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView b, VecView x,
+                                                            VecView xc, VecView x2, VecView r, VecView d)
+{
+    mg_post_first_body(L, f1, f2, f3, cd2, cd3, b, x, xc, x2, r, d, MG_GRID_ARGS);
 }
 
 // residual of the fine level summed over each aggregate:  bc(s, I) = sum_{c in I} (b - A x)(s, c)
@@ -420,7 +483,7 @@ __global__ void __launch_bounds__(256) mg_halo_push_kernel(int nspec, int ncell,
 struct MgTailLevel {
     MgLevelDev D;
     int f1, f2, f3;
-    double *b, *x, *r, *d;
+    double *b, *x, *r, *d, *x2;
 };
 constexpr int MG_TAIL_THREADS = 1024;
 constexpr int MG_TAIL_CELLS = 4096;
@@ -437,9 +500,13 @@ __global__ void __launch_bounds__(MG_TAIL_THREADS) mg_tail_kernel(const MgTailLe
         const MgLevelDev Dn = lv[l + 1].D;
         const VecView b = (l == l0 && b0.p != nullptr) ? b0 : VecView{T.b, T.D.ncell, 0};
         const VecView x = {T.x, T.D.ncell, 0}, d = {T.d, T.D.ncell, 0};
-        mg_first_body<NS>(T.D, b, d, c0, cs);
-        __syncthreads();
-        mg_second_body<NS, false>(T.D, b, d, none, x, none, c0, cs);
+        if (NS == 1) {
+            mg_pre_body(T.D, b, x, c0, cs);
+        } else {
+            mg_first_body<NS>(T.D, b, d, c0, cs);
+            __syncthreads();
+            mg_second_body<NS, false>(T.D, b, d, none, x, none, c0, cs);
+        }
         __syncthreads();
         mg_resid_restrict_body<NS>(T.D, T.f1, T.f2, T.f3, Dn, 0, b, x, VecView{lv[l + 1].b, Dn.ncell, 0}, c0, cs);
         __syncthreads();
@@ -461,12 +528,18 @@ __global__ void __launch_bounds__(MG_TAIL_THREADS) mg_tail_kernel(const MgTailLe
         const bool top = l == l0 && b0.p != nullptr;
         const VecView b = top ? b0 : VecView{T.b, T.D.ncell, 0};
         const VecView x = {T.x, T.D.ncell, 0}, r = {T.r, T.D.ncell, 0}, d = {T.d, T.D.ncell, 0};
-        mg_prolong_body(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, 0, VecView{lv[l + 1].x, Dn.ncell, 0}, x, c0, cs);
+        VecView xin = x;
+        if (NS == 1) {
+            xin = VecView{T.x2, T.D.ncell, 0};
+            mg_post_first_body(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, b, x, VecView{lv[l + 1].x, Dn.ncell, 0}, xin, r, d, c0, cs);
+        } else {
+            mg_prolong_body(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, 0, VecView{lv[l + 1].x, Dn.ncell, 0}, x, c0, cs);
+            __syncthreads();
+            mg_resid_first_body<NS>(T.D, b, x, r, d, c0, cs);
+        }
         __syncthreads();
-        mg_resid_first_body<NS>(T.D, b, x, r, d, c0, cs);
-        __syncthreads();
-        if (top && want_dot) acc = mg_second_body<NS, true>(T.D, r, d, x, xout0, b, c0, cs);
-        else mg_second_body<NS, false>(T.D, r, d, x, top ? xout0 : x, none, c0, cs);
+        if (top && want_dot) acc = mg_second_body<NS, true>(T.D, r, d, xin, xout0, b, c0, cs);
+        else mg_second_body<NS, false>(T.D, r, d, xin, top ? xout0 : x, none, c0, cs);
         __syncthreads();
     }
     if (want_dot) {   // <r, z> over the block
@@ -856,6 +929,7 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
         RS_TRY(L.dinv.alloc(D.nspec == 1 ? (size_t)D.n : (size_t)D.nspec * D.n));
         RS_TRY(L.r.alloc(D.n));
         if (!L.global) { RS_TRY(L.x.alloc(D.n)); RS_TRY(L.d.alloc(D.n)); L.xp = L.x.p; L.dp = L.d.p; }   // global: below
+        if (!L.global && D.nspec == 1) RS_TRY(L.x2.alloc(D.n));
         if (nlev > 0) RS_TRY(L.b.alloc(D.n));
         D.ell = L.ell.p; D.dinv = L.dinv.p;
         nlev++;
@@ -909,7 +983,7 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
             MgLevel &L = M->lev[l];
             tl[l].D = L.dev;
             tl[l].f1 = L.f[0]; tl[l].f2 = L.f[1]; tl[l].f3 = L.f[2];
-            tl[l].b = L.b.p; tl[l].x = L.xp; tl[l].r = L.r.p; tl[l].d = L.dp;
+            tl[l].b = L.b.p; tl[l].x = L.xp; tl[l].r = L.r.p; tl[l].d = L.dp; tl[l].x2 = L.x2.p;
         }
         RS_TRY(M->tail_levels.alloc(sizeof(MgTailLevel) * nlev));
         RS_CUDA(cudaMemcpyAsync(M->tail_levels.p, tl.data(), sizeof(MgTailLevel) * nlev, cudaMemcpyHostToDevice, c.stream));
@@ -1003,12 +1077,15 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     MgLevel &Cn = M.lev[l + 1];
     const VecView x = view(L.xp, D.ncell), r = view(L.r.p, D.ncell), d = view(L.dp, D.ncell);
     const VecView none = view(nullptr, 0);
-    {   // pre-smoothing from a zero guess: two Chebyshev steps, one pass over the matrix
-        Launch La(c, k_smooth, 16.0 * n + 8.0 * D.nspec * n);
-        mg_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, d);
-    }
-    if (L.global) mg_halo(c, M, L, false);
-    {
+    if (NS == 1 && !L.global) {   // pre-smoothing from a zero guess: two Chebyshev steps, one pass, d never stored
+        Launch La(c, k_smooth, mat + 24.0 * n);
+        mg_pre_kernel<<<grid, 256, 0, st>>>(D, b, x);
+    } else {
+        {
+            Launch La(c, k_smooth, 16.0 * n + 8.0 * D.nspec * n);
+            mg_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, d);
+        }
+        if (L.global) mg_halo(c, M, L, false);
         Launch La(c, k_smooth, mat + 24.0 * n + 8.0 * D.nspec * n);
         mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, b, d, none, x, none, nullptr, nullptr, nullptr, PeerRed());
     }
@@ -1019,23 +1096,31 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
                                                                                    b, x, view(Cn.b.p, Cn.dev.ncell));
     }
     mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.xp, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
-    {
-        Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
-        mg_prolong_kernel<<<grid, 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.xp, Cn.dev.ncell), x);
+    VecView xin = x;
+    if (NS == 1 && !L.global) {   // prolongation folded into the first post-smoothing pass; the corrected x lands in x2
+        xin = view(L.x2.p, D.ncell);
+        Launch La(c, k_smooth, mat + 40.0 * n + 8.0 * Cn.dev.n);
+        mg_post_first_kernel<<<mg_wave_grid(mg_post_first_kernel, D.ce - D.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, b, x,
+                                                                                            view(Cn.xp, Cn.dev.ncell), xin, r, d);
+    } else {
+        {
+            Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
+            mg_prolong_kernel<<<grid, 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.xp, Cn.dev.ncell), x);
+        }
+        if (L.global) mg_halo(c, M, L, true);
+        {   // post-smoothing: the same two Chebyshev steps, two passes
+            Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
+            mg_resid_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, x, r, d);
+        }
+        if (L.global) mg_halo(c, M, L, false);
     }
-    if (L.global) mg_halo(c, M, L, true);
-    {   // post-smoothing: the same two Chebyshev steps, two passes
-        Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
-        mg_resid_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, x, r, d);
-    }
-    if (L.global) mg_halo(c, M, L, false);
     {
         Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         if (dot_out)
-            mg_second_kernel<NS, true><<<mg_wave_grid(mg_second_kernel<NS, true>, D.ce - D.cb), 256, 0, st>>>(D, r, d, x, xout, b, partials, ticket,
+            mg_second_kernel<NS, true><<<mg_wave_grid(mg_second_kernel<NS, true>, D.ce - D.cb), 256, 0, st>>>(D, r, d, xin, xout, b, partials, ticket,
                                                                                                             dot_out, pr);
         else
-            mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, r, d, x, xout, none, nullptr, nullptr, nullptr, PeerRed());
+            mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, r, d, xin, xout, none, nullptr, nullptr, nullptr, PeerRed());
     }
 }
 
