@@ -460,7 +460,22 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         t_last = now;
     };
     RS_TRY(s.y.alloc(n));
-    RS_TRY(s.y.upload(a->y, n, c.stream));
+    // Grid types: structure and grouping do not read y, so a large state crosses PCIe on a stream of its own beside
+    // them (134 MB at 256^3: ~3 ms next to 13 ms of grouping); the solver's stream waits for it before the first
+    // kernel that reads y.  The guard drains the copy on every return path: y must not go back to the pool under it.
+    struct SideCopy {
+        cudaStream_t st = nullptr; cudaEvent_t done = nullptr; bool pending = false;
+        ~SideCopy() { if (pending) cudaStreamSynchronize(st); if (done) cudaEventDestroy(done); if (st) cudaStreamDestroy(st); }
+    } side;
+    const bool grid_type = std::abs(a->Type) == RS_TYPE_1D || std::abs(a->Type) == RS_TYPE_2D || std::abs(a->Type) == RS_TYPE_3D;
+    if (grid_type && n >= (1 << 18) && !debug_setup) {
+        RS_CUDA(cudaStreamCreateWithFlags(&side.st, cudaStreamNonBlocking));
+        RS_CUDA(cudaEventCreateWithFlags(&side.done, cudaEventDisableTiming));
+        side.pending = true;
+        RS_TRY(s.y.upload(a->y, n, side.st));
+        RS_CUDA(cudaEventRecord(side.done, side.st));
+    } else
+        RS_TRY(s.y.upload(a->y, n, c.stream));
     mark("state upload");
     // structure (xsparsestruct, src/sparse.f:300-455)
     if (std::abs(a->Type) == RS_TYPE_DETECT) {
@@ -537,6 +552,7 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
             s.halo.has_lo = rk > 0; s.halo.has_hi = rk < nr - 1;
         }
         mark("newton vectors");
+        if (side.pending) RS_CUDA(cudaStreamWaitEvent(c.stream, side.done, 0));
         RS_TRY(fd_setup(c, s.fd, n, s.ngp, a->nout, a->rpar, a->nrpar, a->ipar, a->nipar, s.slab_j0, s.slab_j1));
         mark("fd work arrays");
         RS_TRY(krylov_setup(c, s.kry, n, s.nnz, s.rowptr.p, s.col.p, s.val.p, s.ctl.precond, s.grid.type ? s.grid.nspec : 1,

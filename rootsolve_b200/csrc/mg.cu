@@ -33,6 +33,8 @@
 #include <cmath>
 #include <cstdlib>
 #include <memory>
+#include <mutex>
+#include <unordered_map>
 
 #include "solver.cuh"
 
@@ -194,6 +196,25 @@ __device__ __forceinline__ Cheb cheb_coeffs(const MgLevelDev &L)
 #define MG_CELL_LOOP(c, L) for (int c = (L).cb + c0; c < (L).ce; c += cs)
 #define MG_GRID_ARGS (int)(blockIdx.x * blockDim.x + threadIdx.x), (int)(gridDim.x * blockDim.x)
 
+// The same loop with the cell's coordinates carried along: two integer divisions before the loop (first cell and stride)
+// instead of two per cell.
+struct CellWalk {
+    int c; Cell3 q; int cs; Cell3 sq; int d2, d3;
+    __device__ __forceinline__ CellWalk(const MgLevelDev &L, int c0, int cs_) : c(L.cb + c0), cs(cs_), d2(L.d2), d3(L.d3)
+    {
+        q = cell_coords(c, d2, d3);
+        sq = cell_coords(cs, d2, d3);
+    }
+    __device__ __forceinline__ void next()
+    {
+        c += cs;
+        q.l += sq.l; if (q.l >= d3) { q.l -= d3; q.k++; }
+        q.k += sq.k; if (q.k >= d2) { q.k -= d2; q.j++; }
+        q.j += sq.j;
+    }
+};
+#define MG_CELL_WALK(w, L) for (CellWalk w(L, c0, cs); w.c < (L).ce; w.next())
+
 // ---- cycle kernels (thread per cell, all species of the cell) ------------------------------------------------
 // first Chebyshev step from a zero guess:  d = Dinv b / theta   (x = d is implied)
 template <int NS>
@@ -229,6 +250,36 @@ __device__ __forceinline__ double mg_second_body(const MgLevelDev &L, VecView r,
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
     double acc[1] = {0.0};
+    if (NS == 1) {   // one species: coordinates carried along, every load of the cell issued before the first use
+        const double *dp = d.p + d.off;
+        const double *rp = r.p + r.off;
+        const double *__restrict__ dinv = L.dinv;
+        const mg_real *__restrict__ ell = L.ell;
+        const double *xi = xin.p ? xin.p + xin.off : nullptr;
+        MG_CELL_WALK(w, L) {
+            const int c = w.c;
+            int nb[6];
+            bool has[6];
+            neighbours(L, c, w.q, nb, has);
+            mg_real a[7];
+            double dn[6];
+#pragma unroll
+            for (int k = 0; k < 7; k++) a[k] = ell[(long long)k * L.n + c];
+#pragma unroll
+            for (int k = 0; k < 6; k++) dn[k] = dp[nb[k]];
+            const double dv = dp[c], rc = rp[c], dic = dinv[c];
+            const double xv = xi ? xi[c] : 0.0;
+            const double wv = DOT ? w_.at(0, c) : 0.0;
+            double t = a[0] * dv;
+#pragma unroll
+            for (int k = 0; k < 6; k++) t += a[1 + k] * dn[k];
+            double xn = dv + (ch.c1 * dv + ch.c2 * (dic * (rc - t)));
+            if (xi) xn += xv;
+            xout.at(0, c) = xn;
+            if (DOT) acc[0] += wv * xn;
+        }
+        return acc[0];
+    }
     MG_CELL_LOOP(c, L) {
         const Cell3 q = cell_coords(c, L.d2, L.d3);
         int nb[6];
@@ -254,7 +305,7 @@ __device__ __forceinline__ double mg_second_body(const MgLevelDev &L, VecView r,
 }
 
 template <int NS, bool DOT>
-__global__ void __launch_bounds__(256) mg_second_kernel(MgLevelDev L, VecView r, VecView d, VecView xin, VecView xout, VecView w_,
+__global__ void __launch_bounds__(256, NS == 1 ? (DOT ? 3 : 4) : 1) mg_second_kernel(MgLevelDev L, VecView r, VecView d, VecView xin, VecView xout, VecView w_,
                                                         double *partials, unsigned *ticket, double *out, PeerRed pr)
 {
     double acc[1];
@@ -268,20 +319,31 @@ __global__ void __launch_bounds__(256) mg_second_kernel(MgLevelDev L, VecView r,
 __device__ __forceinline__ void mg_pre_body(const MgLevelDev &L, VecView b, VecView x, int c0, int cs)
 {
     const Cheb ch = cheb_coeffs(L);
-    MG_CELL_LOOP(c, L) {
-        const Cell3 q = cell_coords(c, L.d2, L.d3);
+    const double *bp = b.p + b.off;
+    const double *__restrict__ dinv = L.dinv;
+    const mg_real *__restrict__ ell = L.ell;
+    MG_CELL_WALK(w, L) {
+        const int c = w.c;
         int nb[6];
         bool has[6];
-        neighbours(L, c, q, nb, has);
-        const double bc = b.at(0, c), dic = L.dinv[c];
-        const double dc = ch.inv_theta * dic * bc;
-        double t = L.ell[c] * dc;
+        neighbours(L, c, w.q, nb, has);
+        // all 21 loads of the cell are issued before the first use (a missing neighbour reads the cell itself; its
+        // matrix entry is zero): the pass is bound by memory latency, not by registers
+        mg_real a[7];
+        double dn[6], bn[6];
 #pragma unroll
-        for (int k = 0; k < 6; k++) t += L.ell[(long long)(1 + k) * L.n + c] * (ch.inv_theta * L.dinv[nb[k]] * b.at(0, nb[k]));
+        for (int k = 0; k < 7; k++) a[k] = ell[(long long)k * L.n + c];
+#pragma unroll
+        for (int k = 0; k < 6; k++) { dn[k] = dinv[nb[k]]; bn[k] = bp[nb[k]]; }
+        const double bc = bp[c], dic = dinv[c];
+        const double dc = ch.inv_theta * dic * bc;
+        double t = a[0] * dc;
+#pragma unroll
+        for (int k = 0; k < 6; k++) t += a[1 + k] * (ch.inv_theta * dn[k] * bn[k]);
         x.at(0, c) = dc + (ch.c1 * dc + ch.c2 * (dic * (bc - t)));
     }
 }
-__global__ void __launch_bounds__(256) mg_pre_kernel(MgLevelDev L, VecView b, VecView x)
+__global__ void __launch_bounds__(256, 4) mg_pre_kernel(MgLevelDev L, VecView b, VecView x)
 {
     mg_pre_body(L, b, x, MG_GRID_ARGS);
 }
@@ -324,8 +386,12 @@ __device__ __forceinline__ void mg_post_first_body(const MgLevelDev &L, int f1, 
 {
     const Cheb ch = cheb_coeffs(L);
     const int s1 = f1 == 2 ? 1 : 0, s2 = f2 == 2 ? 1 : 0, s3 = f3 == 2 ? 1 : 0;   // coarsening factors are 1 or 2: shifts
-    MG_CELL_LOOP(c, L) {
-        const Cell3 q = cell_coords(c, L.d2, L.d3);
+    const double *xp = x.p + x.off;
+    const double *xcp = xc.p + xc.off;
+    const mg_real *__restrict__ ell = L.ell;
+    MG_CELL_WALK(w, L) {
+        const int c = w.c;
+        const Cell3 q = w.q;
         int nb[6];
         bool has[6];
         neighbours(L, c, q, nb, has);
@@ -337,18 +403,26 @@ __device__ __forceinline__ void mg_post_first_body(const MgLevelDev &L, int f1, 
         const int lm = q.l > 0 ? q.l - 1 : L.d3 - 1, lp = q.l < L.d3 - 1 ? q.l + 1 : 0;
         const int In[6] = {I + ((jm >> s1) - J) * cd2 * cd3, I + ((jp >> s1) - J) * cd2 * cd3, I + ((km >> s2) - K) * cd3,
                            I + ((kp >> s2) - K) * cd3,       I + ((lm >> s3) - Lc),            I + ((lp >> s3) - Lc)};
-        const double xt = x.at(0, c) + xc.at(0, I);
-        double t = L.ell[c] * xt;
+        // every load before the first use; a missing neighbour reads the cell itself (zero matrix entry) and an
+        // aggregate inside the grid
+        mg_real a[7];
+        double xn[6], cn[6];
 #pragma unroll
-        for (int k = 0; k < 6; k++)
-            if (has[k]) t += L.ell[(long long)(1 + k) * L.n + c] * (x.at(0, nb[k]) + xc.at(0, In[k]));
-        const double rr = b.at(0, c) - t;
+        for (int k = 0; k < 7; k++) a[k] = ell[(long long)k * L.n + c];
+#pragma unroll
+        for (int k = 0; k < 6; k++) { xn[k] = xp[nb[k]]; cn[k] = xcp[In[k]]; }
+        const double xv = xp[c], cv = xcp[I], bv = b.at(0, c), dic = L.dinv[c];
+        const double xt = xv + cv;
+        double t = a[0] * xt;
+#pragma unroll
+        for (int k = 0; k < 6; k++) t += a[1 + k] * (xn[k] + cn[k]);
+        const double rr = bv - t;
         x2.at(0, c) = xt;
         r.at(0, c) = rr;
-        d.at(0, c) = ch.inv_theta * (L.dinv[c] * rr);
+        d.at(0, c) = ch.inv_theta * (dic * rr);
     }
 }
-__global__ void __launch_bounds__(256) mg_post_first_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView b, VecView x,
+__global__ void __launch_bounds__(256, 4) mg_post_first_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView b, VecView x,
                                                             VecView xc, VecView x2, VecView r, VecView d)
 {
     mg_post_first_body(L, f1, f2, f3, cd2, cd3, b, x, xc, x2, r, d, MG_GRID_ARGS);
@@ -361,6 +435,51 @@ __device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int 
                                                        VecView b, VecView x, VecView bc, int c0, int cs)
 {
     const int ns = NS > 0 ? NS : L.nspec;
+    if (NS == 1) {   // one species: coordinates carried along; the (up to) two cells of a line that share the aggregate
+                     // are staged together, every load before the first use
+        const double *xp = x.p + x.off;
+        const double *bp = b.p + b.off;
+        const mg_real *__restrict__ ell = L.ell;
+        MG_CELL_WALK(w, Cc) {
+            const int Qj = w.q.j + cjoff;
+            const int l0 = w.q.l * f3, nl = min(f3, L.d3 - l0);
+            double sum = 0.0;
+            for (int dj = 0; dj < f1; dj++) {
+                const int j = Qj * f1 + dj;
+                if (j >= L.d1) break;
+                for (int dk = 0; dk < f2; dk++) {
+                    const int k = w.q.k * f2 + dk;
+                    if (k >= L.d2) break;
+                    mg_real a[2][7];
+                    double xn[2][6], xv[2], bv[2];
+#pragma unroll
+                    for (int dl = 0; dl < 2; dl++) {
+                        Cell3 q;
+                        q.j = j; q.k = k; q.l = l0 + (dl < nl ? dl : 0);   // an absent second cell re-reads the first
+                        const int c = (j * L.d2 + k) * L.d3 + q.l;
+                        int nb[6];
+                        bool has[6];
+                        neighbours(L, c, q, nb, has);
+#pragma unroll
+                        for (int t = 0; t < 7; t++) a[dl][t] = ell[(long long)t * L.n + c];
+#pragma unroll
+                        for (int t = 0; t < 6; t++) xn[dl][t] = xp[nb[t]];
+                        xv[dl] = xp[c];
+                        bv[dl] = bp[c];
+                    }
+#pragma unroll
+                    for (int dl = 0; dl < 2; dl++) {
+                        double t = a[dl][0] * xv[dl];
+#pragma unroll
+                        for (int q = 0; q < 6; q++) t += a[dl][1 + q] * xn[dl][q];
+                        if (dl < nl) sum += bv[dl] - t;
+                    }
+                }
+            }
+            bc.at(0, w.c) = sum;
+        }
+        return;
+    }
     MG_CELL_LOOP(I, Cc) {
         Cell3 Q = cell_coords(I, Cc.d2, Cc.d3);
         Q.j += cjoff;   // plane of the aggregate in the fine level's coordinates / f1
@@ -397,7 +516,7 @@ __device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int 
 }
 
 template <int NS>
-__global__ void __launch_bounds__(256) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, MgLevelDev Cc, int cjoff,
+__global__ void __launch_bounds__(256, NS == 1 ? 4 : 1) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, MgLevelDev Cc, int cjoff,
                                                                 VecView b, VecView x, VecView bc)
 {
     mg_resid_restrict_body<NS>(L, f1, f2, f3, Cc, cjoff, b, x, bc, MG_GRID_ARGS);
@@ -834,13 +953,23 @@ static inline int mg_grid(long long work) { return grid_for(work, 256, 148 * 8);
 template <typename K>
 static int mg_wave_grid(K kernel, long long work)
 {
-    static int resident = 0;   // per instantiation = per kernel
+    // resident blocks of each kernel, by its address (kernels of one signature share this instantiation)
+    static std::mutex mu;
+    static std::unordered_map<const void *, int> known;
+    int resident = 0;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = known.find((const void *)kernel);
+        if (it != known.end()) resident = it->second;
+    }
     if (resident == 0) {
         int dev = 0, sms = 148, occ = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 256, 0) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 4; }
         resident = sms * occ;
+        std::lock_guard<std::mutex> lk(mu);
+        known[(const void *)kernel] = resident;
     }
     return grid_for(work, 256, resident);
 }
@@ -1079,7 +1208,7 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     const VecView none = view(nullptr, 0);
     if (NS == 1 && !L.global) {   // pre-smoothing from a zero guess: two Chebyshev steps, one pass, d never stored
         Launch La(c, k_smooth, mat + 24.0 * n);
-        mg_pre_kernel<<<grid, 256, 0, st>>>(D, b, x);
+        mg_pre_kernel<<<mg_wave_grid(mg_pre_kernel, D.ce - D.cb), 256, 0, st>>>(D, b, x);
     } else {
         {
             Launch La(c, k_smooth, 16.0 * n + 8.0 * D.nspec * n);
@@ -1087,7 +1216,8 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
         }
         if (L.global) mg_halo(c, M, L, false);
         Launch La(c, k_smooth, mat + 24.0 * n + 8.0 * D.nspec * n);
-        mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, b, d, none, x, none, nullptr, nullptr, nullptr, PeerRed());
+        mg_second_kernel<NS, false><<<mg_wave_grid(mg_second_kernel<NS, false>, D.ce - D.cb), 256, 0, st>>>(D, b, d, none, x, none, nullptr, nullptr,
+                                                                                                         nullptr, PeerRed());
     }
     if (L.global) mg_halo(c, M, L, true);
     {   // residual, summed over the aggregates
@@ -1120,7 +1250,8 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
             mg_second_kernel<NS, true><<<mg_wave_grid(mg_second_kernel<NS, true>, D.ce - D.cb), 256, 0, st>>>(D, r, d, xin, xout, b, partials, ticket,
                                                                                                             dot_out, pr);
         else
-            mg_second_kernel<NS, false><<<grid, 256, 0, st>>>(D, r, d, xin, xout, none, nullptr, nullptr, nullptr, PeerRed());
+            mg_second_kernel<NS, false><<<mg_wave_grid(mg_second_kernel<NS, false>, D.ce - D.cb), 256, 0, st>>>(D, r, d, xin, xout, none, nullptr, nullptr,
+                                                                                                             nullptr, PeerRed());
     }
 }
 
