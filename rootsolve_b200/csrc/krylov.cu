@@ -896,12 +896,11 @@ static int cg_scale_matrix(Ctx &c, Krylov &k, bool inverse)
     return RS_OK;
 }
 
-int krylov_precond_update(Ctx &c, Krylov &k)
+// The (block-)Jacobi data of the handle's own preconditioner.  Under the multigrid cycle or the band solve nothing reads
+// them, so they are only formed when one of those is not in charge -- or has just failed (krylov_solve's fallback).
+static int diag_precond_setup(Ctx &c, Krylov &k)
 {
-    k.use_cg = false;
-    k.scaled = false;
-    k.norm_conv = 1.0;
-    bool mg_built = false;
+    if (k.diag_valid) return RS_OK;
     if (k.precond == RS_PRECOND_JACOBI) {
         for (int q = 0; q < k.own.n; q++) {
             const int rows = k.own.e[q] - k.own.b[q];
@@ -909,6 +908,29 @@ int krylov_precond_update(Ctx &c, Krylov &k)
             Launch L(c, K_PRECOND_SETUP, 20.0 * rows);
             jacobi_setup_kernel<<<(rows + 255) / 256, 256, 0, c.stream>>>(k.own.b[q], k.own.e[q], k.rowptr, k.col, k.val, k.dinv.p);
         }
+    } else if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
+        const int cells = k.cell1 - k.cell0;
+        if (cells > 0) {
+            Launch L(c, K_PRECOND_SETUP, 20.0 * k.nspec * k.nspec * cells);
+            block_setup_kernel<<<(cells + 127) / 128, 128, 0, c.stream>>>(k.nspec, k.ncell, k.cell0, k.cell1, k.rowptr, k.col, k.val, k.binv.p);
+        }
+    }
+    RS_CUDA(cudaGetLastError());
+    k.diag_valid = true;
+    return RS_OK;
+}
+
+int krylov_precond_update(Ctx &c, Krylov &k)
+{
+    k.use_cg = false;
+    k.scaled = false;
+    k.norm_conv = 1.0;
+    k.diag_valid = false;
+    bool mg_built = false;
+    // the band solve of a general structure is only decided below (btd_decide == 1): the diagonal data are formed then
+    const bool ext_wanted = (k.mg != nullptr && !k.mg_failed) || (k.btd != nullptr && !k.btd_failed && k.btd_decide != 1);
+    if (!ext_wanted) RS_TRY(diag_precond_setup(c, k));
+    if (k.precond == RS_PRECOND_JACOBI) {
         // A Jacobian that is symmetric up to finite-difference noise (single-species diffusion-reaction: the
         // reference's own examples) is solved by preconditioned CG: one SpMV per step instead of two.
         static const bool no_cg = getenv("RS_NO_CG") != nullptr;
@@ -916,7 +938,7 @@ int krylov_precond_update(Ctx &c, Krylov &k)
             if (k.mg != nullptr && !k.mg_failed) {
                 // the hierarchy's slot-major copy of the matrix knows where every transposed entry is: build it now and
                 // read the asymmetry off it (0.15 ms at 256^3 against 0.7 ms for the search through the row-wise arrays)
-                RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));
+                RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val, k.gridcols));
                 mg_built = true;
                 RS_TRY(mg_asymmetry(c, *k.mg, k.partials.p, k.ticket.p, k.scal.p + S_SYM));
             } else {
@@ -958,16 +980,10 @@ int krylov_precond_update(Ctx &c, Krylov &k)
                 }
             }
         }
-    } else if (k.precond == RS_PRECOND_BLOCK_JACOBI) {
-        const int cells = k.cell1 - k.cell0;
-        if (cells > 0) {
-            Launch L(c, K_PRECOND_SETUP, 20.0 * k.nspec * k.nspec * cells);
-            block_setup_kernel<<<(cells + 127) / 128, 128, 0, c.stream>>>(k.nspec, k.ncell, k.cell0, k.cell1, k.rowptr, k.col, k.val, k.binv.p);
-        }
     }
     // the hierarchy is rebuilt from the values the solve will use
     k.mg_on = k.mg != nullptr && !k.mg_failed;
-    if (k.mg_on && !mg_built) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));
+    if (k.mg_on && !mg_built) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val, k.gridcols));
     if (k.btd && !k.btd_failed && k.btd_decide == 1) {   // general structure: is the matrix banded enough?
         double share = 0.0;
         RS_TRY(btd_band_share(c, k.n, k.rowptr, k.col, k.val, k.partials.p, k.ticket.p, k.scal.p + S_SYM, &share));
@@ -976,6 +992,7 @@ int krylov_precond_update(Ctx &c, Krylov &k)
     }
     k.btd_on = k.btd != nullptr && !k.btd_failed;
     if (k.btd_on) RS_TRY(btd_update(c, *k.btd, k.rowptr, k.col, k.val));
+    if (!k.mg_on && !k.btd_on) RS_TRY(diag_precond_setup(c, k));
     RS_CUDA(cudaGetLastError());
     return RS_OK;
 }
@@ -1241,7 +1258,7 @@ __global__ void __launch_bounds__(256) cg_start_kernel(int b, int e, const doubl
             if (ax != nullptr) ri -= ax[i]; else x[i] = 0.0;
             r[i] = ri;
             acc[0] += ri * ri;
-            acc[1] += ri * dinv[i] * ri;
+            if (dinv != nullptr) acc[1] += ri * dinv[i] * ri;   // under the multigrid cycle <r, z> comes from the cycle
         }
     }
     grid_reduce<2>(acc, 0u, partials, ticket, out2, accumulate != 0, &pr);
@@ -1267,7 +1284,8 @@ static int cg_start(Ctx &c, Krylov &k, const double *b, double *x, bool restart,
         Launch L(c, K_VEC, 40.0 * rows);
         const PeerRed peer = comm_next_peer_red();
         for (int q = 0; q < k.own.n; q++)
-            cg_start_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, restart ? k.v.p : nullptr, k.dinv.p,
+            cg_start_kernel<<<grid_for(k.own.e[q] - k.own.b[q], 256), 256, 0, st>>>(k.own.b[q], k.own.e[q], b, restart ? k.v.p : nullptr,
+                                                                                k.mg_on ? nullptr : k.dinv.p,
                                                                                 k.scaled ? k.sc.p : nullptr, k.sigma,
                                                                                 k.r.p, x, k.partials.p, k.ticket.p, k.scal.p + 6, q > 0,
                                                                                 q == k.own.n - 1 ? peer : PeerRed());
@@ -1491,7 +1509,7 @@ static int krylov_solve_inner(Ctx &c, Krylov &k, const double *b, double *x, dou
         k.use_cg = false;   // not a CG matrix after all: BiCGStab below, from x = 0
         if (k.scaled) {
             RS_TRY(cg_scale_matrix(c, k, true));   // ... on the matrix as assembled
-            if (k.mg_on) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val));   // and so is the hierarchy
+            if (k.mg_on) RS_TRY(mg_update(c, *k.mg, k.rowptr, k.col, k.val, k.gridcols));   // and so is the hierarchy
         }
     }
     {
@@ -1590,6 +1608,7 @@ int krylov_solve(Ctx &c, Krylov &k, const double *b, double *x, double abs_floor
         if (k.btd_on) k.btd_failed = true;
         k.mg_on = false;
         k.btd_on = false;
+        RS_TRY(diag_precond_setup(c, k));   // skipped while the cycle / band solve was in charge
         const int it0 = *iters;
         rc = krylov_solve_inner(c, k, b, x, abs_floor, iters, relres, converged);
         *iters += it0;

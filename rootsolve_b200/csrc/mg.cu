@@ -136,6 +136,36 @@ template <int NS>
 __device__ __forceinline__ void cell_apply(const MgLevelDev &L, int c, const int (&nb)[6], const VecView &v, double (&t)[MG_NSA])
 {
     const int ns = NS > 0 ? NS : L.nspec;
+    if (NS >= 1 && NS <= 3) {   // few species, known at compile time: every load of the cell before the first use
+        constexpr int M = NS >= 1 ? NS : 1;
+        const mg_real *__restrict__ ell = L.ell;
+        mg_real a[M][6 + M];
+        double vn[M][6], vcc[M];
+#pragma unroll
+        for (int s = 0; s < M; s++) {
+            const long long r = (long long)s * L.ncell + c;
+#pragma unroll
+            for (int q = 0; q < 6 + M; q++) a[s][q] = ell[(long long)q * L.n + r];
+#pragma unroll
+            for (int q = 0; q < 6; q++) vn[s][q] = v.at(s, nb[q]);
+            vcc[s] = v.at(s, c);
+        }
+#pragma unroll
+        for (int s = 0; s < M; s++) {
+            double acc = a[s][0] * vcc[s];
+#pragma unroll
+            for (int q = 0; q < 6; q++) acc += a[s][1 + q] * vn[s][q];
+            int o = 0;
+#pragma unroll
+            for (int s2 = 0; s2 < M; s2++) {
+                if (s2 == s) continue;
+                acc += a[s][7 + o] * vcc[s2];
+                o++;
+            }
+            t[s] = acc;
+        }
+        return;
+    }
     double vc[MG_NSA];
 #pragma unroll
     for (int s = 0; s < MG_NSA; s++)
@@ -280,11 +310,11 @@ __device__ __forceinline__ double mg_second_body(const MgLevelDev &L, VecView r,
         }
         return acc[0];
     }
-    MG_CELL_LOOP(c, L) {
-        const Cell3 q = cell_coords(c, L.d2, L.d3);
+    MG_CELL_WALK(cw, L) {
+        const int c = cw.c;
         int nb[6];
         bool has[6];
-        neighbours(L, c, q, nb, has);
+        neighbours(L, c, cw.q, nb, has);
         double t[MG_NSA], r1[MG_NSA], w[MG_NSA];
         cell_apply<NS>(L, c, nb, d, t);
 #pragma unroll
@@ -354,11 +384,11 @@ __device__ __forceinline__ void mg_resid_first_body(const MgLevelDev &L, VecView
 {
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
-    MG_CELL_LOOP(c, L) {
-        const Cell3 q = cell_coords(c, L.d2, L.d3);
+    MG_CELL_WALK(cw, L) {
+        const int c = cw.c;
         int nb[6];
         bool has[6];
-        neighbours(L, c, q, nb, has);
+        neighbours(L, c, cw.q, nb, has);
         double t[MG_NSA], rr[MG_NSA], w[MG_NSA];
         cell_apply<NS>(L, c, nb, x, t);
 #pragma unroll
@@ -480,8 +510,9 @@ __device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int 
         }
         return;
     }
-    MG_CELL_LOOP(I, Cc) {
-        Cell3 Q = cell_coords(I, Cc.d2, Cc.d3);
+    MG_CELL_WALK(cw, Cc) {
+        const int I = cw.c;
+        Cell3 Q = cw.q;
         Q.j += cjoff;   // plane of the aggregate in the fine level's coordinates / f1
         double sum[MG_NSA];
 #pragma unroll
@@ -526,9 +557,11 @@ __global__ void __launch_bounds__(256, NS == 1 ? 4 : 1) mg_resid_restrict_kernel
 __device__ __forceinline__ void mg_prolong_body(const MgLevelDev &L, int f1, int f2, int f3, int cd2, int cd3, int cjoff,
                                                 VecView xc, VecView x, int c0, int cs)
 {
-    MG_CELL_LOOP(c, L) {
-        const Cell3 q = cell_coords(c, L.d2, L.d3);
-        const int I = ((q.j / f1 - cjoff) * cd2 + (q.k / f2)) * cd3 + (q.l / f3);
+    const int s1 = f1 == 2 ? 1 : 0, s2 = f2 == 2 ? 1 : 0, s3 = f3 == 2 ? 1 : 0;   // coarsening factors are 1 or 2
+    MG_CELL_WALK(cw, L) {
+        const int c = cw.c;
+        const Cell3 q = cw.q;
+        const int I = (((q.j >> s1) - cjoff) * cd2 + (q.k >> s2)) * cd3 + (q.l >> s3);
         for (int s = 0; s < L.nspec; s++) x.at(s, c) += xc.at(s, I);
     }
 }
@@ -675,6 +708,11 @@ __global__ void __launch_bounds__(MG_TAIL_THREADS) mg_tail_kernel(const MgTailLe
 }
 
 // ---- set-up kernels ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void atomic_max_pos(double *addr, double v)   // v >= 0: the bit patterns order like the values
+{
+    atomicMax(reinterpret_cast<unsigned long long *>(addr), (unsigned long long)__double_as_longlong(v));
+}
+
 // Level 0 from the solver's row-wise arrays (global indices, columns ascending).  Thread per (species, local cell).
 // An entry of the same species goes to the slot of the neighbour it addresses, an entry of another species of the
 // same cell to that species' slot; anything else -- a column outside the rank's slab, a pattern entry that is not
@@ -712,6 +750,118 @@ __global__ void __launch_bounds__(256) mg_build_l0_kernel(MgLevelDev L, int gstr
 #pragma unroll
         for (int t = 0; t < 7; t++) ell[(long long)t * L.n + r] = (mg_real)acc[t];
     }
+}
+
+// One species: the smoother data of a row whose seven entries are in registers (what mg_smoother_setup_kernel reads back
+// from the level for the general case): dinv = 1 / a_cc of the stored (rounded) value, and the row's Gershgorin bound.
+__device__ __forceinline__ double row_smoother_data(const mg_real (&e)[7], double *dinv_out)
+{
+    const double a = (double)e[0];
+    const double di = fabs(a) > 0.0 ? 1.0 / a : 1.0;
+    double ts = 0.0;
+#pragma unroll
+    for (int t = 0; t < 6; t++) ts += fabs((double)e[1 + t]);
+    *dinv_out = di;
+    return 1.0 + fabs(di) * ts;
+}
+
+// Level 0, one species, pattern verified as the grid's own (grid_stencil.cuh): the entries of a row are its neighbours
+// in ascending column order -j -k -l diag +l +k +j, the present ones only -- no column is read, nothing is searched.
+// Writes all seven slots (no zero-fill needed), dinv and the level's Gershgorin bound.
+__global__ void __launch_bounds__(256, 4) mg_build_l0_grid_kernel(MgLevelDev L, const int *__restrict__ rowptr, const double *__restrict__ val,
+                                                                  mg_real *__restrict__ ell, double *__restrict__ dinv, double *__restrict__ lmax)
+{
+    const int c0 = blockIdx.x * blockDim.x + threadIdx.x, cs = gridDim.x * blockDim.x;
+    double worst = 0.0;
+    MG_CELL_WALK(w, L) {
+        const int c = w.c;
+        const Cell3 q = w.q;
+        // slot of each candidate in column order, and whether the row has it
+        const bool has[7] = {q.j > 0, q.k > 0, q.l > 0, true, q.l < L.d3 - 1, q.k < L.d2 - 1, q.j < L.d1 - 1};
+        constexpr int slot[7] = {1, 3, 5, 0, 6, 4, 2};
+        const int p0 = rowptr[c];
+        double v[7];
+        int p = p0;
+#pragma unroll
+        for (int t = 0; t < 7; t++) {
+            v[t] = has[t] ? val[p] : 0.0;
+            p += has[t] ? 1 : 0;
+        }
+        mg_real e[7];
+#pragma unroll
+        for (int t = 0; t < 7; t++) e[slot[t]] = (mg_real)v[t];
+#pragma unroll
+        for (int t = 0; t < 7; t++) ell[(long long)t * L.n + c] = e[t];
+        double di;
+        worst = fmax(worst, row_smoother_data(e, &di));
+        dinv[c] = di;
+    }
+    worst = warp_max(worst);
+    if ((threadIdx.x & 31) == 0 && worst > 0.0) atomic_max_pos(lmax, worst);
+}
+
+// Galerkin coarse operator, one species: as mg_build_coarse_kernel below, with the coordinates carried along, the (up
+// to) two cells of a line that share the aggregate loaded together, no division, and the coarse level's smoother data
+// formed from the sums while they are in registers.
+__global__ void __launch_bounds__(256, 4) mg_build_coarse1_kernel(MgLevelDev F, MgLevelDev Cc, int f1, int f2, int f3, int cjoff, double w,
+                                                                  mg_real *__restrict__ ellc, double *__restrict__ dinvc,
+                                                                  double *__restrict__ lmaxc)
+{
+    const int c0 = blockIdx.x * blockDim.x + threadIdx.x, cs = gridDim.x * blockDim.x;
+    const mg_real *__restrict__ ellf = F.ell;
+    double worst = 0.0;
+    MG_CELL_WALK(cw, Cc) {
+        const Cell3 Q = cw.q;
+        double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        const int l0 = Q.l * f3, nl = min(f3, F.d3 - l0);
+        for (int dj = 0; dj < f1; dj++) {
+            const int j = (Q.j + cjoff) * f1 + dj;
+            if (j >= F.d1) break;
+            for (int dk = 0; dk < f2; dk++) {
+                const int k = Q.k * f2 + dk;
+                if (k >= F.d2) break;
+                mg_real a[2][7];
+#pragma unroll
+                for (int dl = 0; dl < 2; dl++) {
+                    const int c = (j * F.d2 + k) * F.d3 + l0 + (dl < nl ? dl : 0);   // an absent second cell re-reads the first
+#pragma unroll
+                    for (int t = 0; t < 7; t++) a[dl][t] = ellf[(long long)t * F.n + c];
+                }
+#pragma unroll
+                for (int dl = 0; dl < 2; dl++) {
+                    if (dl >= nl) continue;
+                    const int l = l0 + dl;
+                    acc[0] += (double)a[dl][0];
+                    // neighbour t of the fine cell: its aggregate's coordinate in the direction of t (wrap-around as in
+                    // neighbours()); present iff the grid goes on there or is cyclic
+                    const int co[3] = {j, k, l}, dsz[3] = {F.d1, F.d2, F.d3}, cyc[3] = {F.cyc1, F.cyc2, F.cyc3};
+                    const int fq[3] = {f1, f2, f3}, IQ[3] = {Q.j, Q.k, Q.l};
+#pragma unroll
+                    for (int t = 0; t < 6; t++) {
+                        const int dim = t >> 1;
+                        const bool up = t & 1;
+                        const bool inside = up ? co[dim] < dsz[dim] - 1 : co[dim] > 0;
+                        if (!inside && !(cyc[dim] && dsz[dim] > 1)) continue;
+                        const int cn = up ? (inside ? co[dim] + 1 : 0) : (inside ? co[dim] - 1 : dsz[dim] - 1);
+                        const double v = (double)a[dl][1 + t];
+                        const int an = (fq[dim] == 2 ? cn >> 1 : cn) - (dim == 0 ? cjoff : 0);
+                        if (dim == 0 && (an < 0 || an >= Cc.d1)) continue;        // another rank's
+                        if (an == IQ[dim]) acc[0] += v;                           // inside the aggregate
+                        else if (fq[dim] == 2) { acc[1 + t] += w * v; acc[0] += (1.0 - w) * v; }
+                        else acc[1 + t] += v;
+                    }
+                }
+            }
+        }
+        mg_real e[7];
+#pragma unroll
+        for (int t = 0; t < 7; t++) { e[t] = (mg_real)acc[t]; ellc[(long long)t * Cc.n + cw.c] = e[t]; }
+        double di;
+        worst = fmax(worst, row_smoother_data(e, &di));
+        dinvc[cw.c] = di;
+    }
+    worst = warp_max(worst);
+    if ((threadIdx.x & 31) == 0 && worst > 0.0) atomic_max_pos(lmaxc, worst);
 }
 
 // Galerkin coarse operator by summation.  Thread per (species, coarse cell).  w = weight kept by an entry that
@@ -771,11 +921,6 @@ __global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLe
         for (int t = 0; t < 7; t++) ellc[(long long)t * Cc.n + R] = (mg_real)acc[t];
         for (int o = 0; o < nother; o++) ellc[(long long)(7 + o) * Cc.n + R] = (mg_real)oth[o];
     }
-}
-
-__device__ __forceinline__ void atomic_max_pos(double *addr, double v)   // v >= 0: the bit patterns order like the values
-{
-    atomicMax(reinterpret_cast<unsigned long long *>(addr), (unsigned long long)__double_as_longlong(v));
 }
 
 // Smoother data of a level: the inverse of every cell block (nspec = 1: of the diagonal) and the Gershgorin bound
@@ -841,10 +986,34 @@ __global__ void __launch_bounds__(128) mg_smoother_setup_kernel(MgLevelDev L, do
 // entry of slot t of cell c is slot t^1 of the neighbour (the other species' slot of the same cell) -- no search.
 // Pairs whose partner row belongs to another rank are skipped.  Single precision is enough for the 1e-6 threshold of
 // the symmetric / nonsymmetric decision (krylov.cu).
-__global__ void __launch_bounds__(256) mg_asymmetry_kernel(MgLevelDev L, double *partials, unsigned *ticket, double *out)
+__global__ void __launch_bounds__(256, 4) mg_asymmetry_kernel(MgLevelDev L, double *partials, unsigned *ticket, double *out)
 {
     const int c0 = blockIdx.x * blockDim.x + threadIdx.x, cs = gridDim.x * blockDim.x;
     double acc[2] = {0.0, 0.0};
+    if (L.nspec == 1) {   // coordinates carried along, the thirteen loads of a cell issued together
+        const mg_real *__restrict__ ell = L.ell;
+        MG_CELL_WALK(w, L) {
+            const int c = w.c;
+            int nb[6];
+            bool has[6];
+            neighbours(L, c, w.q, nb, has);
+            mg_real a[7], tr[6];
+#pragma unroll
+            for (int t = 0; t < 7; t++) a[t] = ell[(long long)t * L.n + c];
+#pragma unroll
+            for (int t = 0; t < 6; t++) tr[t] = ell[(long long)(1 + (t ^ 1)) * L.n + nb[t]];   // a missing neighbour: the cell itself
+            float hi = fabsf(a[0]), df = 0.f;
+#pragma unroll
+            for (int t = 0; t < 6; t++) {
+                hi = fmaxf(hi, fabsf(a[1 + t]));
+                if (has[t] && nb[t] >= L.cb && nb[t] < L.ce) df = fmaxf(df, fabsf(a[1 + t] - tr[t]));
+            }
+            acc[0] = fmax(acc[0], (double)df);
+            acc[1] = fmax(acc[1], (double)hi);
+        }
+        grid_reduce<2>(acc, 3u, partials, ticket, out, false);
+        return;
+    }
     MG_CELL_LOOP(c, L) {
         const Cell3 q = cell_coords(c, L.d2, L.d3);
         int nb[6];
@@ -1123,30 +1292,46 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
 }
 
 // Rebuilds every level from the matrix values the Krylov solver is about to use (once per Newton iteration).
-int mg_update(Ctx &c, Mg &M, const int *rowptr, const int *col, const double *val)
+int mg_update(Ctx &c, Mg &M, const int *rowptr, const int *col, const double *val, bool grid_order)
 {
     cudaStream_t st = c.stream;
     RS_TRY(M.lmax.zero(st));
     RS_TRY(M.flag.zero(st));
+    // one species: the kernel that forms a level's rows also leaves its smoother data (dinv, Gershgorin bound)
+    const bool one = M.lev[0].dev.nspec == 1;
+    bool smoother_done = false;   // of the level the loop is at
     {
         MgLevel &L = M.lev[0];
-        RS_TRY(L.ell.zero(st));
-        const double nz = (double)L.dev.n * (6.0 + L.dev.nspec);
-        Launch La(c, K_PRECOND_SETUP, 12.0 * nz + 8.0 * nz);
-        mg_build_l0_kernel<<<mg_grid((long long)L.dev.nspec * (L.dev.ce - L.dev.cb)), 256, 0, st>>>(L.dev, M.gstride, M.goff, rowptr, col, val, L.ell.p);
+        const double nz = (double)L.dev.n * (6.0 + L.dev.nspec), rows = (double)(L.dev.ce - L.dev.cb);
+        if (one && grid_order && M.goff == 0 && L.dev.ncell == M.gstride) {
+            Launch La(c, K_PRECOND_SETUP, (4.0 + 56.0 + 28.0 + 8.0) * rows);
+            mg_build_l0_grid_kernel<<<mg_wave_grid(mg_build_l0_grid_kernel, L.dev.ce - L.dev.cb), 256, 0, st>>>(L.dev, rowptr, val, L.ell.p, L.dinv.p,
+                                                                                                           M.lmax.p);
+            smoother_done = true;
+        } else {
+            RS_TRY(L.ell.zero(st));
+            Launch La(c, K_PRECOND_SETUP, 12.0 * nz + 8.0 * nz);
+            mg_build_l0_kernel<<<mg_grid((long long)L.dev.nspec * (L.dev.ce - L.dev.cb)), 256, 0, st>>>(L.dev, M.gstride, M.goff, rowptr, col, val, L.ell.p);
+        }
     }
     for (int l = 0; l < M.nlev; l++) {
         MgLevel &L = M.lev[l];
         const double nz = (double)L.dev.n * (6.0 + L.dev.nspec);
-        if (l + 1 < M.nlev) {
-            MgLevel &Cn = M.lev[l + 1];
-            Launch La(c, K_PRECOND_SETUP, 8.0 * nz + 8.0 * nz / 8.0);
-            mg_build_coarse_kernel<<<mg_grid((long long)Cn.dev.nspec * (Cn.dev.ce - Cn.dev.cb)), 256, 0, st>>>(L.dev, Cn.dev, L.f[0], L.f[1], L.f[2], L.cjoff, 0.5,
-                                                                                                         Cn.ell.p);
-        }
-        {
+        if (!smoother_done) {   // before the coarse build overwrites nothing of this level: order is free, kept as it was
             Launch La(c, K_PRECOND_SETUP, 8.0 * nz + 8.0 * L.dev.nspec * L.dev.n);
             mg_smoother_setup_kernel<<<grid_for(L.dev.ce - L.dev.cb, 128, 148 * 16), 128, 0, st>>>(L.dev, L.dinv.p, M.lmax.p + l);
+        }
+        smoother_done = false;
+        if (l + 1 < M.nlev) {
+            MgLevel &Cn = M.lev[l + 1];
+            Launch La(c, K_PRECOND_SETUP, sizeof(mg_real) * nz + sizeof(mg_real) * nz / 8.0 + (one ? 8.0 * Cn.dev.n : 0.0));
+            if (one) {
+                mg_build_coarse1_kernel<<<mg_wave_grid(mg_build_coarse1_kernel, Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(L.dev, Cn.dev, L.f[0], L.f[1], L.f[2], L.cjoff, 0.5,
+                                                                                                                 Cn.ell.p, Cn.dinv.p, M.lmax.p + l + 1);
+                smoother_done = true;
+            } else
+                mg_build_coarse_kernel<<<mg_grid((long long)Cn.dev.nspec * (Cn.dev.ce - Cn.dev.cb)), 256, 0, st>>>(L.dev, Cn.dev, L.f[0], L.f[1], L.f[2], L.cjoff,
+                                                                                                             0.5, Cn.ell.p);
         }
     }
     // a global level is one operator: every rank smooths with the same polynomial
@@ -1185,7 +1370,6 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     MgLevel &L = M.lev[l];
     const MgLevelDev &D = L.dev;
     const double n = (double)D.nspec * (D.ce - D.cb), mat = (double)sizeof(mg_real) * n * (6.0 + D.nspec);
-    const int grid = mg_grid(D.ce - D.cb);
     // statistics: the smoothing passes and the transfers of the finest level on their own, every level below as one class
     const int k_smooth = l == 0 ? K_MG_SMOOTH_L0 : K_MG_COARSE, k_transfer = l == 0 ? K_MG_TRANSFER_L0 : K_MG_COARSE;
     if (l == M.tail && !(l == 0 && dot_out && pr.nranks > 1)) {
@@ -1212,7 +1396,7 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     } else {
         {
             Launch La(c, k_smooth, 16.0 * n + 8.0 * D.nspec * n);
-            mg_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, d);
+            mg_first_kernel<NS><<<mg_wave_grid(mg_first_kernel<NS>, D.ce - D.cb), 256, 0, st>>>(D, b, d);
         }
         if (L.global) mg_halo(c, M, L, false);
         Launch La(c, k_smooth, mat + 24.0 * n + 8.0 * D.nspec * n);
@@ -1235,12 +1419,12 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     } else {
         {
             Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
-            mg_prolong_kernel<<<grid, 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.xp, Cn.dev.ncell), x);
+            mg_prolong_kernel<<<mg_wave_grid(mg_prolong_kernel, D.ce - D.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.xp, Cn.dev.ncell), x);
         }
         if (L.global) mg_halo(c, M, L, true);
         {   // post-smoothing: the same two Chebyshev steps, two passes
             Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
-            mg_resid_first_kernel<NS><<<grid, 256, 0, st>>>(D, b, x, r, d);
+            mg_resid_first_kernel<NS><<<mg_wave_grid(mg_resid_first_kernel<NS>, D.ce - D.cb), 256, 0, st>>>(D, b, x, r, d);
         }
         if (L.global) mg_halo(c, M, L, false);
     }
@@ -1277,7 +1461,7 @@ int mg_asymmetry(Ctx &c, Mg &M, double *partials, unsigned *ticket, double *out2
 {
     const MgLevelDev &D = M.lev[0].dev;
     Launch La(c, K_PRECOND_SETUP, 2.0 * sizeof(mg_real) * (double)D.nspec * (D.ce - D.cb) * (6.0 + D.nspec));
-    mg_asymmetry_kernel<<<mg_grid(D.ce - D.cb), 256, 0, c.stream>>>(D, partials, ticket, out2);
+    mg_asymmetry_kernel<<<mg_wave_grid(mg_asymmetry_kernel, D.ce - D.cb), 256, 0, c.stream>>>(D, partials, ticket, out2);
     RS_CUDA(cudaGetLastError());
     return RS_OK;
 }

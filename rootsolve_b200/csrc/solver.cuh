@@ -82,7 +82,8 @@ int scatter_csc_values(Ctx &c, int n, int nnz, const int *d_ian, const int *d_ja
 struct Mg;
 bool mg_applicable(const GridDesc &g, int j0, int j1);
 int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1);   // planes [j0, j1) of the slowest dimension; j1 <= j0: all
-int mg_update(Ctx &c, Mg &m, const int *rowptr, const int *col, const double *val);
+// grid_order: the rows were verified to be the grid's own stencil in ascending column order (grid_stencil.cuh)
+int mg_update(Ctx &c, Mg &m, const int *rowptr, const int *col, const double *val, bool grid_order);
 // z = M^-1 r (one V-cycle) on the rank's slab of global-index vectors; dot_out: <r, z>, all-reduced through pr
 int mg_apply(Ctx &c, Mg &m, const double *r, double *z, double *partials, unsigned *ticket, double *dot_out, const PeerRed &pr);
 int mg_levels(const Mg &m);
@@ -112,6 +113,7 @@ struct Krylov {
     Mg *mg = nullptr;          // multigrid preconditioner; z = M^-1 r of preconditioned CG
     bool mg_on = false;        // the current solve is preconditioned by the cycle
     bool mg_failed = false;    // a solve with it did not converge: this handle goes back to (block-)Jacobi
+    bool diag_valid = false;   // dinv / binv hold the current matrix (formed lazily while the cycle or the band solve is in charge)
     Btd *btd = nullptr;        // block-tridiagonal preconditioner (same life cycle as mg)
     bool btd_on = false, btd_failed = false;
     int pool_generation = 0;   // of the peer-mapped buffers this handle points into (sharded solves)
