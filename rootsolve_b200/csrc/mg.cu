@@ -67,7 +67,7 @@ struct MgLevelDev {
     int nspec, d1, d2, d3, cyc1, cyc2, cyc3, ncell, n;
     int cb, ce;           // cells this rank works on: all of a local level's box, the rank's planes of a global level
     const mg_real *ell;   // [7 + nspec - 1][n]
-    const double *dinv;   // nspec == 1: 1/diag per row; else the inverse cell blocks [s][s'][cell]
+    const mg_real *dinv;  // nspec == 1: 1/diag per row; else the inverse cell blocks [s][s'][cell]
     const double *lmax;   // Gershgorin bound of the (block-)Jacobi-preconditioned operator of this level
 };
 
@@ -80,7 +80,9 @@ struct MgLevel {
     double *xp = nullptr, *dp = nullptr;   // x and d of the level (own buffers, or slices of the peer-mapped arena)
     double *x_lo = nullptr, *x_hi = nullptr, *d_lo = nullptr, *d_hi = nullptr;   // the slab neighbours' copies (halo push)
     DevBuf<mg_real> ell;
-    DevBuf<double> dinv, b, x, r, d, x2;   // x2: the corrected x of the fused prolongation (one species, local levels)
+    DevBuf<mg_real> dinv;
+    DevBuf<double> b, x, r, d;
+    DevBuf<mg_real> df;     // one species, local level: the d of the post-smoothing (the only vector its two passes share)
 };
 
 struct Mg {
@@ -208,13 +210,14 @@ __device__ __forceinline__ void cell_dinv(const MgLevelDev &L, int c, const doub
     }
 }
 
-struct Cheb { double inv_theta, c1, c2; };
+struct Cheb { double theta, inv_theta, c1, c2; };
 __device__ __forceinline__ Cheb cheb_coeffs(const MgLevelDev &L)
 {
     const double lmax = *L.lmax, lmin = lmax / MG_CHEB_RATIO;
     const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin);
     const double sigma = theta / delta, rho0 = 1.0 / sigma, rho1 = 1.0 / (2.0 * sigma - rho0);
     Cheb ch;
+    ch.theta = theta;
     ch.inv_theta = 1.0 / theta;
     ch.c1 = rho1 * rho0;
     ch.c2 = 2.0 * rho1 / delta;
@@ -283,7 +286,7 @@ __device__ __forceinline__ double mg_second_body(const MgLevelDev &L, VecView r,
     if (NS == 1) {   // one species: coordinates carried along, every load of the cell issued before the first use
         const double *dp = d.p + d.off;
         const double *rp = r.p + r.off;
-        const double *__restrict__ dinv = L.dinv;
+        const mg_real *__restrict__ dinv = L.dinv;
         const mg_real *__restrict__ ell = L.ell;
         const double *xi = xin.p ? xin.p + xin.off : nullptr;
         MG_CELL_WALK(w, L) {
@@ -350,7 +353,7 @@ __device__ __forceinline__ void mg_pre_body(const MgLevelDev &L, VecView b, VecV
 {
     const Cheb ch = cheb_coeffs(L);
     const double *bp = b.p + b.off;
-    const double *__restrict__ dinv = L.dinv;
+    const mg_real *__restrict__ dinv = L.dinv;
     const mg_real *__restrict__ ell = L.ell;
     MG_CELL_WALK(w, L) {
         const int c = w.c;
@@ -360,7 +363,8 @@ __device__ __forceinline__ void mg_pre_body(const MgLevelDev &L, VecView b, VecV
         // all 21 loads of the cell are issued before the first use (a missing neighbour reads the cell itself; its
         // matrix entry is zero): the pass is bound by memory latency, not by registers
         mg_real a[7];
-        double dn[6], bn[6];
+        mg_real dn[6];
+        double bn[6];
 #pragma unroll
         for (int k = 0; k < 7; k++) a[k] = ell[(long long)k * L.n + c];
 #pragma unroll
@@ -407,34 +411,47 @@ __global__ void __launch_bounds__(256) mg_resid_first_kernel(MgLevelDev L, VecVi
     mg_resid_first_body<NS>(L, b, x, r, d, MG_GRID_ARGS);
 }
 
-// Prolongation and the start of the post-smoothing in one pass (one species, local levels):
-//     xt = x + P xc ;  r = b - A xt ;  d = Dinv r / theta
-// The corrected value of a neighbour is formed on the fly from its x and its aggregate's xc; xt of the cell itself goes
-// to a second buffer (x2), because the neighbours still read the uncorrected x.
+// Post-smoothing with the prolongation folded in (one species, local levels), two passes that share one vector:
+//     xt = x + P xc ;  r = b - A xt ;  d = Dinv r / theta                        (first pass: writes d)
+//     xout = xt + d + c1 d + c2 Dinv (r - A d)                                   (second pass)
+// The corrected value of a neighbour is formed on the fly from its x and its aggregate's xc, so xt is never stored
+// (the second pass forms the cell's own again); r is not stored either: the second pass recovers it from d,
+// r = theta a_cc d (Dinv = 1 / a_cc).  d is single precision like the matrix: preconditioner data.
+struct AggMap {   // aggregate of a cell and of its six neighbours
+    int s1, s2, s3, cd2, cd3;
+    __device__ __forceinline__ AggMap(int f1, int f2, int f3, int cd2_, int cd3_)
+        : s1(f1 == 2 ? 1 : 0), s2(f2 == 2 ? 1 : 0), s3(f3 == 2 ? 1 : 0), cd2(cd2_), cd3(cd3_) {}   // coarsening factors are 1 or 2: shifts
+    __device__ __forceinline__ int own(const Cell3 &q) const { return ((q.j >> s1) * cd2 + (q.k >> s2)) * cd3 + (q.l >> s3); }
+    // one coarse coordinate may differ (the neighbour's own coordinate with wrap-around); a missing neighbour maps to
+    // an aggregate inside the grid
+    __device__ __forceinline__ void around(const MgLevelDev &L, const Cell3 &q, int I, int (&In)[6]) const
+    {
+        const int J = q.j >> s1, K = q.k >> s2, Lc = q.l >> s3;
+        const int jm = q.j > 0 ? q.j - 1 : L.d1 - 1, jp = q.j < L.d1 - 1 ? q.j + 1 : 0;
+        const int km = q.k > 0 ? q.k - 1 : L.d2 - 1, kp = q.k < L.d2 - 1 ? q.k + 1 : 0;
+        const int lm = q.l > 0 ? q.l - 1 : L.d3 - 1, lp = q.l < L.d3 - 1 ? q.l + 1 : 0;
+        In[0] = I + ((jm >> s1) - J) * cd2 * cd3; In[1] = I + ((jp >> s1) - J) * cd2 * cd3;
+        In[2] = I + ((km >> s2) - K) * cd3;       In[3] = I + ((kp >> s2) - K) * cd3;
+        In[4] = I + ((lm >> s3) - Lc);            In[5] = I + ((lp >> s3) - Lc);
+    }
+};
+
 __device__ __forceinline__ void mg_post_first_body(const MgLevelDev &L, int f1, int f2, int f3, int cd2, int cd3, VecView b, VecView x,
-                                                   VecView xc, VecView x2, VecView r, VecView d, int c0, int cs)
+                                                   VecView xc, mg_real *df, int c0, int cs)
 {
     const Cheb ch = cheb_coeffs(L);
-    const int s1 = f1 == 2 ? 1 : 0, s2 = f2 == 2 ? 1 : 0, s3 = f3 == 2 ? 1 : 0;   // coarsening factors are 1 or 2: shifts
+    const AggMap agg(f1, f2, f3, cd2, cd3);
     const double *xp = x.p + x.off;
     const double *xcp = xc.p + xc.off;
     const mg_real *__restrict__ ell = L.ell;
     MG_CELL_WALK(w, L) {
         const int c = w.c;
-        const Cell3 q = w.q;
-        int nb[6];
+        int nb[6], In[6];
         bool has[6];
-        neighbours(L, c, q, nb, has);
-        const int J = q.j >> s1, K = q.k >> s2, Lc = q.l >> s3;
-        const int I = (J * cd2 + K) * cd3 + Lc;
-        // aggregate of each neighbour: one coarse coordinate may differ (the neighbour's own coordinate with wrap-around)
-        const int jm = q.j > 0 ? q.j - 1 : L.d1 - 1, jp = q.j < L.d1 - 1 ? q.j + 1 : 0;
-        const int km = q.k > 0 ? q.k - 1 : L.d2 - 1, kp = q.k < L.d2 - 1 ? q.k + 1 : 0;
-        const int lm = q.l > 0 ? q.l - 1 : L.d3 - 1, lp = q.l < L.d3 - 1 ? q.l + 1 : 0;
-        const int In[6] = {I + ((jm >> s1) - J) * cd2 * cd3, I + ((jp >> s1) - J) * cd2 * cd3, I + ((km >> s2) - K) * cd3,
-                           I + ((kp >> s2) - K) * cd3,       I + ((lm >> s3) - Lc),            I + ((lp >> s3) - Lc)};
-        // every load before the first use; a missing neighbour reads the cell itself (zero matrix entry) and an
-        // aggregate inside the grid
+        neighbours(L, c, w.q, nb, has);
+        const int I = agg.own(w.q);
+        agg.around(L, w.q, I, In);
+        // every load before the first use; a missing neighbour reads the cell itself (zero matrix entry)
         mg_real a[7];
         double xn[6], cn[6];
 #pragma unroll
@@ -442,20 +459,59 @@ __device__ __forceinline__ void mg_post_first_body(const MgLevelDev &L, int f1, 
 #pragma unroll
         for (int k = 0; k < 6; k++) { xn[k] = xp[nb[k]]; cn[k] = xcp[In[k]]; }
         const double xv = xp[c], cv = xcp[I], bv = b.at(0, c), dic = L.dinv[c];
-        const double xt = xv + cv;
-        double t = a[0] * xt;
+        double t = a[0] * (xv + cv);
 #pragma unroll
         for (int k = 0; k < 6; k++) t += a[1 + k] * (xn[k] + cn[k]);
-        const double rr = bv - t;
-        x2.at(0, c) = xt;
-        r.at(0, c) = rr;
-        d.at(0, c) = ch.inv_theta * (dic * rr);
+        df[c] = (mg_real)(ch.inv_theta * (dic * (bv - t)));
     }
 }
 __global__ void __launch_bounds__(256, 4) mg_post_first_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView b, VecView x,
-                                                            VecView xc, VecView x2, VecView r, VecView d)
+                                                               VecView xc, mg_real *df)
 {
-    mg_post_first_body(L, f1, f2, f3, cd2, cd3, b, x, xc, x2, r, d, MG_GRID_ARGS);
+    mg_post_first_body(L, f1, f2, f3, cd2, cd3, b, x, xc, df, MG_GRID_ARGS);
+}
+
+// DOT: also <w, xout> (see mg_second_body).  xout may be x itself (every cell reads only its own x).
+template <bool DOT>
+__device__ __forceinline__ double mg_post_second_body(const MgLevelDev &L, int f1, int f2, int f3, int cd2, int cd3, VecView x, VecView xc,
+                                                      const mg_real *df, VecView xout, VecView w_, int c0, int cs)
+{
+    const Cheb ch = cheb_coeffs(L);
+    const AggMap agg(f1, f2, f3, cd2, cd3);
+    const mg_real *__restrict__ ell = L.ell;
+    double acc = 0.0;
+    MG_CELL_WALK(w, L) {
+        const int c = w.c;
+        int nb[6];
+        bool has[6];
+        neighbours(L, c, w.q, nb, has);
+        const int I = agg.own(w.q);
+        mg_real a[7], dn[6];
+#pragma unroll
+        for (int k = 0; k < 7; k++) a[k] = ell[(long long)k * L.n + c];
+#pragma unroll
+        for (int k = 0; k < 6; k++) dn[k] = df[nb[k]];
+        const double dv = df[c], xt = x.at(0, c) + xc.at(0, I);
+        const double wv = DOT ? w_.at(0, c) : 0.0;
+        const double a0 = a[0], dic = L.dinv[c];
+        const double rc = ch.theta * dv * (a0 != 0.0 ? a0 : 1.0);   // dinv = 1 / a_cc (1 for an empty diagonal)
+        double t = a0 * dv;
+#pragma unroll
+        for (int k = 0; k < 6; k++) t += a[1 + k] * (double)dn[k];
+        const double xn = xt + (dv + (ch.c1 * dv + ch.c2 * (dic * (rc - t))));
+        xout.at(0, c) = xn;
+        if (DOT) acc += wv * xn;
+    }
+    return acc;
+}
+template <bool DOT>
+__global__ void __launch_bounds__(256, DOT ? 3 : 4) mg_post_second_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView x,
+                                                                          VecView xc, const mg_real *df, VecView xout, VecView w_,
+                                                                          double *partials, unsigned *ticket, double *out, PeerRed pr)
+{
+    double acc[1];
+    acc[0] = mg_post_second_body<DOT>(L, f1, f2, f3, cd2, cd3, x, xc, df, xout, w_, MG_GRID_ARGS);
+    if (DOT) grid_reduce<1>(acc, 0u, partials, ticket, out, false, &pr);
 }
 
 // residual of the fine level summed over each aggregate:  bc(s, I) = sum_{c in I} (b - A x)(s, c)
@@ -635,7 +691,8 @@ __global__ void __launch_bounds__(256) mg_halo_push_kernel(int nspec, int ncell,
 struct MgTailLevel {
     MgLevelDev D;
     int f1, f2, f3;
-    double *b, *x, *r, *d, *x2;
+    double *b, *x, *r, *d;
+    mg_real *df;
 };
 constexpr int MG_TAIL_THREADS = 1024;
 constexpr int MG_TAIL_CELLS = 4096;
@@ -680,18 +737,20 @@ __global__ void __launch_bounds__(MG_TAIL_THREADS) mg_tail_kernel(const MgTailLe
         const bool top = l == l0 && b0.p != nullptr;
         const VecView b = top ? b0 : VecView{T.b, T.D.ncell, 0};
         const VecView x = {T.x, T.D.ncell, 0}, r = {T.r, T.D.ncell, 0}, d = {T.d, T.D.ncell, 0};
-        VecView xin = x;
+        const VecView xc = {lv[l + 1].x, Dn.ncell, 0};
         if (NS == 1) {
-            xin = VecView{T.x2, T.D.ncell, 0};
-            mg_post_first_body(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, b, x, VecView{lv[l + 1].x, Dn.ncell, 0}, xin, r, d, c0, cs);
+            mg_post_first_body(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, b, x, xc, T.df, c0, cs);
+            __syncthreads();
+            if (top && want_dot) acc = mg_post_second_body<true>(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, x, xc, T.df, xout0, b, c0, cs);
+            else mg_post_second_body<false>(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, x, xc, T.df, top ? xout0 : x, none, c0, cs);
         } else {
-            mg_prolong_body(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, 0, VecView{lv[l + 1].x, Dn.ncell, 0}, x, c0, cs);
+            mg_prolong_body(T.D, T.f1, T.f2, T.f3, Dn.d2, Dn.d3, 0, xc, x, c0, cs);
             __syncthreads();
             mg_resid_first_body<NS>(T.D, b, x, r, d, c0, cs);
+            __syncthreads();
+            if (top && want_dot) acc = mg_second_body<NS, true>(T.D, r, d, x, xout0, b, c0, cs);
+            else mg_second_body<NS, false>(T.D, r, d, x, top ? xout0 : x, none, c0, cs);
         }
-        __syncthreads();
-        if (top && want_dot) acc = mg_second_body<NS, true>(T.D, r, d, xin, xout0, b, c0, cs);
-        else mg_second_body<NS, false>(T.D, r, d, xin, top ? xout0 : x, none, c0, cs);
         __syncthreads();
     }
     if (want_dot) {   // <r, z> over the block
@@ -754,14 +813,14 @@ __global__ void __launch_bounds__(256) mg_build_l0_kernel(MgLevelDev L, int gstr
 
 // One species: the smoother data of a row whose seven entries are in registers (what mg_smoother_setup_kernel reads back
 // from the level for the general case): dinv = 1 / a_cc of the stored (rounded) value, and the row's Gershgorin bound.
-__device__ __forceinline__ double row_smoother_data(const mg_real (&e)[7], double *dinv_out)
+__device__ __forceinline__ double row_smoother_data(const mg_real (&e)[7], mg_real *dinv_out)
 {
     const double a = (double)e[0];
     const double di = fabs(a) > 0.0 ? 1.0 / a : 1.0;
     double ts = 0.0;
 #pragma unroll
     for (int t = 0; t < 6; t++) ts += fabs((double)e[1 + t]);
-    *dinv_out = di;
+    *dinv_out = (mg_real)di;
     return 1.0 + fabs(di) * ts;
 }
 
@@ -769,7 +828,7 @@ __device__ __forceinline__ double row_smoother_data(const mg_real (&e)[7], doubl
 // in ascending column order -j -k -l diag +l +k +j, the present ones only -- no column is read, nothing is searched.
 // Writes all seven slots (no zero-fill needed), dinv and the level's Gershgorin bound.
 __global__ void __launch_bounds__(256, 4) mg_build_l0_grid_kernel(MgLevelDev L, const int *__restrict__ rowptr, const double *__restrict__ val,
-                                                                  mg_real *__restrict__ ell, double *__restrict__ dinv, double *__restrict__ lmax)
+                                                                  mg_real *__restrict__ ell, mg_real *__restrict__ dinv, double *__restrict__ lmax)
 {
     const int c0 = blockIdx.x * blockDim.x + threadIdx.x, cs = gridDim.x * blockDim.x;
     double worst = 0.0;
@@ -792,7 +851,7 @@ __global__ void __launch_bounds__(256, 4) mg_build_l0_grid_kernel(MgLevelDev L, 
         for (int t = 0; t < 7; t++) e[slot[t]] = (mg_real)v[t];
 #pragma unroll
         for (int t = 0; t < 7; t++) ell[(long long)t * L.n + c] = e[t];
-        double di;
+        mg_real di;
         worst = fmax(worst, row_smoother_data(e, &di));
         dinv[c] = di;
     }
@@ -804,7 +863,7 @@ __global__ void __launch_bounds__(256, 4) mg_build_l0_grid_kernel(MgLevelDev L, 
 // to) two cells of a line that share the aggregate loaded together, no division, and the coarse level's smoother data
 // formed from the sums while they are in registers.
 __global__ void __launch_bounds__(256, 4) mg_build_coarse1_kernel(MgLevelDev F, MgLevelDev Cc, int f1, int f2, int f3, int cjoff, double w,
-                                                                  mg_real *__restrict__ ellc, double *__restrict__ dinvc,
+                                                                  mg_real *__restrict__ ellc, mg_real *__restrict__ dinvc,
                                                                   double *__restrict__ lmaxc)
 {
     const int c0 = blockIdx.x * blockDim.x + threadIdx.x, cs = gridDim.x * blockDim.x;
@@ -856,7 +915,7 @@ __global__ void __launch_bounds__(256, 4) mg_build_coarse1_kernel(MgLevelDev F, 
         mg_real e[7];
 #pragma unroll
         for (int t = 0; t < 7; t++) { e[t] = (mg_real)acc[t]; ellc[(long long)t * Cc.n + cw.c] = e[t]; }
-        double di;
+        mg_real di;
         worst = fmax(worst, row_smoother_data(e, &di));
         dinvc[cw.c] = di;
     }
@@ -926,7 +985,7 @@ __global__ void __launch_bounds__(256) mg_build_coarse_kernel(MgLevelDev F, MgLe
 // Smoother data of a level: the inverse of every cell block (nspec = 1: of the diagonal) and the Gershgorin bound
 //   lmax = 1 + max over rows of  sum_s' |Binv(s,s')| * (sum over the six neighbour entries of row (s', cell))
 // of the block-Jacobi-preconditioned operator Binv A = I + Binv T.  lmax[0] must be zero on entry.
-__global__ void __launch_bounds__(128) mg_smoother_setup_kernel(MgLevelDev L, double *__restrict__ dinv, double *__restrict__ lmax)
+__global__ void __launch_bounds__(128) mg_smoother_setup_kernel(MgLevelDev L, mg_real *__restrict__ dinv, double *__restrict__ lmax)
 {
     const int ns = L.nspec;
     double worst = 0.0;
@@ -972,8 +1031,8 @@ __global__ void __launch_bounds__(128) mg_smoother_setup_kernel(MgLevelDev L, do
             double g = 0.0;
             for (int q = 0; q < ns; q++) {
                 g += fabs(B[s][q]) * tsum[q];
-                if (ns == 1) dinv[c] = B[0][0];
-                else dinv[((long long)s * ns + q) * L.ncell + c] = B[s][q];
+                if (ns == 1) dinv[c] = (mg_real)B[0][0];
+                else dinv[((long long)s * ns + q) * L.ncell + c] = (mg_real)B[s][q];
             }
             worst = fmax(worst, 1.0 + g);
         }
@@ -1225,9 +1284,14 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
         const size_t nslot = 7 + (size_t)D.nspec - 1;
         RS_TRY(L.ell.alloc(nslot * D.n));
         RS_TRY(L.dinv.alloc(D.nspec == 1 ? (size_t)D.n : (size_t)D.nspec * D.n));
-        RS_TRY(L.r.alloc(D.n));
-        if (!L.global) { RS_TRY(L.x.alloc(D.n)); RS_TRY(L.d.alloc(D.n)); L.xp = L.x.p; L.dp = L.d.p; }   // global: below
-        if (!L.global && D.nspec == 1) RS_TRY(L.x2.alloc(D.n));
+        const bool lean = !L.global && D.nspec == 1;   // one-species local level: its passes share x and df only
+        if (!lean) RS_TRY(L.r.alloc(D.n));
+        if (!L.global) {   // global: below
+            RS_TRY(L.x.alloc(D.n));
+            if (!lean) RS_TRY(L.d.alloc(D.n));
+            L.xp = L.x.p; L.dp = L.d.p;
+        }
+        if (lean) RS_TRY(L.df.alloc(D.n));
         if (nlev > 0) RS_TRY(L.b.alloc(D.n));
         D.ell = L.ell.p; D.dinv = L.dinv.p;
         nlev++;
@@ -1281,7 +1345,7 @@ int mg_setup(Ctx &c, Mg **out, const GridDesc &g, int j0, int j1)
             MgLevel &L = M->lev[l];
             tl[l].D = L.dev;
             tl[l].f1 = L.f[0]; tl[l].f2 = L.f[1]; tl[l].f3 = L.f[2];
-            tl[l].b = L.b.p; tl[l].x = L.xp; tl[l].r = L.r.p; tl[l].d = L.dp; tl[l].x2 = L.x2.p;
+            tl[l].b = L.b.p; tl[l].x = L.xp; tl[l].r = L.r.p; tl[l].d = L.dp; tl[l].df = L.df.p;
         }
         RS_TRY(M->tail_levels.alloc(sizeof(MgTailLevel) * nlev));
         RS_CUDA(cudaMemcpyAsync(M->tail_levels.p, tl.data(), sizeof(MgTailLevel) * nlev, cudaMemcpyHostToDevice, c.stream));
@@ -1391,7 +1455,7 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     const VecView x = view(L.xp, D.ncell), r = view(L.r.p, D.ncell), d = view(L.dp, D.ncell);
     const VecView none = view(nullptr, 0);
     if (NS == 1 && !L.global) {   // pre-smoothing from a zero guess: two Chebyshev steps, one pass, d never stored
-        Launch La(c, k_smooth, mat + 24.0 * n);
+        Launch La(c, k_smooth, mat + (sizeof(mg_real) + 16.0) * n);   // + dinv, b, x out
         mg_pre_kernel<<<mg_wave_grid(mg_pre_kernel, D.ce - D.cb), 256, 0, st>>>(D, b, x);
     } else {
         {
@@ -1410,31 +1474,40 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
                                                                                    b, x, view(Cn.b.p, Cn.dev.ncell));
     }
     mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.xp, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
-    VecView xin = x;
-    if (NS == 1 && !L.global) {   // prolongation folded into the first post-smoothing pass; the corrected x lands in x2
-        xin = view(L.x2.p, D.ncell);
-        Launch La(c, k_smooth, mat + 40.0 * n + 8.0 * Cn.dev.n);
-        mg_post_first_kernel<<<mg_wave_grid(mg_post_first_kernel, D.ce - D.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, b, x,
-                                                                                            view(Cn.xp, Cn.dev.ncell), xin, r, d);
-    } else {
+    if (NS == 1 && !L.global) {   // prolongation folded into the post-smoothing; its two passes share only d (single precision)
+        const VecView xc = view(Cn.xp, Cn.dev.ncell);
+        const double ms = sizeof(mg_real);
         {
-            Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
-            mg_prolong_kernel<<<mg_wave_grid(mg_prolong_kernel, D.ce - D.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.xp, Cn.dev.ncell), x);
+            Launch La(c, k_smooth, mat + (ms + 16.0 + ms) * n + 8.0 * Cn.dev.n);   // + dinv, b, x, d out; xc
+            mg_post_first_kernel<<<mg_wave_grid(mg_post_first_kernel, D.ce - D.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, b, x,
+                                                                                                xc, L.df.p);
         }
-        if (L.global) mg_halo(c, M, L, true);
-        {   // post-smoothing: the same two Chebyshev steps, two passes
-            Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
-            mg_resid_first_kernel<NS><<<mg_wave_grid(mg_resid_first_kernel<NS>, D.ce - D.cb), 256, 0, st>>>(D, b, x, r, d);
-        }
-        if (L.global) mg_halo(c, M, L, false);
+        Launch La(c, k_smooth, mat + (ms + ms + 16.0 + (dot_out ? 8.0 : 0.0)) * n + 8.0 * Cn.dev.n);   // + dinv, d, x, xout[, b]; xc
+        if (dot_out)
+            mg_post_second_kernel<true><<<mg_wave_grid(mg_post_second_kernel<true>, D.ce - D.cb), 256, 0, st>>>(
+                D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, x, xc, L.df.p, xout, b, partials, ticket, dot_out, pr);
+        else
+            mg_post_second_kernel<false><<<mg_wave_grid(mg_post_second_kernel<false>, D.ce - D.cb), 256, 0, st>>>(
+                D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, x, xc, L.df.p, xout, none, nullptr, nullptr, nullptr, PeerRed());
+        return;
     }
+    {
+        Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
+        mg_prolong_kernel<<<mg_wave_grid(mg_prolong_kernel, D.ce - D.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.xp, Cn.dev.ncell), x);
+    }
+    if (L.global) mg_halo(c, M, L, true);
+    {   // post-smoothing: the same two Chebyshev steps, two passes
+        Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
+        mg_resid_first_kernel<NS><<<mg_wave_grid(mg_resid_first_kernel<NS>, D.ce - D.cb), 256, 0, st>>>(D, b, x, r, d);
+    }
+    if (L.global) mg_halo(c, M, L, false);
     {
         Launch La(c, k_smooth, mat + 32.0 * n + 8.0 * D.nspec * n);
         if (dot_out)
-            mg_second_kernel<NS, true><<<mg_wave_grid(mg_second_kernel<NS, true>, D.ce - D.cb), 256, 0, st>>>(D, r, d, xin, xout, b, partials, ticket,
+            mg_second_kernel<NS, true><<<mg_wave_grid(mg_second_kernel<NS, true>, D.ce - D.cb), 256, 0, st>>>(D, r, d, x, xout, b, partials, ticket,
                                                                                                             dot_out, pr);
         else
-            mg_second_kernel<NS, false><<<mg_wave_grid(mg_second_kernel<NS, false>, D.ce - D.cb), 256, 0, st>>>(D, r, d, xin, xout, none, nullptr, nullptr,
+            mg_second_kernel<NS, false><<<mg_wave_grid(mg_second_kernel<NS, false>, D.ce - D.cb), 256, 0, st>>>(D, r, d, x, xout, none, nullptr, nullptr,
                                                                                                              nullptr, PeerRed());
     }
 }
