@@ -131,6 +131,17 @@ def test_jgroup_wavefront_larger_grid(built, oracle):
     _jg_case(built, oracle, "2D", 1, (300, 200), (0, 0), [3, 1, 300, 200, 1, 0, 0, 0])
 
 
+PLANE_SHAPES = [(2, 2, 2), (2, 1, 1), (3, 1, 7), (4, 9, 1), (5, 6, 7), (7, 2, 3), (16, 16, 16), (33, 5, 18), (9, 31, 4),
+                (300, 3, 4), (620, 2, 5), (64, 40, 24)]
+
+
+@pytest.mark.parametrize("dims", PLANE_SHAPES, ids=str)
+def test_jgroup_3d_plane_pipeline(built, oracle, dims):
+    """one species on a 3-D grid: planes pipelined block to block (jg_plane_kernel) -- thin, flat and odd boxes, and
+    more planes than blocks can be resident (a block then takes several planes in turn); bit for bit the sequential JGROUP"""
+    _jg_case(built, oracle, "3D", 1, dims, (0, 0, 0), [4, 1, dims[0], dims[1], dims[2], 0, 0, 0])
+
+
 CASES = {
     # name: (model, parms, sparsetype, nnz-vector builder, ipar, y0)
     "diff2d_lin": ("diff2d", H.P_DIFF2D_LIN, "2D", lambda d: [1, d[0], d[1], 0, 0], lambda d: [1, d[0], d[1], 1, 0], 10.0),
