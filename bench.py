@@ -433,9 +433,9 @@ def run_ours(args):
     traffic, prof_note = None, None
     if "mg_smooth_l0" in raw and raw["mg_smooth_l0"]["ms"] >= raw.get("spmv_grid", {"ms": 0.0})["ms"]:
         dom = "mg_smooth_l0"
-        dom_desc = ("mg_smooth_l0: Chebyshev smoothing passes of the finest multigrid level (slot-major matrix 8*7N bytes + "
-                    "3-4 vectors per pass; mg_first/mg_second/mg_resid_first kernels)")
-        prof = os.path.join(ROOT, "profiles", "r02_ncu_mg_smooth_full.json")
+        dom_desc = ("mg_smooth_l0: Chebyshev smoothing passes of the finest multigrid level (slot-major single-precision matrix "
+                    "4*7N + dinv 4N bytes + 2-4 vectors per pass: 48N / 53N / 61N; mg_pre / mg_post_first / mg_post_second kernels)")
+        prof = os.path.join(ROOT, "profiles", "r02_ncu_mg_level_kernels_full.json")
     else:
         dom = "spmv_grid" if raw.get("spmv_grid", {}).get("launches", 0) > 0 else "spmv_csr"
         dom_desc = dom + (" (implicit columns: 8Z+4(N+1)+16N bytes, <p,Ap> fused)" if dom == "spmv_grid" else " (12Z+4(N+1)+16N bytes)")

@@ -377,7 +377,8 @@ __device__ __forceinline__ void mg_pre_body(const MgLevelDev &L, VecView b, VecV
         x.at(0, c) = dc + (ch.c1 * dc + ch.c2 * (dic * (bc - t)));
     }
 }
-__global__ void __launch_bounds__(256, 4) mg_pre_kernel(MgLevelDev L, VecView b, VecView x)
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) mg_pre_kernel(MgLevelDev L, VecView b, VecView x)
 {
     mg_pre_body(L, b, x, MG_GRID_ARGS);
 }
@@ -465,7 +466,8 @@ __device__ __forceinline__ void mg_post_first_body(const MgLevelDev &L, int f1, 
         df[c] = (mg_real)(ch.inv_theta * (dic * (bv - t)));
     }
 }
-__global__ void __launch_bounds__(256, 4) mg_post_first_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView b, VecView x,
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) mg_post_first_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView b, VecView x,
                                                                VecView xc, mg_real *df)
 {
     mg_post_first_body(L, f1, f2, f3, cd2, cd3, b, x, xc, df, MG_GRID_ARGS);
@@ -504,8 +506,8 @@ __device__ __forceinline__ double mg_post_second_body(const MgLevelDev &L, int f
     }
     return acc;
 }
-template <bool DOT>
-__global__ void __launch_bounds__(256, DOT ? 3 : 4) mg_post_second_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView x,
+template <bool DOT, int MINB>
+__global__ void __launch_bounds__(256, MINB) mg_post_second_kernel(MgLevelDev L, int f1, int f2, int f3, int cd2, int cd3, VecView x,
                                                                           VecView xc, const mg_real *df, VecView xout, VecView w_,
                                                                           double *partials, unsigned *ticket, double *out, PeerRed pr)
 {
@@ -602,8 +604,8 @@ __device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int 
     }
 }
 
-template <int NS>
-__global__ void __launch_bounds__(256, NS == 1 ? 4 : 1) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, MgLevelDev Cc, int cjoff,
+template <int NS, int MINB>
+__global__ void __launch_bounds__(256, MINB) mg_resid_restrict_kernel(MgLevelDev L, int f1, int f2, int f3, MgLevelDev Cc, int cjoff,
                                                                 VecView b, VecView x, VecView bc)
 {
     mg_resid_restrict_body<NS>(L, f1, f2, f3, Cc, cjoff, b, x, bc, MG_GRID_ARGS);
@@ -1426,6 +1428,20 @@ static void mg_halo(Ctx &c, Mg &M, MgLevel &L, bool is_x)
                                                                                             v, hp, M.hticket.p);
 }
 
+// resident blocks per SM the one-species level kernels are compiled for (RS_MG_MINB: 3..6, tuning)
+static int mg_minb()
+{
+    static const int v = getenv("RS_MG_MINB") ? atoi(getenv("RS_MG_MINB")) : 4;
+    return v;
+}
+#define MG_MINB_SWITCH(MB, ...)                                      \
+    switch (mg_minb()) {                                             \
+    case 3: { constexpr int MB = 3; __VA_ARGS__; } break;            \
+    case 5: { constexpr int MB = 5; __VA_ARGS__; } break;            \
+    case 6: { constexpr int MB = 6; __VA_ARGS__; } break;            \
+    default: { constexpr int MB = 4; __VA_ARGS__; } break;           \
+    }
+
 template <int NS>
 static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double *partials, unsigned *ticket, double *dot_out,
                            const PeerRed &pr)
@@ -1456,7 +1472,7 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     const VecView none = view(nullptr, 0);
     if (NS == 1 && !L.global) {   // pre-smoothing from a zero guess: two Chebyshev steps, one pass, d never stored
         Launch La(c, k_smooth, mat + (sizeof(mg_real) + 16.0) * n);   // + dinv, b, x out
-        mg_pre_kernel<<<mg_wave_grid(mg_pre_kernel, D.ce - D.cb), 256, 0, st>>>(D, b, x);
+        MG_MINB_SWITCH(MB, mg_pre_kernel<MB><<<mg_wave_grid(mg_pre_kernel<MB>, D.ce - D.cb), 256, 0, st>>>(D, b, x));
     } else {
         {
             Launch La(c, k_smooth, 16.0 * n + 8.0 * D.nspec * n);
@@ -1470,8 +1486,13 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     if (L.global) mg_halo(c, M, L, true);
     {   // residual, summed over the aggregates
         Launch La(c, k_transfer, mat + 16.0 * n + 8.0 * Cn.dev.n);
-        mg_resid_restrict_kernel<NS><<<mg_wave_grid(mg_resid_restrict_kernel<NS>, Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev, L.cjoff,
-                                                                                   b, x, view(Cn.b.p, Cn.dev.ncell));
+        const VecView bcv = view(Cn.b.p, Cn.dev.ncell);
+        if (NS == 1) {
+            MG_MINB_SWITCH(MB, mg_resid_restrict_kernel<1, MB><<<mg_wave_grid(mg_resid_restrict_kernel<1, MB>, Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(
+                                   D, L.f[0], L.f[1], L.f[2], Cn.dev, L.cjoff, b, x, bcv));
+        } else
+            mg_resid_restrict_kernel<NS, 1><<<mg_wave_grid(mg_resid_restrict_kernel<NS, 1>, Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev,
+                                                                                                                   L.cjoff, b, x, bcv);
     }
     mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.xp, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
     if (NS == 1 && !L.global) {   // prolongation folded into the post-smoothing; its two passes share only d (single precision)
@@ -1479,16 +1500,17 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
         const double ms = sizeof(mg_real);
         {
             Launch La(c, k_smooth, mat + (ms + 16.0 + ms) * n + 8.0 * Cn.dev.n);   // + dinv, b, x, d out; xc
-            mg_post_first_kernel<<<mg_wave_grid(mg_post_first_kernel, D.ce - D.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, b, x,
-                                                                                                xc, L.df.p);
+            MG_MINB_SWITCH(MB, mg_post_first_kernel<MB><<<mg_wave_grid(mg_post_first_kernel<MB>, D.ce - D.cb), 256, 0, st>>>(
+                                   D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, b, x, xc, L.df.p));
         }
         Launch La(c, k_smooth, mat + (ms + ms + 16.0 + (dot_out ? 8.0 : 0.0)) * n + 8.0 * Cn.dev.n);   // + dinv, d, x, xout[, b]; xc
         if (dot_out)
-            mg_post_second_kernel<true><<<mg_wave_grid(mg_post_second_kernel<true>, D.ce - D.cb), 256, 0, st>>>(
+            mg_post_second_kernel<true, 3><<<mg_wave_grid(mg_post_second_kernel<true, 3>, D.ce - D.cb), 256, 0, st>>>(
                 D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, x, xc, L.df.p, xout, b, partials, ticket, dot_out, pr);
-        else
-            mg_post_second_kernel<false><<<mg_wave_grid(mg_post_second_kernel<false>, D.ce - D.cb), 256, 0, st>>>(
-                D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, x, xc, L.df.p, xout, none, nullptr, nullptr, nullptr, PeerRed());
+        else {
+            MG_MINB_SWITCH(MB, mg_post_second_kernel<false, MB><<<mg_wave_grid(mg_post_second_kernel<false, MB>, D.ce - D.cb), 256, 0, st>>>(
+                                   D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, x, xc, L.df.p, xout, none, nullptr, nullptr, nullptr, PeerRed()));
+        }
         return;
     }
     {
