@@ -18,17 +18,22 @@
 //              val[slot][row], slot 0 = diagonal, 1..6 = -j +j -k +k -l +l neighbour of the same species,
 //              7.. = the other species of the same cell.  Columns are implicit, loads are coalesced, there is
 //              no row pointer.  The finest level is a copy of the solver's row-wise arrays (one pass per Newton
-//              iteration) restricted to the rank's slab: the preconditioner is slab-local, so a
-//              cycle needs no communication.
+//              iteration).  Matrices, Dinv and (one species) the d of the post-smoothing are single precision.
+//   sharding   the top levels of a sharded solve are global: every rank works on its planes of one operator and
+//              the halo planes of x / d travel before each application (NVLink stores + flags, mg_halo); below
+//              them every rank continues on its own box.  RS_MG_GLOBAL_LEVELS (default 3), RS_MG_LOCAL.
 //   smoother   Chebyshev polynomial of degree 2 in (block-)Jacobi-preconditioned form on [lmax/4, lmax], lmax
 //              from a Gershgorin bound computed on the device; the cell block (nspec x nspec) is inverted
 //              exactly, which takes the stiff reaction coupling out of the iteration.  Same smoother before and
 //              after the coarse correction: for a symmetric matrix the cycle is a symmetric positive definite
 //              operator and preconditions CG; BiCGStab uses the same cycle on nonsymmetric Jacobians.
 //
-// Bytes (level 0, N rows, 7-point): a cycle makes 4 passes over the matrix (56 N each) plus ~170 N of vector
-// traffic; levels below add 1/7 in 3-D.  All kernels are thread-per-cell with grid-stride loops and run on the
-// solver's stream without host synchronisation, so whole Krylov steps including the cycle replay from CUDA graphs.
+// Bytes (level 0, N cells, one species, 7-point): a cycle makes 4 passes -- pre-smoothing 48 N, residual + restriction
+// 45 N, the two post-smoothing passes 53 N and 61 N (matrix 28 N and Dinv 4 N in each, the rest vectors) -- 207 N in all
+// (round-2 start: 4 x 56 N of matrix + ~170 N of vectors); levels below add 1/7 in 3-D.  The general form (several
+// species, global levels of a sharded solve) takes 5 passes and stores r and d in double.  All kernels are thread-per-
+// cell with grid-stride loops and run on the solver's stream without host synchronisation, so whole Krylov steps
+// including the cycle replay from CUDA graphs.
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
