@@ -690,6 +690,22 @@ __global__ void __launch_bounds__(256) mg_halo_push_kernel(int nspec, int ncell,
     }
 }
 
+// A flag of the exchange above says "my planes have arrived", not "I have finished reading yours".  Two consecutive
+// exchanges target different buffers (d, x, then the next level's) except the x of the deepest global level: pushed
+// before its restriction and again after its prolongation, with only this rank's local levels -- no exchange -- in
+// between.  There the reader acknowledges: after the restriction it raises a flag of its own ("done reading"), and the
+// second push waits for the neighbours' before it writes into their halo planes.  Two one-thread kernels per cycle;
+// the wait is over long before it is asked for (the neighbour's whole local hierarchy lies in between).
+__global__ void mg_halo_raise_kernel(HaloSignal sig)
+{
+    const unsigned seq = *sig.seq + 1u;
+    __threadfence_system();
+    if (sig.tell_lo) *(volatile double *)sig.tell_lo = (double)seq;
+    if (sig.tell_hi) *(volatile double *)sig.tell_hi = (double)seq;
+    *sig.seq = seq;
+}
+__global__ void mg_halo_wait_kernel(HaloSignal sig) { halo_wait(sig); }
+
 // ---- the small levels in one launch ---------------------------------------------------------------------------
 // Below a few thousand cells a level is a handful of microseconds of work per kernel and six kernels per visit: launch
 // latency, not bandwidth.  One block walks all those levels -- down, the dense coarsest solve, up -- with a block
@@ -1499,6 +1515,12 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
             mg_resid_restrict_kernel<NS, 1><<<mg_wave_grid(mg_resid_restrict_kernel<NS, 1>, Cn.dev.ce - Cn.dev.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev,
                                                                                                                    L.cjoff, b, x, bcv);
     }
+    // deepest global level: acknowledge that the x halo has been read (see mg_halo_raise_kernel)
+    const bool ack = L.global && l == M.nglobal - 1 && M.push;
+    if (ack) {
+        Launch La(c, K_HALO, 16.0);
+        mg_halo_raise_kernel<<<1, 1, 0, st>>>(comm_next_halo_signal());
+    }
     mg_cycle_level<NS>(c, M, l + 1, view(Cn.b.p, Cn.dev.ncell), view(Cn.xp, Cn.dev.ncell), nullptr, nullptr, nullptr, PeerRed());
     if (NS == 1 && !L.global) {   // prolongation folded into the post-smoothing; its two passes share only d (single precision)
         const VecView xc = view(Cn.xp, Cn.dev.ncell);
@@ -1521,6 +1543,10 @@ static void mg_cycle_level(Ctx &c, Mg &M, int l, VecView b, VecView xout, double
     {
         Launch La(c, k_transfer, 16.0 * n + 8.0 * Cn.dev.n);
         mg_prolong_kernel<<<mg_wave_grid(mg_prolong_kernel, D.ce - D.cb), 256, 0, st>>>(D, L.f[0], L.f[1], L.f[2], Cn.dev.d2, Cn.dev.d3, L.cjoff, view(Cn.xp, Cn.dev.ncell), x);
+    }
+    if (ack) {   // the neighbours have finished reading the x planes the push below overwrites
+        Launch La(c, K_HALO, 16.0);
+        mg_halo_wait_kernel<<<1, 32, 0, st>>>(comm_next_halo_signal());
     }
     if (L.global) mg_halo(c, M, L, true);
     {   // post-smoothing: the same two Chebyshev steps, two passes
