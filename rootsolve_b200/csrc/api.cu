@@ -509,7 +509,8 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
     mark("structure (ian, jan)");
     if (!s.structure_only) {
         RS_TRY(init_model(a->func, a->initpar, a->ninitpar, a->forcs, a->nforcs));
-        RS_TRY(build_csr_pattern(c, n, s.nnz, s.ian.p, s.jan.p, s.rowptr, s.col));
+        if (grid_pattern_applicable(s.grid)) RS_TRY(build_csr_pattern_grid(c, s.grid, n, s.nnz, s.ian.p, s.jan.p, s.rowptr, s.col));
+        else RS_TRY(build_csr_pattern(c, n, s.nnz, s.ian.p, s.jan.p, s.rowptr, s.col));
         mark("row-wise pattern");
         RS_TRY(jgroup_device(c, s.grid, n, s.nnz, s.ian.p, s.jan.p, s.rowptr.p, s.col.p, s.maxg, s.group_of, &s.ngp));
         mark("column grouping");

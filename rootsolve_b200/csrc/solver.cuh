@@ -36,6 +36,10 @@ int build_mapped_structure(Ctx &c, const GridDesc &g, int n, int totn, const int
                            DevBuf<int> &d_jan, int *nnz);
 int build_csr_pattern(Ctx &c, int n, int nnz, const int *d_ian, const int *d_jan, DevBuf<int> &rowptr,
                       DevBuf<int> &col);
+// non-cyclic 1-D / 2-D / 3-D grids: the same pattern written down in closed form (structure.cu)
+bool grid_pattern_applicable(const GridDesc &g);
+int build_csr_pattern_grid(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, const int *d_jan, DevBuf<int> &rowptr,
+                           DevBuf<int> &col);
 
 // jgroup.cu -- group_of[j] = 0-based group of column j; ngp = number of groups.
 int jgroup_device(Ctx &c, const GridDesc &g, int n, int nnz, const int *d_ian, const int *d_jan,

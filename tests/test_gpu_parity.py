@@ -384,6 +384,32 @@ def test_steady_state_matches_oracle(built, oracle, name, rdims, lrw):
     assert A["precis"][-1] <= 1e-9
 
 
+PATTERN_SHAPES = [("diff2d_lin", (30, 20)), ("diff2d_lin", (1, 40)), ("diff2d_lin", (40, 1)), ("diff2d_monod", (37, 5)),
+                  ("diff3d", (16, 12, 10)), ("diff3d", (1, 7, 9)), ("diff3d", (9, 1, 7)), ("diff3d", (2, 2, 2)), ("diff3d", (5, 6, 1)),
+                  ("rd3d", (10, 9, 8)), ("rd3d", (3, 1, 4)), ("rt1d", (300,)), ("rt1d", (2,))]
+
+
+@pytest.mark.parametrize("name,rdims", PATTERN_SHAPES, ids=str)
+def test_closed_form_row_pattern_is_the_transposed_structure(built, name, rdims, monkeypatch):
+    """non-cyclic grids get their row-wise pattern written down in closed form (structure.cu); with
+    RS_CHECK_GRID_PATTERN the library also transposes (ian, jan) the general way and refuses to go on if the two
+    differ anywhere -- flat, thin and tiny boxes, one / two / five species"""
+    import rootsolve_b200 as rs
+    monkeypatch.setenv("RS_CHECK_GRID_PATTERN", "1")
+    model, parms, st, nnzf, ipf, _ = CASES[name]
+    sd = tuple(reversed(rdims))
+    y0 = _y0(name, sd)
+    nspec = nnzf(sd)[0]
+    kw = dict(func=model, parms=parms, positive=True, ipar=ipf(sd), **H.TOL)
+    if st == "1D":
+        out = rs.steady_1D(y0, nspec=nspec, method="stodes", **kw)
+    elif st == "2D":
+        out = rs.steady_2D(y0, nspec=nspec, dimens=list(rdims), **kw)
+    else:
+        out = rs.steady_3D(y0, nspec=nspec, dimens=list(rdims), **kw)
+    assert out.attributes["steady"]
+
+
 def test_golden_pdf_example_on_gpu(built):
     """the reference's frozen output (inst/doc/rootSolve.pdf p.16): nnz, ngp, iteration count, precis[0]"""
     import json
