@@ -143,7 +143,7 @@ template <int NS>
 __device__ __forceinline__ void cell_apply(const MgLevelDev &L, int c, const int (&nb)[6], const VecView &v, double (&t)[MG_NSA])
 {
     const int ns = NS > 0 ? NS : L.nspec;
-    if (NS >= 1 && NS <= 3) {   // few species, known at compile time: every load of the cell before the first use
+    if constexpr (NS >= 1 && NS <= 3) {   // few species, known at compile time: every load of the cell before the first use
         constexpr int M = NS >= 1 ? NS : 1;
         const mg_real *__restrict__ ell = L.ell;
         mg_real a[M][6 + M];
@@ -172,27 +172,28 @@ __device__ __forceinline__ void cell_apply(const MgLevelDev &L, int c, const int
             t[s] = acc;
         }
         return;
-    }
-    double vc[MG_NSA];
+    } else {
+        double vc[MG_NSA];
 #pragma unroll
-    for (int s = 0; s < MG_NSA; s++)
-        if (s < ns) vc[s] = v.at(s, c);
+        for (int s = 0; s < MG_NSA; s++)
+            if (s < ns) vc[s] = v.at(s, c);
 #pragma unroll
-    for (int s = 0; s < MG_NSA; s++) {
-        if (s >= ns) break;
-        const long long r = (long long)s * L.ncell + c;
-        double a = L.ell[r] * vc[s];
+        for (int s = 0; s < MG_NSA; s++) {
+            if (s >= ns) break;
+            const long long r = (long long)s * L.ncell + c;
+            double a = L.ell[r] * vc[s];
 #pragma unroll
-        for (int q = 0; q < 6; q++) a += L.ell[(long long)(1 + q) * L.n + r] * v.at(s, nb[q]);
-        int o = 0;
+            for (int q = 0; q < 6; q++) a += L.ell[(long long)(1 + q) * L.n + r] * v.at(s, nb[q]);
+            int o = 0;
 #pragma unroll
-        for (int s2 = 0; s2 < MG_NSA; s2++) {
-            if (s2 >= ns) break;
-            if (s2 == s) continue;
-            a += L.ell[(long long)(7 + o) * L.n + r] * vc[s2];
-            o++;
+            for (int s2 = 0; s2 < MG_NSA; s2++) {
+                if (s2 >= ns) break;
+                if (s2 == s) continue;
+                a += L.ell[(long long)(7 + o) * L.n + r] * vc[s2];
+                o++;
+            }
+            t[s] = a;
         }
-        t[s] = a;
     }
 }
 
@@ -201,17 +202,20 @@ template <int NS>
 __device__ __forceinline__ void cell_dinv(const MgLevelDev &L, int c, const double (&v)[MG_NSA], double (&w)[MG_NSA])
 {
     const int ns = NS > 0 ? NS : L.nspec;
-    if (NS == 1) { w[0] = L.dinv[c] * v[0]; return; }
+    if constexpr (NS == 1) {
+        w[0] = L.dinv[c] * v[0];
+    } else {
 #pragma unroll
-    for (int s = 0; s < MG_NSA; s++) {
-        if (s >= ns) break;
-        double a = 0.0;
+        for (int s = 0; s < MG_NSA; s++) {
+            if (s >= ns) break;
+            double a = 0.0;
 #pragma unroll
-        for (int s2 = 0; s2 < MG_NSA; s2++) {
-            if (s2 >= ns) break;
-            a += L.dinv[((long long)s * ns + s2) * L.ncell + c] * v[s2];
+            for (int s2 = 0; s2 < MG_NSA; s2++) {
+                if (s2 >= ns) break;
+                a += L.dinv[((long long)s * ns + s2) * L.ncell + c] * v[s2];
+            }
+            w[s] = a;
         }
-        w[s] = a;
     }
 }
 
@@ -288,7 +292,7 @@ __device__ __forceinline__ double mg_second_body(const MgLevelDev &L, VecView r,
     const int ns = NS > 0 ? NS : L.nspec;
     const Cheb ch = cheb_coeffs(L);
     double acc[1] = {0.0};
-    if (NS == 1) {   // one species: coordinates carried along, every load of the cell issued before the first use
+    if constexpr (NS == 1) {   // one species: coordinates carried along, every load of the cell issued before the first use
         const double *dp = d.p + d.off;
         const double *rp = r.p + r.off;
         const mg_real *__restrict__ dinv = L.dinv;
@@ -317,29 +321,30 @@ __device__ __forceinline__ double mg_second_body(const MgLevelDev &L, VecView r,
             if (DOT) acc[0] += wv * xn;
         }
         return acc[0];
-    }
-    MG_CELL_WALK(cw, L) {
-        const int c = cw.c;
-        int nb[6];
-        bool has[6];
-        neighbours(L, c, cw.q, nb, has);
-        double t[MG_NSA], r1[MG_NSA], w[MG_NSA];
-        cell_apply<NS>(L, c, nb, d, t);
+    } else {
+        MG_CELL_WALK(cw, L) {
+            const int c = cw.c;
+            int nb[6];
+            bool has[6];
+            neighbours(L, c, cw.q, nb, has);
+            double t[MG_NSA], r1[MG_NSA], w[MG_NSA];
+            cell_apply<NS>(L, c, nb, d, t);
 #pragma unroll
-        for (int s = 0; s < MG_NSA; s++)
-            if (s < ns) r1[s] = r.at(s, c) - t[s];
-        cell_dinv<NS>(L, c, r1, w);
+            for (int s = 0; s < MG_NSA; s++)
+                if (s < ns) r1[s] = r.at(s, c) - t[s];
+            cell_dinv<NS>(L, c, r1, w);
 #pragma unroll
-        for (int s = 0; s < MG_NSA; s++) {
-            if (s >= ns) break;
-            const double dv = d.at(s, c);
-            double xn = dv + (ch.c1 * dv + ch.c2 * w[s]);
-            if (xin.p != nullptr) xn += xin.at(s, c);
-            xout.at(s, c) = xn;
-            if (DOT) acc[0] += w_.at(s, c) * xn;
+            for (int s = 0; s < MG_NSA; s++) {
+                if (s >= ns) break;
+                const double dv = d.at(s, c);
+                double xn = dv + (ch.c1 * dv + ch.c2 * w[s]);
+                if (xin.p != nullptr) xn += xin.at(s, c);
+                xout.at(s, c) = xn;
+                if (DOT) acc[0] += w_.at(s, c) * xn;
+            }
         }
+        return acc[0];
     }
-    return acc[0];
 }
 
 template <int NS, bool DOT>
@@ -528,7 +533,7 @@ __device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int 
                                                        VecView b, VecView x, VecView bc, int c0, int cs)
 {
     const int ns = NS > 0 ? NS : L.nspec;
-    if (NS == 1) {   // one species: coordinates carried along; the (up to) two cells of a line that share the aggregate
+    if constexpr (NS == 1) {   // one species: coordinates carried along; the (up to) two cells of a line that share the aggregate
                      // are staged together, every load before the first use
         const double *xp = x.p + x.off;
         const double *bp = b.p + b.off;
@@ -572,40 +577,41 @@ __device__ __forceinline__ void mg_resid_restrict_body(const MgLevelDev &L, int 
             bc.at(0, w.c) = sum;
         }
         return;
-    }
-    MG_CELL_WALK(cw, Cc) {
-        const int I = cw.c;
-        Cell3 Q = cw.q;
-        Q.j += cjoff;   // plane of the aggregate in the fine level's coordinates / f1
-        double sum[MG_NSA];
+    } else {
+        MG_CELL_WALK(cw, Cc) {
+            const int I = cw.c;
+            Cell3 Q = cw.q;
+            Q.j += cjoff;   // plane of the aggregate in the fine level's coordinates / f1
+            double sum[MG_NSA];
 #pragma unroll
-        for (int s = 0; s < MG_NSA; s++) sum[s] = 0.0;
-        for (int dj = 0; dj < f1; dj++) {
-            const int j = Q.j * f1 + dj;
-            if (j >= L.d1) break;
-            for (int dk = 0; dk < f2; dk++) {
-                const int k = Q.k * f2 + dk;
-                if (k >= L.d2) break;
-                for (int dl = 0; dl < f3; dl++) {
-                    const int l = Q.l * f3 + dl;
-                    if (l >= L.d3) break;
-                    const int c = (j * L.d2 + k) * L.d3 + l;
-                    Cell3 q;
-                    q.j = j; q.k = k; q.l = l;
-                    int nb[6];
-                    bool has[6];
-                    neighbours(L, c, q, nb, has);
-                    double t[MG_NSA];
-                    cell_apply<NS>(L, c, nb, x, t);
+            for (int s = 0; s < MG_NSA; s++) sum[s] = 0.0;
+            for (int dj = 0; dj < f1; dj++) {
+                const int j = Q.j * f1 + dj;
+                if (j >= L.d1) break;
+                for (int dk = 0; dk < f2; dk++) {
+                    const int k = Q.k * f2 + dk;
+                    if (k >= L.d2) break;
+                    for (int dl = 0; dl < f3; dl++) {
+                        const int l = Q.l * f3 + dl;
+                        if (l >= L.d3) break;
+                        const int c = (j * L.d2 + k) * L.d3 + l;
+                        Cell3 q;
+                        q.j = j; q.k = k; q.l = l;
+                        int nb[6];
+                        bool has[6];
+                        neighbours(L, c, q, nb, has);
+                        double t[MG_NSA];
+                        cell_apply<NS>(L, c, nb, x, t);
 #pragma unroll
-                    for (int s = 0; s < MG_NSA; s++)
-                        if (s < ns) sum[s] += b.at(s, c) - t[s];
+                        for (int s = 0; s < MG_NSA; s++)
+                            if (s < ns) sum[s] += b.at(s, c) - t[s];
+                    }
                 }
             }
-        }
 #pragma unroll
-        for (int s = 0; s < MG_NSA; s++)
-            if (s < ns) bc.at(s, I) = sum[s];
+            for (int s = 0; s < MG_NSA; s++)
+                if (s < ns) bc.at(s, I) = sum[s];
+        }
     }
 }
 
