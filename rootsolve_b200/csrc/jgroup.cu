@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(256, MINB) jg_wave_kernel(GridDesc g, int S, i
     // pairs through each round trip together: all their group_of loads, then all their covered loads, then the
     // updates -- the loads of a phase are independent and in flight at once.
     for (int step = 0; step < nsteps; step++) {
-        if (ONE) {
+        if constexpr (ONE) {
             // Single species: the (up to) 7 rows of a cell are computed branch-free -- a neighbour beyond the grid
             // is replaced by the cell itself -- and every load is unconditional (a pair without a cell on this
             // level reads cell 0 and is ignored), so the loads of all U pairs really are in flight together.
@@ -178,38 +178,37 @@ __global__ void __launch_bounds__(256, MINB) jg_wave_kernel(GridDesc g, int S, i
                     top = max(top, base + slot);
                 }
             }
-            grid.sync();
-            continue;
-        }
-        for (int w0 = tid; w0 < work; w0 += nthreads * U) {
-            int cc[U];
+        } else {
+            for (int w0 = tid; w0 < work; w0 += nthreads * U) {
+                int cc[U];
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int wq = w0 + u * nthreads;
-                cc[u] = -1;
-                if (wq < work) {
-                    const int last = step - (wq & (WAVE_SLOTS - 1)) - line_level[wq >> 4];   // slot g sweeps level step - g
-                    if (last >= 0 && last < dl) cc[u] = (wq >> 4) * dl + last;
+                for (int u = 0; u < U; u++) {
+                    const int wq = w0 + u * nthreads;
+                    cc[u] = -1;
+                    if (wq < work) {
+                        const int last = step - (wq & (WAVE_SLOTS - 1)) - line_level[wq >> 4];   // slot g sweeps level step - g
+                        if (last >= 0 && last < dl) cc[u] = (wq >> 4) * dl + last;
+                    }
                 }
-            }
-            int taken[U];
+                int taken[U];
 #pragma unroll
-            for (int u = 0; u < U; u++) taken[u] = cc[u] >= 0 ? group_of[cc[u]] : 0;   // >= 0: in an earlier group
-            unsigned seen[U];
+                for (int u = 0; u < U; u++) taken[u] = cc[u] >= 0 ? group_of[cc[u]] : 0;   // >= 0: in an earlier group
+                unsigned seen[U];
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                seen[u] = 0u;
-                if (cc[u] >= 0 && taken[u] < 0) emit_column(g, cc[u] + 1, [&](int row) { seen[u] |= covered[row - 1]; });
-            }
+                for (int u = 0; u < U; u++) {
+                    seen[u] = 0u;
+                    if (cc[u] >= 0 && taken[u] < 0) emit_column(g, cc[u] + 1, [&](int row) { seen[u] |= covered[row - 1]; });
+                }
 #pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int slot = (w0 + u * nthreads) & (WAVE_SLOTS - 1);
-                const unsigned bit = 1u << slot;
-                if (cc[u] < 0 || taken[u] >= 0 || (seen[u] & bit)) continue;
-                group_of[cc[u]] = base + slot;
-                emit_column(g, cc[u] + 1, [&](int row) { atomicOr(&covered[row - 1], bit); });
-                count++;
-                top = max(top, base + slot);
+                for (int u = 0; u < U; u++) {
+                    const int slot = (w0 + u * nthreads) & (WAVE_SLOTS - 1);
+                    const unsigned bit = 1u << slot;
+                    if (cc[u] < 0 || taken[u] >= 0 || (seen[u] & bit)) continue;
+                    group_of[cc[u]] = base + slot;
+                    emit_column(g, cc[u] + 1, [&](int row) { atomicOr(&covered[row - 1], bit); });
+                    count++;
+                    top = max(top, base + slot);
+                }
             }
         }
         grid.sync();
