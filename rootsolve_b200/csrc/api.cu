@@ -460,15 +460,18 @@ extern "C" int rs_solver_create(const rs_stsparse_args *a, rs_solver **out)
         t_last = now;
     };
     RS_TRY(s.y.alloc(n));
-    // Grid types: structure and grouping do not read y, so a large state crosses PCIe on a stream of its own beside
-    // them (134 MB at 256^3: ~3 ms next to 13 ms of grouping); the solver's stream waits for it before the first
-    // kernel that reads y.  The guard drains the copy on every return path: y must not go back to the pool under it.
+    // Grid types: structure and grouping do not read y, so a large state could cross PCIe on a stream of its own beside
+    // them; the solver's stream then waits for it before the first kernel that reads y.  Opt-in (RS_SIDE_COPY=1): on
+    // the B200 boxes this was measured on the copy did not overlap the set-up kernels at all -- 11.8 ms of set-up at
+    // 256^3 with it against 10.95 ms with the upload simply first on the solver's stream (2.4 + 8.5 ms).  The guard
+    // drains the copy on every return path: y must not go back to the pool under it.
     struct SideCopy {
         cudaStream_t st = nullptr; cudaEvent_t done = nullptr; bool pending = false;
         ~SideCopy() { if (pending) cudaStreamSynchronize(st); if (done) cudaEventDestroy(done); if (st) cudaStreamDestroy(st); }
     } side;
     const bool grid_type = std::abs(a->Type) == RS_TYPE_1D || std::abs(a->Type) == RS_TYPE_2D || std::abs(a->Type) == RS_TYPE_3D;
-    if (grid_type && n >= (1 << 18) && !debug_setup) {
+    static const bool side_copy = getenv("RS_SIDE_COPY") != nullptr;
+    if (side_copy && grid_type && n >= (1 << 18) && !debug_setup) {
         RS_CUDA(cudaStreamCreateWithFlags(&side.st, cudaStreamNonBlocking));
         RS_CUDA(cudaEventCreateWithFlags(&side.done, cudaEventDisableTiming));
         side.pending = true;
